@@ -96,6 +96,15 @@ def check_f32(desc: ModelDesc, q: np.ndarray, nthreads: int = 0) -> np.ndarray:
     return hit
 
 
+def flops(desc: ModelDesc, q: np.ndarray) -> np.ndarray:
+    """Algorithmic FP32 flops per configuration (SURVEY 8d formula; roofline numerator)."""
+    q = np.ascontiguousarray(np.atleast_2d(q), dtype=np.float64)
+    out = np.zeros(len(q))
+    rc = lib().orc_flops_batch(C.byref(desc.struct), _p(q, C.c_double), C.c_int64(len(q)), C.c_int(q.shape[1]), _p(out, C.c_double))
+    assert rc == 0
+    return out
+
+
 def num_threads() -> int:
     return int(lib().orc_num_threads())
 

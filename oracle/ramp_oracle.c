@@ -891,3 +891,67 @@ int orc_check_edges(const RampModelDesc *d, const uint8_t *active, const RampQMa
   }
   return 0;
 }
+
+/* ---------------------------------------------------------- flop accounting */
+/* Algorithmic FP32 work of one validity check, SURVEY §8(d): FK (83 per
+ * revolute, 69 per prismatic, 150 per free-flyer/planar/spherical joint, minus
+ * 63 for a root joint), 63 per movable geometry, and per pair: 11 when the
+ * bounding spheres are disjoint, else the closed-form cost of the class or
+ * GJK iterations x (6 (V1 + V2) + 2*33 + 150), iterations counted by THIS
+ * oracle's GJK in its boolean early-out mode.  Used by bench.py for the
+ * roofline numerator only. */
+static double bound_radius(const RampGeom *g, const double *verts) {
+  switch (g->type) {
+  case RAMP_SHAPE_SPHERE: return g->params[0];
+  case RAMP_SHAPE_CAPSULE: return g->params[0] + g->params[1];
+  case RAMP_SHAPE_BOX: return sqrt(g->params[0] * g->params[0] + g->params[1] * g->params[1] + g->params[2] * g->params[2]);
+  case RAMP_SHAPE_CYLINDER: return sqrt(g->params[0] * g->params[0] + g->params[1] * g->params[1]);
+  case RAMP_SHAPE_ELLIPSOID: return fmax(g->params[0], fmax(g->params[1], g->params[2]));
+  default: {
+    double r = 0;
+    const double *p = verts + 3 * (size_t)g->vert_offset;
+    for (int i = 0; i < g->vert_count; ++i) r = fmax(r, sqrt(p[3 * i] * p[3 * i] + p[3 * i + 1] * p[3 * i + 1] + p[3 * i + 2] * p[3 * i + 2]));
+    return r;
+  }
+  }
+}
+
+int orc_flops_batch(const RampModelDesc *d, const double *q, int64_t n, int ld, double *flops) {
+  if (check_desc(d)) return -1;
+  double fk = 0;
+  for (int i = 0; i < d->n_joints; ++i) {
+    const int t = d->joints[i].type;
+    double f = 83;
+    if (t >= RAMP_JOINT_PX && t <= RAMP_JOINT_PRISMATIC_UNALIGNED) f = 69;
+    else if (t >= RAMP_JOINT_PLANAR) f = 150;
+    if (d->joints[i].parent < 0) f -= 63;
+    fk += f;
+  }
+  for (int g = 0; g < d->n_geoms; ++g) if (d->geoms[g].parent_joint >= 0) fk += 63;
+  double br[ORC_MAX_GEOMS];
+  for (int g = 0; g < d->n_geoms; ++g) br[g] = bound_radius(&d->geoms[g], d->verts);
+#pragma omp parallel for schedule(dynamic, 64)
+  for (int64_t i = 0; i < n; ++i) {
+    double oMi[12 * ORC_MAX_JOINTS], oMg[12 * ORC_MAX_GEOMS];
+    fk_one(d, q + i * ld, oMi);
+    placements_one(d, oMi, oMg);
+    double f = fk;
+    for (int p = 0; p < d->n_pairs; ++p) {
+      const int a = d->pairs[2 * p], b = d->pairs[2 * p + 1];
+      const RampGeom *ga = &d->geoms[a], *gb = &d->geoms[b];
+      const double dc = vnorm(vsub(m_trans(oMg + 12 * a), m_trans(oMg + 12 * b)));
+      f += 11;
+      if (dc > br[a] + br[b]) continue;
+      const int t1 = ga->type < gb->type ? ga->type : gb->type, t2 = ga->type < gb->type ? gb->type : ga->type;
+      if (t1 == RAMP_SHAPE_SPHERE && t2 == RAMP_SHAPE_SPHERE) continue;
+      if (t1 == RAMP_SHAPE_SPHERE && t2 <= RAMP_SHAPE_CYLINDER) { f += 30; continue; }
+      if (t1 == RAMP_SHAPE_CAPSULE && t2 == RAMP_SHAPE_CAPSULE) { f += 90; continue; }
+      int it = 0;
+      shape_distance(ga, oMg + 12 * a, gb, oMg + 12 * b, d->verts, 0, 0.0, &it);
+      const double v = (ga->type == RAMP_SHAPE_CONVEX ? ga->vert_count : 0) + (gb->type == RAMP_SHAPE_CONVEX ? gb->vert_count : 0);
+      f += it * (6.0 * v + 2 * 33 + 150);
+    }
+    flops[i] = f;
+  }
+  return 0;
+}

@@ -1,0 +1,85 @@
+// model_image.h -- layout of the packed, device-resident model ("image").
+//
+// One contiguous, 16-byte aligned blob lives in HBM per RampModel.  Every CTA copies it
+// into shared memory once with a single TMA bulk copy (cp.async.bulk + mbarrier) and all
+// table reads on the hot path are shared-memory broadcasts.  Shared by the host packer
+// and the kernels in ramp_b200.cu.
+#pragma once
+#include <stdint.h>
+
+namespace ramp {
+
+constexpr int kMaxJoints = 64;
+constexpr int kMaxGeoms = 128;
+constexpr int kMaxPairs = 2048;
+constexpr int kMaxNq = 128;
+constexpr int kMaxSubspaces = 48;
+constexpr int kLanes = 32;             // configurations per warp tile
+constexpr int kChunkPairs = 32;        // pairs culled per queue round
+constexpr int kQueueCap = kChunkPairs * kLanes;
+
+// parent_code of a joint
+constexpr int kParentUniverse = -1;  // child of the universe: oMi = liMi
+constexpr int kParentRunning = -2;   // parent is the previous joint: use the register copy
+
+// narrow-phase class of a pair (decided on the host from the two shape types)
+enum PairClass : int32_t {
+  kClsInactive = 0,
+  kClsSphereSphere = 1,   // decided exactly by the bounding-sphere test
+  kClsSphereCapsule = 2,
+  kClsSphereBox = 3,
+  kClsSphereCylinder = 4,
+  kClsCapsuleCapsule = 5,
+  kClsBoxBox = 6,         // exact separating-axis test
+  kClsGjk = 7             // OBB cull, then GJK on the cores
+};
+
+struct ImgHeader {  // 32 words
+  int32_t total_bytes, nq, n_joints, n_geoms, n_dyn, n_static, n_pairs, n_verts;
+  int32_t n_act, n_mimic, n_cont, n_save, mask_words, n_robot_geoms, n_robot_pairs, reserved0;
+  int32_t off_joints, off_geoms, off_pairs, off_verts, off_static, off_dyn, off_act, off_mimic;
+  int32_t off_cont, off_refq, reserved1[6];
+};
+static_assert(sizeof(ImgHeader) == 128, "header is 32 words");
+
+struct DJoint {  // 24 words
+  int32_t type, parent_code, idx_q, save_slot;
+  float ax, ay, az;
+  int32_t gfirst, gcount;  // range in the dyn-geometry order list
+  int32_t pad[3];
+  float pl[12];
+};
+static_assert(sizeof(DJoint) == 96, "DJoint");
+
+struct DGeom {  // 24 words
+  int32_t type, gslot, voff, vcnt;  // gslot >= 0: per-config slot; < 0: static transform -1-gslot
+  float p0, p1, p2, bound_r;
+  float hx, hy, hz;  // local-frame box that contains the shape (OBB cull)
+  int32_t parent;
+  float pl[12];  // placement in the parent joint frame (dyn) / world (static)
+};
+static_assert(sizeof(DGeom) == 96, "DGeom");
+
+struct DPair {  // 4 words; a/b ordered so that type(a) <= type(b)
+  int32_t a, b, cls;
+  float rs2;  // (bound_r(a)+bound_r(b))^2, inflated for culls, exact for sphere-sphere
+};
+
+struct DMimic {
+  int32_t dst, src;
+  float mult, off;
+};
+
+struct DSub {  // one OMPL subspace, by value in the edge kernels' parameter block
+  int32_t type, col, dim, pad;
+  float lo[3], hi[3];
+  float inv_lvs_real;  // 1 / (0.01 * extent) of the RealVector part
+  float inv_lvs_rot;   // same for the SO2 / SO3 part
+};
+
+struct DSpace {
+  int32_t n_sub, check_bounds, n_cols, pad;
+  DSub sub[kMaxSubspaces];
+};
+
+}  // namespace ramp

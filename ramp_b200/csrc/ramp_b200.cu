@@ -1,0 +1,1237 @@
+// ramp_b200.cu -- sm_100a kernels and the C ABI of libramp_b200.so (include/ramp_b200.h).
+//
+// Execution model (DESIGN.md has the full account):
+//   * one persistent CTA per SM; the packed model image is staged into shared memory once
+//     per CTA by a TMA bulk copy (cp.async.bulk, mbarrier completion);
+//   * a warp owns a TILE of 32 configurations.  Lane l runs forward kinematics for
+//     configuration l entirely in FP32 registers (thread-per-configuration, no idle lanes)
+//     and leaves the 3x4 placement of every movable geometry in the warp's shared-memory
+//     slab, laid out [geom][entry][lane] so every access is conflict free;
+//   * narrow phase: the warp walks the pair list; lane l runs the bounding-sphere test of
+//     pair p for ITS configuration, survivors are ballot-compacted into a per-warp queue of
+//     (lane, pair) work items; the queue is then drained 32 items at a time -- closed-form
+//     tests / exact box-box SAT / OBB cull first, survivors re-compacted, GJK last -- so the
+//     expensive code always runs with full warps;
+//   * no __syncthreads after the table staging: warps are independent.
+//
+// There is no CPU fallback in this file: every entry point fails with RAMP_ERR_CUDA when
+// no device is usable.
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <atomic>
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <mutex>
+#include <new>
+#include <vector>
+
+#include "../../include/ramp_b200.h"
+#include "device_math.cuh"
+#include "model_image.h"
+
+namespace ramp {
+
+// =============================================================================== device
+struct Tables {
+  const ImgHeader* h;
+  const DJoint* joints;
+  const DGeom* geoms;
+  const DPair* pairs;
+  const float4* verts;
+  const float* stat;  // [n_static][12]
+  const int32_t* dyn; // slot -> geometry index
+  const int32_t* act;
+  const DMimic* mimic;
+  const int32_t* cont;
+  const float* refq;
+};
+
+__device__ __forceinline__ Tables make_tables(const unsigned char* base) {
+  Tables t;
+  t.h = reinterpret_cast<const ImgHeader*>(base);
+  t.joints = reinterpret_cast<const DJoint*>(base + t.h->off_joints);
+  t.geoms = reinterpret_cast<const DGeom*>(base + t.h->off_geoms);
+  t.pairs = reinterpret_cast<const DPair*>(base + t.h->off_pairs);
+  t.verts = reinterpret_cast<const float4*>(base + t.h->off_verts);
+  t.stat = reinterpret_cast<const float*>(base + t.h->off_static);
+  t.dyn = reinterpret_cast<const int32_t*>(base + t.h->off_dyn);
+  t.act = reinterpret_cast<const int32_t*>(base + t.h->off_act);
+  t.mimic = reinterpret_cast<const DMimic*>(base + t.h->off_mimic);
+  t.cont = reinterpret_cast<const int32_t*>(base + t.h->off_cont);
+  t.refq = reinterpret_cast<const float*>(base + t.h->off_refq);
+  return t;
+}
+
+// Per-warp shared-memory slab (offsets in 4-byte words from the slab base).
+struct SlabLayout {
+  int32_t words;      // slab size
+  int32_t off_q;      // [nq][32]   Pinocchio q, slot-major
+  int32_t off_act;    // [n_cols][32] raw actuated input
+  int32_t off_geom;   // [n_dyn][12][32] geometry placements
+  int32_t off_save;   // [n_save][12][32] transforms of branching joints
+  int32_t off_queue;  // uint16[kQueueCap]
+  int32_t off_mask;   // uint32[mask_words][32]
+  int32_t off_first;  // int32[32] first colliding pair per configuration
+  int32_t off_stage;  // [32][stage_stride] output staging of the FK kernels
+  int32_t stage_stride;
+  int32_t table_bytes;  // image size rounded up to 16
+};
+
+__device__ __forceinline__ int64_t imin64(int64_t a, int64_t b) { return a < b ? a : b; }
+
+// ---- TMA bulk copy of the model image into shared memory
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return static_cast<uint32_t>(__cvta_generic_to_shared(p)); }
+
+__device__ __forceinline__ void stage_tables(unsigned char* dst, const unsigned char* __restrict__ src, int bytes,
+                                             uint64_t* mbar) {
+  const uint32_t bar = smem_u32(mbar);
+  if (threadIdx.x == 0) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar));
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                     smem_u32(dst)),
+                 "l"(src), "r"(bytes), "r"(bar)
+                 : "memory");
+  }
+  uint32_t done = 0;
+  while (!done) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], 0;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(done)
+        : "r"(bar)
+        : "memory");
+  }
+}
+
+struct Warp {
+  Tables t;
+  float* q;
+  float* act;
+  float* geom;
+  float* save;
+  uint16_t* queue;
+  uint32_t* mask;
+  int32_t* first;
+  float* stage;
+  int stage_stride;
+  int lane;
+};
+
+__device__ __forceinline__ Warp make_warp(const Tables& t, float* slab, const SlabLayout& L) {
+  Warp w;
+  w.t = t;
+  w.q = slab + L.off_q;
+  w.act = slab + L.off_act;
+  w.geom = slab + L.off_geom;
+  w.save = slab + L.off_save;
+  w.queue = reinterpret_cast<uint16_t*>(slab + L.off_queue);
+  w.mask = reinterpret_cast<uint32_t*>(slab + L.off_mask);
+  w.first = reinterpret_cast<int32_t*>(slab + L.off_first);
+  w.stage = slab + L.off_stage;
+  w.stage_stride = L.stage_stride;
+  w.lane = threadIdx.x & 31;
+  return w;
+}
+
+// ---- coalesced load of a [rows<=32][cols] float tile into slot-major shared memory
+// dst[col*32 + row].  Vectorised float4 path when the tile is 16-byte aligned.
+__device__ __forceinline__ void load_rows(float* dst, const float* __restrict__ src, int64_t row0, int64_t n_rows,
+                                          int cols, int ld, int lane) {
+  const int rows = static_cast<int>(imin64(32, n_rows - row0));
+  const float* base = src + row0 * ld;
+  if (ld == cols && (cols & 3) == 0 && (reinterpret_cast<uintptr_t>(base) & 15) == 0) {
+    const int n4 = rows * cols / 4;
+    const float4* b4 = reinterpret_cast<const float4*>(base);
+    for (int e = lane; e < n4; e += 32) {
+      const float4 v = __ldg(b4 + e);
+      const int r = (4 * e) / cols, c = (4 * e) - r * cols;
+      dst[(c + 0) * 32 + r] = v.x;
+      dst[(c + 1) * 32 + r] = v.y;
+      dst[(c + 2) * 32 + r] = v.z;
+      dst[(c + 3) * 32 + r] = v.w;
+    }
+  } else {
+    const int n = rows * cols;
+    for (int e = lane; e < n; e += 32) {
+      const int r = e / cols, c = e - r * cols;
+      dst[c * 32 + r] = __ldg(base + static_cast<int64_t>(r) * ld + c);
+    }
+  }
+  // lanes past the end of the batch replay row 0 so every lane does well-defined work
+  if (rows < 32) {
+    __syncwarp();
+    if (lane >= rows)
+      for (int c = 0; c < cols; ++c) dst[c * 32 + lane] = dst[c * 32];
+  }
+  __syncwarp();
+}
+
+// ---- actuated values -> Pinocchio q (reference robot_state.py:117-119: scatter, mimic,
+// then continuous).  Lane-private columns of shared memory, no cross-lane traffic.
+__device__ __forceinline__ void expand_q(const Warp& w) {
+  const ImgHeader* h = w.t.h;
+  const int l = w.lane;
+  for (int s = 0; s < h->nq; ++s) w.q[s * 32 + l] = w.t.refq[s];
+  for (int k = 0; k < h->n_act; ++k) w.q[w.t.act[k] * 32 + l] = w.act[k * 32 + l];
+  for (int k = 0; k < h->n_mimic; ++k) {
+    const DMimic m = w.t.mimic[k];
+    w.q[m.dst * 32 + l] = fmaf(w.q[m.src * 32 + l], m.mult, m.off);
+  }
+  for (int k = 0; k < h->n_cont; ++k) {
+    const int c = w.t.cont[k];
+    float s, co;
+    sincosf(w.q[c * 32 + l], &s, &co);
+    w.q[c * 32 + l] = co;
+    w.q[(c + 1) * 32 + l] = s;
+  }
+}
+
+__device__ __forceinline__ Xf load_table_xf(const float* p) {
+  Xf o;
+#pragma unroll
+  for (int k = 0; k < 12; ++k) o.m[k] = p[k];
+  return o;
+}
+
+__device__ __forceinline__ void store_slab_xf(float* slab, int slot, int lane, const Xf& x) {
+#pragma unroll
+  for (int k = 0; k < 12; ++k) slab[(slot * 12 + k) * 32 + lane] = x.m[k];
+}
+
+__device__ __forceinline__ Xf load_slab_xf(const float* slab, int slot, int lane) {
+  Xf o;
+#pragma unroll
+  for (int k = 0; k < 12; ++k) o.m[k] = slab[(slot * 12 + k) * 32 + lane];
+  return o;
+}
+
+// World placement of geometry g for configuration c (lane-divergent g and c allowed).
+__device__ __forceinline__ Xf geom_xf(const Warp& w, int gslot, int c) {
+  const float* p = gslot >= 0 ? w.geom + gslot * 12 * 32 + c : w.t.stat + (-1 - gslot) * 12;
+  const int st = gslot >= 0 ? 32 : 1;
+  Xf o;
+#pragma unroll
+  for (int k = 0; k < 12; ++k) o.m[k] = p[k * st];
+  return o;
+}
+
+// ---- forward kinematics for this lane's configuration (pinocchio::forwardKinematics +
+// updateGeometryPlacements).  kStage: 0 = placements to the slab only, 1 = also stage oMi
+// rows, 2 = also stage oMg rows (output kernels).
+template <int kStage>
+__device__ __forceinline__ void fk_lane(const Warp& w) {
+  const ImgHeader* h = w.t.h;
+  const int l = w.lane;
+  Xf cur = xf_identity();
+  for (int i = 0; i < h->n_joints; ++i) {
+    const DJoint* j = &w.t.joints[i];
+    const int type = j->type;
+    float qv[7];
+    const int n = joint_nq(type);
+#pragma unroll
+    for (int k = 0; k < 7; ++k) qv[k] = k < n ? w.q[(j->idx_q + k) * 32 + l] : 0.f;
+    const Xf loc = xf_mul(load_table_xf(j->pl), joint_xf(type, j->ax, j->ay, j->az, qv));
+    const int pc = j->parent_code;
+    if (pc == kParentUniverse) cur = loc;
+    else if (pc == kParentRunning) cur = xf_mul(cur, loc);
+    else cur = xf_mul(load_slab_xf(w.save, pc, l), loc);
+    if (j->save_slot >= 0) store_slab_xf(w.save, j->save_slot, l, cur);
+    if (kStage == 1) {
+#pragma unroll
+      for (int k = 0; k < 12; ++k) w.stage[l * w.stage_stride + i * 12 + k] = cur.m[k];
+    }
+    for (int s = j->gfirst; s < j->gfirst + j->gcount; ++s) {
+      const int gi = w.t.dyn[s];
+      const Xf og = xf_mul(cur, load_table_xf(w.t.geoms[gi].pl));
+      if (kStage == 2) {
+#pragma unroll
+        for (int k = 0; k < 12; ++k) w.stage[l * w.stage_stride + gi * 12 + k] = og.m[k];
+      } else {
+        store_slab_xf(w.geom, s, l, og);
+      }
+    }
+  }
+}
+
+// ---- narrow phase over the pair list for the 32 configurations of the tile.
+__device__ __forceinline__ void record_hit(const Warp& w, int c, int p, bool want_mask) {
+  atomicMin(&w.first[c], p);
+  if (want_mask) atomicOr(&w.mask[(p >> 5) * 32 + c], 1u << (p & 31));
+}
+
+__device__ __forceinline__ Shape load_shape(const DGeom* g) {
+  Shape s;
+  s.type = g->type; s.p0 = g->p0; s.p1 = g->p1; s.p2 = g->p2; s.voff = g->voff; s.vcnt = g->vcnt;
+  return s;
+}
+
+// exact closed-form decision for the primitive classes; rel = pose of b in a's frame
+__device__ __forceinline__ bool closed_form_hit(int cls, const DGeom* ga, const DGeom* gb, const Xf& rel) {
+  switch (cls) {
+    case kClsSphereCapsule: {  // a sphere, b capsule: sphere centre in b's frame
+      const V3 c = rot_t(rel, -trans(rel));
+      return point_zseg_dist(c, gb->p1) - ga->p0 - gb->p0 <= 0.f;
+    }
+    case kClsSphereBox: {
+      const V3 c = rot_t(rel, -trans(rel));
+      return sphere_box_dist(c, gb->p0, gb->p1, gb->p2, ga->p0) <= 0.f;
+    }
+    case kClsSphereCylinder: {
+      const V3 c = rot_t(rel, -trans(rel));
+      return sphere_cyl_dist(c, gb->p0, gb->p1, ga->p0) <= 0.f;
+    }
+    case kClsCapsuleCapsule: {
+      const V3 zb = mk(rel.m[2], rel.m[6], rel.m[10]);
+      const V3 p2 = trans(rel) - zb * gb->p1;
+      return seg_seg_dist(mk(0.f, 0.f, -ga->p1), mk(0.f, 0.f, 2.f * ga->p1), p2, zb * (2.f * gb->p1)) - ga->p0 -
+                 gb->p0 <= 0.f;
+    }
+    default: return false;
+  }
+}
+
+__device__ __forceinline__ void narrow_phase(const Warp& w, bool stop_at_first, bool want_mask) {
+  const ImgHeader* h = w.t.h;
+  const int l = w.lane;
+  const unsigned FULL = 0xffffffffu;
+  for (int chunk = 0; chunk < h->n_pairs; chunk += kChunkPairs) {
+    const int chunk_end = min(chunk + kChunkPairs, h->n_pairs);
+    const int my_first = w.first[l];
+    int qn = 0;
+    // ---- stage 1: bounding spheres, lane = configuration, pair index uniform
+    for (int p = chunk; p < chunk_end; ++p) {
+      const DPair pr = w.t.pairs[p];
+      if (pr.cls == kClsInactive) continue;
+      bool pass = !(stop_at_first && my_first < p);
+      const int sa = w.t.geoms[pr.a].gslot, sb = w.t.geoms[pr.b].gslot;
+      const float* pa = sa >= 0 ? w.geom + sa * 12 * 32 + l : w.t.stat + (-1 - sa) * 12;
+      const float* pb = sb >= 0 ? w.geom + sb * 12 * 32 + l : w.t.stat + (-1 - sb) * 12;
+      const int sta = sa >= 0 ? 32 : 1, stb = sb >= 0 ? 32 : 1;
+      const float dx = pa[3 * sta] - pb[3 * stb], dy = pa[7 * sta] - pb[7 * stb], dz = pa[11 * sta] - pb[11 * stb];
+      const float d2 = fmaf(dx, dx, fmaf(dy, dy, dz * dz));
+      pass = pass && d2 <= pr.rs2;
+      if (pr.cls == kClsSphereSphere) {
+        if (pass) record_hit(w, l, p, want_mask);
+        pass = false;
+      }
+      const unsigned b = __ballot_sync(FULL, pass);
+      if (pass) w.queue[qn + __popc(b & ((1u << l) - 1))] = static_cast<uint16_t>(((p - chunk) << 5) | l);
+      qn += __popc(b);
+    }
+    __syncwarp();
+    // ---- stage 2: closed forms, exact box-box, OBB cull; survivors re-compacted in place
+    int gn = 0;
+    for (int base = 0; base < qn; base += 32) {
+      const bool live = base + l < qn;
+      const int item = live ? w.queue[base + l] : 0;
+      bool to_gjk = false;
+      if (live) {
+        const int c = item & 31, p = chunk + (item >> 5);
+        const DPair pr = w.t.pairs[p];
+        const DGeom* ga = &w.t.geoms[pr.a];
+        const DGeom* gb = &w.t.geoms[pr.b];
+        const Xf rel = xf_inv_mul(geom_xf(w, ga->gslot, c), geom_xf(w, gb->gslot, c));
+        if (pr.cls == kClsBoxBox) {
+          if (obb_overlap(mk(ga->p0, ga->p1, ga->p2), mk(gb->p0, gb->p1, gb->p2), rel, 0.f)) record_hit(w, c, p, want_mask);
+        } else if (pr.cls == kClsGjk) {
+          to_gjk = obb_overlap(mk(ga->hx, ga->hy, ga->hz), mk(gb->hx, gb->hy, gb->hz), rel, 1e-5f);
+        } else if (closed_form_hit(pr.cls, ga, gb, rel)) {
+          record_hit(w, c, p, want_mask);
+        }
+      }
+      __syncwarp();  // all lanes have read their item before the in-place compaction writes
+      const unsigned b = __ballot_sync(FULL, to_gjk);
+      if (to_gjk) w.queue[gn + __popc(b & ((1u << l) - 1))] = static_cast<uint16_t>(item);
+      gn += __popc(b);
+      __syncwarp();
+    }
+    // ---- stage 3: GJK on dense groups of 32 work items
+    for (int base = 0; base < gn; base += 32) {
+      if (base + l < gn) {
+        const int item = w.queue[base + l];
+        const int c = item & 31, p = chunk + (item >> 5);
+        // a configuration that was hit earlier in this chunk needs no later pair
+        if (!(stop_at_first && w.first[c] < p)) {
+          const DPair pr = w.t.pairs[p];
+          const DGeom* ga = &w.t.geoms[pr.a];
+          const DGeom* gb = &w.t.geoms[pr.b];
+          const Xf rel = xf_inv_mul(geom_xf(w, ga->gslot, c), geom_xf(w, gb->gslot, c));
+          const GjkResult r = gjk(load_shape(ga), load_shape(gb), rel, w.t.verts, false);
+          if (r.hit) record_hit(w, c, p, want_mask);
+        }
+      }
+    }
+    __syncwarp();
+  }
+}
+
+__device__ __forceinline__ void reset_results(const Warp& w, int mask_words) {
+  w.first[w.lane] = INT32_MAX;
+  for (int k = 0; k < mask_words; ++k) w.mask[k * 32 + w.lane] = 0u;
+  __syncwarp();
+}
+
+struct CheckArgs {
+  const unsigned char* img;
+  const float* q;
+  int64_t n;
+  int32_t ld;
+  uint32_t flags;
+  uint8_t* hit;
+  int32_t* first_pair;
+  uint32_t* pair_mask;
+  SlabLayout L;
+};
+
+extern __shared__ __align__(128) unsigned char g_smem[];
+
+// ------------------------------------------------------------------ kernel: validity
+__global__ void __launch_bounds__(512, 1) check_kernel(const __grid_constant__ CheckArgs a) {
+  uint64_t* mbar = reinterpret_cast<uint64_t*>(g_smem);
+  unsigned char* tbl = g_smem + 16;
+  stage_tables(tbl, a.img, a.L.table_bytes, mbar);
+  const Tables t = make_tables(tbl);
+  const int nwarps = blockDim.x >> 5, wid = threadIdx.x >> 5;
+  float* slab = reinterpret_cast<float*>(tbl + a.L.table_bytes) + static_cast<size_t>(wid) * a.L.words;
+  const Warp w = make_warp(t, slab, a.L);
+  const bool actuated = a.flags & RAMP_Q_ACTUATED;
+  const bool want_mask = a.pair_mask != nullptr;
+  const bool stop = !(a.flags & RAMP_ALL_PAIRS) && !want_mask;
+  const int cols = actuated ? t.h->n_act : t.h->nq;
+  const int64_t ntiles = (a.n + 31) >> 5;
+  for (int64_t tile = static_cast<int64_t>(blockIdx.x) * nwarps + wid; tile < ntiles;
+       tile += static_cast<int64_t>(gridDim.x) * nwarps) {
+    const int64_t row0 = tile << 5;
+    load_rows(actuated ? w.act : w.q, a.q, row0, a.n, cols, a.ld, w.lane);
+    if (actuated) expand_q(w);
+    reset_results(w, want_mask ? t.h->mask_words : 0);
+    fk_lane<0>(w);
+    __syncwarp();
+    narrow_phase(w, stop, want_mask);
+    const int64_t row = row0 + w.lane;
+    if (row < a.n) {
+      const int f = w.first[w.lane];
+      a.hit[row] = f != INT32_MAX;
+      if (a.first_pair) a.first_pair[row] = f != INT32_MAX ? f : -1;
+      if (want_mask)
+        for (int k = 0; k < t.h->mask_words; ++k) a.pair_mask[row * t.h->mask_words + k] = w.mask[k * 32 + w.lane];
+    }
+    __syncwarp();
+  }
+}
+
+// --------------------------------------------------------------- kernel: FK / placements
+struct FkArgs {
+  const unsigned char* img;
+  const float* q;
+  int64_t n;
+  int32_t ld;
+  uint32_t flags;
+  float* out;
+  int32_t row_floats;  // n_joints*12 or n_geoms*12
+  SlabLayout L;
+};
+
+template <int kWhat>  // 1 = oMi, 2 = oMg
+__global__ void __launch_bounds__(512, 1) fk_kernel(const __grid_constant__ FkArgs a) {
+  uint64_t* mbar = reinterpret_cast<uint64_t*>(g_smem);
+  unsigned char* tbl = g_smem + 16;
+  stage_tables(tbl, a.img, a.L.table_bytes, mbar);
+  const Tables t = make_tables(tbl);
+  const int nwarps = blockDim.x >> 5, wid = threadIdx.x >> 5;
+  float* slab = reinterpret_cast<float*>(tbl + a.L.table_bytes) + static_cast<size_t>(wid) * a.L.words;
+  const Warp w = make_warp(t, slab, a.L);
+  const bool actuated = a.flags & RAMP_Q_ACTUATED;
+  const int cols = actuated ? t.h->n_act : t.h->nq;
+  const int64_t ntiles = (a.n + 31) >> 5;
+  for (int64_t tile = static_cast<int64_t>(blockIdx.x) * nwarps + wid; tile < ntiles;
+       tile += static_cast<int64_t>(gridDim.x) * nwarps) {
+    const int64_t row0 = tile << 5;
+    load_rows(actuated ? w.act : w.q, a.q, row0, a.n, cols, a.ld, w.lane);
+    if (actuated) expand_q(w);
+    fk_lane<kWhat>(w);
+    if (kWhat == 2) {  // universe-attached geometries have constant placements
+      for (int g = 0; g < t.h->n_geoms; ++g) {
+        const int gs = t.geoms[g].gslot;
+        if (gs < 0)
+          for (int k = 0; k < 12; ++k) w.stage[w.lane * w.stage_stride + g * 12 + k] = t.stat[(-1 - gs) * 12 + k];
+      }
+    }
+    __syncwarp();
+    // the tile's rows are contiguous in the output: stream them out fully coalesced
+    const int rows = static_cast<int>(imin64(32, a.n - row0));
+    float* dst = a.out + row0 * a.row_floats;
+    const int total = rows * a.row_floats;
+    for (int e = w.lane; e < total; e += 32) {
+      const int r = e / a.row_floats, c = e - r * a.row_floats;
+      __stcs(dst + e, w.stage[r * w.stage_stride + c]);
+    }
+    __syncwarp();
+  }
+}
+
+// ------------------------------------------------------------------ kernels: edges
+// OMPL state-space maths in FP32 (reference: OMPL RealVector/SO2/SO3 spaces).
+#define RAMP_PI_F 3.14159265358979323846f
+
+__device__ __forceinline__ float so2_dist(float a, float b) {
+  const float d = fabsf(a - b);
+  return d > RAMP_PI_F ? 2.f * RAMP_PI_F - d : d;
+}
+
+__device__ __forceinline__ float so2_interp(float from, float to, float t) {
+  float diff = to - from, v;
+  if (fabsf(diff) <= RAMP_PI_F) v = fmaf(diff, t, from);
+  else {
+    diff = diff > 0.f ? 2.f * RAMP_PI_F - diff : -2.f * RAMP_PI_F - diff;
+    v = from - diff * t;
+    if (v > RAMP_PI_F) v -= 2.f * RAMP_PI_F;
+    else if (v < -RAMP_PI_F) v += 2.f * RAMP_PI_F;
+  }
+  return v;
+}
+
+__device__ __forceinline__ float so3_arc(const float* a, const float* b, int st) {
+  const float dq = fabsf(a[0] * b[0] + a[st] * b[st] + a[2 * st] * b[2 * st] + a[3 * st] * b[3 * st]);
+  return dq > 1.f - 1e-7f ? 0.f : acosf(dq);
+}
+
+__device__ __forceinline__ int seg_count(float dist, float inv_lvs) { return static_cast<int>(ceilf(dist * inv_lvs)); }
+
+// validSegmentCount of one edge; q0/q1 are the edge's rows in global memory
+__device__ __forceinline__ int edge_nd(const DSpace& sp, const float* __restrict__ q0, const float* __restrict__ q1) {
+  int nd = 0;
+  for (int i = 0; i < sp.n_sub; ++i) {
+    const DSub& s = sp.sub[i];
+    const float* a = q0 + s.col;
+    const float* b = q1 + s.col;
+    int c = 0;
+    const int nreal = s.type == RAMP_SPACE_REAL ? s.dim : (s.type == RAMP_SPACE_SE2 ? 2 : (s.type == RAMP_SPACE_SE3 ? 3 : 0));
+    if (nreal) {
+      float e = 0.f;
+      for (int k = 0; k < nreal; ++k) { const float d = a[k] - b[k]; e = fmaf(d, d, e); }
+      c = seg_count(sqrtf(e), s.inv_lvs_real);
+    }
+    if (s.type == RAMP_SPACE_SO2) c = seg_count(so2_dist(a[0], b[0]), s.inv_lvs_rot);
+    else if (s.type == RAMP_SPACE_SE2) c = max(c, seg_count(so2_dist(a[2], b[2]), s.inv_lvs_rot));
+    else if (s.type == RAMP_SPACE_SE3) c = max(c, seg_count(so3_arc(a + 3, b + 3, 1), s.inv_lvs_rot));
+    else if (s.type == RAMP_SPACE_SO3) c = seg_count(so3_arc(a, b, 1), s.inv_lvs_rot);
+    nd = max(nd, c);
+  }
+  return nd;
+}
+
+struct EdgeArgs {
+  const unsigned char* img;
+  const float* q0;
+  const float* q1;
+  int64_t n_edges;
+  int32_t ld;
+  uint8_t* valid;
+  int32_t* first_invalid;  // always non-null inside the library (scratch when the caller passes none)
+  int32_t* nd;             // idem
+  int64_t* offs;           // [n_edges+1] exclusive prefix of per-edge state counts (scratch)
+  SlabLayout L;
+  DSpace sp;
+};
+
+// pass 1: nd per edge, number of states to check per edge (nd interior+end states, >= 1)
+__global__ void edge_count_kernel(const __grid_constant__ EdgeArgs a) {
+  const int64_t e = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (e >= a.n_edges) return;
+  const int nd = edge_nd(a.sp, a.q0 + e * a.ld, a.q1 + e * a.ld);
+  a.nd[e] = nd;
+  a.first_invalid[e] = INT32_MAX;
+  a.offs[e + 1] = max(nd, 1);
+}
+
+// pass 2: in-place inclusive scan of offs[1..n] by one CTA (offs[0] = 0)
+__global__ void __launch_bounds__(1024) edge_scan_kernel(int64_t* offs, int64_t n) {
+  __shared__ int64_t part[1024];
+  const int t = threadIdx.x;
+  const int64_t per = (n + 1023) / 1024, lo = imin64(n, t * per), hi = imin64(n, lo + per);
+  int64_t s = 0;
+  for (int64_t i = lo; i < hi; ++i) s += offs[i + 1];
+  part[t] = s;
+  __syncthreads();
+  for (int d = 1; d < 1024; d <<= 1) {
+    const int64_t v = t >= d ? part[t - d] : 0;
+    __syncthreads();
+    part[t] += v;
+    __syncthreads();
+  }
+  int64_t run = t ? part[t - 1] : 0;
+  if (t == 0) offs[0] = 0;
+  for (int64_t i = lo; i < hi; ++i) {
+    run += offs[i + 1];
+    offs[i + 1] = run;
+  }
+}
+
+// pass 3: every warp tile is 32 consecutive (edge, j) states of the flattened list
+__global__ void __launch_bounds__(512, 1) edge_check_kernel(const __grid_constant__ EdgeArgs a) {
+  uint64_t* mbar = reinterpret_cast<uint64_t*>(g_smem);
+  unsigned char* tbl = g_smem + 16;
+  stage_tables(tbl, a.img, a.L.table_bytes, mbar);
+  const Tables t = make_tables(tbl);
+  const int nwarps = blockDim.x >> 5, wid = threadIdx.x >> 5;
+  float* slab = reinterpret_cast<float*>(tbl + a.L.table_bytes) + static_cast<size_t>(wid) * a.L.words;
+  const Warp w = make_warp(t, slab, a.L);
+  const int l = w.lane;
+  const int64_t total = a.offs[a.n_edges];
+  const int64_t ntiles = (total + 31) >> 5;
+  for (int64_t tile = static_cast<int64_t>(blockIdx.x) * nwarps + wid; tile < ntiles;
+       tile += static_cast<int64_t>(gridDim.x) * nwarps) {
+    const int64_t s = (tile << 5) + l;
+    const bool live = s < total;
+    // edge of state s: last e with offs[e] <= s
+    int64_t lo = 0, hi = a.n_edges - 1;
+    const int64_t ss = live ? s : total - 1;
+    while (lo < hi) {
+      const int64_t mid = (lo + hi + 1) >> 1;
+      if (a.offs[mid] <= ss) lo = mid; else hi = mid - 1;
+    }
+    const int64_t e = lo;
+    const int nd = a.nd[e];
+    const int j = static_cast<int>(ss - a.offs[e]) + 1;  // 1..max(nd,1); j >= nd means q1 itself
+    const float* r0 = a.q0 + e * a.ld;
+    const float* r1 = a.q1 + e * a.ld;
+    const bool is_end = j >= nd;
+    const float tt = is_end ? 1.f : static_cast<float>(j) / static_cast<float>(nd);
+    // an edge already known to be invalid at a smaller j needs no further states
+    bool skip = !live || a.first_invalid[e] < min(j, nd);
+    bool in_bounds = true;
+    for (int i = 0; i < a.sp.n_sub; ++i) {
+      const DSub& sb = a.sp.sub[i];
+      const float* p0 = r0 + sb.col;
+      const float* p1 = r1 + sb.col;
+      float* o = w.act + sb.col * 32 + l;
+      const int nreal = sb.type == RAMP_SPACE_REAL ? sb.dim : (sb.type == RAMP_SPACE_SE2 ? 2 : (sb.type == RAMP_SPACE_SE3 ? 3 : 0));
+      for (int k = 0; k < nreal; ++k) {
+        const float v = is_end ? p1[k] : fmaf(p1[k] - p0[k], tt, p0[k]);
+        o[k * 32] = v;
+        in_bounds = in_bounds && v <= sb.hi[k] && v >= sb.lo[k];
+      }
+      if (sb.type == RAMP_SPACE_SO2 || sb.type == RAMP_SPACE_SE2) {
+        const int k = sb.type == RAMP_SPACE_SE2 ? 2 : 0;
+        const float v = is_end ? p1[k] : so2_interp(p0[k], p1[k], tt);
+        o[k * 32] = v;
+        in_bounds = in_bounds && v <= RAMP_PI_F && v >= -RAMP_PI_F;
+      } else if (sb.type == RAMP_SPACE_SE3 || sb.type == RAMP_SPACE_SO3) {
+        const int k0 = sb.type == RAMP_SPACE_SE3 ? 3 : 0;
+        const float* qa = p0 + k0;
+        const float* qb = p1 + k0;
+        float out[4] = {qb[0], qb[1], qb[2], qb[3]};
+        if (!is_end) {
+          const float th = so3_arc(qa, qb, 1);
+          if (th > 1e-7f) {
+            const float d = 1.f / sinf(th), s0 = sinf((1.f - tt) * th);
+            float s1 = sinf(tt * th);
+            if (qa[0] * qb[0] + qa[1] * qb[1] + qa[2] * qb[2] + qa[3] * qb[3] < 0.f) s1 = -s1;
+            for (int k = 0; k < 4; ++k) out[k] = (qa[k] * s0 + qb[k] * s1) * d;
+          } else {
+            for (int k = 0; k < 4; ++k) out[k] = qa[k];
+          }
+        }
+        for (int k = 0; k < 4; ++k) o[(k0 + k) * 32] = out[k];
+      }
+    }
+    __syncwarp();
+    expand_q(w);
+    reset_results(w, 0);
+    fk_lane<0>(w);
+    __syncwarp();
+    narrow_phase(w, true, false);
+    const bool invalid = w.first[l] != INT32_MAX || (a.sp.check_bounds && !in_bounds);
+    if (!skip && invalid) atomicMin(&a.first_invalid[e], min(j, nd));
+    __syncwarp();
+  }
+}
+
+// pass 4: fold the per-edge minimum into the caller's outputs
+__global__ void edge_finish_kernel(const __grid_constant__ EdgeArgs a, int32_t* out_first, int32_t* out_nd) {
+  const int64_t e = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (e >= a.n_edges) return;
+  const int f = a.first_invalid[e];
+  a.valid[e] = f == INT32_MAX;
+  if (out_first) out_first[e] = f == INT32_MAX ? -1 : f;
+  if (out_nd && out_nd != a.nd) out_nd[e] = a.nd[e];
+}
+
+// ================================================================================= host
+static thread_local char g_err[512] = "";
+static std::atomic<int64_t> g_launches{0};
+
+static int fail(int code, const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof g_err, fmt, ap);
+  va_end(ap);
+  return code;
+}
+
+#define CUDA_TRY(expr)                                                                          \
+  do {                                                                                          \
+    cudaError_t e_ = (expr);                                                                    \
+    if (e_ != cudaSuccess) return fail(RAMP_ERR_CUDA, "%s: %s", #expr, cudaGetErrorString(e_)); \
+  } while (0)
+
+struct HostGeom {
+  RampGeom g;
+};
+
+}  // namespace ramp
+
+struct RampModel {
+  int device = 0;
+  int sm_count = 0;
+  int max_smem = 0;
+  int32_t nq = 0;
+  std::vector<RampJoint> joints;
+  std::vector<RampGeom> robot_geoms, scene_geoms;
+  std::vector<int32_t> robot_pairs, scene_pairs;  // flattened [][2]
+  std::vector<double> robot_verts, scene_verts;   // [][3]
+  std::vector<uint8_t> pair_active;
+  // qmap
+  bool has_qmap = false;
+  std::vector<int32_t> act_slot, mimic_dst, mimic_src, cont_slot;
+  std::vector<double> mimic_mult, mimic_off, ref_q;
+  // device image
+  std::vector<unsigned char> image;
+  unsigned char* d_image = nullptr;
+  size_t d_image_cap = 0;
+  ramp::ImgHeader hdr{};
+  // scratch for ramp_check_edges (offsets, nd, first_invalid) and ramp_check_host staging
+  mutable std::mutex mu;
+  mutable void* d_scratch = nullptr;
+  mutable size_t scratch_cap = 0;
+  mutable void* h_pinned = nullptr;
+  mutable size_t pinned_cap = 0;
+};
+
+namespace ramp {
+
+static int pair_class(int ta, int tb) {
+  if (ta > tb) std::swap(ta, tb);
+  if (ta == RAMP_SHAPE_SPHERE) {
+    if (tb == RAMP_SHAPE_SPHERE) return kClsSphereSphere;
+    if (tb == RAMP_SHAPE_CAPSULE) return kClsSphereCapsule;
+    if (tb == RAMP_SHAPE_BOX) return kClsSphereBox;
+    if (tb == RAMP_SHAPE_CYLINDER) return kClsSphereCylinder;
+  }
+  if (ta == RAMP_SHAPE_CAPSULE && tb == RAMP_SHAPE_CAPSULE) return kClsCapsuleCapsule;
+  if (ta == RAMP_SHAPE_BOX && tb == RAMP_SHAPE_BOX) return kClsBoxBox;
+  return kClsGjk;
+}
+
+static size_t align16(size_t x) { return (x + 15) & ~size_t(15); }
+
+static void mat_mul34(const double* a, const double* b, double* o) {
+  double r[12];
+  for (int i = 0; i < 3; ++i) {
+    for (int j = 0; j < 3; ++j) r[4 * i + j] = a[4 * i] * b[j] + a[4 * i + 1] * b[4 + j] + a[4 * i + 2] * b[8 + j];
+    r[4 * i + 3] = a[4 * i] * b[3] + a[4 * i + 1] * b[7] + a[4 * i + 2] * b[11] + a[4 * i + 3];
+  }
+  std::memcpy(o, r, sizeof r);
+}
+
+// Pack the host description into the device image.  Convex hulls are re-centred on the
+// centre of their local bounding box (vertices shifted, placement composed with the shift):
+// the placed point set is unchanged, the bounding sphere / OBB get tighter.
+static int build_image(RampModel* m) {
+  const int nj = static_cast<int>(m->joints.size());
+  const int n_robot = static_cast<int>(m->robot_geoms.size());
+  const int ng = n_robot + static_cast<int>(m->scene_geoms.size());
+  const int n_rp = static_cast<int>(m->robot_pairs.size() / 2);
+  const int np = n_rp + static_cast<int>(m->scene_pairs.size() / 2);
+  if (nj > kMaxJoints) return fail(RAMP_ERR_LIMIT, "%d joints > limit %d", nj, kMaxJoints);
+  if (ng > kMaxGeoms) return fail(RAMP_ERR_LIMIT, "%d geometries > limit %d", ng, kMaxGeoms);
+  if (np > kMaxPairs) return fail(RAMP_ERR_LIMIT, "%d pairs > limit %d", np, kMaxPairs);
+  if (m->nq > kMaxNq) return fail(RAMP_ERR_LIMIT, "nq %d > limit %d", m->nq, kMaxNq);
+
+  std::vector<DJoint> dj(nj);
+  std::vector<DGeom> dg(ng);
+  std::vector<float> verts4;  // float4
+  std::vector<float> stat;
+  std::vector<int32_t> dyn;
+
+  // joints: running / saved parents
+  std::vector<int> save_slot(nj, -1);
+  int n_save = 0;
+  for (int i = 0; i < nj; ++i) {
+    const RampJoint& j = m->joints[i];
+    if (j.parent >= i || j.parent < -1) return fail(RAMP_ERR_INVALID, "joint %d: parent %d must precede it", i, j.parent);
+    if (j.type < RAMP_JOINT_RX || j.type > RAMP_JOINT_TRANSLATION) return fail(RAMP_ERR_INVALID, "joint %d: unknown type %d", i, j.type);
+    if (j.parent >= 0 && j.parent != i - 1 && save_slot[j.parent] < 0) save_slot[j.parent] = n_save++;
+  }
+  for (int i = 0; i < nj; ++i) {
+    const RampJoint& j = m->joints[i];
+    DJoint& d = dj[i];
+    std::memset(&d, 0, sizeof d);
+    d.type = j.type;
+    d.idx_q = j.idx_q;
+    d.parent_code = j.parent < 0 ? kParentUniverse : (j.parent == i - 1 ? kParentRunning : save_slot[j.parent]);
+    d.save_slot = save_slot[i];
+    d.ax = static_cast<float>(j.axis[0]); d.ay = static_cast<float>(j.axis[1]); d.az = static_cast<float>(j.axis[2]);
+    for (int k = 0; k < 12; ++k) d.pl[k] = static_cast<float>(j.placement[k]);
+  }
+  // geometries
+  int n_static = 0;
+  std::vector<std::vector<int>> by_joint(nj);
+  for (int g = 0; g < ng; ++g) {
+    const bool scene = g >= n_robot;
+    const RampGeom& src = scene ? m->scene_geoms[g - n_robot] : m->robot_geoms[g];
+    const std::vector<double>& vsrc = scene ? m->scene_verts : m->robot_verts;
+    DGeom& d = dg[g];
+    std::memset(&d, 0, sizeof d);
+    if (src.type < RAMP_SHAPE_SPHERE || src.type > RAMP_SHAPE_ELLIPSOID) return fail(RAMP_ERR_INVALID, "geometry %d: unknown shape %d", g, src.type);
+    if (src.parent_joint >= nj || src.parent_joint < -1) return fail(RAMP_ERR_INVALID, "geometry %d: bad parent joint %d", g, src.parent_joint);
+    d.type = src.type;
+    d.parent = src.parent_joint;
+    d.p0 = static_cast<float>(src.params[0]); d.p1 = static_cast<float>(src.params[1]); d.p2 = static_cast<float>(src.params[2]);
+    double pl[12];
+    std::memcpy(pl, src.placement, sizeof pl);
+    double hx = 0, hy = 0, hz = 0, br = 0;
+    switch (src.type) {
+      case RAMP_SHAPE_SPHERE: hx = hy = hz = br = src.params[0]; break;
+      case RAMP_SHAPE_CAPSULE: hx = hy = src.params[0]; hz = br = src.params[0] + src.params[1]; break;
+      case RAMP_SHAPE_BOX: hx = src.params[0]; hy = src.params[1]; hz = src.params[2]; br = std::sqrt(hx * hx + hy * hy + hz * hz); break;
+      case RAMP_SHAPE_CYLINDER: hx = hy = src.params[0]; hz = src.params[1]; br = std::sqrt(hx * hx + hz * hz); break;
+      case RAMP_SHAPE_ELLIPSOID: hx = src.params[0]; hy = src.params[1]; hz = src.params[2]; br = std::max(hx, std::max(hy, hz)); break;
+      case RAMP_SHAPE_CONVEX: {
+        if (src.vert_count <= 0 || src.vert_offset < 0 || static_cast<size_t>(src.vert_offset + src.vert_count) * 3 > vsrc.size())
+          return fail(RAMP_ERR_INVALID, "geometry %d: vertex range out of bounds", g);
+        const double* v = vsrc.data() + 3 * static_cast<size_t>(src.vert_offset);
+        double lo[3] = {1e300, 1e300, 1e300}, hi[3] = {-1e300, -1e300, -1e300};
+        for (int i = 0; i < src.vert_count; ++i)
+          for (int k = 0; k < 3; ++k) { lo[k] = std::min(lo[k], v[3 * i + k]); hi[k] = std::max(hi[k], v[3 * i + k]); }
+        const double c[3] = {0.5 * (lo[0] + hi[0]), 0.5 * (lo[1] + hi[1]), 0.5 * (lo[2] + hi[2])};
+        hx = 0.5 * (hi[0] - lo[0]); hy = 0.5 * (hi[1] - lo[1]); hz = 0.5 * (hi[2] - lo[2]);
+        d.voff = static_cast<int32_t>(verts4.size() / 4);
+        d.vcnt = src.vert_count;
+        for (int i = 0; i < src.vert_count; ++i) {
+          const double x = v[3 * i] - c[0], y = v[3 * i + 1] - c[1], z = v[3 * i + 2] - c[2];
+          br = std::max(br, std::sqrt(x * x + y * y + z * z));
+          verts4.push_back(static_cast<float>(x)); verts4.push_back(static_cast<float>(y));
+          verts4.push_back(static_cast<float>(z)); verts4.push_back(0.f);
+        }
+        const double shift[12] = {1, 0, 0, c[0], 0, 1, 0, c[1], 0, 0, 1, c[2]};
+        mat_mul34(src.placement, shift, pl);
+      } break;
+    }
+    d.hx = static_cast<float>(hx); d.hy = static_cast<float>(hy); d.hz = static_cast<float>(hz);
+    d.bound_r = static_cast<float>(br);
+    for (int k = 0; k < 12; ++k) d.pl[k] = static_cast<float>(pl[k]);
+    if (src.parent_joint < 0) {
+      d.gslot = -1 - n_static++;
+      for (int k = 0; k < 12; ++k) stat.push_back(d.pl[k]);
+    } else {
+      by_joint[src.parent_joint].push_back(g);
+    }
+  }
+  for (int i = 0; i < nj; ++i) {
+    dj[i].gfirst = static_cast<int32_t>(dyn.size());
+    dj[i].gcount = static_cast<int32_t>(by_joint[i].size());
+    for (int g : by_joint[i]) { dg[g].gslot = static_cast<int32_t>(dyn.size()); dyn.push_back(g); }
+  }
+  // pairs
+  std::vector<DPair> dp(std::max(np, 1));
+  m->pair_active.resize(np, 1);
+  for (int p = 0; p < np; ++p) {
+    const int32_t* pr = p < n_rp ? &m->robot_pairs[2 * p] : &m->scene_pairs[2 * (p - n_rp)];
+    int a = pr[0], b = pr[1];
+    if (a < 0 || b < 0 || a >= ng || b >= ng || a == b) return fail(RAMP_ERR_INVALID, "pair %d: bad geometry indices (%d, %d)", p, a, b);
+    if (dg[a].type > dg[b].type) std::swap(a, b);
+    DPair& d = dp[p];
+    d.a = a; d.b = b;
+    d.cls = m->pair_active[p] ? pair_class(dg[a].type, dg[b].type) : kClsInactive;
+    const double rs = static_cast<double>(dg[a].bound_r) + dg[b].bound_r;
+    // the sphere-sphere test is the decision itself; every other class uses it as a cull
+    d.rs2 = static_cast<float>(d.cls == kClsSphereSphere ? rs * rs : rs * rs * (1.0 + 1e-5) + 1e-9);
+  }
+  // q map
+  std::vector<DMimic> dm(m->mimic_dst.size());
+  for (size_t k = 0; k < dm.size(); ++k)
+    dm[k] = DMimic{m->mimic_dst[k], m->mimic_src[k], static_cast<float>(m->mimic_mult[k]), static_cast<float>(m->mimic_off[k])};
+  std::vector<float> refq(m->nq, 0.f);
+  if (m->has_qmap) for (int k = 0; k < m->nq; ++k) refq[k] = static_cast<float>(m->ref_q[k]);
+
+  ImgHeader h;
+  std::memset(&h, 0, sizeof h);
+  size_t off = sizeof(ImgHeader);
+  auto place = [&](size_t bytes) { const size_t o = off; off = align16(off + bytes); return static_cast<int32_t>(o); };
+  h.off_joints = place(dj.size() * sizeof(DJoint));
+  h.off_geoms = place(dg.size() * sizeof(DGeom));
+  h.off_pairs = place(dp.size() * sizeof(DPair));
+  h.off_verts = place(verts4.size() * sizeof(float));
+  h.off_static = place(stat.size() * sizeof(float));
+  h.off_dyn = place(dyn.size() * sizeof(int32_t));
+  h.off_act = place(m->act_slot.size() * sizeof(int32_t));
+  h.off_mimic = place(dm.size() * sizeof(DMimic));
+  h.off_cont = place(m->cont_slot.size() * sizeof(int32_t));
+  h.off_refq = place(refq.size() * sizeof(float));
+  h.total_bytes = static_cast<int32_t>(off);
+  h.nq = m->nq; h.n_joints = nj; h.n_geoms = ng; h.n_dyn = static_cast<int32_t>(dyn.size());
+  h.n_static = n_static; h.n_pairs = np; h.n_verts = static_cast<int32_t>(verts4.size() / 4);
+  h.n_act = static_cast<int32_t>(m->act_slot.size()); h.n_mimic = static_cast<int32_t>(dm.size());
+  h.n_cont = static_cast<int32_t>(m->cont_slot.size()); h.n_save = n_save;
+  h.mask_words = (np + 31) / 32; h.n_robot_geoms = n_robot; h.n_robot_pairs = n_rp;
+
+  m->image.assign(off, 0);
+  unsigned char* B = m->image.data();
+  std::memcpy(B, &h, sizeof h);
+  auto put = [&](int32_t o, const void* src, size_t bytes) { if (bytes) std::memcpy(B + o, src, bytes); };
+  put(h.off_joints, dj.data(), dj.size() * sizeof(DJoint));
+  put(h.off_geoms, dg.data(), dg.size() * sizeof(DGeom));
+  put(h.off_pairs, dp.data(), static_cast<size_t>(np) * sizeof(DPair));
+  put(h.off_verts, verts4.data(), verts4.size() * sizeof(float));
+  put(h.off_static, stat.data(), stat.size() * sizeof(float));
+  put(h.off_dyn, dyn.data(), dyn.size() * sizeof(int32_t));
+  put(h.off_act, m->act_slot.data(), m->act_slot.size() * sizeof(int32_t));
+  put(h.off_mimic, dm.data(), dm.size() * sizeof(DMimic));
+  put(h.off_cont, m->cont_slot.data(), m->cont_slot.size() * sizeof(int32_t));
+  put(h.off_refq, refq.data(), refq.size() * sizeof(float));
+  m->hdr = h;
+
+  CUDA_TRY(cudaSetDevice(m->device));
+  if (off > m->d_image_cap) {
+    if (m->d_image) cudaFree(m->d_image);
+    m->d_image = nullptr;
+    m->d_image_cap = 0;
+    CUDA_TRY(cudaMalloc(&m->d_image, off));
+    m->d_image_cap = off;
+  }
+  // the image may be in use by kernels queued on caller streams
+  CUDA_TRY(cudaDeviceSynchronize());
+  CUDA_TRY(cudaMemcpy(m->d_image, B, off, cudaMemcpyHostToDevice));
+  return RAMP_OK;
+}
+
+// Shared-memory plan: tables + as many warp slabs as fit (<= 16 warps).
+static int plan_slabs(const RampModel* m, int stage_row_floats, int act_cols, SlabLayout* L, int* nwarps,
+                      size_t* smem_bytes) {
+  const ImgHeader& h = m->hdr;
+  int w = 0;
+  auto take = [&](int words) { const int o = w; w += (words + 3) & ~3; return o; };
+  L->off_q = take(std::max(h.nq, 1) * 32);
+  L->off_act = take(std::max(act_cols, 1) * 32);
+  L->off_geom = take(std::max(h.n_dyn, 1) * 12 * 32);
+  L->off_save = take(std::max(h.n_save, 1) * 12 * 32);
+  L->off_queue = take(kQueueCap / 2);
+  L->off_mask = take(std::max(h.mask_words, 1) * 32);
+  L->off_first = take(32);
+  L->stage_stride = stage_row_floats | 1;  // odd stride: conflict-free lane-private rows
+  L->off_stage = take(stage_row_floats ? 32 * L->stage_stride : 0);
+  L->words = w;
+  L->table_bytes = static_cast<int32_t>(align16(h.total_bytes));
+  const size_t fixed = 16 + L->table_bytes;
+  const size_t per_warp = static_cast<size_t>(w) * 4;
+  if (fixed + per_warp > static_cast<size_t>(m->max_smem))
+    return fail(RAMP_ERR_LIMIT, "model needs %zu B of shared memory per CTA, device allows %d", fixed + per_warp, m->max_smem);
+  const int fit = static_cast<int>((m->max_smem - fixed) / per_warp);
+  *nwarps = std::min(16, fit);
+  *smem_bytes = fixed + per_warp * (*nwarps);
+  return RAMP_OK;
+}
+
+template <typename K>
+static int set_smem(K kernel, size_t bytes) {
+  CUDA_TRY(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(bytes)));
+  return RAMP_OK;
+}
+
+static int grid_for(const RampModel* m, int64_t tiles, int nwarps) {
+  const int64_t ctas = (tiles + nwarps - 1) / nwarps;
+  return static_cast<int>(std::max<int64_t>(1, std::min<int64_t>(m->sm_count, ctas)));
+}
+
+static int check_q_args(const RampModel* m, const void* d_q, int64_t n, int32_t ld, uint32_t flags) {
+  if (!m) return fail(RAMP_ERR_INVALID, "null model");
+  if (n < 0) return fail(RAMP_ERR_INVALID, "negative batch size");
+  if (n > 0 && !d_q) return fail(RAMP_ERR_INVALID, "null q");
+  const int cols = (flags & RAMP_Q_ACTUATED) ? m->hdr.n_act : m->hdr.nq;
+  if ((flags & RAMP_Q_ACTUATED) && !m->has_qmap) return fail(RAMP_ERR_INVALID, "RAMP_Q_ACTUATED without ramp_model_set_qmap");
+  if (ld < cols) return fail(RAMP_ERR_INVALID, "ld_q %d < %d columns", ld, cols);
+  return RAMP_OK;
+}
+
+static int launch_check(const RampModel* m, const float* d_q, int64_t n, int32_t ld, uint32_t flags, uint8_t* d_hit,
+                        int32_t* d_first, uint32_t* d_mask, cudaStream_t st) {
+  CheckArgs a;
+  a.img = m->d_image; a.q = d_q; a.n = n; a.ld = ld; a.flags = flags;
+  a.hit = d_hit; a.first_pair = d_first; a.pair_mask = d_mask;
+  int nwarps; size_t smem;
+  if (int rc = plan_slabs(m, 0, m->hdr.n_act, &a.L, &nwarps, &smem)) return rc;
+  if (int rc = set_smem(check_kernel, smem)) return rc;
+  const int grid = grid_for(m, (n + 31) / 32, nwarps);
+  check_kernel<<<grid, nwarps * 32, smem, st>>>(a);
+  g_launches.fetch_add(1, std::memory_order_relaxed);
+  CUDA_TRY(cudaGetLastError());
+  return RAMP_OK;
+}
+
+static int ensure_scratch(const RampModel* m, size_t bytes) {
+  if (bytes <= m->scratch_cap) return RAMP_OK;
+  if (m->d_scratch) cudaFree(m->d_scratch);
+  m->d_scratch = nullptr; m->scratch_cap = 0;
+  const size_t cap = std::max<size_t>(bytes, 1 << 20);
+  if (cudaMalloc(&m->d_scratch, cap) != cudaSuccess) return fail(RAMP_ERR_ALLOC, "cudaMalloc(%zu) for scratch failed", cap);
+  m->scratch_cap = cap;
+  return RAMP_OK;
+}
+
+}  // namespace ramp
+
+using namespace ramp;
+
+// ================================================================================ C ABI
+extern "C" {
+
+int ramp_abi_version(void) { return RAMP_B200_ABI_VERSION; }
+const char* ramp_last_error(void) { return g_err; }
+int64_t ramp_launch_count(void) { return g_launches.load(); }
+
+int ramp_model_create(const RampModelDesc* d, int device, RampModel** out) {
+  if (!d || !out) return fail(RAMP_ERR_INVALID, "null argument");
+  *out = nullptr;
+  if (d->abi_version != RAMP_B200_ABI_VERSION) return fail(RAMP_ERR_INVALID, "ABI version %d, library is %d", d->abi_version, RAMP_B200_ABI_VERSION);
+  if (d->n_joints < 0 || d->n_geoms < 0 || d->n_pairs < 0 || d->n_verts < 0 || d->nq < 0) return fail(RAMP_ERR_INVALID, "negative count");
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) return fail(RAMP_ERR_CUDA, "no CUDA device (there is no CPU fallback)");
+  if (device < 0 || device >= ndev) return fail(RAMP_ERR_INVALID, "device %d out of range (%d devices)", device, ndev);
+  RampModel* m = new (std::nothrow) RampModel();
+  if (!m) return fail(RAMP_ERR_ALLOC, "out of host memory");
+  m->device = device;
+  cudaDeviceProp prop;
+  if (cudaGetDeviceProperties(&prop, device) != cudaSuccess) { delete m; return fail(RAMP_ERR_CUDA, "cudaGetDeviceProperties failed"); }
+  m->sm_count = prop.multiProcessorCount;
+  m->max_smem = static_cast<int>(prop.sharedMemPerBlockOptin);
+  m->nq = d->nq;
+  m->joints.assign(d->joints, d->joints + d->n_joints);
+  m->robot_geoms.assign(d->geoms, d->geoms + d->n_geoms);
+  m->robot_pairs.assign(d->pairs, d->pairs + 2 * static_cast<size_t>(d->n_pairs));
+  m->robot_verts.assign(d->verts, d->verts + 3 * static_cast<size_t>(d->n_verts));
+  for (int i = 0; i < d->n_joints; ++i)
+    if (d->joints[i].idx_q < 0 || d->joints[i].idx_q >= std::max(d->nq, 1)) { delete m; return fail(RAMP_ERR_INVALID, "joint %d: idx_q out of range", i); }
+  if (int rc = build_image(m)) { ramp_model_destroy(m); return rc; }
+  *out = m;
+  return RAMP_OK;
+}
+
+int ramp_model_set_scene(RampModel* m, const RampGeom* geoms, int32_t n_geoms, const int32_t* pairs, int32_t n_pairs,
+                         const double* verts, int32_t n_verts) {
+  if (!m || n_geoms < 0 || n_pairs < 0 || n_verts < 0) return fail(RAMP_ERR_INVALID, "bad argument");
+  std::lock_guard<std::mutex> lk(m->mu);
+  m->scene_geoms.assign(geoms, geoms + n_geoms);
+  m->scene_pairs.assign(pairs, pairs + 2 * static_cast<size_t>(n_pairs));
+  m->scene_verts.assign(verts, verts + 3 * static_cast<size_t>(n_verts));
+  for (auto& g : m->scene_geoms)
+    if (g.parent_joint != -1) return fail(RAMP_ERR_INVALID, "scene objects must be attached to the universe");
+  m->pair_active.resize(m->robot_pairs.size() / 2);  // scene pairs start active
+  return build_image(m);
+}
+
+int ramp_model_set_qmap(RampModel* m, const RampQMap* q) {
+  if (!m || !q) return fail(RAMP_ERR_INVALID, "null argument");
+  if (q->n_act < 0 || q->n_act > kMaxNq || q->n_mimic < 0 || q->n_cont < 0) return fail(RAMP_ERR_INVALID, "bad qmap counts");
+  for (int k = 0; k < q->n_act; ++k) if (q->act_slot[k] < 0 || q->act_slot[k] >= m->nq) return fail(RAMP_ERR_INVALID, "act_slot[%d] out of range", k);
+  for (int k = 0; k < q->n_mimic; ++k)
+    if (q->mimic_dst[k] < 0 || q->mimic_dst[k] >= m->nq || q->mimic_src[k] < 0 || q->mimic_src[k] >= m->nq) return fail(RAMP_ERR_INVALID, "mimic[%d] out of range", k);
+  for (int k = 0; k < q->n_cont; ++k) if (q->cont_slot[k] < 0 || q->cont_slot[k] + 1 >= m->nq) return fail(RAMP_ERR_INVALID, "cont_slot[%d] out of range", k);
+  std::lock_guard<std::mutex> lk(m->mu);
+  m->has_qmap = true;
+  m->act_slot.assign(q->act_slot, q->act_slot + q->n_act);
+  m->mimic_dst.assign(q->mimic_dst, q->mimic_dst + q->n_mimic);
+  m->mimic_src.assign(q->mimic_src, q->mimic_src + q->n_mimic);
+  m->mimic_mult.assign(q->mimic_mult, q->mimic_mult + q->n_mimic);
+  m->mimic_off.assign(q->mimic_off, q->mimic_off + q->n_mimic);
+  m->cont_slot.assign(q->cont_slot, q->cont_slot + q->n_cont);
+  m->ref_q.assign(q->ref_q, q->ref_q + m->nq);
+  return build_image(m);
+}
+
+int ramp_model_set_pair_active(RampModel* m, int32_t p, int32_t active) {
+  if (!m) return fail(RAMP_ERR_INVALID, "null model");
+  std::lock_guard<std::mutex> lk(m->mu);
+  if (p < 0 || p >= static_cast<int32_t>(m->pair_active.size())) return fail(RAMP_ERR_INVALID, "pair index %d out of range", p);
+  m->pair_active[p] = active ? 1 : 0;
+  return build_image(m);
+}
+
+void ramp_model_destroy(RampModel* m) {
+  if (!m) return;
+  cudaSetDevice(m->device);
+  if (m->d_image) cudaFree(m->d_image);
+  if (m->d_scratch) cudaFree(m->d_scratch);
+  if (m->h_pinned) cudaFreeHost(m->h_pinned);
+  delete m;
+}
+
+int ramp_model_info(const RampModel* m, int32_t out[6]) {
+  if (!m || !out) return fail(RAMP_ERR_INVALID, "null argument");
+  out[0] = m->hdr.nq; out[1] = m->hdr.n_joints; out[2] = m->hdr.n_geoms; out[3] = m->hdr.n_pairs;
+  out[4] = m->has_qmap ? m->hdr.n_act : 0; out[5] = m->device;
+  return RAMP_OK;
+}
+
+static int fk_common(const RampModel* m, const float* d_q, int64_t n, int32_t ld, uint32_t flags, float* d_out, void* stream,
+                     int what) {
+  if (int rc = check_q_args(m, d_q, n, ld, flags)) return rc;
+  if (n == 0) return RAMP_OK;
+  if (!d_out) return fail(RAMP_ERR_INVALID, "null output");
+  CUDA_TRY(cudaSetDevice(m->device));
+  FkArgs a;
+  a.img = m->d_image; a.q = d_q; a.n = n; a.ld = ld; a.flags = flags; a.out = d_out;
+  a.row_floats = 12 * (what == 1 ? m->hdr.n_joints : m->hdr.n_geoms);
+  if (a.row_floats == 0) return RAMP_OK;
+  int nwarps; size_t smem;
+  if (int rc = plan_slabs(m, a.row_floats, m->hdr.n_act, &a.L, &nwarps, &smem)) return rc;
+  const int grid = grid_for(m, (n + 31) / 32, nwarps);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (what == 1) {
+    if (int rc = set_smem(fk_kernel<1>, smem)) return rc;
+    fk_kernel<1><<<grid, nwarps * 32, smem, st>>>(a);
+  } else {
+    if (int rc = set_smem(fk_kernel<2>, smem)) return rc;
+    fk_kernel<2><<<grid, nwarps * 32, smem, st>>>(a);
+  }
+  g_launches.fetch_add(1, std::memory_order_relaxed);
+  CUDA_TRY(cudaGetLastError());
+  return RAMP_OK;
+}
+
+int ramp_fk_batch(const RampModel* m, const float* d_q, int64_t n, int32_t ld, uint32_t flags, float* d_oMi, void* stream) {
+  return fk_common(m, d_q, n, ld, flags, d_oMi, stream, 1);
+}
+
+int ramp_placements_batch(const RampModel* m, const float* d_q, int64_t n, int32_t ld, uint32_t flags, float* d_oMg,
+                          void* stream) {
+  return fk_common(m, d_q, n, ld, flags, d_oMg, stream, 2);
+}
+
+int ramp_check_batch(const RampModel* m, const float* d_q, int64_t n, int32_t ld, uint32_t flags, uint8_t* d_hit,
+                     int32_t* d_first_pair, float* d_min_dist, uint32_t* d_pair_mask, void* stream) {
+  if (int rc = check_q_args(m, d_q, n, ld, flags)) return rc;
+  if (n == 0) return RAMP_OK;
+  if (!d_hit) return fail(RAMP_ERR_INVALID, "null d_hit");
+  if (d_min_dist) return fail(RAMP_ERR_INVALID, "d_min_dist: use ramp_distance_batch");
+  CUDA_TRY(cudaSetDevice(m->device));
+  return launch_check(m, d_q, n, ld, flags, d_hit, d_first_pair, d_pair_mask, static_cast<cudaStream_t>(stream));
+}
+
+int ramp_distance_batch(const RampModel*, const float*, int64_t, int32_t, uint32_t, const int32_t*, int32_t, float*, void*) {
+  return fail(RAMP_ERR_INVALID, "ramp_distance_batch is not implemented yet");
+}
+
+int ramp_check_edges(const RampModel* m, const float* d_q0, const float* d_q1, int64_t n_edges, int32_t ld,
+                     const RampSpaceDesc* sp, uint8_t* d_valid, int32_t* d_first_invalid, int32_t* d_nd, void* stream) {
+  if (!m || !sp) return fail(RAMP_ERR_INVALID, "null argument");
+  if (!m->has_qmap) return fail(RAMP_ERR_INVALID, "ramp_check_edges needs ramp_model_set_qmap");
+  if (n_edges < 0) return fail(RAMP_ERR_INVALID, "negative edge count");
+  if (n_edges == 0) return RAMP_OK;
+  if (!d_q0 || !d_q1 || !d_valid) return fail(RAMP_ERR_INVALID, "null device pointer");
+  if (sp->n_sub < 0 || sp->n_sub > kMaxSubspaces) return fail(RAMP_ERR_LIMIT, "%d subspaces > limit %d", sp->n_sub, kMaxSubspaces);
+  EdgeArgs a;
+  std::memset(&a.sp, 0, sizeof a.sp);
+  const double frac = sp->longest_valid_segment_fraction > 0 ? sp->longest_valid_segment_fraction : 0.01;
+  int n_cols = 0;
+  for (int i = 0; i < sp->n_sub; ++i) {
+    const RampSubspace& s = sp->sub[i];
+    DSub& d = a.sp.sub[i];
+    d.type = s.type; d.col = s.col; d.dim = s.dim;
+    int nreal = 0, width = 0;
+    double rot_extent = 0;
+    switch (s.type) {
+      case RAMP_SPACE_REAL: nreal = s.dim; width = s.dim; break;
+      case RAMP_SPACE_SO2: width = 1; rot_extent = M_PI; break;
+      case RAMP_SPACE_SE2: nreal = 2; width = 3; rot_extent = M_PI; break;
+      case RAMP_SPACE_SE3: nreal = 3; width = 7; rot_extent = 0.5 * M_PI; break;
+      case RAMP_SPACE_SO3: width = 4; rot_extent = 0.5 * M_PI; break;
+      default: return fail(RAMP_ERR_INVALID, "subspace %d: unknown type %d", i, s.type);
+    }
+    if (nreal < 0 || nreal > 3 || s.col < 0) return fail(RAMP_ERR_INVALID, "subspace %d: bad dim/col", i);
+    double ext = 0;
+    for (int k = 0; k < nreal; ++k) { d.lo[k] = static_cast<float>(s.lo[k]); d.hi[k] = static_cast<float>(s.hi[k]); ext += (s.hi[k] - s.lo[k]) * (s.hi[k] - s.lo[k]); }
+    ext = std::sqrt(ext);
+    d.inv_lvs_real = ext > 0 ? static_cast<float>(1.0 / (ext * frac)) : 0.f;
+    d.inv_lvs_rot = rot_extent > 0 ? static_cast<float>(1.0 / (rot_extent * frac)) : 0.f;
+    n_cols = std::max(n_cols, s.col + width);
+  }
+  if (n_cols != m->hdr.n_act) return fail(RAMP_ERR_INVALID, "space covers %d columns, qmap has %d actuated values", n_cols, m->hdr.n_act);
+  if (ld < n_cols) return fail(RAMP_ERR_INVALID, "ld %d < %d columns", ld, n_cols);
+  a.sp.n_sub = sp->n_sub; a.sp.check_bounds = sp->check_bounds; a.sp.n_cols = n_cols;
+  CUDA_TRY(cudaSetDevice(m->device));
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  std::lock_guard<std::mutex> lk(m->mu);
+  // scratch: offs int64[n+1] | nd int32[n] | first int32[n]
+  const size_t off_nd = align16(sizeof(int64_t) * (n_edges + 1));
+  const size_t off_first = off_nd + align16(sizeof(int32_t) * n_edges);
+  if (int rc = ensure_scratch(m, off_first + align16(sizeof(int32_t) * n_edges))) return rc;
+  unsigned char* S = static_cast<unsigned char*>(m->d_scratch);
+  a.img = m->d_image; a.q0 = d_q0; a.q1 = d_q1; a.n_edges = n_edges; a.ld = ld; a.valid = d_valid;
+  a.offs = reinterpret_cast<int64_t*>(S);
+  a.nd = d_nd ? d_nd : reinterpret_cast<int32_t*>(S + off_nd);
+  a.first_invalid = reinterpret_cast<int32_t*>(S + off_first);
+  int nwarps; size_t smem;
+  if (int rc = plan_slabs(m, 0, n_cols, &a.L, &nwarps, &smem)) return rc;
+  if (int rc = set_smem(edge_check_kernel, smem)) return rc;
+  const int eb = static_cast<int>((n_edges + 255) / 256);
+  edge_count_kernel<<<eb, 256, 0, st>>>(a);
+  edge_scan_kernel<<<1, 1024, 0, st>>>(a.offs, n_edges);
+  // the number of states is only known on the device: size the grid for the SM count
+  edge_check_kernel<<<m->sm_count, nwarps * 32, smem, st>>>(a);
+  edge_finish_kernel<<<eb, 256, 0, st>>>(a, d_first_invalid, d_nd);
+  g_launches.fetch_add(4, std::memory_order_relaxed);
+  CUDA_TRY(cudaGetLastError());
+  return RAMP_OK;
+}
+
+int ramp_check_host(const RampModel* m, const float* h_q, int64_t n, int32_t ld, uint32_t flags, uint8_t* h_hit,
+                    int32_t* h_first_pair, float* h_min_dist, uint32_t* h_pair_mask) {
+  if (int rc = check_q_args(m, h_q, n, ld, flags)) return rc;
+  if (n == 0) return RAMP_OK;
+  if (!h_hit) return fail(RAMP_ERR_INVALID, "null h_hit");
+  if (h_min_dist) return fail(RAMP_ERR_INVALID, "h_min_dist: use ramp_distance_batch");
+  CUDA_TRY(cudaSetDevice(m->device));
+  std::lock_guard<std::mutex> lk(m->mu);
+  const int mw = m->hdr.mask_words;
+  const size_t b_q = align16(sizeof(float) * n * ld), b_hit = align16(n), b_first = align16(sizeof(int32_t) * n),
+               b_mask = align16(sizeof(uint32_t) * n * std::max(mw, 1));
+  const size_t total = b_q + b_hit + b_first + b_mask;
+  // staging lives after the edge scratch region is not needed at the same time: one buffer
+  if (int rc = ensure_scratch(m, total)) return rc;
+  if (total > m->pinned_cap) {
+    if (m->h_pinned) cudaFreeHost(m->h_pinned);
+    m->h_pinned = nullptr; m->pinned_cap = 0;
+    if (cudaMallocHost(&m->h_pinned, std::max<size_t>(total, 1 << 16)) != cudaSuccess) return fail(RAMP_ERR_ALLOC, "cudaMallocHost failed");
+    m->pinned_cap = std::max<size_t>(total, 1 << 16);
+  }
+  unsigned char* D = static_cast<unsigned char*>(m->d_scratch);
+  unsigned char* H = static_cast<unsigned char*>(m->h_pinned);
+  std::memcpy(H, h_q, sizeof(float) * n * ld);
+  cudaStream_t st = cudaStreamPerThread;
+  CUDA_TRY(cudaMemcpyAsync(D, H, sizeof(float) * n * ld, cudaMemcpyHostToDevice, st));
+  uint8_t* d_hit = D + b_q;
+  int32_t* d_first = reinterpret_cast<int32_t*>(D + b_q + b_hit);
+  uint32_t* d_mask = reinterpret_cast<uint32_t*>(D + b_q + b_hit + b_first);
+  if (int rc = launch_check(m, reinterpret_cast<const float*>(D), n, ld, flags, d_hit, h_first_pair ? d_first : nullptr,
+                            h_pair_mask ? d_mask : nullptr, st))
+    return rc;
+  CUDA_TRY(cudaMemcpyAsync(H + b_q, D + b_q, total - b_q, cudaMemcpyDeviceToHost, st));
+  CUDA_TRY(cudaStreamSynchronize(st));
+  std::memcpy(h_hit, H + b_q, n);
+  if (h_first_pair) std::memcpy(h_first_pair, H + b_q + b_hit, sizeof(int32_t) * n);
+  if (h_pair_mask) std::memcpy(h_pair_mask, H + b_q + b_hit + b_first, sizeof(uint32_t) * n * mw);
+  return RAMP_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,237 @@
+"""GPU (FP32, CUDA) vs CPU oracle (FP64) on the same seeded inputs, through the C ABI.
+
+Tolerances (BASELINE.json north_star): link poses within 1e-5 (m for translations; rotation
+entries, i.e. < 1e-5 rad), collision booleans bit-exact for every configuration whose oracle
+signed distance lies outside +-1e-4 m; the in-band count is reported.
+"""
+
+import numpy as np
+import pytest
+
+torch = pytest.importorskip("torch")
+pytestmark = pytest.mark.gpu
+
+POSE_TOL = 1e-5
+BAND = 1e-4
+
+ZOO = ["rrr/configs", "rrr/planar_configs", "rrr/floating_configs", "planar_rrr/configs", "rrr_mj/configs",
+       "acrobot/configs", "double_pendulum", "floating", "planar", "panda/configs", "fr3/configs", "ur5e/configs",
+       "unitree_h1/configs"]
+
+
+def _setup(name, scene=None):
+    from ramp_b200 import workloads
+    from ramp_b200.robot_model import load_robot_model
+    from ramp_b200.robot_state import RobotState
+
+    rm = load_robot_model("zoo::" + name)
+    rs = RobotState(rm)
+    if scene == "capsule":
+        rs.add_object(workloads.reference_capsule())
+    elif scene == "obstacles":
+        for o in workloads.obstacle_scene():
+            rs.add_object(o)
+    return rm, rs
+
+
+@pytest.mark.parametrize("name", ZOO)
+def test_fk_matches_oracle(built, name):
+    from oracle import oracle
+    from ramp_b200 import workloads
+    from ramp_b200.desc import ModelDesc
+
+    rm, _ = _setup(name)
+    n = 1000  # not a multiple of 32: exercises the ragged last tile
+    q = workloads.sample_q(rm.model, n, seed=1)
+    got = rm.gpu.forward_kinematics(torch.from_numpy(q).cuda()).cpu().numpy()
+    ref = oracle.fk(ModelDesc(rm.model, rm.collision_model), q[:, : rm.model.nq].astype(np.float64))
+    assert got.shape == ref.shape
+    assert np.abs(got - ref).max() < POSE_TOL
+
+
+@pytest.mark.parametrize("name", ["rrr/floating_configs", "panda/configs", "unitree_h1/configs"])
+def test_placements_match_oracle(built, name):
+    from oracle import oracle
+    from ramp_b200 import workloads
+    from ramp_b200.desc import ModelDesc
+
+    rm, _ = _setup(name, "capsule")
+    q = workloads.sample_q(rm.model, 333, seed=2)
+    got = rm.gpu.placements(torch.from_numpy(q).cuda()).cpu().numpy()
+    ref = oracle.placements(ModelDesc(rm.model, rm.collision_model), q[:, : rm.model.nq].astype(np.float64))
+    assert np.abs(got - ref).max() < POSE_TOL
+
+
+def _compare_check(rm, q, report):
+    from oracle import oracle
+    from ramp_b200.desc import ModelDesc
+
+    d = ModelDesc(rm.model, rm.collision_model)
+    ref = oracle.check(d, q[:, : rm.model.nq].astype(np.float64))
+    res = rm.gpu.check(torch.from_numpy(q).cuda(), first_pair=True, pair_mask=True)
+    hit = res["hit"].cpu().numpy()
+    first = res["first_pair"].cpu().numpy()
+    mask = res["pair_mask"].cpu().numpy()
+    pd = ref["pair_dist"]
+    outside = np.abs(ref["min_dist"]) > BAND
+    # every pair decided on its own: bit-exact outside the band
+    pair_out = np.abs(pd) > BAND
+    ref_mask = pd <= 1e-12
+    assert mask.shape == ref_mask.shape
+    bad_pairs = int(((mask != ref_mask) & pair_out).sum())
+    bad_cfg = int((hit != ref["hit"])[outside].sum())
+    # first colliding pair (list order) wherever no pair of the configuration is in the band
+    clean = pair_out.all(axis=1)
+    bad_first = int((first != ref["first_pair"])[clean].sum())
+    report(n=len(q), colliding=int(ref["hit"].sum()), in_band=int((~outside).sum()), bad_cfg=bad_cfg,
+           bad_pairs=bad_pairs, bad_first=bad_first)
+    assert bad_cfg == 0 and bad_pairs == 0 and bad_first == 0
+    # early-out mode must give the same flags
+    res2 = rm.gpu.check(torch.from_numpy(q).cuda())
+    assert (res2["hit"].cpu().numpy() == hit)[outside].all()
+
+
+CHECK_CASES = [("rrr/configs", None, 20000), ("rrr/planar_configs", "capsule", 20000),
+               ("rrr/floating_configs", "capsule", 20000), ("rrr_mj/configs", "obstacles", 20000),
+               ("planar_rrr/configs", "capsule", 20000), ("floating", "obstacles", 20000),
+               ("panda/configs", "capsule", 20000), ("fr3/configs", "capsule", 20000),
+               ("ur5e/configs", "obstacles", 20000), ("unitree_h1/configs", None, 4000)]
+
+
+@pytest.mark.parametrize("name,scene,n", CHECK_CASES)
+def test_check_matches_oracle(built, name, scene, n, record_property):
+    from ramp_b200 import workloads
+
+    rm, _ = _setup(name, scene)
+    q = workloads.sample_q(rm.model, n, seed=3)
+
+    def report(**kw):
+        print(name, kw)
+        for k, v in kw.items():
+            record_property(k, v)
+
+    _compare_check(rm, q, report)
+
+
+def test_kat_states_valid(built):
+    """The reference's own known answers: home / goal states are collision free."""
+    from ramp_b200.robot_model import as_pinocchio_qpos
+    from ramp_b200.kinematics import neutral
+
+    for cfg, scene, goal in (("rrr/configs", None, [0.0, 1.0, 1.0]), ("rrr/configs", "capsule", [0.0, 2.0, 1.4]),
+                             ("rrr/planar_configs", "capsule", [1.0, -0.5, 1.57, 0.5, 0.25, 0.1]),
+                             ("rrr/floating_configs", "capsule", [1.0, 0.5, 1.0, 1.0, 0.0, 0.0, 0.0, 0.5, 0.25, 0.1])):
+        rm, rs = _setup(cfg, scene)
+        home = as_pinocchio_qpos(rm, neutral(rm.model), "arm", rm["arm"].named_states["home"])
+        g = as_pinocchio_qpos(rm, neutral(rm.model), "arm", goal)
+        res = rm.gpu.check_host(np.stack([home, g]).astype(np.float32))
+        assert not res["hit"].any(), (cfg, res)
+
+
+def test_actuated_input_matches_host_map(built):
+    """RAMP_Q_ACTUATED: mimic then (cos, sin) on the device == the host statement."""
+    from oracle import oracle
+    from ramp_b200 import spaces
+    from ramp_b200.desc import ModelDesc
+
+    for cfg, group in (("panda/configs", "arm"), ("double_pendulum", "arm"), ("rrr/planar_configs", "arm"),
+                       ("planar_rrr/configs", "arm")):
+        rm, _ = _setup(cfg)
+        qmap = spaces.make_qmap(rm, group)
+        rm.gpu.set_qmap(qmap)
+        rng = np.random.default_rng(5)
+        act = rng.uniform(-1.5, 1.5, (257, qmap.n_act)).astype(np.float32)
+        got = rm.gpu.forward_kinematics(torch.from_numpy(act).cuda(), actuated=True).cpu().numpy()
+        q = oracle.qmap_apply(qmap, act.astype(np.float64))
+        assert np.allclose(q, qmap.apply(act.astype(np.float64)))
+        ref = oracle.fk(ModelDesc(rm.model, rm.collision_model), q)
+        assert np.abs(got - ref).max() < POSE_TOL
+
+
+EDGE_CASES = [("rrr/configs", None, 300), ("rrr/planar_configs", "capsule", 200), ("rrr/floating_configs", "capsule", 150),
+              ("panda/configs", "capsule", 200), ("planar_rrr/configs", "capsule", 200)]
+
+
+@pytest.mark.parametrize("name,scene,n_edges", EDGE_CASES)
+def test_edges_match_oracle(built, name, scene, n_edges):
+    from oracle import oracle
+    from ramp_b200 import spaces
+    from ramp_b200.desc import ModelDesc
+
+    rm, _ = _setup(name, scene)
+    space = spaces.make_space(rm, "arm")
+    qmap = spaces.make_qmap(rm, "arm")
+    gpu = rm.gpu
+    gpu.set_qmap(qmap)
+    rng = np.random.default_rng(7)
+    q0 = spaces.sample_uniform(space, n_edges, rng).astype(np.float32)
+    q1 = (q0 + rng.normal(scale=0.35, size=q0.shape)).astype(np.float32)
+    # keep quaternion parts unit and so2 parts in range
+    q1s = spaces.sample_uniform(space, n_edges, rng).astype(np.float32)
+    for s in space.subspaces:
+        c = s["col"]
+        if s["type"] in (3, 4):
+            o = 3 if s["type"] == 3 else 0
+            q1[:, c + o : c + o + 4] = q1s[:, c + o : c + o + 4]
+        if s["type"] in (1, 2):
+            k = c + (2 if s["type"] == 2 else 0)
+            q1[:, k] = q1s[:, k]
+    q1[0] = q0[0]  # a zero-length edge: nd = 0, only the end state is checked
+    got = gpu.check_edges(torch.from_numpy(q0).cuda(), torch.from_numpy(q1).cuda(), space)
+    d = ModelDesc(rm.model, rm.collision_model)
+    ref = oracle.check_edges(d, qmap, space, q0.astype(np.float64), q1.astype(np.float64))
+    nd = got["nd"].cpu().numpy()
+    # FP32 vs FP64 ceil() may differ when dist/lvs sits on an integer: allow +-1 on few edges
+    same_nd = nd == ref["nd"]
+    assert (np.abs(nd - ref["nd"]) <= 1).all() and same_nd.mean() > 0.97
+    valid = got["valid"].cpu().numpy()
+    first = got["first_invalid"].cpu().numpy()
+    agree = (valid == ref["valid"]) & (first == ref["first_invalid"])
+    # disagreements must be explained by a near-contact state (margin band) or an nd tie
+    bad = np.flatnonzero(~agree & same_nd)
+    unexplained = 0
+    for e in bad:
+        n_d = int(ref["nd"][e])
+        js = {int(first[e]), int(ref["first_invalid"][e])} - {-1}
+        ok = False
+        for j in js:
+            st = q1[e].astype(np.float64) if j >= n_d else oracle.edge_interpolate(space, q0[e], q1[e], j / n_d)
+            r = oracle.check(d, oracle.qmap_apply(qmap, st))
+            ok = ok or abs(r["min_dist"][0]) <= BAND
+        unexplained += not ok
+    print(name, dict(edges=n_edges, invalid=int((~ref["valid"]).sum()), nd_mismatch=int((~same_nd).sum()),
+                     disagreements=len(bad), unexplained=unexplained))
+    assert unexplained == 0
+
+
+def test_scene_update_and_pair_toggle(built):
+    """add_object after the handle exists (ramp_model_set_scene) and pair (de)activation."""
+    from ramp_b200 import workloads
+
+    rm, rs = _setup("rrr/configs")
+    q = workloads.sample_q(rm.model, 4096, seed=11)
+    qd = torch.from_numpy(q).cuda()
+    before = rm.gpu.check(qd)["hit"].cpu().numpy()
+    rs.add_object(workloads.reference_capsule())
+    info = rm.gpu.info()
+    assert info["n_geoms"] == 6 and info["n_pairs"] == 6 + 5
+    after = rm.gpu.check(qd, pair_mask=True)
+    assert after["hit"].cpu().numpy().sum() > before.sum()
+    mask = after["pair_mask"].cpu().numpy()
+    p = int(np.argmax(mask.sum(axis=0)))
+    rm.gpu.set_pair_active(p, False)
+    off = rm.gpu.check(qd, pair_mask=True)["pair_mask"].cpu().numpy()
+    assert not off[:, p].any() and (np.delete(off, p, 1) == np.delete(mask, p, 1)).all()
+    rm.gpu.set_pair_active(p, True)
+
+
+def test_empty_and_errors(built):
+    from ramp_b200.exceptions import RampGpuError
+
+    rm, _ = _setup("rrr/configs")
+    empty = torch.zeros((0, 4), dtype=torch.float32, device="cuda")
+    assert rm.gpu.check(empty)["hit"].numel() == 0
+    with pytest.raises(RampGpuError):
+        rm.gpu.check(torch.zeros((4, 2), dtype=torch.float32, device="cuda"))  # ld < nq
+    with pytest.raises(RampGpuError):
+        rm.gpu.forward_kinematics(torch.zeros((4, 3), dtype=torch.float32, device="cuda"), actuated=True)  # no qmap
