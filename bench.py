@@ -1,0 +1,306 @@
+"""Benchmark of the validity-checking hot path (BASELINE.json metric).
+
+    python bench.py --gpus N --steps K --warmup W [--workload NAME] [--impl reference]
+
+A step is one pass of the fused validity kernel (FK -> placements -> all enabled pairs) over
+one batch of synthetic configurations per GPU; for N > 1 the step also all-gathers the
+per-configuration flags over NCCL.  Prints ONE JSON line (rank 0).  ``--impl reference`` times
+the CPU path (this repo's FP64 restatement of Pinocchio + coal: the reference's own
+arithmetic lives in wheels that are not installable here) on the host cores instead.
+"""
+
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+from pathlib import Path
+
+ROOT = Path(__file__).resolve().parent
+if str(ROOT) not in sys.path:
+    sys.path.insert(0, str(ROOT))
+
+METRIC = "collision-checked configs/sec (FK+all pairs)"
+UNIT = "configs/s"
+N_ROTATE = 8  # distinct input batches cycled through so no step re-reads an L2-resident batch
+
+
+def measured_peaks() -> dict:
+    p = ROOT / "MEASURED_PEAKS.json"
+    if p.exists():
+        return {**json.loads(p.read_text()), "_source": "measured"}
+    return {"hbm_gbs": 6650.0, "sm_max_mhz": 1965.0, "_source": "fallback"}
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled every 200 ms during the timed region."""
+
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        self.index, self.proc, self.lines = index, None, []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-lms", "200", "-i", str(self.index)], stdout=subprocess.PIPE, text=True)
+            threading.Thread(target=self._pump, daemon=True).start()
+        except OSError:
+            self.proc = None
+
+    def _pump(self):
+        for line in self.proc.stdout:
+            self.lines.append(line)
+
+    def stop(self) -> dict:
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.25)
+        self.proc.terminate()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for line in self.lines:
+            f = [x.strip() for x in line.split(",")]
+            if len(f) < 9:
+                continue
+            try:
+                sm.append(float(f[1]))
+                mx.append(float(f[2]))
+            except ValueError:
+                continue
+            for name, v in zip(names, f[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+def cpu_baseline(desc, q_host, target_seconds: float = 12.0) -> dict:
+    """The CPU oracle (boolean, stop at first collision, all host threads) on a bounded sample."""
+    from oracle import oracle
+
+    cores = oracle.num_threads()
+    probe = q_host[: min(len(q_host), 1 << 14)]
+    t0 = time.perf_counter()
+    oracle.check_f32(desc, probe)
+    rate = len(probe) / (time.perf_counter() - t0)
+    n = int(min(len(q_host), max(len(probe), rate * target_seconds)))
+    t0 = time.perf_counter()
+    oracle.check_f32(desc, q_host[:n])
+    dt = time.perf_counter() - t0
+    return {"value": n / dt, "unit": UNIT, "cores": cores, "kind": "port",
+            "sample": f"first {n} configurations of the step's batch, boolean stop-at-first, OpenMP {cores} threads, {dt:.1f} s"}
+
+
+def run_reference(args, wl, rm, desc) -> None:
+    """--impl reference: the CPU path on the host cores (rank 0 only)."""
+    import numpy as np
+
+    from oracle import oracle
+    from ramp_b200 import workloads
+
+    if int(os.environ.get("RANK", "0")) != 0:
+        return
+    cores = oracle.num_threads()
+    q = workloads.sample_q(rm.model, 1 << 16, seed=0xB200)
+    t0 = time.perf_counter()
+    oracle.check_f32(desc, q[: 1 << 13])
+    rate = (1 << 13) / (time.perf_counter() - t0)
+    total = args.steps + args.warmup
+    n = int(min(len(q), max(1 << 12, rate * min(20.0, 150.0 / max(total, 1)))))
+    for _ in range(args.warmup):
+        oracle.check_f32(desc, q[:n])
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        oracle.check_f32(desc, q[:n])
+    dt = time.perf_counter() - t0
+    value = n * args.steps / dt
+    sample = f"{n} of the workload's configurations per step (bounded sample), boolean stop-at-first, OpenMP {cores} threads"
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": wl.name, "robot": wl.robot, "scene": wl.scene, "note": wl.note,
+                   "model": "stand-in" if "stand-in" in wl.note else "in-tree"},
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "reference_note": "Pinocchio 3.7.0 / coal 3.0.1 are not installable offline; this is the repo's FP64 "
+                          "restatement of that path (oracle/ramp_oracle.c)",
+    }))
+
+
+def main() -> None:
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="ur5e_1m")
+    ap.add_argument("--n", type=int, default=0, help="override configurations per step per GPU")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
+
+    import __graft_entry__
+
+    rank = int(os.environ.get("RANK", "0"))
+    if rank == 0:
+        __graft_entry__.build()
+
+    from ramp_b200 import workloads
+    from ramp_b200.desc import ModelDesc
+
+    wl = workloads.WORKLOADS[args.workload]
+    rm, _ = workloads.build(args.workload)
+    desc = ModelDesc(rm.model, rm.collision_model)
+    if args.impl == "reference":
+        run_reference(args, wl, rm, desc)
+        return
+
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+
+    from ramp_b200 import engine
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device (there is no CPU fallback); use --impl reference for the CPU path")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+        dist.barrier()
+
+    n = args.n or wl.n
+    gpu = rm.gpu
+    ld = workloads.padded_nq(rm.model)
+    # N_ROTATE distinct batches: 8 x n x ld x 4 B is well above the 126 MB L2 for n >= 2^20
+    batches = [workloads.sample_q_torch(rm.model, n, seed=0xB200 + 97 * rank + 13 * i, device=dev) for i in range(N_ROTATE)]
+    hit = torch.empty(n, dtype=torch.uint8, device=dev)
+    gathered = torch.empty(n * world, dtype=torch.uint8, device=dev) if world > 1 else None
+
+    def step(i: int):
+        gpu.check_raw(batches[i % N_ROTATE], hit)
+        if world > 1:
+            dist.all_gather_into_tensor(gathered, hit)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for i in range(args.warmup):
+        step(i)
+    barrier()
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    launches0 = engine.launch_count()
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps + 1)]
+    barrier()
+    ev[0].record()
+    for i in range(args.steps):
+        step(i)
+        ev[i + 1].record()
+    barrier()
+    launches = engine.launch_count() - launches0
+    clocks = sampler.stop()
+    total_ms = ev[0].elapsed_time(ev[-1])
+    t = torch.tensor([total_ms], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    total_ms = float(t.item())
+    colliding = float(hit.float().mean().item())
+
+    # kernel-only duration: the same launches again, one event pair per launch, no collective
+    kt = []
+    for i in range(min(args.steps, 10)):
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        gpu.check_raw(batches[i % N_ROTATE], hit)
+        b.record()
+        b.synchronize()
+        kt.append(a.elapsed_time(b))
+    kernel_ms = statistics.mean(kt)
+
+    # end to end: the C-ABI host-buffer call (ramp_check_host): H2D of q, kernel, D2H of flags
+    q_host = batches[0].cpu().numpy()
+    e2e_steps = max(3, min(args.steps, 10))
+    gpu.check_host(q_host)
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(e2e_steps):
+        gpu.check_host(q_host)
+    barrier()
+    e2e_s = time.perf_counter() - t0
+    te = torch.tensor([e2e_s], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(te, op=dist.ReduceOp.MAX)
+    e2e_value = n * world * e2e_steps / float(te.item())
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    peaks = measured_peaks()
+    from oracle import oracle
+
+    sample = q_host[:4096, : rm.model.nq].astype(np.float64)
+    flops_per_cfg = float(oracle.flops(desc, sample).mean())
+    bytes_per_cfg = 4 * ld + 1
+    sm_count = torch.cuda.get_device_properties(dev).multi_processor_count
+    fp32_peak = sm_count * 128 * 2 * peaks["sm_max_mhz"] * 1e6 / 1e12
+    achieved_tf = flops_per_cfg * n / (kernel_ms * 1e-3) / 1e12
+    achieved_gbs = bytes_per_cfg * n / (kernel_ms * 1e-3) / 1e9
+    traffic = None
+    tp = ROOT / "profiles" / "traffic.json"
+    if tp.exists():
+        traffic = json.loads(tp.read_text()).get(args.workload)
+    ref = oracle.check(desc, sample[:2048])
+    got = gpu.check(batches[0][:2048])["hit"].cpu().numpy()
+    outside = np.abs(ref["min_dist"]) > 1e-4
+    out = {
+        "metric": METRIC, "value": n * world * args.steps / (total_ms * 1e-3), "unit": UNIT, "n_gpus": world,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": total_ms / args.steps, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": wl.name, "robot": wl.robot, "scene": wl.scene, "note": wl.note,
+                   "model": "stand-in" if "stand-in" in wl.note else "in-tree",
+                   "n_per_gpu": n, "pairs": desc.n_pairs, "geoms": desc.n_geoms, "ld_q": ld,
+                   "colliding_fraction": colliding,
+                   "l2": f"{N_ROTATE} rotating input batches of {n * ld * 4 / 2**20:.0f} MiB each (inputs > 126 MB L2)",
+                   "parallelism": f"config shards x{world}, geometry replicated"
+                                  + (", NCCL all_gather of flags per step" if world > 1 else "")},
+        "roofline": {"bound": "fp32", "achieved": achieved_tf, "peak": fp32_peak, "unit": "TFLOP/s",
+                     "frac": achieved_tf / fp32_peak, "traffic": traffic,
+                     "kernel": "check_kernel", "kernel_ms": kernel_ms, "algorithmic_flops_per_config": flops_per_cfg,
+                     "peak_source": f"derived: {sm_count} SMs x 128 FP32 lanes x 2 x sm_max_mhz "
+                                    f"({peaks['_source']} MEASURED_PEAKS.json); no measured FP32 peak exists",
+                     "hbm": {"achieved": achieved_gbs, "peak": peaks["hbm_gbs"], "unit": "GB/s",
+                             "frac": achieved_gbs / peaks["hbm_gbs"], "algorithmic_bytes_per_config": bytes_per_cfg,
+                             "peak_source": peaks["_source"]}},
+        "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": n * ld * 4, "d2h_bytes_per_step": n,
+                "api": "ramp_check_host (C ABI, host buffers)", "steps": e2e_steps},
+        "gpu_launches": launches,
+        "clocks": clocks,
+        "parity": {"checked": int(len(got)), "in_band": int((~outside).sum()),
+                   "mismatch_outside_band": int((got != ref["hit"])[outside].sum())},
+    }
+    if world == 1 and not args.no_cpu_baseline:
+        out["cpu_baseline"] = cpu_baseline(desc, q_host)
+    print(json.dumps(out))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -102,14 +102,30 @@ __device__ __forceinline__ void rot_quat(Xf& o, float x, float y, float z, float
   o.m[8] = txz - twy;         o.m[9] = tyz + twx;         o.m[10] = 1.f - (txx + tyy);
 }
 
+// sin/cos with Cody-Waite reduction to [-pi/4, pi/4] and minimax polynomials (the fast path
+// of sinf/cosf without their large-argument slow path, which alone is several hundred
+// instructions).  |error| ~ 1e-7 for |x| < 1e4 -- joint angles; pose parity is 1e-5.
+__device__ __noinline__ void sincos_small(float x, float* sn, float* cs) {
+  const float k = rintf(x * 0.636619772367581343f);
+  float r = fmaf(-k, 1.5703125f, x);  // pi/2 split in three: k * 1.5703125 is exact
+  r = fmaf(-k, 4.837512969970703125e-4f, r);
+  r = fmaf(-k, 7.54978995489188216e-8f, r);
+  const int qd = static_cast<int>(k) & 3;
+  const float r2 = r * r;
+  float s = fmaf(fmaf(fmaf(-1.9515295891e-4f, r2, 8.3321608736e-3f), r2, -1.6666654611e-1f), r2 * r, r);
+  float c = fmaf(fmaf(fmaf(fmaf(2.443315711809948e-5f, r2, -1.388731625493765e-3f), r2, 4.166664568298827e-2f), r2, -0.5f), r2, 1.f);
+  if (qd & 1) { const float t = s; s = c; c = -t; }
+  if (qd & 2) { s = -s; c = -c; }
+  *sn = s; *cs = c;
+}
+
 // M_i(q): q0..q6 are the joint's q slots (unused ones are don't-care).
-// sincosf (not __sincosf): pose parity is 1e-5 and joint ranges reach +-2pi.
 __device__ __forceinline__ Xf joint_xf(int type, float ax, float ay, float az, const float* q) {
   Xf o = xf_identity();
   float s, c;
   switch (type) {
-    case 1: case 2: case 3: sincosf(q[0], &s, &c); rot_aligned(o, type - 1, c, s); break;
-    case 4: sincosf(q[0], &s, &c); rot_rodrigues(o, ax, ay, az, c, s); break;
+    case 1: case 2: case 3: sincos_small(q[0], &s, &c); rot_aligned(o, type - 1, c, s); break;
+    case 4: sincos_small(q[0], &s, &c); rot_rodrigues(o, ax, ay, az, c, s); break;
     case 5: case 6: case 7: rot_aligned(o, type - 5, q[0], q[1]); break;
     case 8: rot_rodrigues(o, ax, ay, az, q[0], q[1]); break;
     case 9: o.m[3] = q[0]; break;
@@ -121,9 +137,9 @@ __device__ __forceinline__ Xf joint_xf(int type, float ax, float ay, float az, c
     case 15: rot_quat(o, q[0], q[1], q[2], q[3]); break;
     case 16: {
       Xf rz = xf_identity(), ry = xf_identity(), rx = xf_identity();
-      sincosf(q[0], &s, &c); rot_aligned(rz, 2, c, s);
-      sincosf(q[1], &s, &c); rot_aligned(ry, 1, c, s);
-      sincosf(q[2], &s, &c); rot_aligned(rx, 0, c, s);
+      sincos_small(q[0], &s, &c); rot_aligned(rz, 2, c, s);
+      sincos_small(q[1], &s, &c); rot_aligned(ry, 1, c, s);
+      sincos_small(q[2], &s, &c); rot_aligned(rx, 0, c, s);
       o = xf_mul(xf_mul(rz, ry), rx);
     } break;
     case 17: o.m[3] = q[0]; o.m[7] = q[1]; o.m[11] = q[2]; break;
@@ -147,60 +163,46 @@ __device__ __forceinline__ int joint_nq(int type) {
 // Shape type codes are include/ramp_b200.h RampShapeType.
 enum { SH_SPHERE = 0, SH_CAPSULE = 1, SH_BOX = 2, SH_CYLINDER = 3, SH_CONVEX = 4, SH_ELLIPSOID = 5 };
 
-struct Shape {
-  int type;
-  float p0, p1, p2;  // params
-  int voff, vcnt;    // convex vertices (float4 units) in the staged vertex table
-};
-
-__device__ __forceinline__ float swept_radius(const Shape& s) {
-  return (s.type == SH_SPHERE || s.type == SH_CAPSULE) ? s.p0 : 0.f;
-}
-
-// Support point of the shape CORE (sphere -> point, capsule -> segment) along d, local frame.
-__device__ __forceinline__ V3 support(const Shape& s, const float4* __restrict__ verts, V3 d) {
-  switch (s.type) {
-    case SH_SPHERE: return mk(0.f, 0.f, 0.f);
-    case SH_CAPSULE: return mk(0.f, 0.f, d.z > 0.f ? s.p1 : (d.z < 0.f ? -s.p1 : 0.f));
-    case SH_BOX: return mk(d.x > 0.f ? s.p0 : -s.p0, d.y > 0.f ? s.p1 : -s.p1, d.z > 0.f ? s.p2 : -s.p2);
-    case SH_CYLINDER: {
-      const float zz = d.z > 0.f ? s.p1 : (d.z < 0.f ? -s.p1 : 0.f);
-      const float n2 = fmaf(d.x, d.x, d.y * d.y);
-      if (n2 > 0.f) {
-        const float k = s.p0 * rsqrtf(n2);
-        return mk(d.x * k, d.y * k, zz);
-      }
-      return mk(0.f, 0.f, zz);
-    }
-    case SH_ELLIPSOID: {
-      const V3 v = mk(s.p0 * s.p0 * d.x, s.p1 * s.p1 * d.y, s.p2 * s.p2 * d.z);
-      const float den = dot(v, d);
-      return den > 0.f ? v * rsqrtf(den) : mk(0.f, 0.f, 0.f);
-    }
-    default: {  // SH_CONVEX: brute-force scan of the staged vertices
-      const float4* __restrict__ p = verts + s.voff;
-      float best = -3.0e38f;
-      float4 bv = p[0];
-      int i = 0;
-      for (; i + 4 <= s.vcnt; i += 4) {
-        const float4 a = p[i], b = p[i + 1], c = p[i + 2], e = p[i + 3];
-        const float da = fmaf(a.x, d.x, fmaf(a.y, d.y, a.z * d.z));
-        const float db = fmaf(b.x, d.x, fmaf(b.y, d.y, b.z * d.z));
-        const float dc = fmaf(c.x, d.x, fmaf(c.y, d.y, c.z * d.z));
-        const float de = fmaf(e.x, d.x, fmaf(e.y, d.y, e.z * d.z));
-        if (da > best) { best = da; bv = a; }
-        if (db > best) { best = db; bv = b; }
-        if (dc > best) { best = dc; bv = c; }
-        if (de > best) { best = de; bv = e; }
-      }
-      for (; i < s.vcnt; ++i) {
-        const float4 a = p[i];
-        const float da = fmaf(a.x, d.x, fmaf(a.y, d.y, a.z * d.z));
-        if (da > best) { best = da; bv = a; }
-      }
-      return mk(bv.x, bv.y, bv.z);
-    }
+// Support point of a shape CORE along d in the shape's local frame.  Every polytope core is a
+// vertex list in the staged table -- sphere: 1 vertex (its centre), capsule: the 2 segment
+// ends, box: its 8 corners, convex: the hull vertices -- so one scan loop serves them all and
+// lanes holding different shape types do not diverge.  Cylinder and ellipsoid have closed
+// forms.  (type, p0..p2) are the geometry's shape code and parameters.
+__device__ __forceinline__ V3 support(int type, float p0, float p1, float p2, const float4* __restrict__ p, int vcnt,
+                                      V3 d) {
+  if (type == SH_CYLINDER) {
+    const float zz = d.z > 0.f ? p1 : (d.z < 0.f ? -p1 : 0.f);
+    const float n2 = fmaf(d.x, d.x, d.y * d.y);
+    const float k = n2 > 0.f ? p0 * rsqrtf(n2) : 0.f;
+    return mk(d.x * k, d.y * k, zz);
   }
+  if (type == SH_ELLIPSOID) {
+    const V3 v = mk(p0 * p0 * d.x, p1 * p1 * d.y, p2 * p2 * d.z);
+    const float den = dot(v, d);
+    return den > 0.f ? v * rsqrtf(den) : mk(0.f, 0.f, 0.f);
+  }
+  float best = -3.0e38f;
+  float bx = 0.f, by = 0.f, bz = 0.f;
+  int i = 0;
+#pragma unroll 1
+  for (; i + 4 <= vcnt; i += 4) {
+    const float4 a = p[i], b = p[i + 1], c = p[i + 2], e = p[i + 3];
+    const float da = fmaf(a.x, d.x, fmaf(a.y, d.y, a.z * d.z));
+    const float db = fmaf(b.x, d.x, fmaf(b.y, d.y, b.z * d.z));
+    const float dc = fmaf(c.x, d.x, fmaf(c.y, d.y, c.z * d.z));
+    const float de = fmaf(e.x, d.x, fmaf(e.y, d.y, e.z * d.z));
+    if (da > best) { best = da; bx = a.x; by = a.y; bz = a.z; }
+    if (db > best) { best = db; bx = b.x; by = b.y; bz = b.z; }
+    if (dc > best) { best = dc; bx = c.x; by = c.y; bz = c.z; }
+    if (de > best) { best = de; bx = e.x; by = e.y; bz = e.z; }
+  }
+#pragma unroll 1
+  for (; i < vcnt; ++i) {
+    const float4 a = p[i];
+    const float da = fmaf(a.x, d.x, fmaf(a.y, d.y, a.z * d.z));
+    if (da > best) { best = da; bx = a.x; by = a.y; bz = a.z; }
+  }
+  return mk(bx, by, bz);
 }
 
 // ------------------------------------------------------------- closed-form distances
@@ -292,135 +294,157 @@ __device__ __forceinline__ bool obb_overlap(V3 a, V3 b, const Xf& m, float slack
 }
 
 // ------------------------------------------------------------------------------ GJK
-// Closest point of a simplex to the origin, Voronoi-region form; the simplex is reduced
-// in place to its supporting sub-simplex.
+// Closest point of a simplex to the origin, Voronoi-region form.  Written so that every
+// helper has ONE call site (small instruction footprint: the validity kernel must stay
+// inside the instruction cache while its warps sit in different phases).
 struct Simplex {
   V3 p[4];
   int n;
 };
 
-__device__ __forceinline__ V3 closest_segment(Simplex& s) {
-  const V3 a = s.p[0], b = s.p[1], ab = b - a;
-  const float t = -dot(a, ab), den = dot(ab, ab);
-  if (t <= 0.f || den <= 0.f) { s.n = 1; return a; }
-  if (t >= den) { s.p[0] = b; s.n = 1; return b; }
-  return a + ab * (t / den);
-}
-
-__device__ __forceinline__ V3 closest_triangle(V3 a, V3 b, V3 c, Simplex& o) {
+// closest point of triangle (a,b,c) to the origin; o = supporting sub-simplex
+__device__ __forceinline__ V3 closest_triangle(V3 a, V3 b, V3 c, V3& o0, V3& o1, V3& o2, int& on) {
   const V3 ab = b - a, ac = c - a;
   const float d1 = -dot(ab, a), d2 = -dot(ac, a);
-  if (d1 <= 0.f && d2 <= 0.f) { o.p[0] = a; o.n = 1; return a; }
   const float d3 = -dot(ab, b), d4 = -dot(ac, b);
-  if (d3 >= 0.f && d4 <= d3) { o.p[0] = b; o.n = 1; return b; }
-  const float vc = d1 * d4 - d3 * d2;
-  if (vc <= 0.f && d1 >= 0.f && d3 <= 0.f) {
-    o.p[0] = a; o.p[1] = b; o.n = 2;
-    return a + ab * (d1 / (d1 - d3));
-  }
   const float d5 = -dot(ab, c), d6 = -dot(ac, c);
-  if (d6 >= 0.f && d5 <= d6) { o.p[0] = c; o.n = 1; return c; }
-  const float vb = d5 * d2 - d1 * d6;
-  if (vb <= 0.f && d2 >= 0.f && d6 <= 0.f) {
-    o.p[0] = a; o.p[1] = c; o.n = 2;
-    return a + ac * (d2 / (d2 - d6));
-  }
-  const float va = d3 * d6 - d5 * d4;
+  const float vc = d1 * d4 - d3 * d2, vb = d5 * d2 - d1 * d6, va = d3 * d6 - d5 * d4;
+  o0 = a; o1 = b; o2 = c;
+  if (d1 <= 0.f && d2 <= 0.f) { on = 1; return a; }
+  if (d3 >= 0.f && d4 <= d3) { o0 = b; on = 1; return b; }
+  if (d6 >= 0.f && d5 <= d6) { o0 = c; on = 1; return c; }
+  if (vc <= 0.f && d1 >= 0.f && d3 <= 0.f) { on = 2; return a + ab * (d1 / (d1 - d3)); }
+  if (vb <= 0.f && d2 >= 0.f && d6 <= 0.f) { o1 = c; on = 2; return a + ac * (d2 / (d2 - d6)); }
   if (va <= 0.f && (d4 - d3) >= 0.f && (d5 - d6) >= 0.f) {
-    o.p[0] = b; o.p[1] = c; o.n = 2;
+    o0 = b; o1 = c; on = 2;
     return b + (c - b) * ((d4 - d3) / ((d4 - d3) + (d5 - d6)));
   }
   // interior: project the origin on the plane (more accurate in FP32 than barycentric sums)
   const V3 n = cross(ab, ac);
   const float nn = dot(n, n);
-  o.p[0] = a; o.p[1] = b; o.p[2] = c; o.n = 3;
+  on = 3;
   if (nn > 0.f) return n * (dot(a, n) / nn);
   const float den = 1.f / (va + vb + vc);
   return a + ab * (vb * den) + ac * (vc * den);
 }
 
-// returns true when the origin is inside (or on) the tetrahedron
-__device__ __forceinline__ bool closest_tetra(Simplex& s, V3& out) {
+// Reduce the simplex to the sub-simplex closest to the origin and return that closest point.
+// Returns true when the origin is enclosed by a tetrahedron.
+__device__ __forceinline__ bool solve_simplex(Simplex& s, V3& out) {
+  if (s.n == 1) { out = s.p[0]; return false; }
+  if (s.n == 2) {
+    const V3 a = s.p[0], b = s.p[1], ab = b - a;
+    const float t = -dot(a, ab), den = dot(ab, ab);
+    if (t <= 0.f || den <= 0.f) { s.n = 1; out = a; }
+    else if (t >= den) { s.p[0] = b; s.n = 1; out = b; }
+    else out = a + ab * (t / den);
+    return false;
+  }
+  // triangle: one face; tetrahedron: the four faces, visited by rotating the vertices so the
+  // face code below exists once
+  const bool tetra = s.n == 4;
+  const int nfaces = tetra ? 4 : 1;
+  V3 p0 = s.p[0], p1 = s.p[1], p2 = s.p[2], p3 = s.p[3];
   float best = 3.0e38f;
-  Simplex bs;
-  bs.n = 0;
-  V3 bp = mk(0.f, 0.f, 0.f);
   bool outside_any = false;
-#pragma unroll
-  for (int f = 0; f < 4; ++f) {
-    // faces (0,1,2|3) (0,2,3|1) (0,3,1|2) (1,3,2|0)
-    const int ia = f == 3 ? 1 : 0, ib = f == 0 ? 1 : (f == 1 ? 2 : 3), ic = f == 0 ? 2 : (f == 1 ? 3 : (f == 2 ? 1 : 2)),
-              id = f == 0 ? 3 : (f == 1 ? 1 : (f == 2 ? 2 : 0));
-    const V3 a = s.p[ia], b = s.p[ib], c = s.p[ic], d = s.p[id];
-    const V3 n = cross(b - a, c - a);
-    const float so = -dot(a, n), sd = dot(d - a, n);
-    if (so * sd < 0.f || sd == 0.f) {
-      outside_any = true;
-      Simplex o;
-      const V3 p = closest_triangle(a, b, c, o);
-      const float dd = dot(p, p);
-      if (dd < best) { best = dd; bs = o; bp = p; }
+  V3 b0 = p0, b1 = p1, b2 = p2, bp = mk(0.f, 0.f, 0.f);
+  int bn = 0;
+#pragma unroll 1
+  for (int f = 0; f < nfaces; ++f) {
+    bool outside = true;
+    if (tetra) {
+      const V3 n = cross(p1 - p0, p2 - p0);
+      const float so = -dot(p0, n), sd = dot(p3 - p0, n);
+      outside = so * sd < 0.f || sd == 0.f;
     }
+    if (outside) {
+      outside_any = true;
+      V3 o0, o1, o2;
+      int on;
+      const V3 q = closest_triangle(p0, p1, p2, o0, o1, o2, on);
+      const float dd = dot(q, q);
+      if (dd < best) { best = dd; b0 = o0; b1 = o1; b2 = o2; bn = on; bp = q; }
+    }
+    const V3 t = p0; p0 = p1; p1 = p2; p2 = p3; p3 = t;  // next face
   }
   if (!outside_any) return true;
-  s = bs;
+  s.p[0] = b0; s.p[1] = b1; s.p[2] = b2; s.n = bn;
   out = bp;
   return false;
 }
 
-struct GjkResult {
-  bool hit;     // swept shapes overlap (distance <= 0)
-  float dist;   // core distance estimate minus swept radii; meaningful when !hit
-  int iters;
+// Per-lane GJK state: a lane keeps one (configuration, pair) work item and advances it one
+// iteration per trip of the warp loop; finished lanes fetch the next item, so lanes stay
+// busy even though iteration counts differ per item.
+struct GjkLane {
+  Xf rel;      // pose of shape B in shape A's frame
+  V3 v;        // current closest point of the simplex (a point of A (-) B)
+  float vv;
+  Simplex s;
+  float rsum;  // swept radii of the two cores
+  float lower; // best proven lower bound on the core distance
+  int it;
 };
 
-// Boolean GJK with a distance estimate.  Shape A at the origin of its own frame, shape B at
-// pose m (B in A's frame).  `exact`: iterate to convergence even after a separating plane is
-// known (distance output); otherwise stop as soon as separation or overlap is proven.
-__device__ __forceinline__ GjkResult gjk(const Shape& A, const Shape& B, const Xf& m, const float4* __restrict__ verts,
-                                       bool exact) {
-  const float rsum = swept_radius(A) + swept_radius(B);
-  const float rs2 = rsum * rsum;
+struct GjkShape {
+  int type, vcnt;
+  float p0, p1, p2;
+  const float4* verts;
+};
+
+__device__ __forceinline__ void gjk_init(GjkLane& g, const Xf& rel, float rsum) {
+  g.rel = rel;
+  g.v = -trans(rel);  // centre(A) - centre(B): a point of the Minkowski difference
+  g.vv = dot(g.v, g.v);
+  if (g.vv < 1e-12f) { g.v = mk(1.f, 0.f, 0.f); g.vv = 1.f; }
+  g.s.n = 0;
+  g.rsum = rsum;
+  g.lower = 0.f;
+  g.it = 0;
+}
+
+enum { GJK_CONTINUE = 0, GJK_HIT = 1, GJK_MISS = 2 };
+
+// One GJK iteration.  `exact`: run to convergence (distance output) instead of stopping at
+// the first proof of separation / overlap.  On GJK_MISS / GJK_HIT with exact, dist holds the
+// core distance minus the swept radii.
+__device__ __forceinline__ int gjk_step(GjkLane& g, const GjkShape& A, const GjkShape& B, bool exact, float& dist) {
   const float EPS_REL = 1e-5f, TINY2 = 1e-12f;
-  V3 v = -trans(m);  // centre(A) - centre(B): a point of the Minkowski difference
-  float vv = dot(v, v);
-  if (vv < TINY2) { v = mk(1.f, 0.f, 0.f); vv = 1.f; }
-  Simplex s;
-  s.n = 0;
-  GjkResult r;
-  r.hit = false; r.dist = 0.f; r.iters = 0;
-  float lower = 0.f;  // best proven lower bound on the core distance
-  for (int it = 0; it < 48; ++it) {
-    r.iters = it + 1;
-    const V3 dir = -v;
-    const V3 sa = support(A, verts, dir);
-    const V3 sb = apply(m, support(B, verts, rot_t(m, v)));
-    const V3 w = sa - sb;
-    const float vw = dot(v, w);
-    if (vw > 0.f) {
-      const float om = vw * rsqrtf(vv);
-      lower = fmaxf(lower, om);
-      if (!exact && om > rsum) { r.dist = om - rsum; return r; }  // separating plane
-    }
-    if (s.n > 0 && vv - vw <= EPS_REL * vv) break;  // converged: |v| is the core distance
-    s.p[s.n++] = w;
-    V3 nv;
-    if (s.n == 1) nv = s.p[0];
-    else if (s.n == 2) nv = closest_segment(s);
-    else if (s.n == 3) { Simplex o; nv = closest_triangle(s.p[0], s.p[1], s.p[2], o); s = o; }
-    else if (closest_tetra(s, nv)) { r.hit = true; r.dist = -rsum; return r; }
-    const float nvv = dot(nv, nv);
-    if (nvv <= fmaxf(rs2, TINY2) && !exact) { r.hit = true; r.dist = sqrtf(nvv) - rsum; return r; }
-    if (nvv <= TINY2) { r.hit = true; r.dist = -rsum; return r; }
-    if (it > 0 && nvv >= vv) break;  // no progress at FP32 resolution
-    v = nv; vv = nvv;
+  const float rs2 = g.rsum * g.rsum;
+  V3 sa = mk(0.f, 0.f, 0.f), sb = sa;
+#pragma unroll 1
+  for (int side = 0; side < 2; ++side) {
+    const GjkShape& S = side ? B : A;
+    const V3 d = side ? rot_t(g.rel, g.v) : -g.v;
+    const V3 r = support(S.type, S.p0, S.p1, S.p2, S.verts, S.vcnt, d);
+    if (side) sb = r; else sa = r;
   }
-  const float d = sqrtf(vv);
-  r.dist = d - rsum;
-  r.hit = d <= rsum;
+  const V3 w = sa - apply(g.rel, sb);
+  const float vw = dot(g.v, w);
+  if (vw > 0.f) {
+    const float om = vw * rsqrtf(g.vv);
+    g.lower = fmaxf(g.lower, om);
+    if (!exact && om > g.rsum) { dist = om - g.rsum; return GJK_MISS; }  // separating plane
+  }
+  bool done = g.s.n > 0 && g.vv - vw <= EPS_REL * g.vv;  // converged: |v| is the core distance
+  if (!done) {
+    // no dynamic register indexing (it would spill the simplex to local memory)
+    if (g.s.n == 0) g.s.p[0] = w; else if (g.s.n == 1) g.s.p[1] = w; else if (g.s.n == 2) g.s.p[2] = w; else g.s.p[3] = w;
+    ++g.s.n;
+    V3 nv;
+    if (solve_simplex(g.s, nv)) { dist = -g.rsum; return GJK_HIT; }
+    const float nvv = dot(nv, nv);
+    if (nvv <= fmaxf(rs2, TINY2) && !exact) { dist = sqrtf(nvv) - g.rsum; return GJK_HIT; }
+    if (nvv <= TINY2) { dist = -g.rsum; return GJK_HIT; }
+    if (g.it > 0 && nvv >= g.vv) done = true;  // no progress at FP32 resolution
+    else { g.v = nv; g.vv = nvv; }
+  }
+  if (!done && ++g.it < 48) return GJK_CONTINUE;
+  const float d = sqrtf(g.vv);
+  dist = d - g.rsum;
   // a stalled iteration far from convergence: trust the proven lower bound
-  if (r.hit && lower > rsum) { r.hit = false; r.dist = lower - rsum; }
-  return r;
+  if (d <= g.rsum && g.lower > g.rsum) { dist = g.lower - g.rsum; return GJK_MISS; }
+  return d <= g.rsum ? GJK_HIT : GJK_MISS;
 }
 
 }  // namespace ramp

@@ -151,6 +151,7 @@ __device__ __forceinline__ void load_rows(float* dst, const float* __restrict__ 
   if (ld == cols && (cols & 3) == 0 && (reinterpret_cast<uintptr_t>(base) & 15) == 0) {
     const int n4 = rows * cols / 4;
     const float4* b4 = reinterpret_cast<const float4*>(base);
+#pragma unroll 1
     for (int e = lane; e < n4; e += 32) {
       const float4 v = __ldg(b4 + e);
       const int r = (4 * e) / cols, c = (4 * e) - r * cols;
@@ -161,6 +162,7 @@ __device__ __forceinline__ void load_rows(float* dst, const float* __restrict__ 
     }
   } else {
     const int n = rows * cols;
+#pragma unroll 1
     for (int e = lane; e < n; e += 32) {
       const int r = e / cols, c = e - r * cols;
       dst[c * 32 + r] = __ldg(base + static_cast<int64_t>(r) * ld + c);
@@ -169,8 +171,10 @@ __device__ __forceinline__ void load_rows(float* dst, const float* __restrict__ 
   // lanes past the end of the batch replay row 0 so every lane does well-defined work
   if (rows < 32) {
     __syncwarp();
-    if (lane >= rows)
+    if (lane >= rows) {
+#pragma unroll 1
       for (int c = 0; c < cols; ++c) dst[c * 32 + lane] = dst[c * 32];
+    }
   }
   __syncwarp();
 }
@@ -180,16 +184,20 @@ __device__ __forceinline__ void load_rows(float* dst, const float* __restrict__ 
 __device__ __forceinline__ void expand_q(const Warp& w) {
   const ImgHeader* h = w.t.h;
   const int l = w.lane;
+#pragma unroll 1
   for (int s = 0; s < h->nq; ++s) w.q[s * 32 + l] = w.t.refq[s];
+#pragma unroll 1
   for (int k = 0; k < h->n_act; ++k) w.q[w.t.act[k] * 32 + l] = w.act[k * 32 + l];
+#pragma unroll 1
   for (int k = 0; k < h->n_mimic; ++k) {
     const DMimic m = w.t.mimic[k];
     w.q[m.dst * 32 + l] = fmaf(w.q[m.src * 32 + l], m.mult, m.off);
   }
+#pragma unroll 1
   for (int k = 0; k < h->n_cont; ++k) {
     const int c = w.t.cont[k];
     float s, co;
-    sincosf(w.q[c * 32 + l], &s, &co);
+    sincos_small(w.q[c * 32 + l], &s, &co);
     w.q[c * 32 + l] = co;
     w.q[(c + 1) * 32 + l] = s;
   }
@@ -232,6 +240,7 @@ __device__ __forceinline__ void fk_lane(const Warp& w) {
   const ImgHeader* h = w.t.h;
   const int l = w.lane;
   Xf cur = xf_identity();
+#pragma unroll 1
   for (int i = 0; i < h->n_joints; ++i) {
     const DJoint* j = &w.t.joints[i];
     const int type = j->type;
@@ -249,6 +258,7 @@ __device__ __forceinline__ void fk_lane(const Warp& w) {
 #pragma unroll
       for (int k = 0; k < 12; ++k) w.stage[l * w.stage_stride + i * 12 + k] = cur.m[k];
     }
+#pragma unroll 1
     for (int s = j->gfirst; s < j->gfirst + j->gcount; ++s) {
       const int gi = w.t.dyn[s];
       const Xf og = xf_mul(cur, load_table_xf(w.t.geoms[gi].pl));
@@ -268,10 +278,14 @@ __device__ __forceinline__ void record_hit(const Warp& w, int c, int p, bool wan
   if (want_mask) atomicOr(&w.mask[(p >> 5) * 32 + c], 1u << (p & 31));
 }
 
-__device__ __forceinline__ Shape load_shape(const DGeom* g) {
-  Shape s;
-  s.type = g->type; s.p0 = g->p0; s.p1 = g->p1; s.p2 = g->p2; s.voff = g->voff; s.vcnt = g->vcnt;
+__device__ __forceinline__ GjkShape load_shape(const DGeom* g, const float4* verts) {
+  GjkShape s;
+  s.type = g->type; s.vcnt = g->vcnt; s.p0 = g->p0; s.p1 = g->p1; s.p2 = g->p2; s.verts = verts + g->voff;
   return s;
+}
+
+__device__ __forceinline__ float swept_radius(const DGeom* g) {
+  return (g->type == SH_SPHERE || g->type == SH_CAPSULE) ? g->p0 : 0.f;
 }
 
 // exact closed-form decision for the primitive classes; rel = pose of b in a's frame
@@ -308,6 +322,7 @@ __device__ __forceinline__ void narrow_phase(const Warp& w, bool stop_at_first, 
     const int my_first = w.first[l];
     int qn = 0;
     // ---- stage 1: bounding spheres, lane = configuration, pair index uniform
+#pragma unroll 1
     for (int p = chunk; p < chunk_end; ++p) {
       const DPair pr = w.t.pairs[p];
       if (pr.cls == kClsInactive) continue;
@@ -330,6 +345,7 @@ __device__ __forceinline__ void narrow_phase(const Warp& w, bool stop_at_first, 
     __syncwarp();
     // ---- stage 2: closed forms, exact box-box, OBB cull; survivors re-compacted in place
     int gn = 0;
+#pragma unroll 1
     for (int base = 0; base < qn; base += 32) {
       const bool live = base + l < qn;
       const int item = live ? w.queue[base + l] : 0;
@@ -340,10 +356,15 @@ __device__ __forceinline__ void narrow_phase(const Warp& w, bool stop_at_first, 
         const DGeom* ga = &w.t.geoms[pr.a];
         const DGeom* gb = &w.t.geoms[pr.b];
         const Xf rel = xf_inv_mul(geom_xf(w, ga->gslot, c), geom_xf(w, gb->gslot, c));
-        if (pr.cls == kClsBoxBox) {
-          if (obb_overlap(mk(ga->p0, ga->p1, ga->p2), mk(gb->p0, gb->p1, gb->p2), rel, 0.f)) record_hit(w, c, p, want_mask);
-        } else if (pr.cls == kClsGjk) {
-          to_gjk = obb_overlap(mk(ga->hx, ga->hy, ga->hz), mk(gb->hx, gb->hy, gb->hz), rel, 1e-5f);
+        if (pr.cls >= kClsBoxBox) {
+          // one SAT instance: exact decision on the boxes themselves, or a cull on the
+          // local bounding boxes of two GJK shapes
+          const bool bb = pr.cls == kClsBoxBox;
+          const V3 ha = bb ? mk(ga->p0, ga->p1, ga->p2) : mk(ga->hx, ga->hy, ga->hz);
+          const V3 hb = bb ? mk(gb->p0, gb->p1, gb->p2) : mk(gb->hx, gb->hy, gb->hz);
+          const bool ov = obb_overlap(ha, hb, rel, bb ? 0.f : 1e-5f);
+          if (ov && bb) record_hit(w, c, p, want_mask);
+          to_gjk = ov && !bb;
         } else if (closed_form_hit(pr.cls, ga, gb, rel)) {
           record_hit(w, c, p, want_mask);
         }
@@ -354,19 +375,49 @@ __device__ __forceinline__ void narrow_phase(const Warp& w, bool stop_at_first, 
       gn += __popc(b);
       __syncwarp();
     }
-    // ---- stage 3: GJK on dense groups of 32 work items
-    for (int base = 0; base < gn; base += 32) {
-      if (base + l < gn) {
-        const int item = w.queue[base + l];
-        const int c = item & 31, p = chunk + (item >> 5);
-        // a configuration that was hit earlier in this chunk needs no later pair
-        if (!(stop_at_first && w.first[c] < p)) {
-          const DPair pr = w.t.pairs[p];
-          const DGeom* ga = &w.t.geoms[pr.a];
-          const DGeom* gb = &w.t.geoms[pr.b];
-          const Xf rel = xf_inv_mul(geom_xf(w, ga->gslot, c), geom_xf(w, gb->gslot, c));
-          const GjkResult r = gjk(load_shape(ga), load_shape(gb), rel, w.t.verts, false);
-          if (r.hit) record_hit(w, c, p, want_mask);
+    // ---- stage 3: GJK.  Each lane owns one work item and advances it one iteration per
+    // trip; lanes whose item finished fetch the next one from the queue, so lanes stay busy
+    // although iteration counts differ per item.
+    {
+      int next = 0, c = 0, p = 0;
+      bool active = false;
+      GjkLane g;
+      GjkShape A, B;
+      A.type = B.type = 0; A.vcnt = B.vcnt = 0; A.p0 = A.p1 = A.p2 = B.p0 = B.p1 = B.p2 = 0.f; A.verts = B.verts = w.t.verts;
+      g.s.n = 0; g.it = 0; g.vv = 1.f; g.rsum = 0.f; g.lower = 0.f; g.v = mk(1.f, 0.f, 0.f); g.rel = xf_identity();
+      while (true) {
+        const unsigned need = __ballot_sync(FULL, !active);
+        if (!active) {
+          const int idx = next + __popc(need & ((1u << l) - 1));
+          if (idx < gn) {
+            const int item = w.queue[idx];
+            c = item & 31;
+            p = chunk + (item >> 5);
+            // a configuration that was hit earlier needs no later pair
+            if (!(stop_at_first && w.first[c] < p)) {
+              const DPair pr = w.t.pairs[p];
+              const DGeom* ga = &w.t.geoms[pr.a];
+              const DGeom* gb = &w.t.geoms[pr.b];
+              A = load_shape(ga, w.t.verts);
+              B = load_shape(gb, w.t.verts);
+              gjk_init(g, xf_inv_mul(geom_xf(w, ga->gslot, c), geom_xf(w, gb->gslot, c)),
+                       swept_radius(ga) + swept_radius(gb));
+              active = true;
+            }
+          }
+        }
+        next += __popc(need);
+        if (!__any_sync(FULL, active)) {
+          if (next >= gn) break;
+          continue;
+        }
+        if (active) {
+          float dist;
+          const int st = gjk_step(g, A, B, false, dist);
+          if (st != GJK_CONTINUE) {
+            if (st == GJK_HIT) record_hit(w, c, p, want_mask);
+            active = false;
+          }
         }
       }
     }
@@ -785,7 +836,7 @@ static int build_image(RampModel* m) {
     for (int k = 0; k < 12; ++k) d.pl[k] = static_cast<float>(j.placement[k]);
   }
   // geometries
-  int n_static = 0;
+  int n_static = 0, n_lists = 0;
   std::vector<std::vector<int>> by_joint(nj);
   for (int g = 0; g < ng; ++g) {
     const bool scene = g >= n_robot;
@@ -801,6 +852,7 @@ static int build_image(RampModel* m) {
     double pl[12];
     std::memcpy(pl, src.placement, sizeof pl);
     double hx = 0, hy = 0, hz = 0, br = 0;
+    std::vector<double> core;  // vertices of the shape core, geometry-local
     switch (src.type) {
       case RAMP_SHAPE_SPHERE: hx = hy = hz = br = src.params[0]; break;
       case RAMP_SHAPE_CAPSULE: hx = hy = src.params[0]; hz = br = src.params[0] + src.params[1]; break;
@@ -816,17 +868,34 @@ static int build_image(RampModel* m) {
           for (int k = 0; k < 3; ++k) { lo[k] = std::min(lo[k], v[3 * i + k]); hi[k] = std::max(hi[k], v[3 * i + k]); }
         const double c[3] = {0.5 * (lo[0] + hi[0]), 0.5 * (lo[1] + hi[1]), 0.5 * (lo[2] + hi[2])};
         hx = 0.5 * (hi[0] - lo[0]); hy = 0.5 * (hi[1] - lo[1]); hz = 0.5 * (hi[2] - lo[2]);
-        d.voff = static_cast<int32_t>(verts4.size() / 4);
-        d.vcnt = src.vert_count;
         for (int i = 0; i < src.vert_count; ++i) {
           const double x = v[3 * i] - c[0], y = v[3 * i + 1] - c[1], z = v[3 * i + 2] - c[2];
           br = std::max(br, std::sqrt(x * x + y * y + z * z));
-          verts4.push_back(static_cast<float>(x)); verts4.push_back(static_cast<float>(y));
-          verts4.push_back(static_cast<float>(z)); verts4.push_back(0.f);
+          core.push_back(x); core.push_back(y); core.push_back(z);
         }
         const double shift[12] = {1, 0, 0, c[0], 0, 1, 0, c[1], 0, 0, 1, c[2]};
         mat_mul34(src.placement, shift, pl);
       } break;
+    }
+    // polytope cores as vertex lists: sphere = its centre, capsule = the segment ends,
+    // box = the 8 corners (device_math.cuh support())
+    if (src.type == RAMP_SHAPE_SPHERE) core = {0, 0, 0};
+    if (src.type == RAMP_SHAPE_CAPSULE) core = {0, 0, -src.params[1], 0, 0, src.params[1]};
+    if (src.type == RAMP_SHAPE_BOX)
+      for (int k = 0; k < 8; ++k) {
+        core.push_back((k & 1) ? hx : -hx); core.push_back((k & 2) ? hy : -hy); core.push_back((k & 4) ? hz : -hz);
+      }
+    if (!core.empty()) {
+      // skew the start of every vertex list by one float4 (4 banks) relative to the previous
+      // one, so lanes scanning different lists in lock step hit different banks
+      while ((verts4.size() / 4) % 8 != static_cast<size_t>(n_lists % 8)) verts4.insert(verts4.end(), 4, 0.f);
+      ++n_lists;
+      d.voff = static_cast<int32_t>(verts4.size() / 4);
+      d.vcnt = static_cast<int32_t>(core.size() / 3);
+      for (size_t i = 0; i < core.size(); i += 3) {
+        verts4.push_back(static_cast<float>(core[i])); verts4.push_back(static_cast<float>(core[i + 1]));
+        verts4.push_back(static_cast<float>(core[i + 2])); verts4.push_back(0.f);
+      }
     }
     d.hx = static_cast<float>(hx); d.hy = static_cast<float>(hy); d.hz = static_cast<float>(hz);
     d.bound_r = static_cast<float>(br);
