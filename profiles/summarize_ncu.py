@@ -59,7 +59,8 @@ def main(rep, out):
             break
         files.append(s["file"])
         first.append(s)
-    samp, inst, tinst, noinst, src = (collections.Counter() for _ in range(4)) + ({},)
+    samp, inst, tinst, noinst = (collections.Counter() for _ in range(4))
+    src = {}
     num = lambda x: float(x) if x.replace(".", "", 1).isdigit() else 0.0  # noqa: E731
     for s in first:
         h = s["hdr"]

@@ -51,14 +51,19 @@ struct DJoint {  // 24 words
 };
 static_assert(sizeof(DJoint) == 96, "DJoint");
 
-struct DGeom {  // 24 words
+struct DGeom {  // 36 words
   int32_t type, gslot, voff, vcnt;  // gslot >= 0: per-config slot; < 0: static transform -1-gslot
   float p0, p1, p2, bound_r;
   float hx, hy, hz;  // local-frame box that contains the shape (OBB cull)
   int32_t parent;
   float pl[12];  // placement in the parent joint frame (dyn) / world (static)
+  // two capsules on one local axis (centre cc, unit direction cu): the OUTER one contains the
+  // shape (cull), the INNER one is contained in it (early accept); half lengths / radii
+  float cc[3], cu[3];
+  float s_out, r_out, s_in, r_in;
+  float pad[2];
 };
-static_assert(sizeof(DGeom) == 96, "DGeom");
+static_assert(sizeof(DGeom) == 144, "DGeom");
 
 struct DPair {  // 4 words; a/b ordered so that type(a) <= type(b)
   int32_t a, b, cls;

@@ -273,6 +273,23 @@ __device__ __forceinline__ void fk_lane(const Warp& w) {
 }
 
 // ---- narrow phase over the pair list for the 32 configurations of the tile.
+// A (configuration, pair) work item that survived every cull and needs GJK.  The validity
+// kernel appends such items to a global queue; gjk_queue_kernel drains it with full warps and
+// far more resident warps than the slab-bound validity kernel can have.
+struct __align__(16) GjkItem {
+  float rel[12];  // pose of shape b in shape a's frame
+  uint32_t row;   // configuration index inside the launch's slice
+  uint32_t p;     // pair index
+  uint32_t pad[2];
+};
+static_assert(sizeof(GjkItem) == 64, "GjkItem");
+
+struct GjkQueue {
+  GjkItem* items;    // nullptr: no queue, GJK runs inside the validity kernel
+  uint32_t* count;   // items reserved so far (may exceed capacity: overflow stays in-kernel)
+  uint32_t capacity;
+};
+
 __device__ __forceinline__ void record_hit(const Warp& w, int c, int p, bool want_mask) {
   atomicMin(&w.first[c], p);
   if (want_mask) atomicOr(&w.mask[(p >> 5) * 32 + c], 1u << (p & 31));
@@ -313,7 +330,8 @@ __device__ __forceinline__ bool closed_form_hit(int cls, const DGeom* ga, const 
   }
 }
 
-__device__ __forceinline__ void narrow_phase(const Warp& w, bool stop_at_first, bool want_mask) {
+__device__ __forceinline__ void narrow_phase(const Warp& w, bool stop_at_first, bool want_mask, const GjkQueue& gq,
+                                             uint32_t row_base) {
   const ImgHeader* h = w.t.h;
   const int l = w.lane;
   const unsigned FULL = 0xffffffffu;
@@ -362,14 +380,53 @@ __device__ __forceinline__ void narrow_phase(const Warp& w, bool stop_at_first, 
           const bool bb = pr.cls == kClsBoxBox;
           const V3 ha = bb ? mk(ga->p0, ga->p1, ga->p2) : mk(ga->hx, ga->hy, ga->hz);
           const V3 hb = bb ? mk(gb->p0, gb->p1, gb->p2) : mk(gb->hx, gb->hy, gb->hz);
-          const bool ov = obb_overlap(ha, hb, rel, bb ? 0.f : 1e-5f);
-          if (ov && bb) record_hit(w, c, p, want_mask);
-          to_gjk = ov && !bb;
+          // GJK class: capsule mid-phase first.  Disjoint OUTER capsules prove separation,
+          // overlapping INNER capsules prove collision; only the shell in between needs GJK.
+          int verdict = 0;  // 0 undecided, 1 separated, 2 colliding
+          if (!bb) {
+            const V3 ca = mk(ga->cc[0], ga->cc[1], ga->cc[2]), ua = mk(ga->cu[0], ga->cu[1], ga->cu[2]);
+            const V3 cb = apply(rel, mk(gb->cc[0], gb->cc[1], gb->cc[2])), ub = rot(rel, mk(gb->cu[0], gb->cu[1], gb->cu[2]));
+#pragma unroll 1
+            for (int k = 0; k < 2 && verdict == 0; ++k) {
+              const float sa = k ? ga->s_in : ga->s_out, sb = k ? gb->s_in : gb->s_out;
+              const float rs = k ? ga->r_in + gb->r_in : ga->r_out + gb->r_out;
+              const float dd = seg_seg_dist(ca - ua * sa, ua * (2.f * sa), cb - ub * sb, ub * (2.f * sb));
+              if (k == 0 && dd > rs + 1e-5f) verdict = 1;
+              if (k == 1 && dd < rs - 1e-5f) verdict = 2;
+            }
+          }
+          if (verdict == 2) record_hit(w, c, p, want_mask);
+          if (verdict == 0) {
+            const bool ov = obb_overlap(ha, hb, rel, bb ? 0.f : 1e-5f);
+            if (ov && bb) record_hit(w, c, p, want_mask);
+            to_gjk = ov && !bb;
+          }
         } else if (closed_form_hit(pr.cls, ga, gb, rel)) {
           record_hit(w, c, p, want_mask);
         }
       }
       __syncwarp();  // all lanes have read their item before the in-place compaction writes
+      if (gq.items != nullptr) {
+        // reserve slots of the global queue for this group's survivors (one atomic per group)
+        const unsigned gb_ = __ballot_sync(FULL, to_gjk);
+        if (gb_) {
+          uint32_t base_slot = 0;
+          if (l == __ffs(gb_) - 1) base_slot = atomicAdd(gq.count, static_cast<uint32_t>(__popc(gb_)));
+          base_slot = __shfl_sync(FULL, base_slot, __ffs(gb_) - 1);
+          const uint32_t slot = base_slot + __popc(gb_ & ((1u << l) - 1));
+          if (to_gjk && slot < gq.capacity) {
+            const int c = item & 31, p = chunk + (item >> 5);
+            const DPair pr = w.t.pairs[p];
+            const Xf rel = xf_inv_mul(geom_xf(w, w.t.geoms[pr.a].gslot, c), geom_xf(w, w.t.geoms[pr.b].gslot, c));
+            float4* dst = reinterpret_cast<float4*>(gq.items + slot);
+            dst[0] = make_float4(rel.m[0], rel.m[1], rel.m[2], rel.m[3]);
+            dst[1] = make_float4(rel.m[4], rel.m[5], rel.m[6], rel.m[7]);
+            dst[2] = make_float4(rel.m[8], rel.m[9], rel.m[10], rel.m[11]);
+            dst[3] = make_float4(__uint_as_float(row_base + c), __uint_as_float(static_cast<uint32_t>(p)), 0.f, 0.f);
+            to_gjk = false;  // queued; anything past the capacity stays for the in-kernel loop
+          }
+        }
+      }
       const unsigned b = __ballot_sync(FULL, to_gjk);
       if (to_gjk) w.queue[gn + __popc(b & ((1u << l) - 1))] = static_cast<uint16_t>(item);
       gn += __popc(b);
@@ -378,7 +435,7 @@ __device__ __forceinline__ void narrow_phase(const Warp& w, bool stop_at_first, 
     // ---- stage 3: GJK.  Each lane owns one work item and advances it one iteration per
     // trip; lanes whose item finished fetch the next one from the queue, so lanes stay busy
     // although iteration counts differ per item.
-    {
+    if (gn > 0) {
       int next = 0, c = 0, p = 0;
       bool active = false;
       GjkLane g;
@@ -440,6 +497,7 @@ struct CheckArgs {
   uint8_t* hit;
   int32_t* first_pair;
   uint32_t* pair_mask;
+  GjkQueue gq;
   SlabLayout L;
 };
 
@@ -457,7 +515,8 @@ __global__ void __launch_bounds__(512, 1) check_kernel(const __grid_constant__ C
   const bool actuated = a.flags & RAMP_Q_ACTUATED;
   const bool want_mask = a.pair_mask != nullptr;
   const bool stop = !(a.flags & RAMP_ALL_PAIRS) && !want_mask;
-  const int cols = actuated ? t.h->n_act : t.h->nq;
+  int cols = actuated ? t.h->n_act : t.h->nq;
+  if ((a.ld & 3) == 0 && a.ld <= cols + 3) cols = a.ld;  // padded rows: take the float4 path
   const int64_t ntiles = (a.n + 31) >> 5;
   for (int64_t tile = static_cast<int64_t>(blockIdx.x) * nwarps + wid; tile < ntiles;
        tile += static_cast<int64_t>(gridDim.x) * nwarps) {
@@ -467,7 +526,7 @@ __global__ void __launch_bounds__(512, 1) check_kernel(const __grid_constant__ C
     reset_results(w, want_mask ? t.h->mask_words : 0);
     fk_lane<0>(w);
     __syncwarp();
-    narrow_phase(w, stop, want_mask);
+    narrow_phase(w, stop, want_mask, a.gq, static_cast<uint32_t>(row0));
     const int64_t row = row0 + w.lane;
     if (row < a.n) {
       const int f = w.first[w.lane];
@@ -477,6 +536,90 @@ __global__ void __launch_bounds__(512, 1) check_kernel(const __grid_constant__ C
         for (int k = 0; k < t.h->mask_words; ++k) a.pair_mask[row * t.h->mask_words + k] = w.mask[k * 32 + w.lane];
     }
     __syncwarp();
+  }
+}
+
+
+// ------------------------------------------------------------- kernel: GJK work queue
+// Drains the queue the validity kernel filled.  Only the tables live in shared memory, so many
+// more warps are resident than in the validity kernel; every lane owns one item and advances
+// it one GJK iteration per trip, fetching the next item of its warp's share when it finishes.
+struct GjkQueueArgs {
+  const unsigned char* img;
+  int32_t table_bytes;
+  const GjkItem* items;
+  const uint32_t* count;
+  uint32_t capacity;
+  uint8_t* hit;
+  int32_t* first_pair;
+  uint32_t* pair_mask;
+  int32_t mask_words;
+  int32_t stop;  // early-out semantics: a configuration already hit by an earlier pair is skipped
+};
+
+constexpr int kQueueChunk = 64;  // consecutive items owned by one warp
+
+__global__ void __launch_bounds__(256, 2) gjk_queue_kernel(const __grid_constant__ GjkQueueArgs a) {
+  uint64_t* mbar = reinterpret_cast<uint64_t*>(g_smem);
+  unsigned char* tbl = g_smem + 16;
+  stage_tables(tbl, a.img, a.table_bytes, mbar);
+  const Tables t = make_tables(tbl);
+  const uint32_t total = min(*a.count, a.capacity);
+  const uint64_t W = static_cast<uint64_t>(gridDim.x) * (blockDim.x >> 5);
+  const uint64_t wg = static_cast<uint64_t>(blockIdx.x) * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  const int l = threadIdx.x & 31;
+  const unsigned FULL = 0xffffffffu;
+  uint32_t next = 0, row = 0, p = 0;
+  bool active = false;
+  GjkLane g;
+  GjkShape A, B;
+  A.type = B.type = 0; A.vcnt = B.vcnt = 0; A.p0 = A.p1 = A.p2 = B.p0 = B.p1 = B.p2 = 0.f; A.verts = B.verts = t.verts;
+  g.s.n = 0; g.it = 0; g.vv = 1.f; g.rsum = 0.f; g.lower = 0.f; g.v = mk(1.f, 0.f, 0.f); g.rel = xf_identity();
+  auto global_index = [&](uint32_t i) { return (wg + static_cast<uint64_t>(i / kQueueChunk) * W) * kQueueChunk + (i % kQueueChunk); };
+  while (true) {
+    const unsigned need = __ballot_sync(FULL, !active);
+    if (!active) {
+      const uint64_t gi = global_index(next + __popc(need & ((1u << l) - 1)));
+      if (gi < total) {
+        const float4* src = reinterpret_cast<const float4*>(a.items + gi);
+        const float4 r0 = __ldcs(src), r1 = __ldcs(src + 1), r2 = __ldcs(src + 2), r3 = __ldcs(src + 3);
+        row = __float_as_uint(r3.x);
+        p = __float_as_uint(r3.y);
+        bool skip = false;
+        if (a.stop) skip = a.first_pair ? static_cast<uint32_t>(a.first_pair[row]) < p : a.hit[row] != 0;
+        if (!skip) {
+          const DPair pr = t.pairs[p];
+          const DGeom* ga = &t.geoms[pr.a];
+          const DGeom* gb = &t.geoms[pr.b];
+          A = load_shape(ga, t.verts);
+          B = load_shape(gb, t.verts);
+          Xf rel;
+          rel.m[0] = r0.x; rel.m[1] = r0.y; rel.m[2] = r0.z; rel.m[3] = r0.w;
+          rel.m[4] = r1.x; rel.m[5] = r1.y; rel.m[6] = r1.z; rel.m[7] = r1.w;
+          rel.m[8] = r2.x; rel.m[9] = r2.y; rel.m[10] = r2.z; rel.m[11] = r2.w;
+          gjk_init(g, rel, swept_radius(ga) + swept_radius(gb));
+          active = true;
+        }
+      }
+    }
+    next += __popc(need);
+    if (!__any_sync(FULL, active)) {
+      if (global_index(next) >= total) break;
+      continue;
+    }
+    if (active) {
+      float dist;
+      const int st = gjk_step(g, A, B, false, dist);
+      if (st != GJK_CONTINUE) {
+        if (st == GJK_HIT) {
+          a.hit[row] = 1;
+          // -1 ("none") is the largest unsigned value, so an unsigned min keeps list order
+          if (a.first_pair) atomicMin(reinterpret_cast<uint32_t*>(a.first_pair) + row, p);
+          if (a.pair_mask) atomicOr(a.pair_mask + static_cast<size_t>(row) * a.mask_words + (p >> 5), 1u << (p & 31));
+        }
+        active = false;
+      }
+    }
   }
 }
 
@@ -502,7 +645,8 @@ __global__ void __launch_bounds__(512, 1) fk_kernel(const __grid_constant__ FkAr
   float* slab = reinterpret_cast<float*>(tbl + a.L.table_bytes) + static_cast<size_t>(wid) * a.L.words;
   const Warp w = make_warp(t, slab, a.L);
   const bool actuated = a.flags & RAMP_Q_ACTUATED;
-  const int cols = actuated ? t.h->n_act : t.h->nq;
+  int cols = actuated ? t.h->n_act : t.h->nq;
+  if ((a.ld & 3) == 0 && a.ld <= cols + 3) cols = a.ld;  // padded rows: take the float4 path
   const int64_t ntiles = (a.n + 31) >> 5;
   for (int64_t tile = static_cast<int64_t>(blockIdx.x) * nwarps + wid; tile < ntiles;
        tile += static_cast<int64_t>(gridDim.x) * nwarps) {
@@ -701,7 +845,7 @@ __global__ void __launch_bounds__(512, 1) edge_check_kernel(const __grid_constan
     reset_results(w, 0);
     fk_lane<0>(w);
     __syncwarp();
-    narrow_phase(w, true, false);
+    narrow_phase(w, true, false, GjkQueue{nullptr, nullptr, 0u}, 0u);
     const bool invalid = w.first[l] != INT32_MAX || (a.sp.check_bounds && !in_bounds);
     if (!skip && invalid) atomicMin(&a.first_invalid[e], min(j, nd));
     __syncwarp();
@@ -761,6 +905,8 @@ struct RampModel {
   unsigned char* d_image = nullptr;
   size_t d_image_cap = 0;
   ramp::ImgHeader hdr{};
+  int n_gjk_pairs = 0;            // active pairs of the GJK class
+  cudaMemPool_t pool = nullptr;   // stream-ordered scratch for the GJK work queue
   // scratch for ramp_check_edges (offsets, nd, first_invalid) and ramp_check_host staging
   mutable std::mutex mu;
   mutable void* d_scratch = nullptr;
@@ -793,6 +939,114 @@ static void mat_mul34(const double* a, const double* b, double* o) {
     r[4 * i + 3] = a[4 * i] * b[3] + a[4 * i + 1] * b[7] + a[4 * i + 2] * b[11] + a[4 * i + 3];
   }
   std::memcpy(o, r, sizeof r);
+}
+
+
+// ---- bounding / inscribed capsules of a vertex set (model-build time, FP64)
+static double seg_point_dist(const double* a, const double* b, const double* p) {
+  double ab[3] = {b[0] - a[0], b[1] - a[1], b[2] - a[2]}, ap[3] = {p[0] - a[0], p[1] - a[1], p[2] - a[2]};
+  const double den = ab[0] * ab[0] + ab[1] * ab[1] + ab[2] * ab[2];
+  double t = den > 0 ? (ap[0] * ab[0] + ap[1] * ab[1] + ap[2] * ab[2]) / den : 0.0;
+  t = std::min(1.0, std::max(0.0, t));
+  const double d[3] = {ap[0] - t * ab[0], ap[1] - t * ab[1], ap[2] - t * ab[2]};
+  return std::sqrt(d[0] * d[0] + d[1] * d[1] + d[2] * d[2]);
+}
+
+// principal axis of a point cloud (power iteration on the covariance)
+static void principal_axis(const std::vector<double>& v, const double* c, double* u) {
+  double C[3][3] = {{0}};
+  for (size_t i = 0; i < v.size(); i += 3)
+    for (int a = 0; a < 3; ++a)
+      for (int b = 0; b < 3; ++b) C[a][b] += (v[i + a] - c[a]) * (v[i + b] - c[b]);
+  double best = -1;
+  for (int start = 0; start < 3; ++start) {  // three starts: robust against an orthogonal seed
+    double x[3] = {start == 0 ? 1.0 : 0.1, start == 1 ? 1.0 : 0.1, start == 2 ? 1.0 : 0.1};
+    double lam = 0;
+    for (int it = 0; it < 200; ++it) {
+      double y[3];
+      for (int a = 0; a < 3; ++a) y[a] = C[a][0] * x[0] + C[a][1] * x[1] + C[a][2] * x[2];
+      lam = std::sqrt(y[0] * y[0] + y[1] * y[1] + y[2] * y[2]);
+      if (lam < 1e-300) break;
+      for (int a = 0; a < 3; ++a) x[a] = y[a] / lam;
+    }
+    if (lam > best) { best = lam; u[0] = x[0]; u[1] = x[1]; u[2] = x[2]; }
+  }
+  if (best <= 0) { u[0] = 0; u[1] = 0; u[2] = 1; }
+}
+
+struct CapsuleFit {
+  double c[3], u[3], s_out, r_out, s_in, r_in;
+};
+
+// Outer capsule: smallest-volume capsule on the principal axis that contains every vertex.
+// Inner capsule: largest-volume capsule on the same axis inside every facet plane of the
+// hull; facets are enumerated by brute force (V^4/6, fine for V <= 160 at build time).
+static CapsuleFit fit_capsules(const std::vector<double>& v) {
+  CapsuleFit f{};
+  const int n = static_cast<int>(v.size() / 3);
+  double c[3] = {0, 0, 0};
+  for (int i = 0; i < n; ++i) for (int k = 0; k < 3; ++k) c[k] += v[3 * i + k] / n;
+  double u[3];
+  principal_axis(v, c, u);
+  double tmin = 1e300, tmax = -1e300, rho = 0;
+  for (int i = 0; i < n; ++i) {
+    const double d[3] = {v[3 * i] - c[0], v[3 * i + 1] - c[1], v[3 * i + 2] - c[2]};
+    const double t = d[0] * u[0] + d[1] * u[1] + d[2] * u[2];
+    const double r[3] = {d[0] - t * u[0], d[1] - t * u[1], d[2] - t * u[2]};
+    tmin = std::min(tmin, t); tmax = std::max(tmax, t);
+    rho = std::max(rho, std::sqrt(r[0] * r[0] + r[1] * r[1] + r[2] * r[2]));
+  }
+  const double mid = 0.5 * (tmin + tmax);
+  for (int k = 0; k < 3; ++k) { f.c[k] = c[k] + mid * u[k]; f.u[k] = u[k]; }
+  // facet planes n.x <= d
+  std::vector<double> planes;
+  if (n <= 160) {
+    for (int i = 0; i < n; ++i) for (int j = i + 1; j < n; ++j) for (int k = j + 1; k < n; ++k) {
+      const double* a = &v[3 * i]; const double* b = &v[3 * j]; const double* cc = &v[3 * k];
+      const double e1[3] = {b[0] - a[0], b[1] - a[1], b[2] - a[2]}, e2[3] = {cc[0] - a[0], cc[1] - a[1], cc[2] - a[2]};
+      double nn[3] = {e1[1] * e2[2] - e1[2] * e2[1], e1[2] * e2[0] - e1[0] * e2[2], e1[0] * e2[1] - e1[1] * e2[0]};
+      const double l = std::sqrt(nn[0] * nn[0] + nn[1] * nn[1] + nn[2] * nn[2]);
+      if (l < 1e-14) continue;
+      for (double& x : nn) x /= l;
+      const double d0 = nn[0] * a[0] + nn[1] * a[1] + nn[2] * a[2];
+      bool pos = true, neg = true;
+      for (int m = 0; m < n && (pos || neg); ++m) {
+        const double dd = nn[0] * v[3 * m] + nn[1] * v[3 * m + 1] + nn[2] * v[3 * m + 2] - d0;
+        if (dd > 1e-10) neg = false;
+        if (dd < -1e-10) pos = false;
+      }
+      if (neg) { planes.insert(planes.end(), {nn[0], nn[1], nn[2], d0}); }
+      else if (pos) { planes.insert(planes.end(), {-nn[0], -nn[1], -nn[2], -d0}); }
+    }
+  }
+  const double half = 0.5 * (tmax - tmin);
+  double best_out = 1e300, best_in = -1;
+  f.s_out = 0; f.r_out = 0; f.s_in = 0; f.r_in = 0;
+  for (int step = 0; step <= 40; ++step) {
+    const double s = half * step / 40.0;  // candidate half length of the segment
+    const double a[3] = {f.c[0] - s * u[0], f.c[1] - s * u[1], f.c[2] - s * u[2]};
+    const double b[3] = {f.c[0] + s * u[0], f.c[1] + s * u[1], f.c[2] + s * u[2]};
+    double R = 0;
+    for (int i = 0; i < n; ++i) R = std::max(R, seg_point_dist(a, b, &v[3 * i]));
+    const double vol_out = M_PI * R * R * 2 * s + 4.0 / 3.0 * M_PI * R * R * R;
+    if (vol_out < best_out) { best_out = vol_out; f.s_out = s; f.r_out = R; }
+    if (!planes.empty()) {
+      double r = 1e300;
+      for (size_t k = 0; k < planes.size(); k += 4) {
+        const double da = planes[k + 3] - (planes[k] * a[0] + planes[k + 1] * a[1] + planes[k + 2] * a[2]);
+        const double db = planes[k + 3] - (planes[k] * b[0] + planes[k + 1] * b[1] + planes[k + 2] * b[2]);
+        r = std::min(r, std::min(da, db));
+      }
+      if (r > 0) {
+        const double vol_in = M_PI * r * r * 2 * s + 4.0 / 3.0 * M_PI * r * r * r;
+        if (vol_in > best_in) { best_in = vol_in; f.s_in = s; f.r_in = r; }
+      }
+    }
+  }
+  // FP32 safety: outer grows, inner shrinks by a relative hair
+  f.r_out *= 1.0 + 1e-6;
+  f.r_in = std::max(0.0, f.r_in * (1.0 - 1e-5) - 1e-7);
+  return f;
 }
 
 // Pack the host description into the device image.  Convex hulls are re-centred on the
@@ -877,6 +1131,29 @@ static int build_image(RampModel* m) {
         mat_mul34(src.placement, shift, pl);
       } break;
     }
+    {  // capsules for the mid-phase of the GJK class (DGeom::cc ... r_in)
+      CapsuleFit f{};
+      f.u[2] = 1.0;
+      const double* P = src.params;
+      switch (src.type) {
+        case RAMP_SHAPE_SPHERE: f.r_out = f.r_in = P[0]; break;
+        case RAMP_SHAPE_CAPSULE: f.s_out = f.s_in = P[1]; f.r_out = f.r_in = P[0]; break;
+        case RAMP_SHAPE_BOX: {
+          const int L = (P[0] >= P[1] && P[0] >= P[2]) ? 0 : (P[1] >= P[2] ? 1 : 2), a = (L + 1) % 3, b = (L + 2) % 3;
+          f.u[2] = 0; f.u[L] = 1.0;
+          f.s_out = P[L]; f.r_out = std::sqrt(P[a] * P[a] + P[b] * P[b]);
+          f.r_in = std::min(P[a], P[b]); f.s_in = P[L] - f.r_in;
+        } break;
+        case RAMP_SHAPE_CYLINDER:
+          f.s_out = P[1]; f.r_out = P[0]; f.r_in = std::min(P[0], P[1]); f.s_in = std::max(0.0, P[1] - P[0]); break;
+        case RAMP_SHAPE_ELLIPSOID:
+          f.r_out = std::max(P[0], std::max(P[1], P[2])); f.r_in = std::min(P[0], std::min(P[1], P[2])); break;
+        default: f = fit_capsules(core); break;
+      }
+      for (int k = 0; k < 3; ++k) { d.cc[k] = static_cast<float>(f.c[k]); d.cu[k] = static_cast<float>(f.u[k]); }
+      d.s_out = static_cast<float>(f.s_out); d.r_out = static_cast<float>(f.r_out);
+      d.s_in = static_cast<float>(f.s_in); d.r_in = static_cast<float>(f.r_in);
+    }
     // polytope cores as vertex lists: sphere = its centre, capsule = the segment ends,
     // box = the 8 corners (device_math.cuh support())
     if (src.type == RAMP_SHAPE_SPHERE) core = {0, 0, 0};
@@ -915,6 +1192,7 @@ static int build_image(RampModel* m) {
   // pairs
   std::vector<DPair> dp(std::max(np, 1));
   m->pair_active.resize(np, 1);
+  int n_gjk = 0;
   for (int p = 0; p < np; ++p) {
     const int32_t* pr = p < n_rp ? &m->robot_pairs[2 * p] : &m->scene_pairs[2 * (p - n_rp)];
     int a = pr[0], b = pr[1];
@@ -923,6 +1201,7 @@ static int build_image(RampModel* m) {
     DPair& d = dp[p];
     d.a = a; d.b = b;
     d.cls = m->pair_active[p] ? pair_class(dg[a].type, dg[b].type) : kClsInactive;
+    n_gjk += d.cls == kClsGjk;
     const double rs = static_cast<double>(dg[a].bound_r) + dg[b].bound_r;
     // the sphere-sphere test is the decision itself; every other class uses it as a cull
     d.rs2 = static_cast<float>(d.cls == kClsSphereSphere ? rs * rs : rs * rs * (1.0 + 1e-5) + 1e-9);
@@ -970,6 +1249,7 @@ static int build_image(RampModel* m) {
   put(h.off_cont, m->cont_slot.data(), m->cont_slot.size() * sizeof(int32_t));
   put(h.off_refq, refq.data(), refq.size() * sizeof(float));
   m->hdr = h;
+  m->n_gjk_pairs = n_gjk;
 
   CUDA_TRY(cudaSetDevice(m->device));
   if (off > m->d_image_cap) {
@@ -987,12 +1267,13 @@ static int build_image(RampModel* m) {
 
 // Shared-memory plan: tables + as many warp slabs as fit (<= 16 warps).
 static int plan_slabs(const RampModel* m, int stage_row_floats, int act_cols, SlabLayout* L, int* nwarps,
-                      size_t* smem_bytes) {
+                      size_t* smem_bytes, int ld = 0) {
   const ImgHeader& h = m->hdr;
   int w = 0;
   auto take = [&](int words) { const int o = w; w += (words + 3) & ~3; return o; };
-  L->off_q = take(std::max(h.nq, 1) * 32);
-  L->off_act = take(std::max(act_cols, 1) * 32);
+  // up to 3 padding columns of the input rows are loaded too, so whole rows move as float4
+  L->off_q = take(std::max(std::max(h.nq, ld <= h.nq + 3 ? ld : 0), 1) * 32);
+  L->off_act = take(std::max(std::max(act_cols, ld <= act_cols + 3 ? ld : 0), 1) * 32);
   L->off_geom = take(std::max(h.n_dyn, 1) * 12 * 32);
   L->off_save = take(std::max(h.n_save, 1) * 12 * 32);
   L->off_queue = take(kQueueCap / 2);
@@ -1033,17 +1314,58 @@ static int check_q_args(const RampModel* m, const void* d_q, int64_t n, int32_t 
   return RAMP_OK;
 }
 
+// Rows are processed in slices so the GJK work queue has a bounded size.
+constexpr int64_t kSliceRows = 1 << 21;
+constexpr int64_t kQueueItemsPerRow = 2;   // capacity; overflow is handled inside check_kernel
+constexpr int64_t kQueueMinRows = 1024;    // below this a second launch costs more than it saves
+
 static int launch_check(const RampModel* m, const float* d_q, int64_t n, int32_t ld, uint32_t flags, uint8_t* d_hit,
                         int32_t* d_first, uint32_t* d_mask, cudaStream_t st) {
   CheckArgs a;
-  a.img = m->d_image; a.q = d_q; a.n = n; a.ld = ld; a.flags = flags;
-  a.hit = d_hit; a.first_pair = d_first; a.pair_mask = d_mask;
+  a.img = m->d_image; a.ld = ld; a.flags = flags;
   int nwarps; size_t smem;
-  if (int rc = plan_slabs(m, 0, m->hdr.n_act, &a.L, &nwarps, &smem)) return rc;
+  if (int rc = plan_slabs(m, 0, m->hdr.n_act, &a.L, &nwarps, &smem, ld)) return rc;
   if (int rc = set_smem(check_kernel, smem)) return rc;
-  const int grid = grid_for(m, (n + 31) / 32, nwarps);
-  check_kernel<<<grid, nwarps * 32, smem, st>>>(a);
-  g_launches.fetch_add(1, std::memory_order_relaxed);
+  const bool use_queue = m->pool != nullptr && m->n_gjk_pairs > 0 && n >= kQueueMinRows;
+  unsigned char* scratch = nullptr;
+  uint32_t cap_items = 0;
+  GjkQueueArgs b{};
+  size_t smem_b = 0;
+  if (use_queue) {
+    cap_items = static_cast<uint32_t>(std::min<int64_t>(n, kSliceRows) * kQueueItemsPerRow + 4096);
+    const size_t bytes = 256 + static_cast<size_t>(cap_items) * sizeof(GjkItem);
+    if (cudaMallocFromPoolAsync(reinterpret_cast<void**>(&scratch), bytes, m->pool, st) != cudaSuccess) {
+      cudaGetLastError();
+      return fail(RAMP_ERR_ALLOC, "cudaMallocFromPoolAsync(%zu) for the GJK queue failed", bytes);
+    }
+    smem_b = 16 + a.L.table_bytes;
+    if (int rc = set_smem(gjk_queue_kernel, smem_b)) return rc;
+    b.img = m->d_image; b.table_bytes = a.L.table_bytes;
+    b.items = reinterpret_cast<GjkItem*>(scratch + 256); b.count = reinterpret_cast<uint32_t*>(scratch);
+    b.capacity = cap_items; b.mask_words = m->hdr.mask_words;
+    b.stop = !(flags & RAMP_ALL_PAIRS) && d_mask == nullptr;
+  }
+  const int64_t step = use_queue ? kSliceRows : n;
+  for (int64_t off = 0; off < n; off += step) {
+    const int64_t ns = std::min(step, n - off);
+    a.q = d_q + off * ld; a.n = ns;
+    a.hit = d_hit + off;
+    a.first_pair = d_first ? d_first + off : nullptr;
+    a.pair_mask = d_mask ? d_mask + off * m->hdr.mask_words : nullptr;
+    a.gq = GjkQueue{nullptr, nullptr, 0u};
+    if (use_queue) {
+      CUDA_TRY(cudaMemsetAsync(scratch, 0, 16, st));
+      a.gq = GjkQueue{reinterpret_cast<GjkItem*>(scratch + 256), reinterpret_cast<uint32_t*>(scratch), cap_items};
+    }
+    check_kernel<<<grid_for(m, (ns + 31) / 32, nwarps), nwarps * 32, smem, st>>>(a);
+    g_launches.fetch_add(1, std::memory_order_relaxed);
+    if (use_queue) {
+      b.hit = a.hit; b.first_pair = a.first_pair; b.pair_mask = a.pair_mask;
+      gjk_queue_kernel<<<m->sm_count * 2, 256, smem_b, st>>>(b);
+      g_launches.fetch_add(1, std::memory_order_relaxed);
+    }
+  }
+  if (scratch) CUDA_TRY(cudaFreeAsync(scratch, st));
   CUDA_TRY(cudaGetLastError());
   return RAMP_OK;
 }
@@ -1084,6 +1406,21 @@ int ramp_model_create(const RampModelDesc* d, int device, RampModel** out) {
   if (cudaGetDeviceProperties(&prop, device) != cudaSuccess) { delete m; return fail(RAMP_ERR_CUDA, "cudaGetDeviceProperties failed"); }
   m->sm_count = prop.multiProcessorCount;
   m->max_smem = static_cast<int>(prop.sharedMemPerBlockOptin);
+  {  // a private stream-ordered pool that keeps its memory between calls
+    cudaMemPoolProps pp{};
+    pp.allocType = cudaMemAllocationTypePinned;
+    pp.handleTypes = cudaMemHandleTypeNone;
+    pp.location.type = cudaMemLocationTypeDevice;
+    pp.location.id = device;
+    cudaSetDevice(device);
+    if (cudaMemPoolCreate(&m->pool, &pp) == cudaSuccess) {
+      uint64_t keep = UINT64_MAX;
+      cudaMemPoolSetAttribute(m->pool, cudaMemPoolAttrReleaseThreshold, &keep);
+    } else {
+      cudaGetLastError();
+      m->pool = nullptr;  // no pool: GJK stays inside the validity kernel
+    }
+  }
   m->nq = d->nq;
   m->joints.assign(d->joints, d->joints + d->n_joints);
   m->robot_geoms.assign(d->geoms, d->geoms + d->n_geoms);
@@ -1139,8 +1476,10 @@ int ramp_model_set_pair_active(RampModel* m, int32_t p, int32_t active) {
 void ramp_model_destroy(RampModel* m) {
   if (!m) return;
   cudaSetDevice(m->device);
+  cudaDeviceSynchronize();
   if (m->d_image) cudaFree(m->d_image);
   if (m->d_scratch) cudaFree(m->d_scratch);
+  if (m->pool) cudaMemPoolDestroy(m->pool);
   if (m->h_pinned) cudaFreeHost(m->h_pinned);
   delete m;
 }
@@ -1163,7 +1502,7 @@ static int fk_common(const RampModel* m, const float* d_q, int64_t n, int32_t ld
   a.row_floats = 12 * (what == 1 ? m->hdr.n_joints : m->hdr.n_geoms);
   if (a.row_floats == 0) return RAMP_OK;
   int nwarps; size_t smem;
-  if (int rc = plan_slabs(m, a.row_floats, m->hdr.n_act, &a.L, &nwarps, &smem)) return rc;
+  if (int rc = plan_slabs(m, a.row_floats, m->hdr.n_act, &a.L, &nwarps, &smem, ld)) return rc;
   const int grid = grid_for(m, (n + 31) / 32, nwarps);
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   if (what == 1) {

@@ -106,3 +106,132 @@ def sample_uniform(space: D.SpaceDesc, n: int, rng: np.random.Generator, positio
             v = rng.normal(size=(n, 4))
             out[:, c + o : c + o + 4] = v / np.linalg.norm(v, axis=1, keepdims=True)
     return out
+
+
+# ----------------------------------------------------------------------------------------
+# Host-side (numpy, FP64) statement of the OMPL state-space maths the planner loop needs
+# between validator calls: distance, interpolation, bounds.  The batched
+# validator itself runs these in FP32 on the device (csrc/ramp_b200.cu edge kernels).
+def _so2_dist(a: float, b: float) -> float:
+    d = abs(a - b)
+    return 2 * np.pi - d if d > np.pi else d
+
+
+def _so2_interp(a: float, b: float, t: float) -> float:
+    diff = b - a
+    if abs(diff) <= np.pi:
+        return a + diff * t
+    diff = 2 * np.pi - diff if diff > 0 else -2 * np.pi - diff
+    v = a - diff * t
+    if v > np.pi:
+        v -= 2 * np.pi
+    elif v < -np.pi:
+        v += 2 * np.pi
+    return v
+
+
+def _so3_arc(a, b) -> float:
+    dq = abs(float(np.dot(a, b)))
+    return 0.0 if dq > 1.0 - 1e-9 else float(np.arccos(dq))
+
+
+def _so3_slerp(a, b, t: float):
+    th = _so3_arc(a, b)
+    if th <= np.finfo(float).eps:
+        return np.array(a, dtype=np.float64)
+    s0, s1 = np.sin((1 - t) * th), np.sin(t * th)
+    if np.dot(a, b) < 0:
+        s1 = -s1
+    return (np.asarray(a) * s0 + np.asarray(b) * s1) / np.sin(th)
+
+
+def _parts(s):
+    """(n_real, rotation kind, rotation offset) of a subspace."""
+    t = s["type"]
+    if t == D.SPACE_REAL:
+        return s["dim"], None, 0
+    if t == D.SPACE_SO2:
+        return 0, "so2", 0
+    if t == D.SPACE_SE2:
+        return 2, "so2", 2
+    if t == D.SPACE_SE3:
+        return 3, "so3", 3
+    return 0, "so3", 0
+
+
+def distance(space: D.SpaceDesc, a, b) -> float:
+    """CompoundStateSpace::distance with RAMP's weights (1 per joint subspace; SE2 = R2 + 0.5 SO2,
+    SE3 = R3 + SO3)."""
+    a, b = np.asarray(a, dtype=np.float64), np.asarray(b, dtype=np.float64)
+    total = 0.0
+    for s in space.subspaces:
+        c = s["col"]
+        nreal, rot, off = _parts(s)
+        if nreal:
+            total += float(np.linalg.norm(a[c : c + nreal] - b[c : c + nreal]))
+        if rot == "so2":
+            total += (0.5 if s["type"] == D.SPACE_SE2 else 1.0) * _so2_dist(a[c + off], b[c + off])
+        elif rot == "so3":
+            total += _so3_arc(a[c + off : c + off + 4], b[c + off : c + off + 4])
+    return total
+
+
+def interpolate(space: D.SpaceDesc, a, b, t: float) -> np.ndarray:
+    a, b = np.asarray(a, dtype=np.float64), np.asarray(b, dtype=np.float64)
+    out = np.array(a, dtype=np.float64)
+    for s in space.subspaces:
+        c = s["col"]
+        nreal, rot, off = _parts(s)
+        out[c : c + nreal] = a[c : c + nreal] + (b[c : c + nreal] - a[c : c + nreal]) * t
+        if rot == "so2":
+            out[c + off] = _so2_interp(a[c + off], b[c + off], t)
+        elif rot == "so3":
+            out[c + off : c + off + 4] = _so3_slerp(a[c + off : c + off + 4], b[c + off : c + off + 4], t)
+    return out
+
+
+def valid_segment_count(space: D.SpaceDesc, a, b) -> int:
+    """max over (sub)components of ceil(distance / (fraction * extent))."""
+    a, b = np.asarray(a, dtype=np.float64), np.asarray(b, dtype=np.float64)
+    f = space.struct.longest_valid_segment_fraction
+    nd = 0
+    for s in space.subspaces:
+        c = s["col"]
+        nreal, rot, off = _parts(s)
+        if nreal:
+            ext = float(np.linalg.norm(np.asarray(s["hi"][:nreal]) - np.asarray(s["lo"][:nreal])))
+            if ext > 0 and np.isfinite(ext):
+                nd = max(nd, int(np.ceil(np.linalg.norm(a[c : c + nreal] - b[c : c + nreal]) / (f * ext))))
+        if rot == "so2":
+            nd = max(nd, int(np.ceil(_so2_dist(a[c + off], b[c + off]) / (f * np.pi))))
+        elif rot == "so3":
+            nd = max(nd, int(np.ceil(_so3_arc(a[c + off : c + off + 4], b[c + off : c + off + 4]) / (f * 0.5 * np.pi))))
+    return nd
+
+
+def satisfies_bounds(space: D.SpaceDesc, a) -> bool:
+    a = np.asarray(a, dtype=np.float64)
+    eps = np.finfo(float).eps
+    for s in space.subspaces:
+        c = s["col"]
+        nreal, rot, off = _parts(s)
+        for k in range(nreal):
+            if a[c + k] - eps > s["hi"][k] or a[c + k] + eps < s["lo"][k]:
+                return False
+        if rot == "so2" and not (-np.pi - eps <= a[c + off] <= np.pi + eps):
+            return False
+    return True
+
+
+def maximum_extent(space: D.SpaceDesc) -> float:
+    ext = 0.0
+    for s in space.subspaces:
+        nreal, rot, _ = _parts(s)
+        if nreal:
+            e = float(np.linalg.norm(np.asarray(s["hi"][:nreal]) - np.asarray(s["lo"][:nreal])))
+            ext += e if np.isfinite(e) else 0.0
+        if rot == "so2":
+            ext += (0.5 if s["type"] == D.SPACE_SE2 else 1.0) * np.pi
+        elif rot == "so3":
+            ext += 0.5 * np.pi
+    return ext
