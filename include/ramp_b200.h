@@ -228,6 +228,32 @@ int ramp_check_batch(const RampModel* m, const float* d_q, int64_t n, int32_t ld
                      uint32_t flags, uint8_t* d_hit, int32_t* d_first_pair,
                      float* d_min_dist, uint32_t* d_pair_mask, void* stream);
 
+/* The same check for callers that are not allowed to allocate device memory.
+ * It has no counterpart in the reference: it exists because of where this
+ * library gets embedded.  A planner thread inside a real-time control loop
+ * cannot afford cudaMalloc/cudaFree (they may stall on all other work of the
+ * process and take an unpredictable time); a process that split up its device
+ * memory at start-up has none left to give.  ramp_check_batch draws a work
+ * queue from a memory pool; this variant uses a fixed array inside the library
+ * instead and calls no allocating routine.
+ *
+ *   - at most RAMP_NOALLOC_MAX_ROWS configurations per call; larger n is
+ *     refused with RAMP_ERR_LIMIT (split the batch, or use ramp_check_batch);
+ *   - the fixed array (about 4.3 MB) is part of the library image: every GPU
+ *     that loads the library holds it until the process exits;
+ *   - the first call on each device looks up the array's address
+ *     (cudaGetSymbolAddress); make that first call before any stream capture;
+ *   - all calls share the one array, which keeps the previous call's contents
+ *     (the entry point resets the part that must start at zero).  Two calls
+ *     whose kernels overlap on the GPU -- different streams, or different
+ *     models on one device -- race on it: keep them in one stream or
+ *     otherwise ordered;
+ *   - arguments and results are those of ramp_check_batch without d_min_dist. */
+#define RAMP_NOALLOC_MAX_ROWS 32768
+int ramp_check_batch_noalloc(const RampModel* m, const float* d_q, int64_t n, int32_t ld_q,
+                             uint32_t flags, uint8_t* d_hit, int32_t* d_first_pair,
+                             uint32_t* d_pair_mask, void* stream);
+
 /* Signed distance of selected pairs: d_dist[n, n_sel] for pair indices
  * h_pair_idx[n_sel].  Replaces pinocchio.computeDistance,
  * src/ramp/robot_state.py:360-364. */

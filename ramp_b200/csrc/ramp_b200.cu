@@ -1536,6 +1536,81 @@ int ramp_check_batch(const RampModel* m, const float* d_q, int64_t n, int32_t ld
   return launch_check(m, d_q, n, ld, flags, d_hit, d_first_pair, d_pair_mask, static_cast<cudaStream_t>(stream));
 }
 
+// ---- ramp_check_batch_noalloc: the validity check for callers that must not allocate.
+//
+// Some hosts of this library run where device allocation is off limits: a planner thread
+// inside a real-time control loop (cudaMalloc / cudaFree can block on every other stream of
+// the process and their latency is unbounded), or a process whose device memory was carved
+// up once at start-up and has nothing left to hand out.  ramp_check_batch needs a work queue
+// for its GJK items and takes it from a stream-ordered pool; this variant takes the queue
+// from the fixed array below instead and calls no allocating routine at all.
+//
+// The array lives in the library image: every GPU that loads libramp_b200.so carries these
+// kNoAllocQueueBytes (about 4.3 MB) until the process exits, whether or not the entry point
+// is ever used.  That is why the limit is modest.
+constexpr int64_t kNoAllocMaxRows = RAMP_NOALLOC_MAX_ROWS;
+constexpr uint32_t kNoAllocQueueItems = static_cast<uint32_t>(kNoAllocMaxRows * kQueueItemsPerRow + 4096);
+constexpr size_t kNoAllocQueueBytes = 256 + static_cast<size_t>(kNoAllocQueueItems) * sizeof(GjkItem);
+static __device__ __align__(256) unsigned char g_noalloc_queue[kNoAllocQueueBytes];
+
+// In host code `g_noalloc_queue` is only a handle for the symbol, not an address a kernel
+// could use: the device address differs per GPU and has to be asked for, once per device,
+// with that device current.
+constexpr int kMaxDevices = 64;
+static unsigned char* g_noalloc_ptr[kMaxDevices] = {};
+static std::mutex g_noalloc_mu;
+
+static int noalloc_queue_for(int device, unsigned char** out) {
+  if (device < 0 || device >= kMaxDevices) return fail(RAMP_ERR_LIMIT, "device %d: only %d devices supported", device, kMaxDevices);
+  std::lock_guard<std::mutex> lk(g_noalloc_mu);
+  if (!g_noalloc_ptr[device]) {
+    CUDA_TRY(cudaSetDevice(device));
+    void* p = nullptr;
+    const cudaError_t e = cudaGetSymbolAddress(&p, g_noalloc_queue);
+    if (e != cudaSuccess || p == nullptr)
+      return fail(RAMP_ERR_CUDA, "cudaGetSymbolAddress(g_noalloc_queue) on device %d: %s", device, cudaGetErrorString(e));
+    g_noalloc_ptr[device] = static_cast<unsigned char*>(p);
+  }
+  *out = g_noalloc_ptr[device];
+  return RAMP_OK;
+}
+
+int ramp_check_batch_noalloc(const RampModel* m, const float* d_q, int64_t n, int32_t ld, uint32_t flags, uint8_t* d_hit,
+                             int32_t* d_first_pair, uint32_t* d_pair_mask, void* stream) {
+  if (int rc = check_q_args(m, d_q, n, ld, flags)) return rc;
+  if (n > kNoAllocMaxRows)
+    return fail(RAMP_ERR_LIMIT, "ramp_check_batch_noalloc: %lld configurations exceed the fixed scratch (max %lld per call); "
+                "split the batch or use ramp_check_batch", static_cast<long long>(n), static_cast<long long>(kNoAllocMaxRows));
+  if (n == 0) return RAMP_OK;
+  if (!d_hit) return fail(RAMP_ERR_INVALID, "null d_hit");
+  CUDA_TRY(cudaSetDevice(m->device));
+  unsigned char* scratch = nullptr;
+  if (int rc = noalloc_queue_for(m->device, &scratch)) return rc;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  CheckArgs a;
+  a.img = m->d_image; a.q = d_q; a.n = n; a.ld = ld; a.flags = flags;
+  a.hit = d_hit; a.first_pair = d_first_pair; a.pair_mask = d_pair_mask;
+  int nwarps; size_t smem;
+  if (int rc = plan_slabs(m, 0, m->hdr.n_act, &a.L, &nwarps, &smem, ld)) return rc;
+  if (int rc = set_smem(check_kernel, smem)) return rc;
+  const size_t smem_b = 16 + a.L.table_bytes;
+  if (int rc = set_smem(gjk_queue_kernel, smem_b)) return rc;
+  // the array still holds the previous call's counter and items: only the counter has to
+  // start from zero, the items below it are rewritten before they are read
+  CUDA_TRY(cudaMemsetAsync(scratch, 0, 16, st));
+  a.gq = GjkQueue{reinterpret_cast<GjkItem*>(scratch + 256), reinterpret_cast<uint32_t*>(scratch), kNoAllocQueueItems};
+  check_kernel<<<grid_for(m, (n + 31) / 32, nwarps), nwarps * 32, smem, st>>>(a);
+  GjkQueueArgs b{};
+  b.img = m->d_image; b.table_bytes = a.L.table_bytes;
+  b.items = a.gq.items; b.count = a.gq.count; b.capacity = kNoAllocQueueItems;
+  b.hit = d_hit; b.first_pair = d_first_pair; b.pair_mask = d_pair_mask; b.mask_words = m->hdr.mask_words;
+  b.stop = !(flags & RAMP_ALL_PAIRS) && d_pair_mask == nullptr;
+  gjk_queue_kernel<<<m->sm_count * 2, 256, smem_b, st>>>(b);
+  g_launches.fetch_add(2, std::memory_order_relaxed);
+  CUDA_TRY(cudaGetLastError());
+  return RAMP_OK;
+}
+
 int ramp_distance_batch(const RampModel*, const float*, int64_t, int32_t, uint32_t, const int32_t*, int32_t, float*, void*) {
   return fail(RAMP_ERR_INVALID, "ramp_distance_batch is not implemented yet");
 }

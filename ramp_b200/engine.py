@@ -49,6 +49,7 @@ def load_library():
         "ramp_fk_batch": (C.c_int, [vp, vp, i64, i32, u32, vp, vp]),
         "ramp_placements_batch": (C.c_int, [vp, vp, i64, i32, u32, vp, vp]),
         "ramp_check_batch": (C.c_int, [vp, vp, i64, i32, u32, vp, vp, vp, vp, vp]),
+        "ramp_check_batch_noalloc": (C.c_int, [vp, vp, i64, i32, u32, vp, vp, vp, vp]),
         "ramp_distance_batch": (C.c_int, [vp, vp, i64, i32, u32, C.POINTER(i32), i32, vp, vp]),
         "ramp_check_edges": (C.c_int, [vp, vp, vp, i64, i32, C.POINTER(D.RampSpaceDesc), vp, vp, vp, vp]),
         "ramp_check_host": (C.c_int, [vp, vp, i64, i32, u32, vp, vp, vp, vp]),
