@@ -233,7 +233,8 @@ def main() -> None:
     kernel_ms = statistics.mean(kt)
 
     # end to end: the C-ABI host-buffer call (ramp_check_host): H2D of q, kernel, D2H of flags
-    q_host = batches[0].cpu().numpy()
+    q_pinned = batches[0].cpu().pin_memory()  # the step's inputs start in pinned host memory
+    q_host = q_pinned.numpy()
     e2e_steps = max(3, min(args.steps, 10))
     gpu.check_host(q_host)
     barrier()

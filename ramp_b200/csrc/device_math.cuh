@@ -230,26 +230,23 @@ __device__ __forceinline__ float sphere_cyl_dist(V3 c, float R, float h, float r
   return sqrtf(fmaf(dr, dr, dz * dz)) - r;
 }
 
-// closest distance between segments p1 + s d1 and p2 + t d2, s,t in [0,1]
-__device__ __forceinline__ float seg_seg_dist(V3 p1, V3 d1, V3 p2, V3 d2) {
+// closest points between segments p1 + s d1 and p2 + t d2, s,t in [0,1]: returns the witness
+// vector c1 - c2 (its length is the distance)
+__device__ __forceinline__ V3 seg_seg_witness(V3 p1, V3 d1, V3 p2, V3 d2) {
   const V3 r = p1 - p2;
-  const float a = dot(d1, d1), e = dot(d2, d2), f = dot(d2, r);
+  const float a = dot(d1, d1), e = dot(d2, d2), f = dot(d2, r), c = dot(d1, r), b = dot(d1, d2);
   const float EPS = 1e-20f;
-  float s, t;
-  if (a <= EPS && e <= EPS) return sqrtf(dot(r, r));
-  if (a <= EPS) { s = 0.f; t = clampf(f / e, 0.f, 1.f); }
-  else {
-    const float c = dot(d1, r);
-    if (e <= EPS) { t = 0.f; s = clampf(-c / a, 0.f, 1.f); }
-    else {
-      const float b = dot(d1, d2), den = a * e - b * b;
-      s = den > EPS ? clampf((b * f - c * e) / den, 0.f, 1.f) : 0.f;
-      t = (b * s + f) / e;
-      if (t < 0.f) { t = 0.f; s = clampf(-c / a, 0.f, 1.f); }
-      else if (t > 1.f) { t = 1.f; s = clampf((b - c) / a, 0.f, 1.f); }
-    }
-  }
-  const V3 w = (p1 + d1 * s) - (p2 + d2 * t);
+  // branch-light form of the clamped 2x2 solve (Ericson, Real-Time Collision Detection 5.1.9)
+  const float den = fmaf(a, e, -b * b);
+  float s = (a > EPS && den > EPS) ? clampf((b * f - c * e) / den, 0.f, 1.f) : 0.f;
+  float t = e > EPS ? (fmaf(b, s, f)) / e : 0.f;
+  const float tc = clampf(t, 0.f, 1.f);
+  if (tc != t || e <= EPS) s = a > EPS ? clampf((b * tc - c) / a, 0.f, 1.f) : 0.f;
+  return (r + d1 * s) - d2 * tc;
+}
+
+__device__ __forceinline__ float seg_seg_dist(V3 p1, V3 d1, V3 p2, V3 d2) {
+  const V3 w = seg_seg_witness(p1, d1, p2, d2);
   return sqrtf(dot(w, w));
 }
 
@@ -392,9 +389,11 @@ struct GjkShape {
   const float4* verts;
 };
 
-__device__ __forceinline__ void gjk_init(GjkLane& g, const Xf& rel, float rsum) {
+// v0: a point of the Minkowski difference A (-) B to start from (the closer to the origin the
+// fewer iterations): the witness vector of the two inner capsules, or centre(A) - centre(B).
+__device__ __forceinline__ void gjk_init(GjkLane& g, const Xf& rel, float rsum, V3 v0) {
   g.rel = rel;
-  g.v = -trans(rel);  // centre(A) - centre(B): a point of the Minkowski difference
+  g.v = v0;
   g.vv = dot(g.v, g.v);
   if (g.vv < 1e-12f) { g.v = mk(1.f, 0.f, 0.f); g.vv = 1.f; }
   g.s.n = 0;

@@ -51,24 +51,27 @@ struct DJoint {  // 24 words
 };
 static_assert(sizeof(DJoint) == 96, "DJoint");
 
-struct DGeom {  // 36 words
+struct DGeom {  // 40 words
   int32_t type, gslot, voff, vcnt;  // gslot >= 0: per-config slot; < 0: static transform -1-gslot
   float p0, p1, p2, bound_r;
   float hx, hy, hz;  // local-frame box that contains the shape (OBB cull)
   int32_t parent;
   float pl[12];  // placement in the parent joint frame (dyn) / world (static)
-  // two capsules on one local axis (centre cc, unit direction cu): the OUTER one contains the
-  // shape (cull), the INNER one is contained in it (early accept); half lengths / radii
-  float cc[3], cu[3];
+  // Two capsules around the local z axis, centred on the local origin (the packer re-frames
+  // every geometry that way): the OUTER one contains the shape (cull), the INNER one is
+  // contained in it (early accept); half lengths / radii.
   float s_out, r_out, s_in, r_in;
-  float pad[2];
+  float opl[12];  // the caller's placement, before re-framing: what ramp_placements_batch reports
 };
-static_assert(sizeof(DGeom) == 144, "DGeom");
+static_assert(sizeof(DGeom) == 160, "DGeom");
 
-struct DPair {  // 4 words; a/b ordered so that type(a) <= type(b)
+struct DPair {  // 8 words; a/b ordered so that type(a) <= type(b)
   int32_t a, b, cls;
   float rs2;  // (bound_r(a)+bound_r(b))^2, inflated for culls, exact for sphere-sphere
+  float sa_out, sb_out, rsum_out;  // outer capsules of a and b (GJK class): half lengths, radius sum
+  int32_t pad;
 };
+static_assert(sizeof(DPair) == 32, "DPair");
 
 struct DMimic {
   int32_t dst, src;

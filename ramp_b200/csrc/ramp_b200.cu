@@ -261,7 +261,7 @@ __device__ __forceinline__ void fk_lane(const Warp& w) {
 #pragma unroll 1
     for (int s = j->gfirst; s < j->gfirst + j->gcount; ++s) {
       const int gi = w.t.dyn[s];
-      const Xf og = xf_mul(cur, load_table_xf(w.t.geoms[gi].pl));
+      const Xf og = xf_mul(cur, load_table_xf(kStage == 2 ? w.t.geoms[gi].opl : w.t.geoms[gi].pl));
       if (kStage == 2) {
 #pragma unroll
         for (int k = 0; k < 12; ++k) w.stage[l * w.stage_stride + gi * 12 + k] = og.m[k];
@@ -277,11 +277,12 @@ __device__ __forceinline__ void fk_lane(const Warp& w) {
 // kernel appends such items to a global queue; gjk_queue_kernel drains it with full warps and
 // far more resident warps than the slab-bound validity kernel can have.
 struct __align__(16) GjkItem {
-  float rel[12];  // pose of shape b in shape a's frame
-  uint32_t row;   // configuration index inside the launch's slice
-  uint32_t p;     // pair index
-  uint32_t pad[2];
+  float rel[12];    // pose of shape b in shape a's frame
+  float v0[3];      // starting point for GJK: witness vector of the two inner capsules
+  uint32_t row_p;   // configuration index inside the slice (21 bits) | pair index << 21 (11 bits)
 };
+constexpr int kItemRowBits = 21;
+static_assert((1 << (32 - kItemRowBits)) >= kMaxPairs, "pair index must fit");
 static_assert(sizeof(GjkItem) == 64, "GjkItem");
 
 struct GjkQueue {
@@ -356,6 +357,14 @@ __device__ __forceinline__ void narrow_phase(const Warp& w, bool stop_at_first, 
         if (pass) record_hit(w, l, p, want_mask);
         pass = false;
       }
+      // GJK class: the OUTER capsules (around each geometry's local z axis) cull most of what
+      // the spheres let through; skipped when no lane of the warp passed the sphere test
+      if (pr.cls == kClsGjk && __any_sync(FULL, pass)) {
+        const V3 ta = mk(pa[3 * sta], pa[7 * sta], pa[11 * sta]), za = mk(pa[2 * sta], pa[6 * sta], pa[10 * sta]);
+        const V3 tb = mk(pb[3 * stb], pb[7 * stb], pb[11 * stb]), zb = mk(pb[2 * stb], pb[6 * stb], pb[10 * stb]);
+        const V3 wv = seg_seg_witness(ta - za * pr.sa_out, za * (2.f * pr.sa_out), tb - zb * pr.sb_out, zb * (2.f * pr.sb_out));
+        pass = pass && dot(wv, wv) <= pr.rsum_out * pr.rsum_out;
+      }
       const unsigned b = __ballot_sync(FULL, pass);
       if (pass) w.queue[qn + __popc(b & ((1u << l) - 1))] = static_cast<uint16_t>(((p - chunk) << 5) | l);
       qn += __popc(b);
@@ -368,35 +377,31 @@ __device__ __forceinline__ void narrow_phase(const Warp& w, bool stop_at_first, 
       const bool live = base + l < qn;
       const int item = live ? w.queue[base + l] : 0;
       bool to_gjk = false;
+      Xf rel = xf_identity();
+      V3 v0 = mk(1.f, 0.f, 0.f);
       if (live) {
         const int c = item & 31, p = chunk + (item >> 5);
         const DPair pr = w.t.pairs[p];
         const DGeom* ga = &w.t.geoms[pr.a];
         const DGeom* gb = &w.t.geoms[pr.b];
-        const Xf rel = xf_inv_mul(geom_xf(w, ga->gslot, c), geom_xf(w, gb->gslot, c));
+        rel = xf_inv_mul(geom_xf(w, ga->gslot, c), geom_xf(w, gb->gslot, c));
         if (pr.cls >= kClsBoxBox) {
           // one SAT instance: exact decision on the boxes themselves, or a cull on the
           // local bounding boxes of two GJK shapes
           const bool bb = pr.cls == kClsBoxBox;
           const V3 ha = bb ? mk(ga->p0, ga->p1, ga->p2) : mk(ga->hx, ga->hy, ga->hz);
           const V3 hb = bb ? mk(gb->p0, gb->p1, gb->p2) : mk(gb->hx, gb->hy, gb->hz);
-          // GJK class: capsule mid-phase first.  Disjoint OUTER capsules prove separation,
-          // overlapping INNER capsules prove collision; only the shell in between needs GJK.
-          int verdict = 0;  // 0 undecided, 1 separated, 2 colliding
+          // GJK class: overlapping INNER capsules prove the collision (the outer ones were
+          // tested in stage 1); only the shell in between goes on to the OBB cull and GJK.
+          bool decided = false;
           if (!bb) {
-            const V3 ca = mk(ga->cc[0], ga->cc[1], ga->cc[2]), ua = mk(ga->cu[0], ga->cu[1], ga->cu[2]);
-            const V3 cb = apply(rel, mk(gb->cc[0], gb->cc[1], gb->cc[2])), ub = rot(rel, mk(gb->cu[0], gb->cu[1], gb->cu[2]));
-#pragma unroll 1
-            for (int k = 0; k < 2 && verdict == 0; ++k) {
-              const float sa = k ? ga->s_in : ga->s_out, sb = k ? gb->s_in : gb->s_out;
-              const float rs = k ? ga->r_in + gb->r_in : ga->r_out + gb->r_out;
-              const float dd = seg_seg_dist(ca - ua * sa, ua * (2.f * sa), cb - ub * sb, ub * (2.f * sb));
-              if (k == 0 && dd > rs + 1e-5f) verdict = 1;
-              if (k == 1 && dd < rs - 1e-5f) verdict = 2;
-            }
+            const V3 zb = mk(rel.m[2], rel.m[6], rel.m[10]);
+            v0 = seg_seg_witness(mk(0.f, 0.f, -ga->s_in), mk(0.f, 0.f, 2.f * ga->s_in), trans(rel) - zb * gb->s_in,
+                                 zb * (2.f * gb->s_in));
+            const float rin = ga->r_in + gb->r_in - 1e-5f;
+            if (rin > 0.f && dot(v0, v0) < rin * rin) { record_hit(w, c, p, want_mask); decided = true; }
           }
-          if (verdict == 2) record_hit(w, c, p, want_mask);
-          if (verdict == 0) {
+          if (!decided) {
             const bool ov = obb_overlap(ha, hb, rel, bb ? 0.f : 1e-5f);
             if (ov && bb) record_hit(w, c, p, want_mask);
             to_gjk = ov && !bb;
@@ -415,14 +420,12 @@ __device__ __forceinline__ void narrow_phase(const Warp& w, bool stop_at_first, 
           base_slot = __shfl_sync(FULL, base_slot, __ffs(gb_) - 1);
           const uint32_t slot = base_slot + __popc(gb_ & ((1u << l) - 1));
           if (to_gjk && slot < gq.capacity) {
-            const int c = item & 31, p = chunk + (item >> 5);
-            const DPair pr = w.t.pairs[p];
-            const Xf rel = xf_inv_mul(geom_xf(w, w.t.geoms[pr.a].gslot, c), geom_xf(w, w.t.geoms[pr.b].gslot, c));
+            const uint32_t c = item & 31, p = chunk + (item >> 5);
             float4* dst = reinterpret_cast<float4*>(gq.items + slot);
             dst[0] = make_float4(rel.m[0], rel.m[1], rel.m[2], rel.m[3]);
             dst[1] = make_float4(rel.m[4], rel.m[5], rel.m[6], rel.m[7]);
             dst[2] = make_float4(rel.m[8], rel.m[9], rel.m[10], rel.m[11]);
-            dst[3] = make_float4(__uint_as_float(row_base + c), __uint_as_float(static_cast<uint32_t>(p)), 0.f, 0.f);
+            dst[3] = make_float4(v0.x, v0.y, v0.z, __uint_as_float((row_base + c) | (p << kItemRowBits)));
             to_gjk = false;  // queued; anything past the capacity stays for the in-kernel loop
           }
         }
@@ -457,8 +460,8 @@ __device__ __forceinline__ void narrow_phase(const Warp& w, bool stop_at_first, 
               const DGeom* gb = &w.t.geoms[pr.b];
               A = load_shape(ga, w.t.verts);
               B = load_shape(gb, w.t.verts);
-              gjk_init(g, xf_inv_mul(geom_xf(w, ga->gslot, c), geom_xf(w, gb->gslot, c)),
-                       swept_radius(ga) + swept_radius(gb));
+              const Xf rl = xf_inv_mul(geom_xf(w, ga->gslot, c), geom_xf(w, gb->gslot, c));
+              gjk_init(g, rl, swept_radius(ga) + swept_radius(gb), -trans(rl));
               active = true;
             }
           }
@@ -583,8 +586,8 @@ __global__ void __launch_bounds__(256, 2) gjk_queue_kernel(const __grid_constant
       if (gi < total) {
         const float4* src = reinterpret_cast<const float4*>(a.items + gi);
         const float4 r0 = __ldcs(src), r1 = __ldcs(src + 1), r2 = __ldcs(src + 2), r3 = __ldcs(src + 3);
-        row = __float_as_uint(r3.x);
-        p = __float_as_uint(r3.y);
+        row = __float_as_uint(r3.w) & ((1u << kItemRowBits) - 1);
+        p = __float_as_uint(r3.w) >> kItemRowBits;
         bool skip = false;
         if (a.stop) skip = a.first_pair ? static_cast<uint32_t>(a.first_pair[row]) < p : a.hit[row] != 0;
         if (!skip) {
@@ -597,7 +600,7 @@ __global__ void __launch_bounds__(256, 2) gjk_queue_kernel(const __grid_constant
           rel.m[0] = r0.x; rel.m[1] = r0.y; rel.m[2] = r0.z; rel.m[3] = r0.w;
           rel.m[4] = r1.x; rel.m[5] = r1.y; rel.m[6] = r1.z; rel.m[7] = r1.w;
           rel.m[8] = r2.x; rel.m[9] = r2.y; rel.m[10] = r2.z; rel.m[11] = r2.w;
-          gjk_init(g, rel, swept_radius(ga) + swept_radius(gb));
+          gjk_init(g, rel, swept_radius(ga) + swept_radius(gb), mk(r3.x, r3.y, r3.z));
           active = true;
         }
       }
@@ -658,7 +661,7 @@ __global__ void __launch_bounds__(512, 1) fk_kernel(const __grid_constant__ FkAr
       for (int g = 0; g < t.h->n_geoms; ++g) {
         const int gs = t.geoms[g].gslot;
         if (gs < 0)
-          for (int k = 0; k < 12; ++k) w.stage[w.lane * w.stage_stride + g * 12 + k] = t.stat[(-1 - gs) * 12 + k];
+          for (int k = 0; k < 12; ++k) w.stage[w.lane * w.stage_stride + g * 12 + k] = t.geoms[g].opl[k];
       }
     }
     __syncwarp();
@@ -913,6 +916,7 @@ struct RampModel {
   mutable size_t scratch_cap = 0;
   mutable void* h_pinned = nullptr;
   mutable size_t pinned_cap = 0;
+  mutable cudaStream_t streams[2] = {nullptr, nullptr};  // ramp_check_host pipeline
 };
 
 namespace ramp {
@@ -1131,26 +1135,74 @@ static int build_image(RampModel* m) {
         mat_mul34(src.placement, shift, pl);
       } break;
     }
-    {  // capsules for the mid-phase of the GJK class (DGeom::cc ... r_in)
+    {  // capsules for the mid-phase of the GJK class, and the re-framing that puts them on the
+       // local z axis through the local origin
       CapsuleFit f{};
       f.u[2] = 1.0;
       const double* P = src.params;
+      int perm = 2;  // index of the local axis that becomes z (boxes / ellipsoids)
       switch (src.type) {
         case RAMP_SHAPE_SPHERE: f.r_out = f.r_in = P[0]; break;
         case RAMP_SHAPE_CAPSULE: f.s_out = f.s_in = P[1]; f.r_out = f.r_in = P[0]; break;
         case RAMP_SHAPE_BOX: {
           const int L = (P[0] >= P[1] && P[0] >= P[2]) ? 0 : (P[1] >= P[2] ? 1 : 2), a = (L + 1) % 3, b = (L + 2) % 3;
-          f.u[2] = 0; f.u[L] = 1.0;
+          perm = L;
           f.s_out = P[L]; f.r_out = std::sqrt(P[a] * P[a] + P[b] * P[b]);
           f.r_in = std::min(P[a], P[b]); f.s_in = P[L] - f.r_in;
         } break;
         case RAMP_SHAPE_CYLINDER:
           f.s_out = P[1]; f.r_out = P[0]; f.r_in = std::min(P[0], P[1]); f.s_in = std::max(0.0, P[1] - P[0]); break;
-        case RAMP_SHAPE_ELLIPSOID:
-          f.r_out = std::max(P[0], std::max(P[1], P[2])); f.r_in = std::min(P[0], std::min(P[1], P[2])); break;
+        case RAMP_SHAPE_ELLIPSOID: {
+          const int L = (P[0] >= P[1] && P[0] >= P[2]) ? 0 : (P[1] >= P[2] ? 1 : 2), a = (L + 1) % 3, b = (L + 2) % 3;
+          perm = L;
+          f.r_out = std::max(P[a], P[b]); f.s_out = std::max(0.0, P[L] - f.r_out);  // contains the ellipsoid
+          f.r_in = std::min(P[L], std::min(P[a], P[b]));
+        } break;
         default: f = fit_capsules(core); break;
       }
-      for (int k = 0; k < 3; ++k) { d.cc[k] = static_cast<float>(f.c[k]); d.cu[k] = static_cast<float>(f.u[k]); }
+      // F = (Rf, c): new local frame expressed in the old one; z' = capsule axis
+      double Rf[3][3] = {{1, 0, 0}, {0, 1, 0}, {0, 0, 1}};
+      if (src.type == RAMP_SHAPE_BOX || src.type == RAMP_SHAPE_ELLIPSOID) {
+        if (perm != 2) {  // cyclic permutation keeps the frame right handed: (x',y',z') = (a, b, L)
+          const int a = (perm + 1) % 3, b = (perm + 2) % 3;
+          const double hp[3] = {P[a], P[b], P[perm]};
+          d.p0 = static_cast<float>(hp[0]); d.p1 = static_cast<float>(hp[1]); d.p2 = static_cast<float>(hp[2]);
+          hx = hp[0]; hy = hp[1]; hz = hp[2];
+          for (int r = 0; r < 3; ++r) { Rf[r][0] = r == a; Rf[r][1] = r == b; Rf[r][2] = r == perm; }
+        }
+      } else if (src.type == RAMP_SHAPE_CONVEX) {
+        double z[3] = {f.u[0], f.u[1], f.u[2]};
+        const double t[3] = {std::fabs(z[0]) < 0.9 ? 1.0 : 0.0, std::fabs(z[0]) < 0.9 ? 0.0 : 1.0, 0.0};
+        double x[3] = {t[1] * z[2] - t[2] * z[1], t[2] * z[0] - t[0] * z[2], t[0] * z[1] - t[1] * z[0]};
+        const double xl = std::sqrt(x[0] * x[0] + x[1] * x[1] + x[2] * x[2]);
+        for (double& v : x) v /= xl;
+        const double y[3] = {z[1] * x[2] - z[2] * x[1], z[2] * x[0] - z[0] * x[2], z[0] * x[1] - z[1] * x[0]};
+        for (int r = 0; r < 3; ++r) { Rf[r][0] = x[r]; Rf[r][1] = y[r]; Rf[r][2] = z[r]; }
+        // vertices into the new frame; bounding box / radius follow
+        double lo[3] = {1e300, 1e300, 1e300}, hi[3] = {-1e300, -1e300, -1e300};
+        br = 0;
+        for (size_t i = 0; i < core.size(); i += 3) {
+          const double w[3] = {core[i] - f.c[0], core[i + 1] - f.c[1], core[i + 2] - f.c[2]};
+          for (int k = 0; k < 3; ++k) {
+            core[i + k] = Rf[0][k] * w[0] + Rf[1][k] * w[1] + Rf[2][k] * w[2];
+            lo[k] = std::min(lo[k], core[i + k]); hi[k] = std::max(hi[k], core[i + k]);
+          }
+          br = std::max(br, std::sqrt(core[i] * core[i] + core[i + 1] * core[i + 1] + core[i + 2] * core[i + 2]));
+        }
+        // the OBB is centred on the origin: take the larger side of each axis
+        hx = std::max(-lo[0], hi[0]); hy = std::max(-lo[1], hi[1]); hz = std::max(-lo[2], hi[2]);
+        const double F[12] = {Rf[0][0], Rf[0][1], Rf[0][2], f.c[0], Rf[1][0], Rf[1][1], Rf[1][2], f.c[1],
+                              Rf[2][0], Rf[2][1], Rf[2][2], f.c[2]};
+        double npl[12];
+        mat_mul34(pl, F, npl);
+        std::memcpy(pl, npl, sizeof pl);
+      }
+      if ((src.type == RAMP_SHAPE_BOX || src.type == RAMP_SHAPE_ELLIPSOID) && perm != 2) {
+        const double F[12] = {Rf[0][0], Rf[0][1], Rf[0][2], 0, Rf[1][0], Rf[1][1], Rf[1][2], 0, Rf[2][0], Rf[2][1], Rf[2][2], 0};
+        double npl[12];
+        mat_mul34(pl, F, npl);
+        std::memcpy(pl, npl, sizeof pl);
+      }
       d.s_out = static_cast<float>(f.s_out); d.r_out = static_cast<float>(f.r_out);
       d.s_in = static_cast<float>(f.s_in); d.r_in = static_cast<float>(f.r_in);
     }
@@ -1176,7 +1228,7 @@ static int build_image(RampModel* m) {
     }
     d.hx = static_cast<float>(hx); d.hy = static_cast<float>(hy); d.hz = static_cast<float>(hz);
     d.bound_r = static_cast<float>(br);
-    for (int k = 0; k < 12; ++k) d.pl[k] = static_cast<float>(pl[k]);
+    for (int k = 0; k < 12; ++k) { d.pl[k] = static_cast<float>(pl[k]); d.opl[k] = static_cast<float>(src.placement[k]); }
     if (src.parent_joint < 0) {
       d.gslot = -1 - n_static++;
       for (int k = 0; k < 12; ++k) stat.push_back(d.pl[k]);
@@ -1205,6 +1257,9 @@ static int build_image(RampModel* m) {
     const double rs = static_cast<double>(dg[a].bound_r) + dg[b].bound_r;
     // the sphere-sphere test is the decision itself; every other class uses it as a cull
     d.rs2 = static_cast<float>(d.cls == kClsSphereSphere ? rs * rs : rs * rs * (1.0 + 1e-5) + 1e-9);
+    d.sa_out = dg[a].s_out; d.sb_out = dg[b].s_out;
+    d.rsum_out = dg[a].r_out + dg[b].r_out + 1e-5f;
+    d.pad = 0;
   }
   // q map
   std::vector<DMimic> dm(m->mimic_dst.size());
@@ -1480,6 +1535,7 @@ void ramp_model_destroy(RampModel* m) {
   if (m->d_image) cudaFree(m->d_image);
   if (m->d_scratch) cudaFree(m->d_scratch);
   if (m->pool) cudaMemPoolDestroy(m->pool);
+  for (cudaStream_t st : m->streams) if (st) cudaStreamDestroy(st);
   if (m->h_pinned) cudaFreeHost(m->h_pinned);
   delete m;
 }
@@ -1678,6 +1734,16 @@ int ramp_check_edges(const RampModel* m, const float* d_q0, const float* d_q1, i
   return RAMP_OK;
 }
 
+static bool is_pinned(const void* p) {
+  cudaPointerAttributes at{};
+  if (cudaPointerGetAttributes(&at, p) != cudaSuccess) { cudaGetLastError(); return false; }
+  return at.type == cudaMemoryTypeHost;
+}
+
+// Host-buffer check, pipelined: the batch moves in chunks over two streams so that the H2D
+// copy of chunk k+1, the kernels of chunk k and the D2H copy of chunk k-1 overlap.  Buffers
+// the caller already pinned (cudaHostAlloc / cudaHostRegister / torch pin_memory) are used for
+// DMA directly; pageable ones are staged through the model's pinned buffers.
 int ramp_check_host(const RampModel* m, const float* h_q, int64_t n, int32_t ld, uint32_t flags, uint8_t* h_hit,
                     int32_t* h_first_pair, float* h_min_dist, uint32_t* h_pair_mask) {
   if (int rc = check_q_args(m, h_q, n, ld, flags)) return rc;
@@ -1686,34 +1752,66 @@ int ramp_check_host(const RampModel* m, const float* h_q, int64_t n, int32_t ld,
   if (h_min_dist) return fail(RAMP_ERR_INVALID, "h_min_dist: use ramp_distance_batch");
   CUDA_TRY(cudaSetDevice(m->device));
   std::lock_guard<std::mutex> lk(m->mu);
-  const int mw = m->hdr.mask_words;
-  const size_t b_q = align16(sizeof(float) * n * ld), b_hit = align16(n), b_first = align16(sizeof(int32_t) * n),
-               b_mask = align16(sizeof(uint32_t) * n * std::max(mw, 1));
-  const size_t total = b_q + b_hit + b_first + b_mask;
-  // staging lives after the edge scratch region is not needed at the same time: one buffer
-  if (int rc = ensure_scratch(m, total)) return rc;
-  if (total > m->pinned_cap) {
+  const int mw = std::max(m->hdr.mask_words, 1);
+  const int64_t chunk = std::min<int64_t>(n, 1 << 18);
+  const size_t b_q = align16(sizeof(float) * chunk * ld), b_hit = align16(chunk), b_first = align16(sizeof(int32_t) * chunk),
+               b_mask = align16(sizeof(uint32_t) * chunk * mw);
+  const size_t per = b_q + b_hit + b_first + b_mask;
+  if (int rc = ensure_scratch(m, 2 * per)) return rc;
+  const bool pin_q = is_pinned(h_q), pin_hit = is_pinned(h_hit);
+  const bool pin_first = !h_first_pair || is_pinned(h_first_pair), pin_mask = !h_pair_mask || is_pinned(h_pair_mask);
+  if (!(pin_q && pin_hit && pin_first && pin_mask) && 2 * per > m->pinned_cap) {
     if (m->h_pinned) cudaFreeHost(m->h_pinned);
     m->h_pinned = nullptr; m->pinned_cap = 0;
-    if (cudaMallocHost(&m->h_pinned, std::max<size_t>(total, 1 << 16)) != cudaSuccess) return fail(RAMP_ERR_ALLOC, "cudaMallocHost failed");
-    m->pinned_cap = std::max<size_t>(total, 1 << 16);
+    const size_t cap = std::max<size_t>(2 * per, 1 << 16);
+    if (cudaMallocHost(&m->h_pinned, cap) != cudaSuccess) return fail(RAMP_ERR_ALLOC, "cudaMallocHost(%zu) failed", cap);
+    m->pinned_cap = cap;
   }
+  for (int k = 0; k < 2; ++k)
+    if (!m->streams[k]) CUDA_TRY(cudaStreamCreateWithFlags(&m->streams[k], cudaStreamNonBlocking));
   unsigned char* D = static_cast<unsigned char*>(m->d_scratch);
   unsigned char* H = static_cast<unsigned char*>(m->h_pinned);
-  std::memcpy(H, h_q, sizeof(float) * n * ld);
-  cudaStream_t st = cudaStreamPerThread;
-  CUDA_TRY(cudaMemcpyAsync(D, H, sizeof(float) * n * ld, cudaMemcpyHostToDevice, st));
-  uint8_t* d_hit = D + b_q;
-  int32_t* d_first = reinterpret_cast<int32_t*>(D + b_q + b_hit);
-  uint32_t* d_mask = reinterpret_cast<uint32_t*>(D + b_q + b_hit + b_first);
-  if (int rc = launch_check(m, reinterpret_cast<const float*>(D), n, ld, flags, d_hit, h_first_pair ? d_first : nullptr,
-                            h_pair_mask ? d_mask : nullptr, st))
-    return rc;
-  CUDA_TRY(cudaMemcpyAsync(H + b_q, D + b_q, total - b_q, cudaMemcpyDeviceToHost, st));
-  CUDA_TRY(cudaStreamSynchronize(st));
-  std::memcpy(h_hit, H + b_q, n);
-  if (h_first_pair) std::memcpy(h_first_pair, H + b_q + b_hit, sizeof(int32_t) * n);
-  if (h_pair_mask) std::memcpy(h_pair_mask, H + b_q + b_hit + b_first, sizeof(uint32_t) * n * mw);
+  const int64_t nchunks = (n + chunk - 1) / chunk;
+  // results of a chunk that went through the pinned staging are copied out once its stream is done
+  auto drain = [&](int64_t k) {
+    const int b = static_cast<int>(k & 1);
+    const int64_t off = k * chunk, ns = std::min(chunk, n - off);
+    unsigned char* Hb = H + b * per;
+    if (!pin_hit) std::memcpy(h_hit + off, Hb + b_q, ns);
+    if (h_first_pair && !pin_first) std::memcpy(h_first_pair + off, Hb + b_q + b_hit, sizeof(int32_t) * ns);
+    if (h_pair_mask && !pin_mask) std::memcpy(h_pair_mask + off * mw, Hb + b_q + b_hit + b_first, sizeof(uint32_t) * ns * mw);
+  };
+  for (int64_t k = 0; k < nchunks; ++k) {
+    const int b = static_cast<int>(k & 1);
+    cudaStream_t st = m->streams[b];
+    const int64_t off = k * chunk, ns = std::min(chunk, n - off);
+    if (k >= 2) {  // the buffers of chunk k-2 are about to be reused
+      CUDA_TRY(cudaStreamSynchronize(st));
+      drain(k - 2);
+    }
+    unsigned char* Db = D + b * per;
+    unsigned char* Hb = H + b * per;
+    const float* src = h_q + off * ld;
+    if (!pin_q) { std::memcpy(Hb, src, sizeof(float) * ns * ld); src = reinterpret_cast<const float*>(Hb); }
+    CUDA_TRY(cudaMemcpyAsync(Db, src, sizeof(float) * ns * ld, cudaMemcpyHostToDevice, st));
+    uint8_t* d_hit = Db + b_q;
+    int32_t* d_first = reinterpret_cast<int32_t*>(Db + b_q + b_hit);
+    uint32_t* d_mask = reinterpret_cast<uint32_t*>(Db + b_q + b_hit + b_first);
+    if (int rc = launch_check(m, reinterpret_cast<const float*>(Db), ns, ld, flags, d_hit, h_first_pair ? d_first : nullptr,
+                              h_pair_mask ? d_mask : nullptr, st))
+      return rc;
+    CUDA_TRY(cudaMemcpyAsync(pin_hit ? h_hit + off : Hb + b_q, d_hit, ns, cudaMemcpyDeviceToHost, st));
+    if (h_first_pair)
+      CUDA_TRY(cudaMemcpyAsync(pin_first ? reinterpret_cast<unsigned char*>(h_first_pair + off) : Hb + b_q + b_hit, d_first,
+                               sizeof(int32_t) * ns, cudaMemcpyDeviceToHost, st));
+    if (h_pair_mask)
+      CUDA_TRY(cudaMemcpyAsync(pin_mask ? reinterpret_cast<unsigned char*>(h_pair_mask + off * mw) : Hb + b_q + b_hit + b_first,
+                               d_mask, sizeof(uint32_t) * ns * mw, cudaMemcpyDeviceToHost, st));
+  }
+  for (int64_t k = std::max<int64_t>(0, nchunks - 2); k < nchunks; ++k) {
+    CUDA_TRY(cudaStreamSynchronize(m->streams[k & 1]));
+    drain(k);
+  }
   return RAMP_OK;
 }
 

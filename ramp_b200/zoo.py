@@ -313,8 +313,8 @@ def _h1():
         b.joint(f"{side}_ankle", f"{side}_knee_link", f"{side}_ankle_link", "JointModelRY", (0, 0, -0.4), lower=-0.87, upper=0.52)
         for link, p0, p1, r in (
             (f"{side}_hip_yaw_link", (-0.02, 0, 0), (0.02, 0, 0), 0.05),
-            (f"{side}_hip_roll_link", (0.02, 0, 0), (0.02, s * 0.06, 0), 0.05),
-            (f"{side}_hip_pitch_link", (0, 0, -0.06), (0, 0, -0.33), 0.065),
+            (f"{side}_hip_roll_link", (0.02, 0, 0), (0.02, s * 0.03, 0), 0.04),
+            (f"{side}_hip_pitch_link", (0, 0, -0.10), (0, 0, -0.33), 0.06),
             (f"{side}_knee_link", (0, 0, -0.06), (0, 0, -0.34), 0.05),
             (f"{side}_ankle_link", (-0.05, 0, -0.045), (0.13, 0, -0.045), 0.03),
         ):
