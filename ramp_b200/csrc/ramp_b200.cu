@@ -41,7 +41,7 @@ struct Tables {
   const DGeom* geoms;
   const DPair* pairs;
   const float4* verts;
-  const float* stat;  // [n_static][12]
+  const float* stat;  // [n_static][9]: x axis, z axis, translation
   const int32_t* dyn; // slot -> geometry index
   const int32_t* act;
   const DMimic* mimic;
@@ -222,13 +222,28 @@ __device__ __forceinline__ Xf load_slab_xf(const float* slab, int slot, int lane
   return o;
 }
 
+// Geometry placements are kept as 9 floats -- x axis, z axis, translation -- in the slab
+// (and in the static table): the y axis is z cross x.  A quarter less shared memory per warp
+// means more resident warps, and stage 1 only ever reads z and t.
+constexpr int kGeomFloats = 9;
+
+__device__ __forceinline__ void store_geom_xf(float* slab, int slot, int lane, const Xf& x) {
+  float* p = slab + slot * kGeomFloats * 32 + lane;
+  p[0 * 32] = x.m[0]; p[1 * 32] = x.m[4]; p[2 * 32] = x.m[8];
+  p[3 * 32] = x.m[2]; p[4 * 32] = x.m[6]; p[5 * 32] = x.m[10];
+  p[6 * 32] = x.m[3]; p[7 * 32] = x.m[7]; p[8 * 32] = x.m[11];
+}
+
 // World placement of geometry g for configuration c (lane-divergent g and c allowed).
 __device__ __forceinline__ Xf geom_xf(const Warp& w, int gslot, int c) {
-  const float* p = gslot >= 0 ? w.geom + gslot * 12 * 32 + c : w.t.stat + (-1 - gslot) * 12;
+  const float* p = gslot >= 0 ? w.geom + gslot * kGeomFloats * 32 + c : w.t.stat + (-1 - gslot) * kGeomFloats;
   const int st = gslot >= 0 ? 32 : 1;
+  const V3 x = mk(p[0], p[st], p[2 * st]), z = mk(p[3 * st], p[4 * st], p[5 * st]);
+  const V3 y = cross(z, x);
   Xf o;
-#pragma unroll
-  for (int k = 0; k < 12; ++k) o.m[k] = p[k * st];
+  o.m[0] = x.x; o.m[1] = y.x; o.m[2] = z.x; o.m[3] = p[6 * st];
+  o.m[4] = x.y; o.m[5] = y.y; o.m[6] = z.y; o.m[7] = p[7 * st];
+  o.m[8] = x.z; o.m[9] = y.z; o.m[10] = z.z; o.m[11] = p[8 * st];
   return o;
 }
 
@@ -266,7 +281,7 @@ __device__ __forceinline__ void fk_lane(const Warp& w) {
 #pragma unroll
         for (int k = 0; k < 12; ++k) w.stage[l * w.stage_stride + gi * 12 + k] = og.m[k];
       } else {
-        store_slab_xf(w.geom, s, l, og);
+        store_geom_xf(w.geom, s, l, og);
       }
     }
   }
@@ -340,34 +355,57 @@ __device__ __forceinline__ void narrow_phase(const Warp& w, bool stop_at_first, 
     const int chunk_end = min(chunk + kChunkPairs, h->n_pairs);
     const int my_first = w.first[l];
     int qn = 0;
-    // ---- stage 1: bounding spheres, lane = configuration, pair index uniform
-#pragma unroll 1
-    for (int p = chunk; p < chunk_end; ++p) {
-      const DPair pr = w.t.pairs[p];
-      if (pr.cls == kClsInactive) continue;
-      bool pass = !(stop_at_first && my_first < p);
+    // ---- stage 1: bounding spheres, then outer capsules; lane = configuration, pair index
+    // uniform.  Two pairs per trip: their shared-memory loads and arithmetic are independent,
+    // which matters because only a few warps fit next to the slabs (latency, not issue, bound).
+    struct S1 {
+      const float *pa, *pb;
+      int sta, stb;
+      V3 ta, tb;
+      bool pass;
+    };
+    auto sphere = [&](int p, const DPair& pr) {
+      S1 r;
       const int sa = w.t.geoms[pr.a].gslot, sb = w.t.geoms[pr.b].gslot;
-      const float* pa = sa >= 0 ? w.geom + sa * 12 * 32 + l : w.t.stat + (-1 - sa) * 12;
-      const float* pb = sb >= 0 ? w.geom + sb * 12 * 32 + l : w.t.stat + (-1 - sb) * 12;
-      const int sta = sa >= 0 ? 32 : 1, stb = sb >= 0 ? 32 : 1;
-      const float dx = pa[3 * sta] - pb[3 * stb], dy = pa[7 * sta] - pb[7 * stb], dz = pa[11 * sta] - pb[11 * stb];
-      const float d2 = fmaf(dx, dx, fmaf(dy, dy, dz * dz));
-      pass = pass && d2 <= pr.rs2;
-      if (pr.cls == kClsSphereSphere) {
+      r.pa = sa >= 0 ? w.geom + sa * kGeomFloats * 32 + l : w.t.stat + (-1 - sa) * kGeomFloats;
+      r.pb = sb >= 0 ? w.geom + sb * kGeomFloats * 32 + l : w.t.stat + (-1 - sb) * kGeomFloats;
+      r.sta = sa >= 0 ? 32 : 1; r.stb = sb >= 0 ? 32 : 1;
+      r.ta = mk(r.pa[6 * r.sta], r.pa[7 * r.sta], r.pa[8 * r.sta]);
+      r.tb = mk(r.pb[6 * r.stb], r.pb[7 * r.stb], r.pb[8 * r.stb]);
+      const V3 d = r.ta - r.tb;
+      r.pass = pr.cls != kClsInactive && !(stop_at_first && my_first < p) && dot(d, d) <= pr.rs2;
+      return r;
+    };
+    // GJK class: the OUTER capsules (around each geometry's local z axis) cull most of what
+    // the spheres let through; skipped when no lane of the warp passed the sphere test
+    auto capsule = [&](const DPair& pr, S1& r) {
+      if (pr.cls == kClsGjk && __any_sync(FULL, r.pass)) {
+        const V3 za = mk(r.pa[3 * r.sta], r.pa[4 * r.sta], r.pa[5 * r.sta]), zb = mk(r.pb[3 * r.stb], r.pb[4 * r.stb], r.pb[5 * r.stb]);
+        const V3 wv = seg_seg_witness(r.ta - za * pr.sa_out, za * (2.f * pr.sa_out), r.tb - zb * pr.sb_out, zb * (2.f * pr.sb_out));
+        r.pass = r.pass && dot(wv, wv) <= pr.rsum_out * pr.rsum_out;
+      }
+    };
+    auto push = [&](int p, const DPair& pr, bool pass) {
+      if (pr.cls == kClsSphereSphere) {  // the sphere test was the decision itself
         if (pass) record_hit(w, l, p, want_mask);
         pass = false;
-      }
-      // GJK class: the OUTER capsules (around each geometry's local z axis) cull most of what
-      // the spheres let through; skipped when no lane of the warp passed the sphere test
-      if (pr.cls == kClsGjk && __any_sync(FULL, pass)) {
-        const V3 ta = mk(pa[3 * sta], pa[7 * sta], pa[11 * sta]), za = mk(pa[2 * sta], pa[6 * sta], pa[10 * sta]);
-        const V3 tb = mk(pb[3 * stb], pb[7 * stb], pb[11 * stb]), zb = mk(pb[2 * stb], pb[6 * stb], pb[10 * stb]);
-        const V3 wv = seg_seg_witness(ta - za * pr.sa_out, za * (2.f * pr.sa_out), tb - zb * pr.sb_out, zb * (2.f * pr.sb_out));
-        pass = pass && dot(wv, wv) <= pr.rsum_out * pr.rsum_out;
       }
       const unsigned b = __ballot_sync(FULL, pass);
       if (pass) w.queue[qn + __popc(b & ((1u << l) - 1))] = static_cast<uint16_t>(((p - chunk) << 5) | l);
       qn += __popc(b);
+    };
+#pragma unroll 1
+    for (int p = chunk; p < chunk_end; p += 2) {
+      const bool two = p + 1 < chunk_end;
+      const DPair pr0 = w.t.pairs[p];
+      const DPair pr1 = w.t.pairs[two ? p + 1 : p];
+      S1 r0 = sphere(p, pr0);
+      S1 r1 = sphere(p + 1, pr1);
+      r1.pass = r1.pass && two;
+      capsule(pr0, r0);
+      capsule(pr1, r1);
+      push(p, pr0, r0.pass);
+      if (two) push(p + 1, pr1, r1.pass);
     }
     __syncwarp();
     // ---- stage 2: closed forms, exact box-box, OBB cull; survivors re-compacted in place
@@ -1231,7 +1269,8 @@ static int build_image(RampModel* m) {
     for (int k = 0; k < 12; ++k) { d.pl[k] = static_cast<float>(pl[k]); d.opl[k] = static_cast<float>(src.placement[k]); }
     if (src.parent_joint < 0) {
       d.gslot = -1 - n_static++;
-      for (int k = 0; k < 12; ++k) stat.push_back(d.pl[k]);
+      // same 9-float form as the slab: x axis, z axis, translation
+      for (int k : {0, 4, 8, 2, 6, 10, 3, 7, 11}) stat.push_back(d.pl[k]);
     } else {
       by_joint[src.parent_joint].push_back(g);
     }
@@ -1327,11 +1366,15 @@ static int plan_slabs(const RampModel* m, int stage_row_floats, int act_cols, Sl
   int w = 0;
   auto take = [&](int words) { const int o = w; w += (words + 3) & ~3; return o; };
   // up to 3 padding columns of the input rows are loaded too, so whole rows move as float4
-  L->off_q = take(std::max(std::max(h.nq, ld <= h.nq + 3 ? ld : 0), 1) * 32);
-  L->off_act = take(std::max(std::max(act_cols, ld <= act_cols + 3 ? ld : 0), 1) * 32);
-  L->off_geom = take(std::max(h.n_dyn, 1) * 12 * 32);
+  // q / actuated rows are dead once FK has run; the work queue of the narrow phase reuses them
+  const int q_words = std::max(std::max(h.nq, ld <= h.nq + 3 ? ld : 0), 1) * 32;
+  const int act_words = std::max(std::max(act_cols, ld <= act_cols + 3 ? ld : 0), 1) * 32;
+  const int region0 = take(std::max(q_words + act_words, kQueueCap / 2));
+  L->off_q = region0;
+  L->off_act = region0 + q_words;
+  L->off_geom = take(std::max(h.n_dyn, 1) * kGeomFloats * 32);
   L->off_save = take(std::max(h.n_save, 1) * 12 * 32);
-  L->off_queue = take(kQueueCap / 2);
+  L->off_queue = region0;
   L->off_mask = take(std::max(h.mask_words, 1) * 32);
   L->off_first = take(32);
   L->stage_stride = stage_row_floats | 1;  // odd stride: conflict-free lane-private rows
