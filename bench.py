@@ -136,6 +136,57 @@ def run_reference(args, wl, rm, desc) -> None:
     }))
 
 
+def run_edges(args, wl, rm, desc, dev) -> None:
+    """BASELINE config 3 (planner edges through the batched motion validator), single GPU:
+    a step is one ramp_check_edges call over E random edges; value = interpolated states
+    checked per second.  Also times one RRTConnect query through the same validator."""
+    import numpy as np
+    import torch
+
+    from ramp_b200 import MotionPlanner, RobotState, engine, spaces
+
+    planner = MotionPlanner(rm, "arm")
+    start = RobotState.from_named_state(rm, "arm", "home")
+    planner.set_reference_state(start)
+    E = args.n or wl.n
+    rng = np.random.default_rng(0xB200)
+    q0 = spaces.sample_uniform(planner.space, E, rng)
+    lo = np.array([s["lo"][0] for s in planner.space.subspaces])
+    hi = np.array([s["hi"][0] for s in planner.space.subspaces])
+    q1 = np.clip(q0 + rng.normal(scale=0.4, size=q0.shape), lo, hi)
+    d0, d1 = torch.from_numpy(q0.astype(np.float32)).to(dev), torch.from_numpy(q1.astype(np.float32)).to(dev)
+    gpu = rm.gpu
+    res = gpu.check_edges(d0, d1, planner.space)
+    states = int(res["nd"].clamp(min=1).sum().item())
+    for _ in range(args.warmup):
+        gpu.check_edges(d0, d1, planner.space)
+    torch.cuda.synchronize()
+    l0 = engine.launch_count()
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.record()
+    for _ in range(args.steps):
+        res = gpu.check_edges(d0, d1, planner.space)
+    b.record()
+    torch.cuda.synchronize()
+    ms = a.elapsed_time(b) / args.steps
+    launches = engine.launch_count() - l0
+    t0 = time.perf_counter()
+    path = planner.plan(start, [0.0, 0.25, 0.0, -1.25, 0.0, 1.5, 0.0], timeout=5.0)
+    plan_s = time.perf_counter() - t0
+    print(json.dumps({
+        "metric": METRIC, "value": states / (ms * 1e-3), "unit": UNIT, "n_gpus": 1, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": wl.name, "robot": wl.robot, "scene": wl.scene, "note": wl.note, "model": "stand-in",
+                   "edges": E, "states": states, "mean_nd": states / E, "edges_per_s": E / (ms * 1e-3),
+                   "valid_edge_fraction": float(res["valid"].float().mean().item())},
+        "gpu_launches": launches,
+        "planning": {"planner": "built-in RRTConnect over GpuMotionValidator", "found": path is not None,
+                     "seconds": plan_s, "waypoints": 0 if path is None else len(path),
+                     "edges_checked": planner.validator.valid_count + planner.validator.invalid_count,
+                     "states_checked": planner.validator.states_checked},
+    }))
+
+
 def main() -> None:
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -181,6 +232,9 @@ def main() -> None:
         dist.init_process_group("nccl", device_id=dev)
         dist.barrier()
 
+    if args.workload == "fr3_edges":
+        run_edges(args, wl, rm, desc, dev)
+        return
     n = args.n or wl.n
     gpu = rm.gpu
     ld = workloads.padded_nq(rm.model)

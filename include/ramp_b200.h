@@ -239,7 +239,7 @@ int ramp_check_batch(const RampModel* m, const float* d_q, int64_t n, int32_t ld
  *
  *   - at most RAMP_NOALLOC_MAX_ROWS configurations per call; larger n is
  *     refused with RAMP_ERR_LIMIT (split the batch, or use ramp_check_batch);
- *   - the fixed array (about 4.3 MB) is part of the library image: every GPU
+ *   - the fixed array (about 5.6 MB) is part of the library image: every GPU
  *     that loads the library holds it until the process exits;
  *   - the first call on each device looks up the array's address
  *     (cudaGetSymbolAddress); make that first call before any stream capture;

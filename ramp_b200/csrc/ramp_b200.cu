@@ -292,13 +292,13 @@ __device__ __forceinline__ void fk_lane(const Warp& w) {
 // kernel appends such items to a global queue; gjk_queue_kernel drains it with full warps and
 // far more resident warps than the slab-bound validity kernel can have.
 struct __align__(16) GjkItem {
-  float rel[12];    // pose of shape b in shape a's frame
-  float v0[3];      // starting point for GJK: witness vector of the two inner capsules
-  uint32_t row_p;   // configuration index inside the slice (21 bits) | pair index << 21 (11 bits)
+  float rel[12];   // pose of shape b in shape a's frame
+  float v0[3];     // starting point for GJK: witness vector of the two inner capsules
+  uint32_t row;    // configuration index inside the launch's slice / flat state index (edges)
+  uint32_t p;      // pair index
+  uint32_t pad[3];
 };
-constexpr int kItemRowBits = 21;
-static_assert((1 << (32 - kItemRowBits)) >= kMaxPairs, "pair index must fit");
-static_assert(sizeof(GjkItem) == 64, "GjkItem");
+static_assert(sizeof(GjkItem) == 80, "GjkItem");
 
 struct GjkQueue {
   GjkItem* items;    // nullptr: no queue, GJK runs inside the validity kernel
@@ -463,7 +463,8 @@ __device__ __forceinline__ void narrow_phase(const Warp& w, bool stop_at_first, 
             dst[0] = make_float4(rel.m[0], rel.m[1], rel.m[2], rel.m[3]);
             dst[1] = make_float4(rel.m[4], rel.m[5], rel.m[6], rel.m[7]);
             dst[2] = make_float4(rel.m[8], rel.m[9], rel.m[10], rel.m[11]);
-            dst[3] = make_float4(v0.x, v0.y, v0.z, __uint_as_float((row_base + c) | (p << kItemRowBits)));
+            dst[3] = make_float4(v0.x, v0.y, v0.z, __uint_as_float(row_base + c));
+            dst[4] = make_float4(__uint_as_float(p), 0.f, 0.f, 0.f);
             to_gjk = false;  // queued; anything past the capacity stays for the in-kernel loop
           }
         }
@@ -596,9 +597,18 @@ struct GjkQueueArgs {
   uint32_t* pair_mask;
   int32_t mask_words;
   int32_t stop;  // early-out semantics: a configuration already hit by an earlier pair is skipped
+  // edge mode (offs != nullptr): `row` is a flat state index; a hit lowers first_invalid[edge]
+  const int64_t* offs;
+  const int32_t* nd;
+  int32_t* first_invalid;
+  int64_t n_edges;
 };
 
 constexpr int kQueueChunk = 64;  // consecutive items owned by one warp
+
+#ifdef RAMP_STATS
+__device__ unsigned long long g_stats[64];  // [0] items [1] iterations [2] hits [3] skipped, [8+it] histogram
+#endif
 
 __global__ void __launch_bounds__(256, 2) gjk_queue_kernel(const __grid_constant__ GjkQueueArgs a) {
   uint64_t* mbar = reinterpret_cast<uint64_t*>(g_smem);
@@ -623,11 +633,11 @@ __global__ void __launch_bounds__(256, 2) gjk_queue_kernel(const __grid_constant
       const uint64_t gi = global_index(next + __popc(need & ((1u << l) - 1)));
       if (gi < total) {
         const float4* src = reinterpret_cast<const float4*>(a.items + gi);
-        const float4 r0 = __ldcs(src), r1 = __ldcs(src + 1), r2 = __ldcs(src + 2), r3 = __ldcs(src + 3);
-        row = __float_as_uint(r3.w) & ((1u << kItemRowBits) - 1);
-        p = __float_as_uint(r3.w) >> kItemRowBits;
+        const float4 r0 = __ldcs(src), r1 = __ldcs(src + 1), r2 = __ldcs(src + 2), r3 = __ldcs(src + 3), r4 = __ldcs(src + 4);
+        row = __float_as_uint(r3.w);
+        p = __float_as_uint(r4.x);
         bool skip = false;
-        if (a.stop) skip = a.first_pair ? static_cast<uint32_t>(a.first_pair[row]) < p : a.hit[row] != 0;
+        if (a.stop && !a.offs) skip = a.first_pair ? static_cast<uint32_t>(a.first_pair[row]) < p : a.hit[row] != 0;
         if (!skip) {
           const DPair pr = t.pairs[p];
           const DGeom* ga = &t.geoms[pr.a];
@@ -651,8 +661,21 @@ __global__ void __launch_bounds__(256, 2) gjk_queue_kernel(const __grid_constant
     if (active) {
       float dist;
       const int st = gjk_step(g, A, B, false, dist);
+#ifdef RAMP_STATS
+      atomicAdd(&g_stats[1], 1ull);
+      if (st != GJK_CONTINUE) { atomicAdd(&g_stats[0], 1ull); atomicAdd(&g_stats[2], st == GJK_HIT ? 1ull : 0ull); atomicAdd(&g_stats[8 + min(g.it, 40)], 1ull); }
+#endif
       if (st != GJK_CONTINUE) {
-        if (st == GJK_HIT) {
+        if (st == GJK_HIT && a.offs) {
+          // edge of flat state `row`: last e with offs[e] <= row; its 1-based index j
+          int64_t lo = 0, hi = a.n_edges - 1;
+          while (lo < hi) {
+            const int64_t mid = (lo + hi + 1) >> 1;
+            if (a.offs[mid] <= static_cast<int64_t>(row)) lo = mid; else hi = mid - 1;
+          }
+          const int j = static_cast<int>(static_cast<int64_t>(row) - a.offs[lo]) + 1;
+          atomicMin(&a.first_invalid[lo], min(j, a.nd[lo]));
+        } else if (st == GJK_HIT) {
           a.hit[row] = 1;
           // -1 ("none") is the largest unsigned value, so an unsigned min keeps list order
           if (a.first_pair) atomicMin(reinterpret_cast<uint32_t*>(a.first_pair) + row, p);
@@ -776,6 +799,7 @@ struct EdgeArgs {
   int32_t* first_invalid;  // always non-null inside the library (scratch when the caller passes none)
   int32_t* nd;             // idem
   int64_t* offs;           // [n_edges+1] exclusive prefix of per-edge state counts (scratch)
+  GjkQueue gq;
   SlabLayout L;
   DSpace sp;
 };
@@ -886,7 +910,7 @@ __global__ void __launch_bounds__(512, 1) edge_check_kernel(const __grid_constan
     reset_results(w, 0);
     fk_lane<0>(w);
     __syncwarp();
-    narrow_phase(w, true, false, GjkQueue{nullptr, nullptr, 0u}, 0u);
+    narrow_phase(w, true, false, a.gq, static_cast<uint32_t>(tile << 5));
     const bool invalid = w.first[l] != INT32_MAX || (a.sp.check_bounds && !in_bounds);
     if (!skip && invalid) atomicMin(&a.first_invalid[e], min(j, nd));
     __syncwarp();
@@ -1488,6 +1512,14 @@ extern "C" {
 int ramp_abi_version(void) { return RAMP_B200_ABI_VERSION; }
 const char* ramp_last_error(void) { return g_err; }
 int64_t ramp_launch_count(void) { return g_launches.load(); }
+#ifdef RAMP_STATS
+int ramp_debug_stats(unsigned long long* out, int reset) {
+  cudaDeviceSynchronize();
+  cudaMemcpyFromSymbol(out, g_stats, sizeof(unsigned long long) * 64);
+  if (reset) { unsigned long long z[64] = {0}; cudaMemcpyToSymbol(g_stats, z, sizeof z); }
+  return 0;
+}
+#endif
 
 int ramp_model_create(const RampModelDesc* d, int device, RampModel** out) {
   if (!d || !out) return fail(RAMP_ERR_INVALID, "null argument");
@@ -1645,7 +1677,7 @@ int ramp_check_batch(const RampModel* m, const float* d_q, int64_t n, int32_t ld
 // from the fixed array below instead and calls no allocating routine at all.
 //
 // The array lives in the library image: every GPU that loads libramp_b200.so carries these
-// kNoAllocQueueBytes (about 4.3 MB) until the process exits, whether or not the entry point
+// kNoAllocQueueBytes (about 5.6 MB) until the process exits, whether or not the entry point
 // is ever used.  That is why the limit is modest.
 constexpr int64_t kNoAllocMaxRows = RAMP_NOALLOC_MAX_ROWS;
 constexpr uint32_t kNoAllocQueueItems = static_cast<uint32_t>(kNoAllocMaxRows * kQueueItemsPerRow + 4096);
@@ -1766,13 +1798,35 @@ int ramp_check_edges(const RampModel* m, const float* d_q0, const float* d_q1, i
   int nwarps; size_t smem;
   if (int rc = plan_slabs(m, 0, n_cols, &a.L, &nwarps, &smem)) return rc;
   if (int rc = set_smem(edge_check_kernel, smem)) return rc;
+  // GJK work queue (only worth a launch when there are enough edges to fill warps)
+  a.gq = GjkQueue{nullptr, nullptr, 0u};
+  unsigned char* qmem = nullptr;
+  const bool use_queue = m->pool != nullptr && m->n_gjk_pairs > 0 && n_edges >= 64;
+  GjkQueueArgs b{};
+  size_t smem_b = 0;
+  if (use_queue) {
+    const uint32_t cap = static_cast<uint32_t>(std::min<int64_t>(std::max<int64_t>(1 << 16, n_edges * 64), 1 << 21));
+    const size_t bytes = 256 + static_cast<size_t>(cap) * sizeof(GjkItem);
+    if (cudaMallocFromPoolAsync(reinterpret_cast<void**>(&qmem), bytes, m->pool, st) != cudaSuccess) {
+      cudaGetLastError();
+      return fail(RAMP_ERR_ALLOC, "cudaMallocFromPoolAsync(%zu) for the GJK queue failed", bytes);
+    }
+    CUDA_TRY(cudaMemsetAsync(qmem, 0, 16, st));
+    a.gq = GjkQueue{reinterpret_cast<GjkItem*>(qmem + 256), reinterpret_cast<uint32_t*>(qmem), cap};
+    smem_b = 16 + a.L.table_bytes;
+    if (int rc = set_smem(gjk_queue_kernel, smem_b)) return rc;
+    b.img = m->d_image; b.table_bytes = a.L.table_bytes; b.items = a.gq.items; b.count = a.gq.count; b.capacity = cap;
+    b.offs = a.offs; b.nd = a.nd; b.first_invalid = a.first_invalid; b.n_edges = n_edges;
+  }
   const int eb = static_cast<int>((n_edges + 255) / 256);
   edge_count_kernel<<<eb, 256, 0, st>>>(a);
   edge_scan_kernel<<<1, 1024, 0, st>>>(a.offs, n_edges);
   // the number of states is only known on the device: size the grid for the SM count
   edge_check_kernel<<<m->sm_count, nwarps * 32, smem, st>>>(a);
+  if (use_queue) gjk_queue_kernel<<<m->sm_count * 2, 256, smem_b, st>>>(b);
   edge_finish_kernel<<<eb, 256, 0, st>>>(a, d_first_invalid, d_nd);
-  g_launches.fetch_add(4, std::memory_order_relaxed);
+  g_launches.fetch_add(use_queue ? 5 : 4, std::memory_order_relaxed);
+  if (qmem) CUDA_TRY(cudaFreeAsync(qmem, st));
   CUDA_TRY(cudaGetLastError());
   return RAMP_OK;
 }

@@ -1,0 +1,113 @@
+"""MotionPlanner over the batched GPU validator: the reference's planning known answers
+(reference tests/motion_planner_test.py:17-65 -- "a plan is found") plus checks the reference
+cannot make: every waypoint and every edge of the returned path is valid under the CPU oracle."""
+
+import numpy as np
+import pytest
+
+torch = pytest.importorskip("torch")
+pytestmark = pytest.mark.gpu
+
+
+def _oracle_path_valid(rm, planner, path):
+    from oracle import oracle
+    from ramp_b200 import spaces
+    from ramp_b200.desc import ModelDesc
+
+    d = ModelDesc(rm.model, rm.collision_model)
+    q = np.stack([s.qpos for s in path])
+    res = oracle.check(d, q)
+    states = np.stack([planner.as_state(s) for s in path])
+    nd = [spaces.valid_segment_count(planner.space, a, b) for a, b in zip(states[:-1], states[1:])]
+    return res, max(nd)
+
+
+@pytest.mark.parametrize("cfg,scene,goal,timeout", [
+    ("rrr/configs", None, [0.0, 1.0, 1.0], 2.0),
+    ("rrr/configs", "capsule", [0.0, 2.0, 1.4], 5.0),
+    ("rrr/planar_configs", "capsule", [1.0, -0.5, 1.57, 0.5, 0.25, 0.1], 5.0),
+    ("rrr/floating_configs", "capsule", [1.0, 0.5, 1.0, 1.0, 0.0, 0.0, 0.0, 0.5, 0.25, 0.1], 5.0),
+    ("panda/configs", "capsule", [0.0, 0.25, 0.0, -1.25, 0.0, 1.5, 0.785], 5.0),
+])
+def test_plan_found_and_valid_under_oracle(built, cfg, scene, goal, timeout):
+    from ramp_b200 import MotionPlanner, RobotState, load_robot_model, workloads
+
+    rm = load_robot_model("zoo::" + cfg)
+    start = RobotState.from_named_state(rm, "arm", "home")
+    if scene:
+        start.add_object(workloads.reference_capsule())
+    planner = MotionPlanner(rm, "arm")
+    path = planner.plan(start, goal, timeout=timeout)
+    assert path is not None, "Expected a plan to be found"
+    assert np.allclose(planner.as_state(path[0]), planner.as_state(start), atol=1e-6)
+    res, max_nd = _oracle_path_valid(rm, planner, path)
+    # interpolated path: consecutive states at most one valid segment apart
+    assert max_nd <= 1
+    # every waypoint collision free (or inside the +-1e-4 margin band)
+    assert (~res["hit"] | (np.abs(res["min_dist"]) <= 1e-4)).all()
+    goal_state = start.clone()
+    goal_state.set_group_qpos("arm", goal)
+    assert np.allclose(path[-1].qpos, goal_state.qpos, atol=1e-5)
+
+
+def test_invalid_start_or_goal_returns_none(built):
+    from ramp_b200 import MotionPlanner, RobotState, load_robot_model
+
+    rm = load_robot_model("zoo::rrr/configs")
+    planner = MotionPlanner(rm, "arm")
+    start = RobotState.from_named_state(rm, "arm", "home")
+    assert planner.plan(start, [0.0, 2.9, 2.9]) is None       # goal folds the arm into itself
+    assert planner.plan(start, [0.0, 4.0, 0.0]) is None       # goal out of bounds
+    assert planner.is_state_valid(start)
+    bad = start.clone()
+    bad.set_group_qpos("arm", [0.0, 2.9, 2.9])
+    assert not planner.is_state_valid(bad)
+
+
+def test_check_motion_overloads_follow_ompl(built):
+    from oracle import oracle
+    from ramp_b200 import MotionPlanner, RobotState, spaces, workloads
+    from ramp_b200.desc import ModelDesc
+
+    rm, rs = workloads.build("rrr_float")
+    planner = MotionPlanner(rm, "arm")
+    planner.set_reference_state(rs)
+    d = ModelDesc(rm.model, rm.collision_model)
+    rng = np.random.default_rng(5)
+    q0 = spaces.sample_uniform(planner.space, 30, rng)
+    q1 = spaces.sample_uniform(planner.space, 30, rng)
+    q1[:, :3] = q0[:, :3] + rng.normal(scale=0.3, size=(30, 3))
+    ref = oracle.check_edges(d, planner._qmap, planner.space, q0, q1)
+    seen_invalid = 0
+    for e in range(30):
+        lv = []
+        ok = planner.validator.checkMotion(q0[e], q1[e], lv)
+        assert ok == planner.validator.checkMotion(q0[e], q1[e])
+        if ok != bool(ref["valid"][e]):
+            continue  # a margin-band state; covered by test_edges_match_oracle's accounting
+        if not ok and ref["nd"][e] > 0:
+            seen_invalid += 1
+            assert lv[1] == pytest.approx((ref["first_invalid"][e] - 1) / ref["nd"][e], abs=1.5 / ref["nd"][e])
+            assert np.allclose(lv[0], spaces.interpolate(planner.space, q0[e], q1[e], lv[1]))
+    assert seen_invalid >= 3
+
+
+def test_get_frame_pose_and_collision_pairs(built):
+    """RobotState.get_frame_pose (FK + frame placement) and the all-pairs report."""
+    from ramp_b200 import RobotState, load_robot_model
+    from ramp_b200.compute_disable_collisions import default_collisions, get_collision_pairs
+
+    rm = load_robot_model("zoo::rrr/configs")
+    rs = RobotState.from_named_state(rm, "arm", "home")
+    rs.set_group_qpos("arm", [0.3, 0.5, -0.2])
+    pose = rs.get_frame_pose("end_effector")
+    # joint3 origin + 0.3 along link3's z (pitch 0.3 total, yaw 0.3)
+    j3 = np.array([0.4 * np.sin(0.5) * np.cos(0.3), 0.4 * np.sin(0.5) * np.sin(0.3), 0.525 + 0.4 * np.cos(0.5)])
+    z = np.array([np.sin(0.3) * np.cos(0.3), np.sin(0.3) * np.sin(0.3), np.cos(0.3)])
+    assert np.allclose(pose.translation, j3 + 0.3 * z, atol=1e-5)
+    assert pose.np.shape == (4, 4)
+    rs.set_group_qpos("arm", [0.0, 2.9, 2.9])
+    pairs = get_collision_pairs(rm, rs.qpos)
+    assert ("link1", "link3") in pairs or ("link1", "end_effector") in pairs
+    assert default_collisions(rm) == []  # nothing collides at the neutral configuration
+    assert rs.check_collision() and rs.check_collision(verbose=True)
