@@ -136,6 +136,46 @@ def run_reference(args, wl, rm, desc) -> None:
     }))
 
 
+def run_fk(args, wl, rm, dev) -> None:
+    """FK with poses stored (ramp_fk_batch): the HBM-bound kernel of the path."""
+    import torch
+
+    from ramp_b200 import engine, workloads
+
+    n = args.n or min(wl.n, 1 << 22)
+    ld = workloads.padded_nq(rm.model)
+    nj = rm.model.njoints - 1
+    gpu = rm.gpu
+    q = workloads.sample_q_torch(rm.model, n, seed=0xB200, device=dev)
+    out = torch.empty((n, nj, 3, 4), dtype=torch.float32, device=dev)
+    lib, h, st = gpu.lib, gpu.handle, torch.cuda.current_stream(dev).cuda_stream
+    for _ in range(args.warmup):
+        lib.ramp_fk_batch(h, q.data_ptr(), n, ld, 0, out.data_ptr(), st)
+    torch.cuda.synchronize()
+    l0 = engine.launch_count()
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.record()
+    for _ in range(args.steps):
+        lib.ramp_fk_batch(h, q.data_ptr(), n, ld, 0, out.data_ptr(), st)
+    b.record()
+    torch.cuda.synchronize()
+    ms = a.elapsed_time(b) / args.steps
+    peaks = measured_peaks()
+    bytes_per_cfg = 4 * ld + 48 * nj
+    gbs = bytes_per_cfg * n / (ms * 1e-3) / 1e9
+    print(json.dumps({
+        "metric": "FK configs/sec (poses stored)", "value": n / (ms * 1e-3), "unit": UNIT, "n_gpus": 1, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "f32", "data": "synthetic",
+        "config": {"workload": wl.name + ":fk", "robot": wl.robot, "n": n, "joints": nj, "ld_q": ld,
+                   "l2": f"output {48 * nj * n / 2**20:.0f} MiB per step streams through L2 (> 126 MB)"},
+        "roofline": {"bound": "hbm", "achieved": gbs, "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": gbs / peaks["hbm_gbs"],
+                     "traffic": None, "kernel": "fk_kernel<1>", "algorithmic_bytes_per_config": bytes_per_cfg,
+                     "peak_source": peaks["_source"]},
+        "gpu_launches": engine.launch_count() - l0,
+    }))
+
+
 def run_edges(args, wl, rm, desc, dev) -> None:
     """BASELINE config 3 (planner edges through the batched motion validator), single GPU:
     a step is one ramp_check_edges call over E random edges; value = interpolated states
@@ -196,6 +236,7 @@ def main() -> None:
     ap.add_argument("--workload", default="ur5e_1m")
     ap.add_argument("--n", type=int, default=0, help="override configurations per step per GPU")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--kernel", default="check", choices=["check", "fk"], help="fk: time ramp_fk_batch (poses stored)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
 
@@ -234,6 +275,9 @@ def main() -> None:
 
     if args.workload == "fr3_edges":
         run_edges(args, wl, rm, desc, dev)
+        return
+    if args.kernel == "fk":
+        run_fk(args, wl, rm, dev)
         return
     n = args.n or wl.n
     gpu = rm.gpu

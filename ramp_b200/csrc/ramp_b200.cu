@@ -250,6 +250,59 @@ __device__ __forceinline__ Xf geom_xf(const Warp& w, int gslot, int c) {
 // ---- forward kinematics for this lane's configuration (pinocchio::forwardKinematics +
 // updateGeometryPlacements).  kStage: 0 = placements to the slab only, 1 = also stage oMi
 // rows, 2 = also stage oMg rows (output kernels).
+// liMi = placement * M(q).  The aligned revolute / prismatic joints -- all but a handful in
+// practice -- only mix two columns of the placement's rotation (or slide along one), a third of
+// the arithmetic of a general 3x4 product.
+template <int A, int B>
+__device__ __forceinline__ void mix_columns(Xf& o, float c, float s) {  // columns A, B of R times a plane rotation
+#pragma unroll
+  for (int r = 0; r < 3; ++r) {
+    const float ua = o.m[4 * r + A], ub = o.m[4 * r + B];
+    o.m[4 * r + A] = fmaf(c, ua, s * ub);
+    o.m[4 * r + B] = fmaf(c, ub, -s * ua);
+  }
+}
+
+template <int A>
+__device__ __forceinline__ void slide_column(Xf& o, float d) {
+#pragma unroll
+  for (int r = 0; r < 3; ++r) o.m[4 * r + 3] = fmaf(d, o.m[4 * r + A], o.m[4 * r + 3]);
+}
+
+__device__ __forceinline__ Xf local_xf(const DJoint* j, const float* qv) {
+  Xf o = load_table_xf(j->pl);
+  const int type = j->type;
+  if (type <= 3) {  // RX / RY / RZ
+    float s, c;
+    sincos_small(qv[0], &s, &c);
+    if (type == 1) mix_columns<1, 2>(o, c, s);
+    else if (type == 2) mix_columns<2, 0>(o, c, s);
+    else mix_columns<0, 1>(o, c, s);
+    return o;
+  }
+  if (type >= 9 && type <= 11) {  // PX / PY / PZ
+    if (type == 9) slide_column<0>(o, qv[0]);
+    else if (type == 10) slide_column<1>(o, qv[0]);
+    else slide_column<2>(o, qv[0]);
+    return o;
+  }
+  return xf_mul(o, joint_xf(type, j->ax, j->ay, j->az, qv));
+}
+
+// Staging of output rows for the FK kernels: row l (this lane's configuration) holds its 3x4
+// matrices as float4 triples.  The row pitch (in float4) is odd, so the 32 lanes' STS.128 of
+// one matrix row land in distinct bank groups; an odd pitch that equals the row length makes
+// the tile in shared memory the exact image of the tile in global memory.
+__device__ __forceinline__ void stage_xf(const Warp& w, int slot, const Xf& x) {
+  float4* p = reinterpret_cast<float4*>(w.stage) + w.lane * w.stage_stride + slot * 3;
+  p[0] = make_float4(x.m[0], x.m[1], x.m[2], x.m[3]);
+  p[1] = make_float4(x.m[4], x.m[5], x.m[6], x.m[7]);
+  p[2] = make_float4(x.m[8], x.m[9], x.m[10], x.m[11]);
+}
+
+// ---- forward kinematics for this lane's configuration (pinocchio::forwardKinematics +
+// updateGeometryPlacements).  kStage: 0 = geometry placements to the slab (validity path),
+// 1 = stage the oMi rows, 2 = stage the oMg rows (output kernels).
 template <int kStage>
 __device__ __forceinline__ void fk_lane(const Warp& w) {
   const ImgHeader* h = w.t.h;
@@ -258,31 +311,24 @@ __device__ __forceinline__ void fk_lane(const Warp& w) {
 #pragma unroll 1
   for (int i = 0; i < h->n_joints; ++i) {
     const DJoint* j = &w.t.joints[i];
-    const int type = j->type;
     float qv[7];
-    const int n = joint_nq(type);
+    const int n = joint_nq(j->type);
 #pragma unroll
     for (int k = 0; k < 7; ++k) qv[k] = k < n ? w.q[(j->idx_q + k) * 32 + l] : 0.f;
-    const Xf loc = xf_mul(load_table_xf(j->pl), joint_xf(type, j->ax, j->ay, j->az, qv));
+    const Xf loc = local_xf(j, qv);
     const int pc = j->parent_code;
     if (pc == kParentUniverse) cur = loc;
     else if (pc == kParentRunning) cur = xf_mul(cur, loc);
     else cur = xf_mul(load_slab_xf(w.save, pc, l), loc);
     if (j->save_slot >= 0) store_slab_xf(w.save, j->save_slot, l, cur);
-    if (kStage == 1) {
-#pragma unroll
-      for (int k = 0; k < 12; ++k) w.stage[l * w.stage_stride + i * 12 + k] = cur.m[k];
-    }
+    if (kStage == 1) stage_xf(w, i, cur);
+    const int gend = kStage == 1 ? j->gfirst : j->gfirst + j->gcount;
 #pragma unroll 1
-    for (int s = j->gfirst; s < j->gfirst + j->gcount; ++s) {
+    for (int s = j->gfirst; s < gend; ++s) {
       const int gi = w.t.dyn[s];
       const Xf og = xf_mul(cur, load_table_xf(kStage == 2 ? w.t.geoms[gi].opl : w.t.geoms[gi].pl));
-      if (kStage == 2) {
-#pragma unroll
-        for (int k = 0; k < 12; ++k) w.stage[l * w.stage_stride + gi * 12 + k] = og.m[k];
-      } else {
-        store_geom_xf(w.geom, s, l, og);
-      }
+      if (kStage == 2) stage_xf(w, gi, og);
+      else store_geom_xf(w.geom, s, l, og);
     }
   }
 }
@@ -717,25 +763,35 @@ __global__ void __launch_bounds__(512, 1) fk_kernel(const __grid_constant__ FkAr
     const int64_t row0 = tile << 5;
     load_rows(actuated ? w.act : w.q, a.q, row0, a.n, cols, a.ld, w.lane);
     if (actuated) expand_q(w);
+    // the bulk stores of the previous tile must have finished READING the staging rows
+    asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+    __syncwarp();
     fk_lane<kWhat>(w);
     if (kWhat == 2) {  // universe-attached geometries have constant placements
-      for (int g = 0; g < t.h->n_geoms; ++g) {
-        const int gs = t.geoms[g].gslot;
-        if (gs < 0)
-          for (int k = 0; k < 12; ++k) w.stage[w.lane * w.stage_stride + g * 12 + k] = t.geoms[g].opl[k];
-      }
+      for (int g = 0; g < t.h->n_geoms; ++g)
+        if (t.geoms[g].gslot < 0) stage_xf(w, g, load_table_xf(t.geoms[g].opl));
     }
+    // make the generic-proxy writes to shared memory visible to the async (TMA) proxy
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
     __syncwarp();
-    // the tile's rows are contiguous in the output: stream them out fully coalesced
+    // the tile's rows are contiguous in the output: one TMA bulk store for the whole tile when
+    // the staging pitch equals the row length, else one per row (cp.async.bulk, SASS UBLKCP)
     const int rows = static_cast<int>(imin64(32, a.n - row0));
     float* dst = a.out + row0 * a.row_floats;
-    const int total = rows * a.row_floats;
-    for (int e = w.lane; e < total; e += 32) {
-      const int r = e / a.row_floats, c = e - r * a.row_floats;
-      __stcs(dst + e, w.stage[r * w.stage_stride + c]);
+    const uint32_t row_bytes = static_cast<uint32_t>(a.row_floats) * 4u;
+    if (w.stage_stride * 4 == a.row_floats) {
+      if (w.lane == 0)
+        asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(dst), "r"(smem_u32(w.stage)),
+                     "r"(row_bytes * rows)
+                     : "memory");
+    } else if (w.lane < rows) {
+      asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(dst + static_cast<size_t>(w.lane) * a.row_floats),
+                   "r"(smem_u32(reinterpret_cast<float4*>(w.stage) + w.lane * w.stage_stride)), "r"(row_bytes)
+                   : "memory");
     }
-    __syncwarp();
+    asm volatile("cp.async.bulk.commit_group;" ::: "memory");
   }
+  asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
 }
 
 // ------------------------------------------------------------------ kernels: edges
@@ -1393,16 +1449,19 @@ static int plan_slabs(const RampModel* m, int stage_row_floats, int act_cols, Sl
   // q / actuated rows are dead once FK has run; the work queue of the narrow phase reuses them
   const int q_words = std::max(std::max(h.nq, ld <= h.nq + 3 ? ld : 0), 1) * 32;
   const int act_words = std::max(std::max(act_cols, ld <= act_cols + 3 ? ld : 0), 1) * 32;
-  const int region0 = take(std::max(q_words + act_words, kQueueCap / 2));
+  const int region0 = take(std::max(q_words + act_words, stage_row_floats > 0 ? 0 : kQueueCap / 2));
   L->off_q = region0;
   L->off_act = region0 + q_words;
-  L->off_geom = take(std::max(h.n_dyn, 1) * kGeomFloats * 32);
+  const bool fk_only = stage_row_floats > 0;  // the FK kernels need no slab, queue or result rows
+  L->off_geom = take(fk_only ? 0 : std::max(h.n_dyn, 1) * kGeomFloats * 32);
   L->off_save = take(std::max(h.n_save, 1) * 12 * 32);
   L->off_queue = region0;
-  L->off_mask = take(std::max(h.mask_words, 1) * 32);
-  L->off_first = take(32);
-  L->stage_stride = stage_row_floats | 1;  // odd stride: conflict-free lane-private rows
-  L->off_stage = take(stage_row_floats ? 32 * L->stage_stride : 0);
+  L->off_mask = take(fk_only ? 0 : std::max(h.mask_words, 1) * 32);
+  L->off_first = take(fk_only ? 0 : 32);
+  // staging pitch in float4 units, odd (see stage_xf); 16-byte aligned region
+  L->stage_stride = (stage_row_floats / 4) | 1;
+  w = (w + 3) & ~3;
+  L->off_stage = take(stage_row_floats ? 32 * L->stage_stride * 4 : 0);
   L->words = w;
   L->table_bytes = static_cast<int32_t>(align16(h.total_bytes));
   const size_t fixed = 16 + L->table_bytes;
