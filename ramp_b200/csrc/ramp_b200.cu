@@ -179,6 +179,70 @@ __device__ __forceinline__ void load_rows(float* dst, const float* __restrict__ 
   __syncwarp();
 }
 
+// ---- software prefetch of the NEXT tile's rows.  Each warp works through load -> FK ->
+// store on its own, so without this the global-load latency of every tile is exposed
+// (long_scoreboard was the top stall of the FK kernel).  The next tile's float4s are fetched
+// into registers before the current tile's arithmetic and committed to shared memory after it.
+// kVec float4 per lane cover rows of up to 4 * kVec floats (8 in the FK kernels, 4 in the
+// register-tight validity kernel; wider rows fall back to the plain load)
+template <int kVec>
+struct RowPrefetch {
+  float4 v[kVec];
+  bool valid;  // the vector path applied (else commit falls back to load_rows)
+};
+
+template <int kVec>
+__device__ __forceinline__ bool rows_vectorisable(const float* base, int cols, int ld) {
+  return ld == cols && (cols & 3) == 0 && cols <= 4 * kVec && (reinterpret_cast<uintptr_t>(base) & 15) == 0;
+}
+
+template <int kVec>
+__device__ __forceinline__ void prefetch_rows(RowPrefetch<kVec>& pf, const float* __restrict__ src, int64_t row0, int64_t n_rows,
+                                              int cols, int ld, int lane) {
+  pf.valid = false;
+  if (row0 >= n_rows) return;
+  const float* base = src + row0 * ld;
+  if (!rows_vectorisable<kVec>(base, cols, ld)) return;
+  pf.valid = true;
+  const int n4 = static_cast<int>(imin64(32, n_rows - row0)) * cols / 4;
+  const float4* b4 = reinterpret_cast<const float4*>(base);
+#pragma unroll
+  for (int k = 0; k < kVec; ++k) {
+    const int e = lane + 32 * k;
+    if (e < n4) pf.v[k] = __ldg(b4 + e);
+  }
+}
+
+template <int kVec>
+__device__ __forceinline__ void commit_rows(const RowPrefetch<kVec>& pf, float* dst, const float* __restrict__ src, int64_t row0,
+                                            int64_t n_rows, int cols, int ld, int lane) {
+  if (!pf.valid) {
+    load_rows(dst, src, row0, n_rows, cols, ld, lane);
+    return;
+  }
+  const int rows = static_cast<int>(imin64(32, n_rows - row0));
+  const int n4 = rows * cols / 4;
+#pragma unroll
+  for (int k = 0; k < kVec; ++k) {
+    const int e = lane + 32 * k;
+    if (e < n4) {
+      const int r = (4 * e) / cols, c = (4 * e) - r * cols;
+      dst[(c + 0) * 32 + r] = pf.v[k].x;
+      dst[(c + 1) * 32 + r] = pf.v[k].y;
+      dst[(c + 2) * 32 + r] = pf.v[k].z;
+      dst[(c + 3) * 32 + r] = pf.v[k].w;
+    }
+  }
+  if (rows < 32) {
+    __syncwarp();
+    if (lane >= rows) {
+#pragma unroll 1
+      for (int c = 0; c < cols; ++c) dst[c * 32 + lane] = dst[c * 32];
+    }
+  }
+  __syncwarp();
+}
+
 // ---- actuated values -> Pinocchio q (reference robot_state.py:117-119: scatter, mimic,
 // then continuous).  Lane-private columns of shared memory, no cross-lane traffic.
 __device__ __forceinline__ void expand_q(const Warp& w) {
@@ -606,10 +670,13 @@ __global__ void __launch_bounds__(512, 1) check_kernel(const __grid_constant__ C
   int cols = actuated ? t.h->n_act : t.h->nq;
   if ((a.ld & 3) == 0 && a.ld <= cols + 3) cols = a.ld;  // padded rows: take the float4 path
   const int64_t ntiles = (a.n + 31) >> 5;
-  for (int64_t tile = static_cast<int64_t>(blockIdx.x) * nwarps + wid; tile < ntiles;
-       tile += static_cast<int64_t>(gridDim.x) * nwarps) {
+  const int64_t tile_step = static_cast<int64_t>(gridDim.x) * nwarps;
+  RowPrefetch<4> pf;
+  prefetch_rows(pf, a.q, (static_cast<int64_t>(blockIdx.x) * nwarps + wid) << 5, a.n, cols, a.ld, w.lane);
+  for (int64_t tile = static_cast<int64_t>(blockIdx.x) * nwarps + wid; tile < ntiles; tile += tile_step) {
     const int64_t row0 = tile << 5;
-    load_rows(actuated ? w.act : w.q, a.q, row0, a.n, cols, a.ld, w.lane);
+    commit_rows(pf, actuated ? w.act : w.q, a.q, row0, a.n, cols, a.ld, w.lane);
+    prefetch_rows(pf, a.q, (tile + tile_step) << 5, a.n, cols, a.ld, w.lane);
     if (actuated) expand_q(w);
     reset_results(w, want_mask ? t.h->mask_words : 0);
     fk_lane<0>(w);
@@ -758,10 +825,13 @@ __global__ void __launch_bounds__(512, 1) fk_kernel(const __grid_constant__ FkAr
   int cols = actuated ? t.h->n_act : t.h->nq;
   if ((a.ld & 3) == 0 && a.ld <= cols + 3) cols = a.ld;  // padded rows: take the float4 path
   const int64_t ntiles = (a.n + 31) >> 5;
-  for (int64_t tile = static_cast<int64_t>(blockIdx.x) * nwarps + wid; tile < ntiles;
-       tile += static_cast<int64_t>(gridDim.x) * nwarps) {
+  const int64_t tile_step = static_cast<int64_t>(gridDim.x) * nwarps;
+  RowPrefetch<8> pf;
+  prefetch_rows(pf, a.q, (static_cast<int64_t>(blockIdx.x) * nwarps + wid) << 5, a.n, cols, a.ld, w.lane);
+  for (int64_t tile = static_cast<int64_t>(blockIdx.x) * nwarps + wid; tile < ntiles; tile += tile_step) {
     const int64_t row0 = tile << 5;
-    load_rows(actuated ? w.act : w.q, a.q, row0, a.n, cols, a.ld, w.lane);
+    commit_rows(pf, actuated ? w.act : w.q, a.q, row0, a.n, cols, a.ld, w.lane);
+    prefetch_rows(pf, a.q, (tile + tile_step) << 5, a.n, cols, a.ld, w.lane);
     if (actuated) expand_q(w);
     // the bulk stores of the previous tile must have finished READING the staging rows
     asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
