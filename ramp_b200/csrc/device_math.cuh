@@ -316,13 +316,13 @@ __device__ __forceinline__ V3 closest_triangle(V3 a, V3 b, V3 c, V3& o0, V3& o1,
     o0 = b; o1 = c; on = 2;
     return b + (c - b) * ((d4 - d3) / ((d4 - d3) + (d5 - d6)));
   }
-  // interior: project the origin on the plane (more accurate in FP32 than barycentric sums)
-  const V3 n = cross(ab, ac);
-  const float nn = dot(n, n);
+  // interior: barycentric combination.  It must stay a CONVEX combination of the vertices (a
+  // point of the Minkowski difference, so |v| never drops below the true distance); projecting
+  // the origin on the plane instead breaks that for sliver triangles, whose FP32 normal is noise.
   on = 3;
-  if (nn > 0.f) return n * (dot(a, n) / nn);
   const float den = 1.f / (va + vb + vc);
-  return a + ab * (vb * den) + ac * (vc * den);
+  const float bv = clampf(vb * den, 0.f, 1.f), bw = clampf(vc * den, 0.f, 1.f - bv);
+  return a + ab * bv + ac * bw;
 }
 
 // Reduce the simplex to the sub-simplex closest to the origin and return that closest point.
@@ -350,9 +350,13 @@ __device__ __forceinline__ bool solve_simplex(Simplex& s, V3& out) {
   for (int f = 0; f < nfaces; ++f) {
     bool outside = true;
     if (tetra) {
-      const V3 n = cross(p1 - p0, p2 - p0);
-      const float so = -dot(p0, n), sd = dot(p3 - p0, n);
-      outside = so * sd < 0.f || sd == 0.f;
+      // The origin is outside this face when it lies on the other side than the opposite
+      // vertex.  A sliver tetrahedron (tiny height over the face) or an origin within rounding
+      // of the face plane makes those signs noise in FP32: treat both as "outside", i.e. fall
+      // back to the projection on the face, so a false "origin enclosed" cannot happen.
+      const V3 n = cross(p1 - p0, p2 - p0), e = p3 - p0;
+      const float so = -dot(p0, n), sd = dot(e, n), nn = dot(n, n);
+      outside = so * sd < 0.f || sd * sd <= 1e-10f * dot(e, e) * nn || so * so <= 1e-10f * dot(p0, p0) * nn;
     }
     if (outside) {
       outside_any = true;
@@ -408,7 +412,9 @@ enum { GJK_CONTINUE = 0, GJK_HIT = 1, GJK_MISS = 2 };
 // the first proof of separation / overlap.  On GJK_MISS / GJK_HIT with exact, dist holds the
 // core distance minus the swept radii.
 __device__ __forceinline__ int gjk_step(GjkLane& g, const GjkShape& A, const GjkShape& B, bool exact, float& dist) {
-  const float EPS_REL = 1e-5f, TINY2 = 1e-12f;
+  // |v| below 2e-5 m counts as touching: FP32 cannot resolve a simplex face through the origin
+  // any better, and such a pair is inside the +-1e-4 m margin band either way
+  const float EPS_REL = 1e-5f, TINY2 = 4e-10f;
   const float rs2 = g.rsum * g.rsum;
   V3 sa = mk(0.f, 0.f, 0.f), sb = sa;
 #pragma unroll 1
@@ -431,10 +437,14 @@ __device__ __forceinline__ int gjk_step(GjkLane& g, const GjkShape& A, const Gjk
     if (g.s.n == 0) g.s.p[0] = w; else if (g.s.n == 1) g.s.p[1] = w; else if (g.s.n == 2) g.s.p[2] = w; else g.s.p[3] = w;
     ++g.s.n;
     V3 nv;
-    if (solve_simplex(g.s, nv)) { dist = -g.rsum; return GJK_HIT; }
+    if (solve_simplex(g.s, nv)) {  // origin enclosed by the simplex
+      // ... which cannot be when a separating plane beyond the swept radii was already proven
+      if (g.lower > g.rsum) { dist = sqrtf(g.vv) - g.rsum; return GJK_MISS; }
+      g.vv = 0.f; dist = -g.rsum; return GJK_HIT;
+    }
     const float nvv = dot(nv, nv);
     if (nvv <= fmaxf(rs2, TINY2) && !exact) { dist = sqrtf(nvv) - g.rsum; return GJK_HIT; }
-    if (nvv <= TINY2) { dist = -g.rsum; return GJK_HIT; }
+    if (nvv <= TINY2) { g.vv = 0.f; dist = -g.rsum; return GJK_HIT; }
     if (g.it > 0 && nvv >= g.vv) done = true;  // no progress at FP32 resolution
     else { g.v = nv; g.vv = nvv; }
   }
@@ -444,6 +454,132 @@ __device__ __forceinline__ int gjk_step(GjkLane& g, const GjkShape& A, const Gjk
   // a stalled iteration far from convergence: trust the proven lower bound
   if (d <= g.rsum && g.lower > g.rsum) { dist = g.lower - g.rsum; return GJK_MISS; }
   return d <= g.rsum ? GJK_HIT : GJK_MISS;
+}
+
+// ------------------------------------------------------------------------------ EPA
+// Penetration depth of two overlapping cores (expanding polytope algorithm).  Only the signed
+// distance output (ramp_distance_batch) uses it; the boolean paths never do.  The polytope lives
+// in per-thread local memory.
+constexpr int kEpaMaxV = 68, kEpaMaxF = 160, kEpaIters = 64;
+
+struct EpaFace {
+  unsigned char a, b, c, alive;
+  V3 n;
+  float d;
+};
+
+__device__ __forceinline__ V3 mink_support(const GjkShape& A, const GjkShape& B, const Xf& rel, V3 d) {
+  const V3 sa = support(A.type, A.p0, A.p1, A.p2, A.verts, A.vcnt, d);
+  const V3 sb = support(B.type, B.p0, B.p1, B.p2, B.verts, B.vcnt, rot_t(rel, -d));
+  return sa - apply(rel, sb);
+}
+
+__device__ __noinline__ bool epa_face(const V3* vt, int a, int b, int c, EpaFace& f) {
+  V3 n = cross(vt[b] - vt[a], vt[c] - vt[a]);
+  const float l2 = dot(n, n);
+  f.a = a; f.b = b; f.c = c; f.alive = 0;
+  if (l2 < 1e-30f) return false;
+  n = n * rsqrtf(l2);
+  f.n = n; f.d = dot(n, vt[a]); f.alive = 1;
+  return true;
+}
+
+// Grow a degenerate terminal simplex of GJK into a tetrahedron around the origin.
+__device__ __noinline__ bool epa_enclose(const GjkShape& A, const GjkShape& B, const Xf& rel, Simplex& s) {
+  const V3 AX[6] = {{1, 0, 0}, {-1, 0, 0}, {0, 1, 0}, {0, -1, 0}, {0, 0, 1}, {0, 0, -1}};
+  if (s.n == 0) { s.p[0] = mink_support(A, B, rel, AX[0]); s.n = 1; }
+  if (s.n == 1) {
+    for (int k = 0; k < 6 && s.n == 1; ++k) {
+      const V3 w = mink_support(A, B, rel, AX[k]), e = w - s.p[0];
+      if (dot(e, e) > 1e-12f) { s.p[1] = w; s.n = 2; }
+    }
+    if (s.n == 1) return false;
+  }
+  if (s.n == 2) {
+    const V3 e = s.p[1] - s.p[0];
+    for (int k = 0; k < 6 && s.n == 2; k += 2) {
+      const V3 dir = cross(e, AX[k]);
+      if (dot(dir, dir) < 1e-12f) continue;
+      for (int sg = 0; sg < 2 && s.n == 2; ++sg) {
+        const V3 w = mink_support(A, B, rel, sg ? -dir : dir), n = cross(e, w - s.p[0]);
+        if (dot(n, n) > 1e-14f) { s.p[2] = w; s.n = 3; }
+      }
+    }
+    if (s.n == 2) return false;
+  }
+  if (s.n == 3) {
+    const V3 n = cross(s.p[1] - s.p[0], s.p[2] - s.p[0]);
+    for (int sg = 0; sg < 2 && s.n == 3; ++sg) {
+      const V3 w = mink_support(A, B, rel, sg ? -n : n);
+      if (fabsf(dot(w - s.p[0], n)) > 1e-7f * (1.f + dot(n, n))) { s.p[3] = w; s.n = 4; }
+    }
+    if (s.n == 3) return false;
+  }
+  return true;
+}
+
+__device__ __noinline__ float epa_depth(const GjkShape& A, const GjkShape& B, const Xf& rel, Simplex s) {
+  V3 vt[kEpaMaxV];
+  EpaFace fc[kEpaMaxF];
+  int nv = 0, nf = 0;
+  if (!epa_enclose(A, B, rel, s)) return 0.f;
+  for (int i = 0; i < 4; ++i) vt[nv++] = s.p[i];
+  for (int i = 0; i < 4; ++i) {  // faces (0,1,2|3) (0,1,3|2) (0,2,3|1) (1,2,3|0), wound outwards
+    int a = i == 3 ? 1 : 0, b = i < 2 ? 1 : 2, c = i == 0 ? 2 : 3;
+    const int opp = 6 - a - b - c;
+    const V3 n = cross(vt[b] - vt[a], vt[c] - vt[a]);
+    if (dot(n, vt[opp] - vt[a]) > 0.f) { const int t = b; b = c; c = t; }
+    if (!epa_face(vt, a, b, c, fc[nf++])) return 0.f;
+  }
+  float best = 0.f;
+  for (int it = 0; it < kEpaIters; ++it) {
+    int bi = -1;
+    float bd = 3.0e38f;
+    for (int i = 0; i < nf; ++i)
+      if (fc[i].alive && fc[i].d < bd) { bd = fc[i].d; bi = i; }
+    if (bi < 0) break;
+    best = bd;
+    const V3 w = mink_support(A, B, rel, fc[bi].n);
+    if (dot(fc[bi].n, w) - bd <= 1e-6f * (1.f + bd) || nv >= kEpaMaxV) break;
+    // drop the faces that see w, keep the horizon
+    unsigned char eh[96][2];
+    int ne = 0;
+    for (int i = 0; i < nf; ++i) {
+      if (!fc[i].alive || dot(fc[i].n, w) - fc[i].d <= 1e-7f) continue;
+      fc[i].alive = 0;
+      const unsigned char ed[3][2] = {{fc[i].a, fc[i].b}, {fc[i].b, fc[i].c}, {fc[i].c, fc[i].a}};
+      for (int k = 0; k < 3; ++k) {
+        int found = -1;
+        for (int e = 0; e < ne; ++e)
+          if (eh[e][0] == ed[k][1] && eh[e][1] == ed[k][0]) { found = e; break; }
+        if (found >= 0) { eh[found][0] = eh[ne - 1][0]; eh[found][1] = eh[ne - 1][1]; --ne; }
+        else if (ne < 96) { eh[ne][0] = ed[k][0]; eh[ne][1] = ed[k][1]; ++ne; }
+      }
+    }
+    if (ne == 0) break;
+    vt[nv] = w;
+    bool ok = true;
+    for (int e = 0; e < ne && ok; ++e) {
+      int slot = -1;
+      for (int i = 0; i < nf; ++i) if (!fc[i].alive) { slot = i; break; }
+      if (slot < 0) { if (nf >= kEpaMaxF) { ok = false; break; } slot = nf++; }
+      epa_face(vt, eh[e][0], eh[e][1], nv, fc[slot]);
+    }
+    ++nv;
+    if (!ok) break;
+  }
+  return best;
+}
+
+// Signed distance of two shapes through GJK (+ EPA when the cores overlap).
+__device__ __forceinline__ float gjk_signed_distance(const GjkShape& A, const GjkShape& B, const Xf& rel, float rsum) {
+  GjkLane g;
+  gjk_init(g, rel, rsum, -trans(rel));
+  float dist = 0.f;
+  int st = GJK_CONTINUE;
+  while (st == GJK_CONTINUE) st = gjk_step(g, A, B, true, dist);
+  if (st == GJK_MISS || g.vv > 0.f) return dist;  // cores apart: |v| - radii (negative if the sweeps overlap)
+  return -epa_depth(A, B, rel, g.s) - rsum;
 }
 
 }  // namespace ramp

@@ -431,29 +431,40 @@ __device__ __forceinline__ float swept_radius(const DGeom* g) {
   return (g->type == SH_SPHERE || g->type == SH_CAPSULE) ? g->p0 : 0.f;
 }
 
-// exact closed-form decision for the primitive classes; rel = pose of b in a's frame
-__device__ __forceinline__ bool closed_form_hit(int cls, const DGeom* ga, const DGeom* gb, const Xf& rel) {
+__device__ __forceinline__ int pair_class_of(int ta, int tb) {  // ta <= tb (pairs are stored ordered)
+  if (ta == SH_SPHERE && tb <= SH_CYLINDER) return kClsSphereSphere + tb;
+  if (ta == SH_CAPSULE && tb == SH_CAPSULE) return kClsCapsuleCapsule;
+  if (ta == SH_BOX && tb == SH_BOX) return kClsBoxBox;
+  return kClsGjk;
+}
+
+// exact closed-form signed distance of the primitive classes; rel = pose of b in a's frame
+__device__ __forceinline__ float closed_form_dist(int cls, const DGeom* ga, const DGeom* gb, const Xf& rel) {
   switch (cls) {
+    case kClsSphereSphere: return sqrtf(dot(trans(rel), trans(rel))) - ga->p0 - gb->p0;
     case kClsSphereCapsule: {  // a sphere, b capsule: sphere centre in b's frame
       const V3 c = rot_t(rel, -trans(rel));
-      return point_zseg_dist(c, gb->p1) - ga->p0 - gb->p0 <= 0.f;
+      return point_zseg_dist(c, gb->p1) - ga->p0 - gb->p0;
     }
     case kClsSphereBox: {
       const V3 c = rot_t(rel, -trans(rel));
-      return sphere_box_dist(c, gb->p0, gb->p1, gb->p2, ga->p0) <= 0.f;
+      return sphere_box_dist(c, gb->p0, gb->p1, gb->p2, ga->p0);
     }
     case kClsSphereCylinder: {
       const V3 c = rot_t(rel, -trans(rel));
-      return sphere_cyl_dist(c, gb->p0, gb->p1, ga->p0) <= 0.f;
+      return sphere_cyl_dist(c, gb->p0, gb->p1, ga->p0);
     }
     case kClsCapsuleCapsule: {
       const V3 zb = mk(rel.m[2], rel.m[6], rel.m[10]);
       const V3 p2 = trans(rel) - zb * gb->p1;
-      return seg_seg_dist(mk(0.f, 0.f, -ga->p1), mk(0.f, 0.f, 2.f * ga->p1), p2, zb * (2.f * gb->p1)) - ga->p0 -
-                 gb->p0 <= 0.f;
+      return seg_seg_dist(mk(0.f, 0.f, -ga->p1), mk(0.f, 0.f, 2.f * ga->p1), p2, zb * (2.f * gb->p1)) - ga->p0 - gb->p0;
     }
-    default: return false;
+    default: return 3.0e38f;
   }
+}
+
+__device__ __forceinline__ bool closed_form_hit(int cls, const DGeom* ga, const DGeom* gb, const Xf& rel) {
+  return closed_form_dist(cls, ga, gb, rel) <= 0.f;
 }
 
 __device__ __forceinline__ void narrow_phase(const Warp& w, bool stop_at_first, bool want_mask, const GjkQueue& gq,
@@ -862,6 +873,58 @@ __global__ void __launch_bounds__(512, 1) fk_kernel(const __grid_constant__ FkAr
     asm volatile("cp.async.bulk.commit_group;" ::: "memory");
   }
   asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+}
+
+// ------------------------------------------------------------- kernel: signed distances
+struct DistArgs {
+  const unsigned char* img;
+  const float* q;
+  int64_t n;
+  int32_t ld;
+  uint32_t flags;
+  const int32_t* sel;  // [n_sel] pair indices (device); nullptr = every pair
+  int32_t n_sel;
+  float* out;          // [n][n_sel]
+  SlabLayout L;
+};
+
+// pinocchio::computeDistance for selected pairs: FK per configuration, then lane l walks the
+// selected pairs of ITS configuration (closed forms, or GJK to convergence + EPA).  Not a
+// throughput kernel: lanes diverge in GJK/EPA and the EPA polytope sits in local memory.
+__global__ void __launch_bounds__(256, 1) distance_kernel(const __grid_constant__ DistArgs a) {
+  uint64_t* mbar = reinterpret_cast<uint64_t*>(g_smem);
+  unsigned char* tbl = g_smem + 16;
+  stage_tables(tbl, a.img, a.L.table_bytes, mbar);
+  const Tables t = make_tables(tbl);
+  const int nwarps = blockDim.x >> 5, wid = threadIdx.x >> 5;
+  float* slab = reinterpret_cast<float*>(tbl + a.L.table_bytes) + static_cast<size_t>(wid) * a.L.words;
+  const Warp w = make_warp(t, slab, a.L);
+  const bool actuated = a.flags & RAMP_Q_ACTUATED;
+  int cols = actuated ? t.h->n_act : t.h->nq;
+  if ((a.ld & 3) == 0 && a.ld <= cols + 3) cols = a.ld;
+  const int64_t ntiles = (a.n + 31) >> 5;
+  for (int64_t tile = static_cast<int64_t>(blockIdx.x) * nwarps + wid; tile < ntiles;
+       tile += static_cast<int64_t>(gridDim.x) * nwarps) {
+    const int64_t row0 = tile << 5;
+    load_rows(actuated ? w.act : w.q, a.q, row0, a.n, cols, a.ld, w.lane);
+    if (actuated) expand_q(w);
+    fk_lane<0>(w);
+    __syncwarp();
+    const int64_t row = row0 + w.lane;
+    for (int k = 0; k < a.n_sel; ++k) {
+      const int p = a.sel ? a.sel[k] : k;
+      const DPair pr = t.pairs[p];
+      const DGeom* ga = &t.geoms[pr.a];
+      const DGeom* gb = &t.geoms[pr.b];
+      const Xf rel = xf_inv_mul(geom_xf(w, ga->gslot, w.lane), geom_xf(w, gb->gslot, w.lane));
+      const int cls = pair_class_of(ga->type, gb->type);  // also for inactive pairs
+      float d = cls < kClsBoxBox ? closed_form_dist(cls, ga, gb, rel)
+                                 : gjk_signed_distance(load_shape(ga, t.verts), load_shape(gb, t.verts), rel,
+                                                       swept_radius(ga) + swept_radius(gb));
+      if (row < a.n) a.out[row * a.n_sel + k] = d;
+    }
+    __syncwarp();
+  }
 }
 
 // ------------------------------------------------------------------ kernels: edges
@@ -1642,6 +1705,45 @@ int ramp_abi_version(void) { return RAMP_B200_ABI_VERSION; }
 const char* ramp_last_error(void) { return g_err; }
 int64_t ramp_launch_count(void) { return g_launches.load(); }
 #ifdef RAMP_STATS
+int ramp_debug_image(const RampModel* m, unsigned char* out, int cap) {
+  const int n = static_cast<int>(m->image.size());
+  if (out && cap >= n) std::memcpy(out, m->image.data(), n);
+  return n;
+}
+}  // extern "C"
+namespace ramp {
+// single-thread trace of the exact-mode GJK for one pair (debug builds only)
+__global__ void debug_gjk_kernel(const float4* va, int na, const float4* vb, int nb, Xf rel, float* trace, int max_it) {
+  GjkShape A, B;
+  A.type = SH_CONVEX; A.vcnt = na; A.p0 = A.p1 = A.p2 = 0.f; A.verts = va;
+  B.type = SH_CONVEX; B.vcnt = nb; B.p0 = B.p1 = B.p2 = 0.f; B.verts = vb;
+  GjkLane g;
+  gjk_init(g, rel, 0.f, -trans(rel));
+  float dist = 0.f;
+  int st = GJK_CONTINUE, it = 0;
+  while (st == GJK_CONTINUE && it < max_it) {
+    st = gjk_step(g, A, B, true, dist);
+    trace[8 * it + 0] = g.vv; trace[8 * it + 1] = g.s.n; trace[8 * it + 2] = st; trace[8 * it + 3] = dist;
+    trace[8 * it + 4] = g.v.x; trace[8 * it + 5] = g.v.y; trace[8 * it + 6] = g.v.z; trace[8 * it + 7] = g.lower;
+    ++it;
+  }
+}
+}  // namespace ramp
+extern "C" {
+int ramp_debug_gjk(const float* h_va, int na, const float* h_vb, int nb, const float* h_rel, float* h_trace, int max_it) {
+  float4 *da, *db; float* dt;
+  cudaMalloc(&da, 16 * na); cudaMalloc(&db, 16 * nb); cudaMalloc(&dt, 32 * max_it);
+  cudaMemcpy(da, h_va, 16 * na, cudaMemcpyHostToDevice); cudaMemcpy(db, h_vb, 16 * nb, cudaMemcpyHostToDevice);
+  cudaMemset(dt, 0, 32 * max_it);
+  ramp::Xf rel; for (int k = 0; k < 12; ++k) rel.m[k] = h_rel[k];
+  ramp::debug_gjk_kernel<<<1, 1>>>(da, na, db, nb, rel, dt, max_it);
+  cudaMemcpy(h_trace, dt, 32 * max_it, cudaMemcpyDeviceToHost);
+  cudaFree(da); cudaFree(db); cudaFree(dt);
+  return 0;
+}
+#endif
+
+#ifdef RAMP_STATS
 int ramp_debug_stats(unsigned long long* out, int reset) {
   cudaDeviceSynchronize();
   cudaMemcpyFromSymbol(out, g_stats, sizeof(unsigned long long) * 64);
@@ -1871,8 +1973,41 @@ int ramp_check_batch_noalloc(const RampModel* m, const float* d_q, int64_t n, in
   return RAMP_OK;
 }
 
-int ramp_distance_batch(const RampModel*, const float*, int64_t, int32_t, uint32_t, const int32_t*, int32_t, float*, void*) {
-  return fail(RAMP_ERR_INVALID, "ramp_distance_batch is not implemented yet");
+int ramp_distance_batch(const RampModel* m, const float* d_q, int64_t n, int32_t ld, uint32_t flags, const int32_t* h_pair_idx,
+                        int32_t n_sel, float* d_dist, void* stream) {
+  if (int rc = check_q_args(m, d_q, n, ld, flags)) return rc;
+  const int np = m->hdr.n_pairs;
+  if (!h_pair_idx) n_sel = np;
+  if (n_sel < 0 || n_sel > np) return fail(RAMP_ERR_INVALID, "n_sel %d out of range (%d pairs)", n_sel, np);
+  if (n == 0 || n_sel == 0) return RAMP_OK;
+  if (!d_dist) return fail(RAMP_ERR_INVALID, "null d_dist");
+  if (h_pair_idx)
+    for (int k = 0; k < n_sel; ++k)
+      if (h_pair_idx[k] < 0 || h_pair_idx[k] >= np) return fail(RAMP_ERR_INVALID, "pair index %d out of range", h_pair_idx[k]);
+  CUDA_TRY(cudaSetDevice(m->device));
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  DistArgs a;
+  a.img = m->d_image; a.q = d_q; a.n = n; a.ld = ld; a.flags = flags; a.n_sel = n_sel; a.out = d_dist; a.sel = nullptr;
+  int32_t* d_sel = nullptr;
+  if (h_pair_idx) {
+    if (!m->pool) return fail(RAMP_ERR_ALLOC, "no memory pool for the pair selection");
+    if (cudaMallocFromPoolAsync(reinterpret_cast<void**>(&d_sel), sizeof(int32_t) * n_sel, m->pool, st) != cudaSuccess) {
+      cudaGetLastError();
+      return fail(RAMP_ERR_ALLOC, "cudaMallocFromPoolAsync for the pair selection failed");
+    }
+    CUDA_TRY(cudaMemcpyAsync(d_sel, h_pair_idx, sizeof(int32_t) * n_sel, cudaMemcpyHostToDevice, st));
+    a.sel = d_sel;
+  }
+  int nwarps; size_t smem;
+  if (int rc = plan_slabs(m, 0, m->hdr.n_act, &a.L, &nwarps, &smem, ld)) return rc;
+  nwarps = std::min(nwarps, 8);
+  smem = 16 + a.L.table_bytes + static_cast<size_t>(a.L.words) * 4 * nwarps;
+  if (int rc = set_smem(distance_kernel, smem)) return rc;
+  distance_kernel<<<grid_for(m, (n + 31) / 32, nwarps), nwarps * 32, smem, st>>>(a);
+  g_launches.fetch_add(1, std::memory_order_relaxed);
+  if (d_sel) CUDA_TRY(cudaFreeAsync(d_sel, st));
+  CUDA_TRY(cudaGetLastError());
+  return RAMP_OK;
 }
 
 int ramp_check_edges(const RampModel* m, const float* d_q0, const float* d_q1, int64_t n_edges, int32_t ld,

@@ -199,6 +199,21 @@ class GpuModel:
             res["pair_mask"] = bits.reshape(n, -1)[:, :npairs].bool()
         return res
 
+    def distance(self, q, pair_idx=None, *, actuated: bool = False) -> torch.Tensor:
+        """Signed distance of the selected pairs (all pairs when ``pair_idx`` is None):
+        float32[N, n_sel], positive separation / negative penetration depth (ramp_distance_batch)."""
+        q = self._q(q)
+        n = q.shape[0]
+        if pair_idx is None:
+            sel, n_sel = None, self.info()["n_pairs"]
+        else:
+            arr = np.ascontiguousarray(pair_idx, dtype=np.int32)
+            sel, n_sel = arr.ctypes.data_as(C.POINTER(C.c_int32)), len(arr)
+        out = torch.empty((n, n_sel), dtype=torch.float32, device=self.device)
+        _check(self.lib.ramp_distance_batch(self.handle, q.data_ptr(), n, q.shape[1], D.Q_ACTUATED if actuated else 0,
+                                            sel, n_sel, out.data_ptr(), _stream_ptr(self.device)), "ramp_distance_batch")
+        return out
+
     def check_raw(self, q: torch.Tensor, hit: torch.Tensor, flags: int = 0) -> None:
         """Zero-overhead variant for benchmarks: caller-owned contiguous tensors, no allocations."""
         _check(self.lib.ramp_check_batch(self.handle, q.data_ptr(), q.shape[0], q.shape[1], flags, hit.data_ptr(),

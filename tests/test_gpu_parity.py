@@ -235,3 +235,36 @@ def test_empty_and_errors(built):
         rm.gpu.check(torch.zeros((4, 2), dtype=torch.float32, device="cuda"))  # ld < nq
     with pytest.raises(RampGpuError):
         rm.gpu.forward_kinematics(torch.zeros((4, 3), dtype=torch.float32, device="cuda"), actuated=True)  # no qmap
+
+
+@pytest.mark.parametrize("name,scene,n", [("rrr/floating_configs", "capsule", 4000), ("rrr_mj/configs", "obstacles", 4000),
+                                          ("panda/configs", "capsule", 3000), ("ur5e/configs", "obstacles", 3000)])
+def test_signed_distance_matches_oracle(built, name, scene, n):
+    """ramp_distance_batch (closed forms, GJK to convergence, EPA) against the oracle's signed
+    distance of every pair.  Separations agree to 5e-5 (1 + d) m (FP32 GJK converges to a relative
+    1e-5); penetration depths, which both sides reach through an expanding polytope (FP32, 64
+    iterations here; curved shapes converge slowly), to 1e-3 m + 2 % of the depth."""
+    from oracle import oracle
+    from ramp_b200 import workloads
+    from ramp_b200.desc import ModelDesc
+
+    rm, rs = _setup(name, scene)
+    q = workloads.sample_q(rm.model, n, seed=13)
+    got = rm.gpu.distance(torch.from_numpy(q).cuda()).cpu().numpy().astype(np.float64)
+    oracle.set_params(1e-8, 128, 1e-8, 255)
+    try:
+        ref = oracle.check(ModelDesc(rm.model, rm.collision_model), q[:, : rm.model.nq].astype(np.float64))["pair_dist"]
+    finally:
+        oracle.set_params()
+    sep = ref > 1e-4
+    pen = ref < -1e-4
+    assert sep.sum() > 1000 and pen.sum() > 20
+    err_sep = (np.abs(got - ref) / (1.0 + np.abs(ref)))[sep].max()
+    err_pen = (np.abs(got - ref) / (1e-3 + 0.02 * np.abs(ref)))[pen].max()
+    print(name, dict(pairs=ref.size, separated=int(sep.sum()), penetrating=int(pen.sum()), err_sep=err_sep, err_pen=err_pen))
+    assert err_sep < 5e-5 and err_pen < 1.0
+    assert ((got <= 0) == (ref <= 0))[sep | pen].all()  # the sign is the collision boolean
+    # a sub-selection returns the same columns; RobotState.compute_distance is one of them
+    sel = [0, ref.shape[1] - 1]
+    sub = rm.gpu.distance(torch.from_numpy(q[:16]).cuda(), sel).cpu().numpy()
+    assert np.allclose(sub, got[:16][:, sel], atol=1e-6)
