@@ -69,7 +69,7 @@ struct DPair {  // 8 words; a/b ordered so that type(a) <= type(b)
   int32_t a, b, cls;
   float rs2;  // (bound_r(a)+bound_r(b))^2, inflated for culls, exact for sphere-sphere
   float sa_out, sb_out, rsum_out;  // outer capsules of a and b (GJK class): half lengths, radius sum
-  int32_t pad;
+  float slack;  // widening of every conservative test: 1e-5 m + the pair's share of non-rigid placements
 };
 static_assert(sizeof(DPair) == 32, "DPair");
 

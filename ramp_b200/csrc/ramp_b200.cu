@@ -41,7 +41,7 @@ struct Tables {
   const DGeom* geoms;
   const DPair* pairs;
   const float4* verts;
-  const float* stat;  // [n_static][9]: x axis, z axis, translation
+  const float* stat;  // [n_static][12]: x axis, z axis, translation, y axis
   const int32_t* dyn; // slot -> geometry index
   const int32_t* act;
   const DMimic* mimic;
@@ -290,6 +290,9 @@ __device__ __forceinline__ Xf load_slab_xf(const float* slab, int slot, int lane
 // (and in the static table): the y axis is z cross x.  A quarter less shared memory per warp
 // means more resident warps, and stage 1 only ever reads z and t.
 constexpr int kGeomFloats = 9;
+// static placements keep their own y axis too (x, z, t, y): a scene object may carry a rotation
+// that is not orthonormal (the reference builds poses from un-normalised quaternions)
+constexpr int kStatFloats = 12;
 
 __device__ __forceinline__ void store_geom_xf(float* slab, int slot, int lane, const Xf& x) {
   float* p = slab + slot * kGeomFloats * 32 + lane;
@@ -300,10 +303,10 @@ __device__ __forceinline__ void store_geom_xf(float* slab, int slot, int lane, c
 
 // World placement of geometry g for configuration c (lane-divergent g and c allowed).
 __device__ __forceinline__ Xf geom_xf(const Warp& w, int gslot, int c) {
-  const float* p = gslot >= 0 ? w.geom + gslot * kGeomFloats * 32 + c : w.t.stat + (-1 - gslot) * kGeomFloats;
+  const float* p = gslot >= 0 ? w.geom + gslot * kGeomFloats * 32 + c : w.t.stat + (-1 - gslot) * kStatFloats;
   const int st = gslot >= 0 ? 32 : 1;
   const V3 x = mk(p[0], p[st], p[2 * st]), z = mk(p[3 * st], p[4 * st], p[5 * st]);
-  const V3 y = cross(z, x);
+  const V3 y = gslot >= 0 ? cross(z, x) : mk(p[9], p[10], p[11]);
   Xf o;
   o.m[0] = x.x; o.m[1] = y.x; o.m[2] = z.x; o.m[3] = p[6 * st];
   o.m[4] = x.y; o.m[5] = y.y; o.m[6] = z.y; o.m[7] = p[7 * st];
@@ -488,8 +491,8 @@ __device__ __forceinline__ void narrow_phase(const Warp& w, bool stop_at_first, 
     auto sphere = [&](int p, const DPair& pr) {
       S1 r;
       const int sa = w.t.geoms[pr.a].gslot, sb = w.t.geoms[pr.b].gslot;
-      r.pa = sa >= 0 ? w.geom + sa * kGeomFloats * 32 + l : w.t.stat + (-1 - sa) * kGeomFloats;
-      r.pb = sb >= 0 ? w.geom + sb * kGeomFloats * 32 + l : w.t.stat + (-1 - sb) * kGeomFloats;
+      r.pa = sa >= 0 ? w.geom + sa * kGeomFloats * 32 + l : w.t.stat + (-1 - sa) * kStatFloats;
+      r.pb = sb >= 0 ? w.geom + sb * kGeomFloats * 32 + l : w.t.stat + (-1 - sb) * kStatFloats;
       r.sta = sa >= 0 ? 32 : 1; r.stb = sb >= 0 ? 32 : 1;
       r.ta = mk(r.pa[6 * r.sta], r.pa[7 * r.sta], r.pa[8 * r.sta]);
       r.tb = mk(r.pb[6 * r.stb], r.pb[7 * r.stb], r.pb[8 * r.stb]);
@@ -557,11 +560,11 @@ __device__ __forceinline__ void narrow_phase(const Warp& w, bool stop_at_first, 
             const V3 zb = mk(rel.m[2], rel.m[6], rel.m[10]);
             v0 = seg_seg_witness(mk(0.f, 0.f, -ga->s_in), mk(0.f, 0.f, 2.f * ga->s_in), trans(rel) - zb * gb->s_in,
                                  zb * (2.f * gb->s_in));
-            const float rin = ga->r_in + gb->r_in - 1e-5f;
+            const float rin = ga->r_in + gb->r_in - pr.slack;
             if (rin > 0.f && dot(v0, v0) < rin * rin) { record_hit(w, c, p, want_mask); decided = true; }
           }
           if (!decided) {
-            const bool ov = obb_overlap(ha, hb, rel, bb ? 0.f : 1e-5f);
+            const bool ov = obb_overlap(ha, hb, rel, bb ? 0.f : pr.slack);
             if (ov && bb) record_hit(w, c, p, want_mask);
             to_gjk = ov && !bb;
           }
@@ -1346,6 +1349,7 @@ static int build_image(RampModel* m) {
   }
   // geometries
   int n_static = 0, n_lists = 0;
+  std::vector<double> nonrigid(ng, 0.0);  // max |R^T R - I| of each placement
   std::vector<std::vector<int>> by_joint(nj);
   for (int g = 0; g < ng; ++g) {
     const bool scene = g >= n_robot;
@@ -1480,10 +1484,15 @@ static int build_image(RampModel* m) {
     d.hx = static_cast<float>(hx); d.hy = static_cast<float>(hy); d.hz = static_cast<float>(hz);
     d.bound_r = static_cast<float>(br);
     for (int k = 0; k < 12; ++k) { d.pl[k] = static_cast<float>(pl[k]); d.opl[k] = static_cast<float>(src.placement[k]); }
+    for (int i = 0; i < 3; ++i)
+      for (int j = 0; j < 3; ++j) {
+        const double gram = pl[i] * pl[j] + pl[4 + i] * pl[4 + j] + pl[8 + i] * pl[8 + j];
+        nonrigid[g] = std::max(nonrigid[g], std::fabs(gram - (i == j ? 1.0 : 0.0)));
+      }
     if (src.parent_joint < 0) {
       d.gslot = -1 - n_static++;
       // same 9-float form as the slab: x axis, z axis, translation
-      for (int k : {0, 4, 8, 2, 6, 10, 3, 7, 11}) stat.push_back(d.pl[k]);
+      for (int k : {0, 4, 8, 2, 6, 10, 3, 7, 11, 1, 5, 9}) stat.push_back(d.pl[k]);
     } else {
       by_joint[src.parent_joint].push_back(g);
     }
@@ -1510,8 +1519,11 @@ static int build_image(RampModel* m) {
     // the sphere-sphere test is the decision itself; every other class uses it as a cull
     d.rs2 = static_cast<float>(d.cls == kClsSphereSphere ? rs * rs : rs * rs * (1.0 + 1e-5) + 1e-9);
     d.sa_out = dg[a].s_out; d.sb_out = dg[b].s_out;
-    d.rsum_out = dg[a].r_out + dg[b].r_out + 1e-5f;
-    d.pad = 0;
+    // Conservative tests are widened by 1e-5 m, plus -- when a placement is not a rigid
+    // motion -- the amount by which lengths measured in its frame can be off
+    const double nr = nonrigid[a] + nonrigid[b];
+    d.slack = static_cast<float>(1e-5 + (nr > 1e-6 ? 2.0 * nr * rs : 0.0));
+    d.rsum_out = dg[a].r_out + dg[b].r_out + d.slack;
   }
   // q map
   std::vector<DMimic> dm(m->mimic_dst.size());
@@ -1713,16 +1725,17 @@ int ramp_debug_image(const RampModel* m, unsigned char* out, int cap) {
 }  // extern "C"
 namespace ramp {
 // single-thread trace of the exact-mode GJK for one pair (debug builds only)
-__global__ void debug_gjk_kernel(const float4* va, int na, const float4* vb, int nb, Xf rel, float* trace, int max_it) {
+__global__ void debug_gjk_kernel(const float4* va, int na, const float4* vb, int nb, Xf rel, float* trace, int max_it,
+                                 float rsum, V3 v0, int use_v0, int exact) {
   GjkShape A, B;
   A.type = SH_CONVEX; A.vcnt = na; A.p0 = A.p1 = A.p2 = 0.f; A.verts = va;
   B.type = SH_CONVEX; B.vcnt = nb; B.p0 = B.p1 = B.p2 = 0.f; B.verts = vb;
   GjkLane g;
-  gjk_init(g, rel, 0.f, -trans(rel));
+  gjk_init(g, rel, rsum, use_v0 ? v0 : -trans(rel));
   float dist = 0.f;
   int st = GJK_CONTINUE, it = 0;
   while (st == GJK_CONTINUE && it < max_it) {
-    st = gjk_step(g, A, B, true, dist);
+    st = gjk_step(g, A, B, exact != 0, dist);
     trace[8 * it + 0] = g.vv; trace[8 * it + 1] = g.s.n; trace[8 * it + 2] = st; trace[8 * it + 3] = dist;
     trace[8 * it + 4] = g.v.x; trace[8 * it + 5] = g.v.y; trace[8 * it + 6] = g.v.z; trace[8 * it + 7] = g.lower;
     ++it;
@@ -1730,13 +1743,15 @@ __global__ void debug_gjk_kernel(const float4* va, int na, const float4* vb, int
 }
 }  // namespace ramp
 extern "C" {
-int ramp_debug_gjk(const float* h_va, int na, const float* h_vb, int nb, const float* h_rel, float* h_trace, int max_it) {
+int ramp_debug_gjk(const float* h_va, int na, const float* h_vb, int nb, const float* h_rel, float* h_trace, int max_it,
+                   float rsum, const float* v0, int exact) {
   float4 *da, *db; float* dt;
   cudaMalloc(&da, 16 * na); cudaMalloc(&db, 16 * nb); cudaMalloc(&dt, 32 * max_it);
   cudaMemcpy(da, h_va, 16 * na, cudaMemcpyHostToDevice); cudaMemcpy(db, h_vb, 16 * nb, cudaMemcpyHostToDevice);
   cudaMemset(dt, 0, 32 * max_it);
   ramp::Xf rel; for (int k = 0; k < 12; ++k) rel.m[k] = h_rel[k];
-  ramp::debug_gjk_kernel<<<1, 1>>>(da, na, db, nb, rel, dt, max_it);
+  ramp::V3 vv0{v0 ? v0[0] : 0.f, v0 ? v0[1] : 0.f, v0 ? v0[2] : 0.f};
+  ramp::debug_gjk_kernel<<<1, 1>>>(da, na, db, nb, rel, dt, max_it, rsum, vv0, v0 != nullptr, exact);
   cudaMemcpy(h_trace, dt, 32 * max_it, cudaMemcpyDeviceToHost);
   cudaFree(da); cudaFree(db); cudaFree(dt);
   return 0;

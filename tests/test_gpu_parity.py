@@ -268,3 +268,26 @@ def test_signed_distance_matches_oracle(built, name, scene, n):
     sel = [0, ref.shape[1] - 1]
     sub = rm.gpu.distance(torch.from_numpy(q[:16]).cuda(), sel).cpu().numpy()
     assert np.allclose(sub, got[:16][:, sel], atol=1e-6)
+
+
+@pytest.mark.parametrize("name,scene,n", [("ur5e/configs", "obstacles", 400000), ("panda/configs", "capsule", 400000),
+                                          ("unitree_h1/configs", None, 60000), ("rrr/floating_configs", "capsule", 400000)])
+def test_large_sweep_flags_and_first_pair(built, name, scene, n):
+    """A wide sweep for rare numerical events (FP32 GJK degeneracies show up once in 10^3-10^4
+    near-contact pairs): flags and first-pair indices against the oracle, margin band honoured."""
+    from oracle import oracle
+    from ramp_b200 import workloads
+    from ramp_b200.desc import ModelDesc
+
+    rm, _ = _setup(name, scene)
+    q = workloads.sample_q(rm.model, n, seed=101)
+    res = rm.gpu.check(torch.from_numpy(q).cuda(), first_pair=True)
+    hit, first = res["hit"].cpu().numpy(), res["first_pair"].cpu().numpy()
+    ref = oracle.check(ModelDesc(rm.model, rm.collision_model), q[:, : rm.model.nq].astype(np.float64))
+    pd = ref["pair_dist"]
+    outside = np.abs(ref["min_dist"]) > BAND
+    clean = (np.abs(pd) > BAND).all(axis=1)
+    bad_cfg = int((hit != ref["hit"])[outside].sum())
+    bad_first = int((first != ref["first_pair"])[clean].sum())
+    print(name, dict(n=n, colliding=int(ref["hit"].sum()), in_band=int((~outside).sum()), bad_cfg=bad_cfg, bad_first=bad_first))
+    assert bad_cfg == 0 and bad_first == 0
