@@ -81,3 +81,38 @@ def adjacent_collisions(robot_model) -> list:
             continue
         out.add((par.name, cur.name, DisabledReason.ADJACENT))
     return list(out)
+
+
+def sampled_collisions(robot_model, n_samples: int = 1 << 17, seed: int = 0, batch: int = 1 << 17) -> list:
+    """ALWAYS / NEVER in collision, the two reasons the reference leaves as TODOs
+    (reference src/ramp/compute_disable_collisions.py:229-230): the all-pairs mode of the
+    validity kernel over ``n_samples`` random configurations, reduced per pair.  Returns
+    [(link1, link2, DisabledReason.ALWAYS | NEVER), ...] for the pairs currently enabled."""
+    import torch
+
+    from ramp_b200 import workloads
+
+    gpu = robot_model.gpu
+    cm = robot_model.collision_model
+    npairs = len(cm.collisionPairs)
+    if npairs == 0:
+        return []
+    any_hit = torch.zeros(npairs, dtype=torch.bool, device=gpu.device)
+    all_hit = torch.ones(npairs, dtype=torch.bool, device=gpu.device)
+    done = 0
+    while done < n_samples:
+        n = min(batch, n_samples - done)
+        q = workloads.sample_q_torch(robot_model.model, n, seed=seed + done, device=gpu.device)
+        mask = gpu.check(q, pair_mask=True)["pair_mask"]
+        any_hit |= mask.any(dim=0)
+        all_hit &= mask.all(dim=0)
+        done += n
+    any_hit, all_hit = any_hit.cpu().numpy(), all_hit.cpu().numpy()
+    out = []
+    for k, pair in enumerate(cm.collisionPairs):
+        names = get_collision_pair_names(robot_model.model, cm, pair)
+        if all_hit[k]:
+            out.append((*names, DisabledReason.ALWAYS))
+        elif not any_hit[k]:
+            out.append((*names, DisabledReason.NEVER))
+    return out

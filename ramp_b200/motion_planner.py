@@ -110,6 +110,22 @@ class MotionPlanner:
         hit = self._robot_model.gpu.check(states.astype(np.float32), actuated=True)["hit"].cpu().numpy()
         return inb & ~hit
 
+    def project(self, states) -> np.ndarray:
+        """TCP positions of a batch of actuated states: the projection
+        ``ProjectionEvaluatorLinkPose`` evaluates one FK at a time (reference
+        src/ramp/motion_planner.py:209-244,485-506), here one ramp_fk_batch call."""
+        tcp = self._robot_model[self._group_name].tcp_link_name
+        assert tcp is not None, f"tcp_link_name is not defined for group '{self._group_name}'"
+        self._sync_gpu()
+        model = self._robot_model.model
+        frame = model.frames[model.getFrameId(tcp)]
+        states = np.atleast_2d(np.asarray(states, dtype=np.float32))
+        if frame.parentJoint == 0:
+            return np.tile(frame.placement.translation, (len(states), 1))
+        omi = self._robot_model.gpu.forward_kinematics(states, actuated=True)[:, frame.parentJoint - 1]
+        p = torch.as_tensor(frame.placement.translation, dtype=torch.float32, device=omi.device)
+        return (omi[:, :, :3] @ p + omi[:, :, 3]).cpu().numpy()
+
     # ---------------------------------------------------------------------- planning
     def _sample(self) -> np.ndarray:
         return spaces.sample_uniform(self.space, 1, self.rng, position_bound=10.0)[0]

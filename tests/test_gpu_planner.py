@@ -111,3 +111,38 @@ def test_get_frame_pose_and_collision_pairs(built):
     assert ("link1", "link3") in pairs or ("link1", "end_effector") in pairs
     assert default_collisions(rm) == []  # nothing collides at the neutral configuration
     assert rs.check_collision() and rs.check_collision(verbose=True)
+
+
+def test_sampled_always_never_pairs(built):
+    """ALWAYS / NEVER classification (the reference's TODO): rrr_mj has no SRDF, so its adjacent
+    link boxes overlap in every configuration; far-apart pairs never touch."""
+    from ramp_b200 import load_robot_model
+    from ramp_b200.compute_disable_collisions import DisabledReason, disable_collision, sampled_collisions
+
+    rm = load_robot_model("zoo::rrr_mj/configs")
+    found = sampled_collisions(rm, n_samples=1 << 15)
+    always = {(a, b) for a, b, r in found if r == DisabledReason.ALWAYS}
+    assert {("link1", "link2"), ("link2", "link3")} <= always
+    n0 = len(rm.collision_model.collisionPairs)
+    disable_collision(rm, found)
+    assert len(rm.collision_model.collisionPairs) == n0 - len(found)
+    # with those pairs gone the home state of the MJCF robot is valid (as its URDF twin's is)
+    from ramp_b200 import RobotState
+
+    assert not RobotState.from_named_state(rm, "arm", "home").check_collision()
+
+
+def test_projection_batch_matches_frame_pose(built):
+    from ramp_b200 import MotionPlanner, RobotState, load_robot_model
+
+    rm = load_robot_model("zoo::panda/configs")
+    planner = MotionPlanner(rm, "arm")
+    rs = RobotState.from_named_state(rm, "arm", "home")
+    planner.set_reference_state(rs)
+    rng = np.random.default_rng(1)
+    states = rng.uniform(-1.5, 1.5, (64, 7))
+    states[:, 3] = rng.uniform(-3.0, -0.1, 64)
+    got = planner.project(states)
+    for i in (0, 17, 63):
+        rs.set_group_qpos("arm", states[i])
+        assert np.allclose(got[i], rs.get_frame_pose("panda_hand_tcp").translation, atol=2e-5)
