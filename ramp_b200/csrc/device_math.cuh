@@ -238,10 +238,12 @@ __device__ __forceinline__ V3 seg_seg_witness(V3 p1, V3 d1, V3 p2, V3 d2) {
   const float EPS = 1e-20f;
   // branch-light form of the clamped 2x2 solve (Ericson, Real-Time Collision Detection 5.1.9)
   const float den = fmaf(a, e, -b * b);
-  float s = (a > EPS && den > EPS) ? clampf((b * f - c * e) / den, 0.f, 1.f) : 0.f;
-  float t = e > EPS ? (fmaf(b, s, f)) / e : 0.f;
+  // __fdividef (2 ulp): the parameters only place the closest points; every user of the
+  // result compares against a radius sum with at least 1e-5 m of slack or of margin band
+  float s = (a > EPS && den > EPS) ? clampf(__fdividef(b * f - c * e, den), 0.f, 1.f) : 0.f;
+  float t = e > EPS ? __fdividef(fmaf(b, s, f), e) : 0.f;
   const float tc = clampf(t, 0.f, 1.f);
-  if (tc != t || e <= EPS) s = a > EPS ? clampf((b * tc - c) / a, 0.f, 1.f) : 0.f;
+  if (tc != t || e <= EPS) s = a > EPS ? clampf(__fdividef(b * tc - c, a), 0.f, 1.f) : 0.f;
   return (r + d1 * s) - d2 * tc;
 }
 

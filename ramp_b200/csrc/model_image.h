@@ -66,9 +66,12 @@ struct DGeom {  // 40 words
 static_assert(sizeof(DGeom) == 160, "DGeom");
 
 struct DPair {  // 8 words; a/b ordered so that type(a) <= type(b)
-  int32_t a, b, cls;
+  int16_t a, b;    // geometry indices
+  int16_t sa, sb;  // their gslot values (>= 0 slab slot, < 0 static placement), copied here so
+                   // stage 1 does not chase the geometry table
+  int32_t cls;
   float rs2;  // (bound_r(a)+bound_r(b))^2, inflated for culls, exact for sphere-sphere
-  float sa_out, sb_out, rsum_out;  // outer capsules of a and b (GJK class): half lengths, radius sum
+  float ha_out, hb_out, rsum_out;  // outer capsules of a and b (GJK class): half lengths, radius sum
   float slack;  // widening of every conservative test: 1e-5 m + the pair's share of non-rigid placements
 };
 static_assert(sizeof(DPair) == 32, "DPair");

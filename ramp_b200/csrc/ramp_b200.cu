@@ -490,7 +490,7 @@ __device__ __forceinline__ void narrow_phase(const Warp& w, bool stop_at_first, 
     };
     auto sphere = [&](int p, const DPair& pr) {
       S1 r;
-      const int sa = w.t.geoms[pr.a].gslot, sb = w.t.geoms[pr.b].gslot;
+      const int sa = pr.sa, sb = pr.sb;
       r.pa = sa >= 0 ? w.geom + sa * kGeomFloats * 32 + l : w.t.stat + (-1 - sa) * kStatFloats;
       r.pb = sb >= 0 ? w.geom + sb * kGeomFloats * 32 + l : w.t.stat + (-1 - sb) * kStatFloats;
       r.sta = sa >= 0 ? 32 : 1; r.stb = sb >= 0 ? 32 : 1;
@@ -505,7 +505,7 @@ __device__ __forceinline__ void narrow_phase(const Warp& w, bool stop_at_first, 
     auto capsule = [&](const DPair& pr, S1& r) {
       if (pr.cls == kClsGjk && __any_sync(FULL, r.pass)) {
         const V3 za = mk(r.pa[3 * r.sta], r.pa[4 * r.sta], r.pa[5 * r.sta]), zb = mk(r.pb[3 * r.stb], r.pb[4 * r.stb], r.pb[5 * r.stb]);
-        const V3 wv = seg_seg_witness(r.ta - za * pr.sa_out, za * (2.f * pr.sa_out), r.tb - zb * pr.sb_out, zb * (2.f * pr.sb_out));
+        const V3 wv = seg_seg_witness(r.ta - za * pr.ha_out, za * (2.f * pr.ha_out), r.tb - zb * pr.hb_out, zb * (2.f * pr.hb_out));
         r.pass = r.pass && dot(wv, wv) <= pr.rsum_out * pr.rsum_out;
       }
     };
@@ -1512,13 +1512,14 @@ static int build_image(RampModel* m) {
     if (a < 0 || b < 0 || a >= ng || b >= ng || a == b) return fail(RAMP_ERR_INVALID, "pair %d: bad geometry indices (%d, %d)", p, a, b);
     if (dg[a].type > dg[b].type) std::swap(a, b);
     DPair& d = dp[p];
-    d.a = a; d.b = b;
+    d.a = static_cast<int16_t>(a); d.b = static_cast<int16_t>(b);
+    d.sa = static_cast<int16_t>(dg[a].gslot); d.sb = static_cast<int16_t>(dg[b].gslot);
     d.cls = m->pair_active[p] ? pair_class(dg[a].type, dg[b].type) : kClsInactive;
     n_gjk += d.cls == kClsGjk;
     const double rs = static_cast<double>(dg[a].bound_r) + dg[b].bound_r;
     // the sphere-sphere test is the decision itself; every other class uses it as a cull
     d.rs2 = static_cast<float>(d.cls == kClsSphereSphere ? rs * rs : rs * rs * (1.0 + 1e-5) + 1e-9);
-    d.sa_out = dg[a].s_out; d.sb_out = dg[b].s_out;
+    d.ha_out = dg[a].s_out; d.hb_out = dg[b].s_out;
     // Conservative tests are widened by 1e-5 m, plus -- when a placement is not a rigid
     // motion -- the amount by which lengths measured in its frame can be off
     const double nr = nonrigid[a] + nonrigid[b];
