@@ -479,8 +479,7 @@ __device__ __forceinline__ void narrow_phase(const Warp& w, bool stop_at_first, 
     const int chunk_end = min(chunk + kChunkPairs, h->n_pairs);
     const int my_first = w.first[l];
     int qn = 0;
-    // ---- stage 1: bounding spheres, then outer capsules; lane = configuration, pair index
-    // uniform.  Two pairs per trip: their shared-memory loads and arithmetic are independent,
+    // ---- stage 1: bounding spheres; lane = configuration, pair index uniform.  Two pairs per trip: their shared-memory loads and arithmetic are independent,
     // which matters because only a few warps fit next to the slabs (latency, not issue, bound).
     struct S1 {
       const float *pa, *pb;
@@ -500,15 +499,6 @@ __device__ __forceinline__ void narrow_phase(const Warp& w, bool stop_at_first, 
       r.pass = pr.cls != kClsInactive && !(stop_at_first && my_first < p) && dot(d, d) <= pr.rs2;
       return r;
     };
-    // GJK class: the OUTER capsules (around each geometry's local z axis) cull most of what
-    // the spheres let through; skipped when no lane of the warp passed the sphere test
-    auto capsule = [&](const DPair& pr, S1& r) {
-      if (pr.cls == kClsGjk && __any_sync(FULL, r.pass)) {
-        const V3 za = mk(r.pa[3 * r.sta], r.pa[4 * r.sta], r.pa[5 * r.sta]), zb = mk(r.pb[3 * r.stb], r.pb[4 * r.stb], r.pb[5 * r.stb]);
-        const V3 wv = seg_seg_witness(r.ta - za * pr.ha_out, za * (2.f * pr.ha_out), r.tb - zb * pr.hb_out, zb * (2.f * pr.hb_out));
-        r.pass = r.pass && dot(wv, wv) <= pr.rsum_out * pr.rsum_out;
-      }
-    };
     auto push = [&](int p, const DPair& pr, bool pass) {
       if (pr.cls == kClsSphereSphere) {  // the sphere test was the decision itself
         if (pass) record_hit(w, l, p, want_mask);
@@ -526,12 +516,41 @@ __device__ __forceinline__ void narrow_phase(const Warp& w, bool stop_at_first, 
       S1 r0 = sphere(p, pr0);
       S1 r1 = sphere(p + 1, pr1);
       r1.pass = r1.pass && two;
-      capsule(pr0, r0);
-      capsule(pr1, r1);
       push(p, pr0, r0.pass);
       if (two) push(p + 1, pr1, r1.pass);
     }
     __syncwarp();
+    // ---- stage 1.5: OUTER capsules for the GJK class, on dense groups of 32 survivors of the
+    // sphere test (only ~20 % of the lanes pass it, so testing capsules per lane in stage 1
+    // would waste four lanes in five).  Needs just the z axis and the origin of each placement.
+    {
+      int kept = 0;
+#pragma unroll 1
+      for (int base = 0; base < qn; base += 32) {
+        const bool live = base + l < qn;
+        const int item = live ? w.queue[base + l] : 0;
+        bool keep = live;
+        if (live) {
+          const int c = item & 31;
+          const DPair pr = w.t.pairs[chunk + (item >> 5)];
+          if (pr.cls == kClsGjk) {
+            const float* pa = pr.sa >= 0 ? w.geom + pr.sa * kGeomFloats * 32 + c : w.t.stat + (-1 - pr.sa) * kStatFloats;
+            const float* pb = pr.sb >= 0 ? w.geom + pr.sb * kGeomFloats * 32 + c : w.t.stat + (-1 - pr.sb) * kStatFloats;
+            const int sta = pr.sa >= 0 ? 32 : 1, stb = pr.sb >= 0 ? 32 : 1;
+            const V3 za = mk(pa[3 * sta], pa[4 * sta], pa[5 * sta]), ta = mk(pa[6 * sta], pa[7 * sta], pa[8 * sta]);
+            const V3 zb = mk(pb[3 * stb], pb[4 * stb], pb[5 * stb]), tb = mk(pb[6 * stb], pb[7 * stb], pb[8 * stb]);
+            const V3 wv = seg_seg_witness(ta - za * pr.ha_out, za * (2.f * pr.ha_out), tb - zb * pr.hb_out, zb * (2.f * pr.hb_out));
+            keep = dot(wv, wv) <= pr.rsum_out * pr.rsum_out;
+          }
+        }
+        __syncwarp();  // every lane has read its item before the in-place compaction writes
+        const unsigned b = __ballot_sync(FULL, keep);
+        if (keep) w.queue[kept + __popc(b & ((1u << l) - 1))] = static_cast<uint16_t>(item);
+        kept += __popc(b);
+        __syncwarp();
+      }
+      qn = kept;
+    }
     // ---- stage 2: closed forms, exact box-box, OBB cull; survivors re-compacted in place
     int gn = 0;
 #pragma unroll 1
