@@ -36,9 +36,9 @@ enum PairClass : int32_t {
 
 struct ImgHeader {  // 32 words
   int32_t total_bytes, nq, n_joints, n_geoms, n_dyn, n_static, n_pairs, n_verts;
-  int32_t n_act, n_mimic, n_cont, n_save, mask_words, n_robot_geoms, n_robot_pairs, reserved0;
+  int32_t n_act, n_mimic, n_cont, n_save, mask_words, n_robot_geoms, n_robot_pairs, n_dd;  // n_dd: DD pairs
   int32_t off_joints, off_geoms, off_pairs, off_verts, off_static, off_dyn, off_act, off_mimic;
-  int32_t off_cont, off_refq, reserved1[6];
+  int32_t off_cont, off_refq, ss_begin, reserved1[5];  // ss_begin: first pair of two universe-attached geometries
 };
 static_assert(sizeof(ImgHeader) == 128, "header is 32 words");
 
@@ -65,16 +65,22 @@ struct DGeom {  // 40 words
 };
 static_assert(sizeof(DGeom) == 160, "DGeom");
 
-struct DPair {  // 8 words; a/b ordered so that type(a) <= type(b)
-  int16_t a, b;    // geometry indices
-  int16_t sa, sb;  // their gslot values (>= 0 slab slot, < 0 static placement), copied here so
-                   // stage 1 does not chase the geometry table
-  int32_t cls;
-  float rs2;  // (bound_r(a)+bound_r(b))^2, inflated for culls, exact for sphere-sphere
-  float ha_out, hb_out, rsum_out;  // outer capsules of a and b (GJK class): half lengths, radius sum
-  float slack;  // widening of every conservative test: 1e-5 m + the pair's share of non-rigid placements
+// Pairs are stored in PROCESSING order: first the pairs of two joint-attached geometries
+// ("DD"), then those of a joint-attached and a universe-attached one ("DS") -- each stage-1
+// loop then addresses placements with constant strides.  `orig` is the index in the caller's
+// list (GeometryModel.collisionPairs order), which is what every result reports.
+struct DPair {  // 12 words
+  int16_t d, s;       // stage 1: DD: slab slots of the two; DS: slab slot of one, static index of the other
+  int16_t cls, orig;  // narrow-phase class; index in the caller's pair list
+  float rs2;          // (bound_r(a)+bound_r(b))^2, inflated for culls, exact for sphere-sphere
+  float slack;        // widening of every conservative test: 1e-5 m + the pair's share of non-rigid placements
+  int16_t a, b;       // geometry indices, ordered so that type(a) <= type(b)
+  int16_t sa, sb;     // their gslot values (>= 0 slab slot, < 0 static placement)
+  float ha_out, hb_out;  // outer capsules of a and b (GJK class): half lengths ...
+  float rsum_out;        // ... and radius sum (+ slack)
+  int32_t pad[3];
 };
-static_assert(sizeof(DPair) == 32, "DPair");
+static_assert(sizeof(DPair) == 48, "DPair");
 
 struct DMimic {
   int32_t dst, src;

@@ -65,6 +65,8 @@ __device__ __forceinline__ Tables make_tables(const unsigned char* base) {
   return t;
 }
 
+extern __shared__ __align__(128) unsigned char g_smem[];
+
 // Per-warp shared-memory slab (offsets in 4-byte words from the slab base).
 struct SlabLayout {
   int32_t words;      // slab size
@@ -124,6 +126,9 @@ struct Warp {
   float* stage;
   int stage_stride;
   int lane;
+  // 32-bit word offsets into the CTA's shared memory (g_smem) of this warp's geometry slab and of
+  // the static placements: placement addressing in the pair loops is plain integer arithmetic
+  int geom_w, stat_w;
 };
 
 __device__ __forceinline__ Warp make_warp(const Tables& t, float* slab, const SlabLayout& L) {
@@ -139,6 +144,8 @@ __device__ __forceinline__ Warp make_warp(const Tables& t, float* slab, const Sl
   w.stage = slab + L.off_stage;
   w.stage_stride = L.stage_stride;
   w.lane = threadIdx.x & 31;
+  w.geom_w = static_cast<int>(w.geom - reinterpret_cast<const float*>(g_smem));
+  w.stat_w = static_cast<int>(t.stat - reinterpret_cast<const float*>(g_smem));
   return w;
 }
 
@@ -303,7 +310,8 @@ __device__ __forceinline__ void store_geom_xf(float* slab, int slot, int lane, c
 
 // World placement of geometry g for configuration c (lane-divergent g and c allowed).
 __device__ __forceinline__ Xf geom_xf(const Warp& w, int gslot, int c) {
-  const float* p = gslot >= 0 ? w.geom + gslot * kGeomFloats * 32 + c : w.t.stat + (-1 - gslot) * kStatFloats;
+  const float* S = reinterpret_cast<const float*>(g_smem);
+  const float* p = S + (gslot >= 0 ? w.geom_w + gslot * (kGeomFloats * 32) + c : w.stat_w - (gslot + 1) * kStatFloats);
   const int st = gslot >= 0 ? 32 : 1;
   const V3 x = mk(p[0], p[st], p[2 * st]), z = mk(p[3 * st], p[4 * st], p[5 * st]);
   const V3 y = gslot >= 0 ? cross(z, x) : mk(p[9], p[10], p[11]);
@@ -481,43 +489,61 @@ __device__ __forceinline__ void narrow_phase(const Warp& w, bool stop_at_first, 
     int qn = 0;
     // ---- stage 1: bounding spheres; lane = configuration, pair index uniform.  Two pairs per trip: their shared-memory loads and arithmetic are independent,
     // which matters because only a few warps fit next to the slabs (latency, not issue, bound).
-    struct S1 {
-      const float *pa, *pb;
-      int sta, stb;
-      V3 ta, tb;
-      bool pass;
-    };
-    auto sphere = [&](int p, const DPair& pr) {
-      S1 r;
-      const int sa = pr.sa, sb = pr.sb;
-      r.pa = sa >= 0 ? w.geom + sa * kGeomFloats * 32 + l : w.t.stat + (-1 - sa) * kStatFloats;
-      r.pb = sb >= 0 ? w.geom + sb * kGeomFloats * 32 + l : w.t.stat + (-1 - sb) * kStatFloats;
-      r.sta = sa >= 0 ? 32 : 1; r.stb = sb >= 0 ? 32 : 1;
-      r.ta = mk(r.pa[6 * r.sta], r.pa[7 * r.sta], r.pa[8 * r.sta]);
-      r.tb = mk(r.pb[6 * r.stb], r.pb[7 * r.stb], r.pb[8 * r.stb]);
-      const V3 d = r.ta - r.tb;
-      r.pass = pr.cls != kClsInactive && !(stop_at_first && my_first < p) && dot(d, d) <= pr.rs2;
-      return r;
-    };
+    const float* S = reinterpret_cast<const float*>(g_smem);
+    const float* T = S + w.geom_w + l + 6 * 32;   // translation rows of this lane's slab column
+    const float* TS = S + w.stat_w + 6;           // translations of the static placements
     auto push = [&](int p, const DPair& pr, bool pass) {
+      pass = pass && pr.cls != kClsInactive && !(stop_at_first && my_first < pr.orig);
       if (pr.cls == kClsSphereSphere) {  // the sphere test was the decision itself
-        if (pass) record_hit(w, l, p, want_mask);
+        if (pass) record_hit(w, l, pr.orig, want_mask);
         pass = false;
       }
       const unsigned b = __ballot_sync(FULL, pass);
       if (pass) w.queue[qn + __popc(b & ((1u << l) - 1))] = static_cast<uint16_t>(((p - chunk) << 5) | l);
       qn += __popc(b);
     };
+    // squared distance of the two placement origins against the bounding-sphere sum
+    auto dd_test = [&](const DPair& pr) {
+      const float* a = T + pr.d * (kGeomFloats * 32);
+      const float* b = T + pr.s * (kGeomFloats * 32);
+      const float dx = a[0] - b[0], dy = a[32] - b[32], dz = a[64] - b[64];
+      return fmaf(dx, dx, fmaf(dy, dy, dz * dz)) <= pr.rs2;
+    };
+    auto ds_test = [&](const DPair& pr) {
+      const float* a = T + pr.d * (kGeomFloats * 32);
+      const float* b = TS + pr.s * kStatFloats;
+      const float dx = a[0] - b[0], dy = a[32] - b[1], dz = a[64] - b[2];
+      return fmaf(dx, dx, fmaf(dy, dy, dz * dz)) <= pr.rs2;
+    };
+    const int dd_end = min(chunk_end, max(chunk, h->n_dd));
 #pragma unroll 1
-    for (int p = chunk; p < chunk_end; p += 2) {
-      const bool two = p + 1 < chunk_end;
+    for (int p = chunk; p < dd_end; p += 2) {
+      const bool two = p + 1 < dd_end;
       const DPair pr0 = w.t.pairs[p];
       const DPair pr1 = w.t.pairs[two ? p + 1 : p];
-      S1 r0 = sphere(p, pr0);
-      S1 r1 = sphere(p + 1, pr1);
-      r1.pass = r1.pass && two;
-      push(p, pr0, r0.pass);
-      if (two) push(p + 1, pr1, r1.pass);
+      const bool k0 = dd_test(pr0), k1 = dd_test(pr1);
+      push(p, pr0, k0);
+      if (two) push(p + 1, pr1, k1);
+    }
+    const int ds_end = min(chunk_end, max(dd_end, h->ss_begin));
+#pragma unroll 1
+    for (int p = dd_end; p < ds_end; p += 2) {
+      const bool two = p + 1 < ds_end;
+      const DPair pr0 = w.t.pairs[p];
+      const DPair pr1 = w.t.pairs[two ? p + 1 : p];
+      const bool k0 = ds_test(pr0), k1 = ds_test(pr1);
+      push(p, pr0, k0);
+      if (two) push(p + 1, pr1, k1);
+    }
+    // two universe-attached geometries (a fixed base link against a scene object): the same
+    // answer for every configuration, but it is part of the pair list
+#pragma unroll 1
+    for (int p = ds_end; p < chunk_end; ++p) {
+      const DPair pr = w.t.pairs[p];
+      const float* a = TS + pr.d * kStatFloats;
+      const float* b = TS + pr.s * kStatFloats;
+      const float dx = a[0] - b[0], dy = a[1] - b[1], dz = a[2] - b[2];
+      push(p, pr, fmaf(dx, dx, fmaf(dy, dy, dz * dz)) <= pr.rs2);
     }
     __syncwarp();
     // ---- stage 1.5: OUTER capsules for the GJK class, on dense groups of 32 survivors of the
@@ -534,8 +560,9 @@ __device__ __forceinline__ void narrow_phase(const Warp& w, bool stop_at_first, 
           const int c = item & 31;
           const DPair pr = w.t.pairs[chunk + (item >> 5)];
           if (pr.cls == kClsGjk) {
-            const float* pa = pr.sa >= 0 ? w.geom + pr.sa * kGeomFloats * 32 + c : w.t.stat + (-1 - pr.sa) * kStatFloats;
-            const float* pb = pr.sb >= 0 ? w.geom + pr.sb * kGeomFloats * 32 + c : w.t.stat + (-1 - pr.sb) * kStatFloats;
+            const float* S = reinterpret_cast<const float*>(g_smem);
+            const float* pa = S + (pr.sa >= 0 ? w.geom_w + pr.sa * (kGeomFloats * 32) + c : w.stat_w - (pr.sa + 1) * kStatFloats);
+            const float* pb = S + (pr.sb >= 0 ? w.geom_w + pr.sb * (kGeomFloats * 32) + c : w.stat_w - (pr.sb + 1) * kStatFloats);
             const int sta = pr.sa >= 0 ? 32 : 1, stb = pr.sb >= 0 ? 32 : 1;
             const V3 za = mk(pa[3 * sta], pa[4 * sta], pa[5 * sta]), ta = mk(pa[6 * sta], pa[7 * sta], pa[8 * sta]);
             const V3 zb = mk(pb[3 * stb], pb[4 * stb], pb[5 * stb]), tb = mk(pb[6 * stb], pb[7 * stb], pb[8 * stb]);
@@ -580,15 +607,15 @@ __device__ __forceinline__ void narrow_phase(const Warp& w, bool stop_at_first, 
             v0 = seg_seg_witness(mk(0.f, 0.f, -ga->s_in), mk(0.f, 0.f, 2.f * ga->s_in), trans(rel) - zb * gb->s_in,
                                  zb * (2.f * gb->s_in));
             const float rin = ga->r_in + gb->r_in - pr.slack;
-            if (rin > 0.f && dot(v0, v0) < rin * rin) { record_hit(w, c, p, want_mask); decided = true; }
+            if (rin > 0.f && dot(v0, v0) < rin * rin) { record_hit(w, c, pr.orig, want_mask); decided = true; }
           }
           if (!decided) {
             const bool ov = obb_overlap(ha, hb, rel, bb ? 0.f : pr.slack);
-            if (ov && bb) record_hit(w, c, p, want_mask);
+            if (ov && bb) record_hit(w, c, pr.orig, want_mask);
             to_gjk = ov && !bb;
           }
         } else if (closed_form_hit(pr.cls, ga, gb, rel)) {
-          record_hit(w, c, p, want_mask);
+          record_hit(w, c, pr.orig, want_mask);
         }
       }
       __syncwarp();  // all lanes have read their item before the in-place compaction writes
@@ -635,9 +662,10 @@ __device__ __forceinline__ void narrow_phase(const Warp& w, bool stop_at_first, 
             const int item = w.queue[idx];
             c = item & 31;
             p = chunk + (item >> 5);
-            // a configuration that was hit earlier needs no later pair
+            // a configuration that was hit earlier (at a smaller list index) needs no later pair
+            const DPair pr = w.t.pairs[p];
+            p = pr.orig;  // results report the caller's index
             if (!(stop_at_first && w.first[c] < p)) {
-              const DPair pr = w.t.pairs[p];
               const DGeom* ga = &w.t.geoms[pr.a];
               const DGeom* gb = &w.t.geoms[pr.b];
               A = load_shape(ga, w.t.verts);
@@ -685,8 +713,6 @@ struct CheckArgs {
   GjkQueue gq;
   SlabLayout L;
 };
-
-extern __shared__ __align__(128) unsigned char g_smem[];
 
 // ------------------------------------------------------------------ kernel: validity
 __global__ void __launch_bounds__(512, 1) check_kernel(const __grid_constant__ CheckArgs a) {
@@ -781,11 +807,11 @@ __global__ void __launch_bounds__(256, 2) gjk_queue_kernel(const __grid_constant
         const float4* src = reinterpret_cast<const float4*>(a.items + gi);
         const float4 r0 = __ldcs(src), r1 = __ldcs(src + 1), r2 = __ldcs(src + 2), r3 = __ldcs(src + 3), r4 = __ldcs(src + 4);
         row = __float_as_uint(r3.w);
-        p = __float_as_uint(r4.x);
+        const DPair pr = t.pairs[__float_as_uint(r4.x)];
+        p = static_cast<uint32_t>(pr.orig);  // results report the caller's index
         bool skip = false;
         if (a.stop && !a.offs) skip = a.first_pair ? static_cast<uint32_t>(a.first_pair[row]) < p : a.hit[row] != 0;
         if (!skip) {
-          const DPair pr = t.pairs[p];
           const DGeom* ga = &t.geoms[pr.a];
           const DGeom* gb = &t.geoms[pr.b];
           A = load_shape(ga, t.verts);
@@ -934,8 +960,8 @@ __global__ void __launch_bounds__(256, 1) distance_kernel(const __grid_constant_
     __syncwarp();
     const int64_t row = row0 + w.lane;
     for (int k = 0; k < a.n_sel; ++k) {
-      const int p = a.sel ? a.sel[k] : k;
-      const DPair pr = t.pairs[p];
+      const DPair pr = t.pairs[a.sel ? a.sel[k] : k];  // sel holds processing indices
+      const int col = a.sel ? k : pr.orig;
       const DGeom* ga = &t.geoms[pr.a];
       const DGeom* gb = &t.geoms[pr.b];
       const Xf rel = xf_inv_mul(geom_xf(w, ga->gslot, w.lane), geom_xf(w, gb->gslot, w.lane));
@@ -943,7 +969,7 @@ __global__ void __launch_bounds__(256, 1) distance_kernel(const __grid_constant_
       float d = cls < kClsBoxBox ? closed_form_dist(cls, ga, gb, rel)
                                  : gjk_signed_distance(load_shape(ga, t.verts), load_shape(gb, t.verts), rel,
                                                        swept_radius(ga) + swept_radius(gb));
-      if (row < a.n) a.out[row * a.n_sel + k] = d;
+      if (row < a.n) a.out[row * a.n_sel + col] = d;
     }
     __syncwarp();
   }
@@ -1171,7 +1197,8 @@ struct RampModel {
   std::vector<RampGeom> robot_geoms, scene_geoms;
   std::vector<int32_t> robot_pairs, scene_pairs;  // flattened [][2]
   std::vector<double> robot_verts, scene_verts;   // [][3]
-  std::vector<uint8_t> pair_active;
+  std::vector<uint8_t> pair_active;   // by the caller's pair index
+  std::vector<int32_t> pair_order;    // caller's pair index -> processing index in the image
   // qmap
   bool has_qmap = false;
   std::vector<int32_t> act_slot, mimic_dst, mimic_src, cont_slot;
@@ -1521,19 +1548,48 @@ static int build_image(RampModel* m) {
     dj[i].gcount = static_cast<int32_t>(by_joint[i].size());
     for (int g : by_joint[i]) { dg[g].gslot = static_cast<int32_t>(dyn.size()); dyn.push_back(g); }
   }
-  // pairs
-  std::vector<DPair> dp(std::max(np, 1));
+  // pairs, in processing order: DD (both joint-attached) first, then DS, then the rest
+  // (two universe-attached geometries cannot collide differently per configuration; such a
+  // pair is kept for index bookkeeping but handled like DS with its first member static)
   m->pair_active.resize(np, 1);
-  int n_gjk = 0;
-  for (int p = 0; p < np; ++p) {
+  std::vector<int> order;
+  order.reserve(np);
+  int n_dd = 0, ss_begin = 0;
+  auto geoms_of = [&](int p, int& a, int& b) {
     const int32_t* pr = p < n_rp ? &m->robot_pairs[2 * p] : &m->scene_pairs[2 * (p - n_rp)];
-    int a = pr[0], b = pr[1];
-    if (a < 0 || b < 0 || a >= ng || b >= ng || a == b) return fail(RAMP_ERR_INVALID, "pair %d: bad geometry indices (%d, %d)", p, a, b);
+    a = pr[0]; b = pr[1];
+  };
+  for (int pass = 0; pass < 3; ++pass) {
+    if (pass == 2) ss_begin = static_cast<int>(order.size());
+    for (int p = 0; p < np; ++p) {
+      int a, b;
+      geoms_of(p, a, b);
+      if (a < 0 || b < 0 || a >= ng || b >= ng || a == b) return fail(RAMP_ERR_INVALID, "pair %d: bad geometry indices (%d, %d)", p, a, b);
+      const int kind = (dg[a].gslot < 0) + (dg[b].gslot < 0);  // 0 DD, 1 DS, 2 SS
+      if (kind == pass) order.push_back(p);
+      n_dd += kind == 0 && pass == 0;
+    }
+  }
+  std::vector<DPair> dp(std::max(np, 1));
+  m->pair_order.assign(np, 0);
+  int n_gjk = 0;
+  for (int k = 0; k < np; ++k) {
+    const int p = order[k];
+    m->pair_order[p] = k;
+    int a, b;
+    geoms_of(p, a, b);
     if (dg[a].type > dg[b].type) std::swap(a, b);
-    DPair& d = dp[p];
+    DPair& d = dp[k];
+    std::memset(&d, 0, sizeof d);
     d.a = static_cast<int16_t>(a); d.b = static_cast<int16_t>(b);
     d.sa = static_cast<int16_t>(dg[a].gslot); d.sb = static_cast<int16_t>(dg[b].gslot);
-    d.cls = m->pair_active[p] ? pair_class(dg[a].type, dg[b].type) : kClsInactive;
+    d.orig = static_cast<int16_t>(p);
+    d.cls = static_cast<int16_t>(m->pair_active[p] ? pair_class(dg[a].type, dg[b].type) : kClsInactive);
+    // stage-1 addressing: DD two slab slots; DS slab slot + static index; SS two static indices
+    if (k < n_dd) { d.d = d.sa; d.s = d.sb; }
+    else if (k >= ss_begin) { d.d = static_cast<int16_t>(-1 - dg[a].gslot); d.s = static_cast<int16_t>(-1 - dg[b].gslot); }
+    else if (dg[a].gslot >= 0) { d.d = d.sa; d.s = static_cast<int16_t>(-1 - dg[b].gslot); }
+    else { d.d = d.sb; d.s = static_cast<int16_t>(-1 - dg[a].gslot); }
     n_gjk += d.cls == kClsGjk;
     const double rs = static_cast<double>(dg[a].bound_r) + dg[b].bound_r;
     // the sphere-sphere test is the decision itself; every other class uses it as a cull
@@ -1571,7 +1627,7 @@ static int build_image(RampModel* m) {
   h.n_static = n_static; h.n_pairs = np; h.n_verts = static_cast<int32_t>(verts4.size() / 4);
   h.n_act = static_cast<int32_t>(m->act_slot.size()); h.n_mimic = static_cast<int32_t>(dm.size());
   h.n_cont = static_cast<int32_t>(m->cont_slot.size()); h.n_save = n_save;
-  h.mask_words = (np + 31) / 32; h.n_robot_geoms = n_robot; h.n_robot_pairs = n_rp;
+  h.mask_words = (np + 31) / 32; h.n_robot_geoms = n_robot; h.n_robot_pairs = n_rp; h.n_dd = n_dd; h.ss_begin = ss_begin;
 
   m->image.assign(off, 0);
   unsigned char* B = m->image.data();
@@ -2030,7 +2086,10 @@ int ramp_distance_batch(const RampModel* m, const float* d_q, int64_t n, int32_t
       cudaGetLastError();
       return fail(RAMP_ERR_ALLOC, "cudaMallocFromPoolAsync for the pair selection failed");
     }
-    CUDA_TRY(cudaMemcpyAsync(d_sel, h_pair_idx, sizeof(int32_t) * n_sel, cudaMemcpyHostToDevice, st));
+    std::vector<int32_t> sel(n_sel);
+    for (int k = 0; k < n_sel; ++k) sel[k] = m->pair_order[h_pair_idx[k]];
+    CUDA_TRY(cudaMemcpyAsync(d_sel, sel.data(), sizeof(int32_t) * n_sel, cudaMemcpyHostToDevice, st));
+    CUDA_TRY(cudaStreamSynchronize(st));  // `sel` is a pageable temporary
     a.sel = d_sel;
   }
   int nwarps; size_t smem;
