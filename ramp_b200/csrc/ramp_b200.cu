@@ -516,14 +516,18 @@ __device__ __forceinline__ void narrow_phase(const Warp& w, bool stop_at_first, 
       return fmaf(dx, dx, fmaf(dy, dy, dz * dz)) <= pr.rs2;
     };
     const int dd_end = min(chunk_end, max(chunk, h->n_dd));
+    // four pairs per trip: their loads are independent, which hides shared-memory latency
+    // when few warps fit next to the slabs (20-geometry robots: 6 warps per SM)
 #pragma unroll 1
-    for (int p = chunk; p < dd_end; p += 2) {
-      const bool two = p + 1 < dd_end;
-      const DPair pr0 = w.t.pairs[p];
-      const DPair pr1 = w.t.pairs[two ? p + 1 : p];
-      const bool k0 = dd_test(pr0), k1 = dd_test(pr1);
+    for (int p = chunk; p < dd_end; p += 4) {
+      const int last = dd_end - 1;
+      const DPair pr0 = w.t.pairs[p], pr1 = w.t.pairs[min(p + 1, last)], pr2 = w.t.pairs[min(p + 2, last)],
+                  pr3 = w.t.pairs[min(p + 3, last)];
+      const bool k0 = dd_test(pr0), k1 = dd_test(pr1), k2 = dd_test(pr2), k3 = dd_test(pr3);
       push(p, pr0, k0);
-      if (two) push(p + 1, pr1, k1);
+      if (p + 1 <= last) push(p + 1, pr1, k1);
+      if (p + 2 <= last) push(p + 2, pr2, k2);
+      if (p + 3 <= last) push(p + 3, pr3, k3);
     }
     const int ds_end = min(chunk_end, max(dd_end, h->ss_begin));
 #pragma unroll 1
