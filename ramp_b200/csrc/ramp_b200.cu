@@ -23,6 +23,7 @@
 #include <cmath>
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <mutex>
 #include <new>
@@ -80,6 +81,9 @@ struct SlabLayout {
   int32_t off_stage;  // [32][stage_stride] output staging of the FK kernels
   int32_t stage_stride;
   int32_t table_bytes;  // image size rounded up to 16
+  int32_t team;         // warps sharing one slab (1, 2 or 4): they split the pair list of a tile
+  int32_t chunk_pairs;  // pairs per queue round of one warp
+  int32_t queue_words;  // per-warp queue size
 };
 
 __device__ __forceinline__ int64_t imin64(int64_t a, int64_t b) { return a < b ? a : b; }
@@ -138,7 +142,7 @@ __device__ __forceinline__ Warp make_warp(const Tables& t, float* slab, const Sl
   w.act = slab + L.off_act;
   w.geom = slab + L.off_geom;
   w.save = slab + L.off_save;
-  w.queue = reinterpret_cast<uint16_t*>(slab + L.off_queue);
+  w.queue = reinterpret_cast<uint16_t*>(slab + L.off_queue + ((threadIdx.x >> 5) % L.team) * L.queue_words);
   w.mask = reinterpret_cast<uint32_t*>(slab + L.off_mask);
   w.first = reinterpret_cast<int32_t*>(slab + L.off_first);
   w.stage = slab + L.off_stage;
@@ -478,13 +482,18 @@ __device__ __forceinline__ bool closed_form_hit(int cls, const DGeom* ga, const 
   return closed_form_dist(cls, ga, gb, rel) <= 0.f;
 }
 
+// `tw` / kTeam: this warp takes every kTeam-th chunk of `chunk_pairs` pairs (kTeam == 1: all of
+// them, in chunks of kChunkPairs -- a compile-time constant on the common path)
+template <int kTeam = 1>
 __device__ __forceinline__ void narrow_phase(const Warp& w, bool stop_at_first, bool want_mask, const GjkQueue& gq,
-                                             uint32_t row_base) {
+                                             uint32_t row_base, int tw = 0, int chunk_pairs_rt = kChunkPairs) {
+  const int team = kTeam;
+  const int chunk_pairs = kTeam == 1 ? kChunkPairs : chunk_pairs_rt;
   const ImgHeader* h = w.t.h;
   const int l = w.lane;
   const unsigned FULL = 0xffffffffu;
-  for (int chunk = 0; chunk < h->n_pairs; chunk += kChunkPairs) {
-    const int chunk_end = min(chunk + kChunkPairs, h->n_pairs);
+  for (int chunk = tw * chunk_pairs; chunk < h->n_pairs; chunk += team * chunk_pairs) {
+    const int chunk_end = min(chunk + chunk_pairs, h->n_pairs);
     const int my_first = w.first[l];
     int qn = 0;
     // ---- stage 1: bounding spheres; lane = configuration, pair index uniform.  Two pairs per trip: their shared-memory loads and arithmetic are independent,
@@ -719,41 +728,58 @@ struct CheckArgs {
 };
 
 // ------------------------------------------------------------------ kernel: validity
+template <int kTeam>
 __global__ void __launch_bounds__(512, 1) check_kernel(const __grid_constant__ CheckArgs a) {
   uint64_t* mbar = reinterpret_cast<uint64_t*>(g_smem);
   unsigned char* tbl = g_smem + 16;
   stage_tables(tbl, a.img, a.L.table_bytes, mbar);
   const Tables t = make_tables(tbl);
   const int nwarps = blockDim.x >> 5, wid = threadIdx.x >> 5;
-  float* slab = reinterpret_cast<float*>(tbl + a.L.table_bytes) + static_cast<size_t>(wid) * a.L.words;
+  // Teams: `team` warps share one slab and one tile.  Warp 0 of the team loads the rows and
+  // runs FK, then all of them split the pair list; a named barrier per team orders the phases.
+  // More warps per slab is what lets robots with many geometries (large slabs) and small
+  // batches (few tiles) keep the schedulers busy.
+  constexpr int team = kTeam;
+  const int tid = wid / team, tw = wid - tid * team, nteams = nwarps / team;
+  float* slab = reinterpret_cast<float*>(tbl + a.L.table_bytes) + static_cast<size_t>(tid) * a.L.words;
   const Warp w = make_warp(t, slab, a.L);
+  auto team_sync = [&]() {
+    if (team == 1) __syncwarp();
+    else asm volatile("bar.sync %0, %1;" ::"r"(1 + tid), "r"(team * 32) : "memory");
+  };
   const bool actuated = a.flags & RAMP_Q_ACTUATED;
   const bool want_mask = a.pair_mask != nullptr;
   const bool stop = !(a.flags & RAMP_ALL_PAIRS) && !want_mask;
   int cols = actuated ? t.h->n_act : t.h->nq;
   if ((a.ld & 3) == 0 && a.ld <= cols + 3) cols = a.ld;  // padded rows: take the float4 path
   const int64_t ntiles = (a.n + 31) >> 5;
-  const int64_t tile_step = static_cast<int64_t>(gridDim.x) * nwarps;
+  const int64_t tile_step = static_cast<int64_t>(gridDim.x) * nteams;
+  const int64_t tile0 = static_cast<int64_t>(blockIdx.x) * nteams + tid;
   RowPrefetch<4> pf;
-  prefetch_rows(pf, a.q, (static_cast<int64_t>(blockIdx.x) * nwarps + wid) << 5, a.n, cols, a.ld, w.lane);
-  for (int64_t tile = static_cast<int64_t>(blockIdx.x) * nwarps + wid; tile < ntiles; tile += tile_step) {
+  pf.valid = false;
+  if (tw == 0) prefetch_rows(pf, a.q, tile0 << 5, a.n, cols, a.ld, w.lane);
+  for (int64_t tile = tile0; tile < ntiles; tile += tile_step) {
     const int64_t row0 = tile << 5;
-    commit_rows(pf, actuated ? w.act : w.q, a.q, row0, a.n, cols, a.ld, w.lane);
-    prefetch_rows(pf, a.q, (tile + tile_step) << 5, a.n, cols, a.ld, w.lane);
-    if (actuated) expand_q(w);
-    reset_results(w, want_mask ? t.h->mask_words : 0);
-    fk_lane<0>(w);
-    __syncwarp();
-    narrow_phase(w, stop, want_mask, a.gq, static_cast<uint32_t>(row0));
+    if (tw == 0) {
+      commit_rows(pf, actuated ? w.act : w.q, a.q, row0, a.n, cols, a.ld, w.lane);
+      prefetch_rows(pf, a.q, (tile + tile_step) << 5, a.n, cols, a.ld, w.lane);
+      if (actuated) expand_q(w);
+      reset_results(w, want_mask ? t.h->mask_words : 0);
+      fk_lane<0>(w);
+    }
+    team_sync();
+    narrow_phase<kTeam>(w, stop, want_mask, a.gq, static_cast<uint32_t>(row0), tw, a.L.chunk_pairs);
+    team_sync();
     const int64_t row = row0 + w.lane;
-    if (row < a.n) {
+    if (tw == 0 && row < a.n) {
       const int f = w.first[w.lane];
       a.hit[row] = f != INT32_MAX;
       if (a.first_pair) a.first_pair[row] = f != INT32_MAX ? f : -1;
       if (want_mask)
         for (int k = 0; k < t.h->mask_words; ++k) a.pair_mask[row * t.h->mask_words + k] = w.mask[k * 32 + w.lane];
     }
-    __syncwarp();
+    // the next trip's rows overwrite the region the team's queues live in
+    team_sync();
   }
 }
 
@@ -1867,7 +1893,7 @@ static int build_image(RampModel* m) {
 
 // Shared-memory plan: tables + as many warp slabs as fit (<= 16 warps).
 static int plan_slabs(const RampModel* m, int stage_row_floats, int act_cols, SlabLayout* L, int* nwarps,
-                      size_t* smem_bytes, int ld = 0) {
+                      size_t* smem_bytes, int ld = 0, int team = 1) {
   const ImgHeader& h = m->hdr;
   int w = 0;
   auto take = [&](int words) { const int o = w; w += (words + 3) & ~3; return o; };
@@ -1875,7 +1901,12 @@ static int plan_slabs(const RampModel* m, int stage_row_floats, int act_cols, Sl
   // q / actuated rows are dead once FK has run; the work queue of the narrow phase reuses them
   const int q_words = std::max(std::max(h.nq, ld <= h.nq + 3 ? ld : 0), 1) * 32;
   const int act_words = std::max(std::max(act_cols, ld <= act_cols + 3 ? ld : 0), 1) * 32;
-  const int region0 = take(std::max(q_words + act_words, stage_row_floats > 0 ? 0 : kQueueCap / 2));
+  // pairs per queue round: the team's warps take chunks in turn, so aim at an even split
+  const int rounds = std::max(1, (h.n_pairs + team * kChunkPairs - 1) / (team * kChunkPairs));
+  L->team = team;
+  L->chunk_pairs = team == 1 ? kChunkPairs : std::min(kChunkPairs, std::max(4, ((h.n_pairs + team * rounds - 1) / (team * rounds) + 3) & ~3));
+  L->queue_words = L->chunk_pairs * kLanes / 2;
+  const int region0 = take(std::max(q_words + act_words, stage_row_floats > 0 ? 0 : team * L->queue_words));
   L->off_q = region0;
   L->off_act = region0 + q_words;
   const bool fk_only = stage_row_floats > 0;  // the FK kernels need no slab, queue or result rows
@@ -1894,9 +1925,10 @@ static int plan_slabs(const RampModel* m, int stage_row_floats, int act_cols, Sl
   const size_t per_warp = static_cast<size_t>(w) * 4;
   if (fixed + per_warp > static_cast<size_t>(m->max_smem))
     return fail(RAMP_ERR_LIMIT, "model needs %zu B of shared memory per CTA, device allows %d", fixed + per_warp, m->max_smem);
-  const int fit = static_cast<int>((m->max_smem - fixed) / per_warp);
-  *nwarps = std::min(16, fit);
-  *smem_bytes = fixed + per_warp * (*nwarps);
+  const int fit = static_cast<int>((m->max_smem - fixed) / per_warp);  // slabs (= teams) that fit
+  const int teams = std::min(std::min(16 / team, 15), fit);
+  *nwarps = teams * team;
+  *smem_bytes = fixed + per_warp * teams;
   return RAMP_OK;
 }
 
@@ -1965,7 +1997,13 @@ static int launch_check(const RampModel* m, const float* d_q, int64_t n, int32_t
   a.img = m->d_image; a.ld = ld; a.flags = flags;
   int nwarps; size_t smem;
   if (int rc = plan_slabs(m, 0, m->hdr.n_act, &a.L, &nwarps, &smem, ld)) return rc;
-  if (int rc = set_smem(check_kernel, smem)) return rc;
+  // Few slabs fit (a robot with many geometries): let pairs of warps share each slab and split
+  // the pair list (measured on the 20-geometry H1 stand-in: +17 %; teams of 4 lose it again to
+  // the FK that only one warp of the team runs, and robots whose slabs fit 12+ times lose ~20 %).
+  int team = nwarps < 12 ? 2 : 1;
+  if (const char* e = std::getenv("RAMP_B200_TEAM")) { team = std::atoi(e); team = team >= 4 ? 4 : (team >= 2 ? 2 : 1); }  // experiments
+  if (team > 1 && plan_slabs(m, 0, m->hdr.n_act, &a.L, &nwarps, &smem, ld, team) != RAMP_OK) return RAMP_ERR_LIMIT;
+  if (int rc = team == 2 ? set_smem(check_kernel<2>, smem) : (team == 4 ? set_smem(check_kernel<4>, smem) : set_smem(check_kernel<1>, smem))) return rc;
   const bool use_queue = m->pool != nullptr && m->n_gjk_pairs > 0 && n >= kQueueMinRows;
   unsigned char* scratch = nullptr;
   uint32_t cap_items = 0;
@@ -1997,7 +2035,12 @@ static int launch_check(const RampModel* m, const float* d_q, int64_t n, int32_t
       CUDA_TRY(cudaMemsetAsync(scratch, 0, 16, st));
       a.gq = GjkQueue{reinterpret_cast<GjkItem*>(scratch + 256), reinterpret_cast<uint32_t*>(scratch), cap_items};
     }
-    check_kernel<<<grid_for(m, (ns + 31) / 32, nwarps), nwarps * 32, smem, st>>>(a);
+    {
+      const int grid = grid_for(m, (ns + 31) / 32, nwarps / a.L.team);
+      if (team == 2) check_kernel<2><<<grid, nwarps * 32, smem, st>>>(a);
+      else if (team == 4) check_kernel<4><<<grid, nwarps * 32, smem, st>>>(a);
+      else check_kernel<1><<<grid, nwarps * 32, smem, st>>>(a);
+    }
     g_launches.fetch_add(1, std::memory_order_relaxed);
     if (use_queue) {
       b.hit = a.hit; b.first_pair = a.first_pair; b.pair_mask = a.pair_mask;
@@ -2283,14 +2326,14 @@ int ramp_check_batch_noalloc(const RampModel* m, const float* d_q, int64_t n, in
   a.hit = d_hit; a.first_pair = d_first_pair; a.pair_mask = d_pair_mask;
   int nwarps; size_t smem;
   if (int rc = plan_slabs(m, 0, m->hdr.n_act, &a.L, &nwarps, &smem, ld)) return rc;
-  if (int rc = set_smem(check_kernel, smem)) return rc;
+  if (int rc = set_smem(check_kernel<1>, smem)) return rc;
   const size_t smem_b = 16 + a.L.table_bytes;
   if (int rc = set_smem(gjk_queue_kernel, smem_b)) return rc;
   // the array still holds the previous call's counter and items: only the counter has to
   // start from zero, the items below it are rewritten before they are read
   CUDA_TRY(cudaMemsetAsync(scratch, 0, 16, st));
   a.gq = GjkQueue{reinterpret_cast<GjkItem*>(scratch + 256), reinterpret_cast<uint32_t*>(scratch), kNoAllocQueueItems};
-  check_kernel<<<grid_for(m, (n + 31) / 32, nwarps), nwarps * 32, smem, st>>>(a);
+  check_kernel<1><<<grid_for(m, (n + 31) / 32, nwarps), nwarps * 32, smem, st>>>(a);
   GjkQueueArgs b{};
   b.img = m->d_image; b.table_bytes = a.L.table_bytes;
   b.items = a.gq.items; b.count = a.gq.count; b.capacity = kNoAllocQueueItems;
