@@ -275,6 +275,14 @@ int ramp_check_edges(const RampModel* m, const float* d_q0, const float* d_q1,
                      uint8_t* d_valid, int32_t* d_first_invalid, int32_t* d_nd,
                      void* stream);
 
+/* Host-buffer form of ramp_check_edges for planners that validate one edge (or a
+ * few) per call: h_q0 / h_q1 / outputs are host arrays, copies and one
+ * synchronisation happen inside.  This is the call a MotionValidator::checkMotion
+ * override makes (src/ramp/motion_planner.py:366 + OMPL's checkMotion). */
+int ramp_check_edges_host(const RampModel* m, const float* h_q0, const float* h_q1,
+                          int64_t n_edges, int32_t ld, const RampSpaceDesc* h_space,
+                          uint8_t* h_valid, int32_t* h_first_invalid, int32_t* h_nd);
+
 /* Host-buffer convenience for the single-state call sites
  * (RobotState.check_collision, src/ramp/robot_state.py:366): copies n rows of
  * h_q to the device, runs ramp_check_batch and copies the results back,

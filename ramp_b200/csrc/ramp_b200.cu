@@ -1384,6 +1384,121 @@ __global__ void __launch_bounds__(512, 1) edge_check_kernel(const __grid_constan
   }
 }
 
+// ---- latency mode for a handful of edges (one planner query calls checkMotion edge by
+// edge): ONE launch, one warp per interpolated state.  Every warp recomputes the (tiny) segment
+// counts of all edges, picks its states, and the last warp to finish folds the per-edge minima
+// into the outputs.  `work` = 33 ints pre-set to 0x7f7f7f7f: [e] smallest invalid j, [32] a
+// counter of finished states.
+constexpr int kSmallEdges = 32;
+constexpr int32_t kWorkInit = 0x7f7f7f7f;
+
+struct EdgeSmallArgs {
+  const unsigned char* img;
+  int32_t table_bytes;
+  const float* q0;
+  const float* q1;
+  int32_t n_edges;
+  int32_t ld;
+  uint8_t* valid;
+  int32_t* first_invalid;  // nullable
+  int32_t* nd;             // nullable
+  int32_t* work;
+  WarpSlab L;
+  DSpace sp;
+};
+
+__global__ void __launch_bounds__(128) edge_warp_kernel(const __grid_constant__ EdgeSmallArgs a) {
+  uint64_t* mbar = reinterpret_cast<uint64_t*>(g_smem);
+  unsigned char* tbl = g_smem + 16;
+  stage_tables(tbl, a.img, a.table_bytes, mbar);
+  const Tables t = make_tables(tbl);
+  const int nwarps = blockDim.x >> 5, wid = threadIdx.x >> 5;
+  float* slab = reinterpret_cast<float*>(tbl + a.table_bytes) + static_cast<size_t>(wid) * a.L.words;
+  const SmallWarp w = make_small_warp(t, slab, a.L);
+  const int l = w.lane;
+  const unsigned FULL = 0xffffffffu;
+  // lane e: segment count of edge e, then an inclusive scan of the states per edge
+  const int my_nd = l < a.n_edges ? edge_nd(a.sp, a.q0 + static_cast<int64_t>(l) * a.ld, a.q1 + static_cast<int64_t>(l) * a.ld) : 0;
+  int incl = l < a.n_edges ? max(my_nd, 1) : 0;
+#pragma unroll
+  for (int d = 1; d < 32; d <<= 1) {
+    const int v = __shfl_up_sync(FULL, incl, d);
+    if (l >= d) incl += v;
+  }
+  const int total = __shfl_sync(FULL, incl, 31);
+  const int gw = blockIdx.x * nwarps + wid, gstep = gridDim.x * nwarps;
+  int done = 0;
+  for (int s = gw; s < total; s += gstep, ++done) {
+    const int e = __popc(__ballot_sync(FULL, l < a.n_edges && incl <= s));
+    const int excl = __shfl_sync(FULL, incl, e) - max(__shfl_sync(FULL, my_nd, e), 1);
+    const int nd = __shfl_sync(FULL, my_nd, e);
+    const int j = s - excl + 1;  // 1 .. max(nd, 1); j >= nd is the end state itself
+    const int jj = min(j, nd);
+    if (*reinterpret_cast<volatile int32_t*>(a.work + e) < jj) continue;  // an earlier state already failed
+    const float* r0 = a.q0 + static_cast<int64_t>(e) * a.ld;
+    const float* r1 = a.q1 + static_cast<int64_t>(e) * a.ld;
+    const bool is_end = j >= nd;
+    const float tt = is_end ? 1.f : static_cast<float>(j) / static_cast<float>(nd);
+    bool in_bounds = true;
+    for (int i = l; i < a.sp.n_sub; i += 32) {  // lane i interpolates subspace i
+      const DSub& sb = a.sp.sub[i];
+      const float* p0 = r0 + sb.col;
+      const float* p1 = r1 + sb.col;
+      float* o = w.act + sb.col;
+      const int nreal = sb.type == RAMP_SPACE_REAL ? sb.dim : (sb.type == RAMP_SPACE_SE2 ? 2 : (sb.type == RAMP_SPACE_SE3 ? 3 : 0));
+      for (int k = 0; k < nreal; ++k) {
+        const float v = is_end ? p1[k] : fmaf(p1[k] - p0[k], tt, p0[k]);
+        o[k] = v;
+        in_bounds = in_bounds && v <= sb.hi[k] && v >= sb.lo[k];
+      }
+      if (sb.type == RAMP_SPACE_SO2 || sb.type == RAMP_SPACE_SE2) {
+        const int k = sb.type == RAMP_SPACE_SE2 ? 2 : 0;
+        const float v = is_end ? p1[k] : so2_interp(p0[k], p1[k], tt);
+        o[k] = v;
+        in_bounds = in_bounds && v <= RAMP_PI_F && v >= -RAMP_PI_F;
+      } else if (sb.type == RAMP_SPACE_SE3 || sb.type == RAMP_SPACE_SO3) {
+        const int k0 = sb.type == RAMP_SPACE_SE3 ? 3 : 0;
+        const float* qa = p0 + k0;
+        const float* qb = p1 + k0;
+        float out[4] = {qb[0], qb[1], qb[2], qb[3]};
+        if (!is_end) {
+          const float th = so3_arc(qa, qb, 1);
+          if (th > 1e-7f) {
+            const float dn = 1.f / sinf(th), s0 = sinf((1.f - tt) * th);
+            float s1 = sinf(tt * th);
+            if (qa[0] * qb[0] + qa[1] * qb[1] + qa[2] * qb[2] + qa[3] * qb[3] < 0.f) s1 = -s1;
+            for (int k = 0; k < 4; ++k) out[k] = (qa[k] * s0 + qb[k] * s1) * dn;
+          } else {
+            for (int k = 0; k < 4; ++k) out[k] = qa[k];
+          }
+        }
+        for (int k = 0; k < 4; ++k) o[k0 + k] = out[k];
+      }
+    }
+    in_bounds = __all_sync(FULL, in_bounds);
+    __syncwarp();
+    expand_q_warp(w);
+    bool invalid = a.sp.check_bounds && !in_bounds;
+    if (!invalid) invalid = check_one_config(w, true, false) != INT32_MAX;
+    if (invalid && l == 0) atomicMin(a.work + e, jj);
+    __syncwarp();
+  }
+  // the last warp to hand in its states folds the minima into the outputs
+  __threadfence();
+  unsigned fin = 0;
+  if (l == 0) fin = atomicAdd(reinterpret_cast<unsigned*>(a.work + kSmallEdges), static_cast<unsigned>(done)) + done;
+  fin = __shfl_sync(FULL, fin, 0);
+  if (fin == static_cast<unsigned>(kWorkInit) + static_cast<unsigned>(total) && done > 0 || (total == 0 && gw == 0)) {
+    __threadfence();
+    if (l < a.n_edges) {
+      const int32_t f = *reinterpret_cast<volatile int32_t*>(a.work + l);
+      a.valid[l] = f == kWorkInit;
+      if (a.first_invalid) a.first_invalid[l] = f == kWorkInit ? -1 : f;
+      if (a.nd) a.nd[l] = my_nd;
+    }
+  }
+}
+
 // pass 4: fold the per-edge minimum into the caller's outputs
 __global__ void edge_finish_kernel(const __grid_constant__ EdgeArgs a, int32_t* out_first, int32_t* out_nd) {
   const int64_t e = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
@@ -1447,6 +1562,9 @@ struct RampModel {
   mutable void* h_pinned = nullptr;
   mutable size_t pinned_cap = 0;
   mutable cudaStream_t streams[2] = {nullptr, nullptr};  // ramp_check_host pipeline
+  mutable void* d_edge_stage = nullptr;  // ramp_check_edges_host staging (device / pinned host)
+  mutable void* h_edge_stage = nullptr;
+  mutable size_t edge_stage_cap = 0;
 };
 
 namespace ramp {
@@ -2215,6 +2333,8 @@ void ramp_model_destroy(RampModel* m) {
   if (m->pool) cudaMemPoolDestroy(m->pool);
   for (cudaStream_t st : m->streams) if (st) cudaStreamDestroy(st);
   if (m->h_pinned) cudaFreeHost(m->h_pinned);
+  if (m->d_edge_stage) cudaFree(m->d_edge_stage);
+  if (m->h_edge_stage) cudaFreeHost(m->h_edge_stage);
   delete m;
 }
 
@@ -2425,6 +2545,26 @@ int ramp_check_edges(const RampModel* m, const float* d_q0, const float* d_q1, i
   CUDA_TRY(cudaSetDevice(m->device));
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   std::lock_guard<std::mutex> lk(m->mu);
+  if (n_edges <= kSmallEdges) {  // a planner's edge-by-edge calls: one launch
+    if (int rc = ensure_scratch(m, 256)) return rc;
+    EdgeSmallArgs b;
+    b.img = m->d_image; b.table_bytes = static_cast<int32_t>(align16(m->hdr.total_bytes));
+    b.q0 = d_q0; b.q1 = d_q1; b.n_edges = static_cast<int32_t>(n_edges); b.ld = ld;
+    b.valid = d_valid; b.first_invalid = d_first_invalid; b.nd = d_nd;
+    b.work = static_cast<int32_t*>(m->d_scratch);
+    b.sp = a.sp;
+    plan_warp_slab(m, n_cols, &b.L);
+    const int nw = 4;
+    const size_t smem = 16 + b.table_bytes + static_cast<size_t>(b.L.words) * 4 * nw;
+    if (smem > static_cast<size_t>(m->max_smem)) return fail(RAMP_ERR_LIMIT, "model needs %zu B of shared memory per CTA", smem);
+    if (int rc = set_smem(edge_warp_kernel, smem)) return rc;
+    CUDA_TRY(cudaMemsetAsync(b.work, 0x7f, (kSmallEdges + 1) * sizeof(int32_t), st));
+    // enough warps for a few hundred states at once; every warp loops over its share
+    edge_warp_kernel<<<std::min(m->sm_count, 128), nw * 32, smem, st>>>(b);
+    g_launches.fetch_add(1, std::memory_order_relaxed);
+    CUDA_TRY(cudaGetLastError());
+    return RAMP_OK;
+  }
   // scratch: offs int64[n+1] | nd int32[n] | first int32[n]
   const size_t off_nd = align16(sizeof(int64_t) * (n_edges + 1));
   const size_t off_first = off_nd + align16(sizeof(int32_t) * n_edges);
@@ -2467,6 +2607,51 @@ int ramp_check_edges(const RampModel* m, const float* d_q0, const float* d_q1, i
   g_launches.fetch_add(use_queue ? 5 : 4, std::memory_order_relaxed);
   if (qmem) CUDA_TRY(cudaFreeAsync(qmem, st));
   CUDA_TRY(cudaGetLastError());
+  return RAMP_OK;
+}
+
+// Host-buffer form of ramp_check_edges for a planner's edge-by-edge calls: end points in,
+// verdict out, one synchronisation.  Copies go through the model's pinned staging buffer.
+int ramp_check_edges_host(const RampModel* m, const float* h_q0, const float* h_q1, int64_t n_edges, int32_t ld,
+                          const RampSpaceDesc* sp, uint8_t* h_valid, int32_t* h_first_invalid, int32_t* h_nd) {
+  if (!m || !sp) return fail(RAMP_ERR_INVALID, "null argument");
+  if (n_edges < 0) return fail(RAMP_ERR_INVALID, "negative edge count");
+  if (n_edges == 0) return RAMP_OK;
+  if (!h_q0 || !h_q1 || !h_valid) return fail(RAMP_ERR_INVALID, "null host pointer");
+  CUDA_TRY(cudaSetDevice(m->device));
+  const size_t b_q = align16(sizeof(float) * n_edges * ld), b_v = align16(n_edges), b_i = align16(sizeof(int32_t) * n_edges);
+  const size_t total = 2 * b_q + b_v + 2 * b_i;
+  unsigned char *D, *H;
+  {
+    std::lock_guard<std::mutex> lk(m->mu);
+    // device staging lives in its own buffer: ramp_check_edges uses d_scratch for its work arrays
+    if (total > m->edge_stage_cap) {
+      if (m->d_edge_stage) cudaFree(m->d_edge_stage);
+      if (m->h_edge_stage) cudaFreeHost(m->h_edge_stage);
+      m->d_edge_stage = nullptr; m->h_edge_stage = nullptr; m->edge_stage_cap = 0;
+      const size_t cap = std::max<size_t>(total, 1 << 16);
+      if (cudaMalloc(&m->d_edge_stage, cap) != cudaSuccess || cudaMallocHost(&m->h_edge_stage, cap) != cudaSuccess)
+        return fail(RAMP_ERR_ALLOC, "staging allocation (%zu B) failed", cap);
+      m->edge_stage_cap = cap;
+    }
+    D = static_cast<unsigned char*>(m->d_edge_stage);
+    H = static_cast<unsigned char*>(m->h_edge_stage);
+  }
+  cudaStream_t st = cudaStreamPerThread;
+  std::memcpy(H, h_q0, sizeof(float) * n_edges * ld);
+  std::memcpy(H + b_q, h_q1, sizeof(float) * n_edges * ld);
+  CUDA_TRY(cudaMemcpyAsync(D, H, 2 * b_q, cudaMemcpyHostToDevice, st));
+  uint8_t* d_valid = D + 2 * b_q;
+  int32_t* d_first = reinterpret_cast<int32_t*>(D + 2 * b_q + b_v);
+  int32_t* d_nd = reinterpret_cast<int32_t*>(D + 2 * b_q + b_v + b_i);
+  if (int rc = ramp_check_edges(m, reinterpret_cast<const float*>(D), reinterpret_cast<const float*>(D + b_q), n_edges, ld, sp,
+                                d_valid, d_first, d_nd, st))
+    return rc;
+  CUDA_TRY(cudaMemcpyAsync(H + 2 * b_q, D + 2 * b_q, b_v + 2 * b_i, cudaMemcpyDeviceToHost, st));
+  CUDA_TRY(cudaStreamSynchronize(st));
+  std::memcpy(h_valid, H + 2 * b_q, n_edges);
+  if (h_first_invalid) std::memcpy(h_first_invalid, H + 2 * b_q + b_v, sizeof(int32_t) * n_edges);
+  if (h_nd) std::memcpy(h_nd, H + 2 * b_q + b_v + b_i, sizeof(int32_t) * n_edges);
   return RAMP_OK;
 }
 

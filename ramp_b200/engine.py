@@ -52,6 +52,7 @@ def load_library():
         "ramp_check_batch_noalloc": (C.c_int, [vp, vp, i64, i32, u32, vp, vp, vp, vp]),
         "ramp_distance_batch": (C.c_int, [vp, vp, i64, i32, u32, C.POINTER(i32), i32, vp, vp]),
         "ramp_check_edges": (C.c_int, [vp, vp, vp, i64, i32, C.POINTER(D.RampSpaceDesc), vp, vp, vp, vp]),
+        "ramp_check_edges_host": (C.c_int, [vp, vp, vp, i64, i32, C.POINTER(D.RampSpaceDesc), vp, vp, vp]),
         "ramp_check_host": (C.c_int, [vp, vp, i64, i32, u32, vp, vp, vp, vp]),
     }
     for name, (res, args) in sig.items():
@@ -231,6 +232,19 @@ class GpuModel:
                                          C.byref(space.struct), valid.data_ptr(), first.data_ptr(), nd.data_ptr(),
                                          _stream_ptr(self.device)), "ramp_check_edges")
         return {"valid": valid.bool(), "first_invalid": first, "nd": nd}
+
+    def check_edges_host(self, q0: np.ndarray, q1: np.ndarray, space: D.SpaceDesc) -> dict:
+        """ramp_check_edges_host: numpy end points in, numpy verdicts out, one library call."""
+        q0 = np.ascontiguousarray(np.atleast_2d(q0), dtype=np.float32)
+        q1 = np.ascontiguousarray(np.atleast_2d(q1), dtype=np.float32)
+        n = len(q0)
+        valid = np.zeros(n, dtype=np.uint8)
+        first = np.zeros(n, dtype=np.int32)
+        nd = np.zeros(n, dtype=np.int32)
+        _check(self.lib.ramp_check_edges_host(self.handle, q0.ctypes.data, q1.ctypes.data, n, q0.shape[1],
+                                              C.byref(space.struct), valid.ctypes.data, first.ctypes.data, nd.ctypes.data),
+               "ramp_check_edges_host")
+        return {"valid": valid.astype(bool), "first_invalid": first, "nd": nd}
 
     def check_host(self, q: np.ndarray, *, actuated: bool = False, first_pair: bool = False,
                    pair_mask: bool = False) -> dict:

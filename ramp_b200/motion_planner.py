@@ -53,9 +53,11 @@ class GpuMotionValidator:
         return res
 
     def checkMotion(self, s1, s2, last_valid: list | None = None) -> bool:  # noqa: N802
-        res = self.check_edges(np.asarray(s1, dtype=np.float32)[None], np.asarray(s2, dtype=np.float32)[None])
-        out = torch.stack([res["valid"].to(torch.int32), res["first_invalid"], res["nd"]]).cpu().numpy()
-        valid, first, nd = bool(out[0, 0]), int(out[1, 0]), int(out[2, 0])
+        p = self._p
+        p._sync_gpu()
+        res = p._robot_model.gpu.check_edges_host(np.asarray(s1, dtype=np.float32)[None], np.asarray(s2, dtype=np.float32)[None],
+                                                  p.space)
+        valid, first, nd = bool(res["valid"][0]), int(res["first_invalid"][0]), int(res["nd"][0])
         self.states_checked += max(nd, 1)
         if valid:
             self.valid_count += 1

@@ -148,7 +148,8 @@ def test_actuated_input_matches_host_map(built):
         assert np.abs(got - ref).max() < POSE_TOL
 
 
-EDGE_CASES = [("rrr/configs", None, 300), ("rrr/planar_configs", "capsule", 200), ("rrr/floating_configs", "capsule", 150),
+EDGE_CASES = [("rrr/configs", None, 20), ("panda/configs", "capsule", 32), ("rrr/floating_configs", "capsule", 7),
+              ("rrr/configs", None, 300), ("rrr/planar_configs", "capsule", 200), ("rrr/floating_configs", "capsule", 150),
               ("panda/configs", "capsule", 200), ("planar_rrr/configs", "capsule", 200)]
 
 
@@ -183,7 +184,7 @@ def test_edges_match_oracle(built, name, scene, n_edges):
     nd = got["nd"].cpu().numpy()
     # FP32 vs FP64 ceil() may differ when dist/lvs sits on an integer: allow +-1 on few edges
     same_nd = nd == ref["nd"]
-    assert (np.abs(nd - ref["nd"]) <= 1).all() and same_nd.mean() > 0.97
+    assert (np.abs(nd - ref["nd"]) <= 1).all() and same_nd.mean() > (0.97 if n_edges > 100 else 0.8)
     valid = got["valid"].cpu().numpy()
     first = got["first_invalid"].cpu().numpy()
     agree = (valid == ref["valid"]) & (first == ref["first_invalid"])
