@@ -2129,6 +2129,8 @@ static int launch_check(const RampModel* m, const float* d_q, int64_t n, int32_t
   size_t smem_b = 0;
   if (use_queue) {
     cap_items = static_cast<uint32_t>(std::min<int64_t>(n, kSliceRows) * kQueueItemsPerRow + 4096);
+    // test hook: a tiny queue forces the overflow path (GJK inside check_kernel)
+    if (const char* e = std::getenv("RAMP_B200_QUEUE_CAP")) cap_items = static_cast<uint32_t>(std::max(1, std::atoi(e)));
     const size_t bytes = 256 + static_cast<size_t>(cap_items) * sizeof(GjkItem);
     if (cudaMallocFromPoolAsync(reinterpret_cast<void**>(&scratch), bytes, m->pool, st) != cudaSuccess) {
       cudaGetLastError();

@@ -292,3 +292,16 @@ def test_large_sweep_flags_and_first_pair(built, name, scene, n):
     bad_first = int((first != ref["first_pair"])[clean].sum())
     print(name, dict(n=n, colliding=int(ref["hit"].sum()), in_band=int((~outside).sum()), bad_cfg=bad_cfg, bad_first=bad_first))
     assert bad_cfg == 0 and bad_first == 0
+
+
+def test_queue_overflow_falls_back_to_in_kernel_gjk(built, monkeypatch, record_property):
+    """The GJK work queue is bounded; items that do not fit are solved inside the validity
+    kernel (cold start instead of the capsule witness, so near-contact pairs may flip inside
+    the margin band).  A 100-item queue forces nearly everything down that path: the answers
+    still match the oracle outside the band."""
+    from ramp_b200 import workloads
+
+    rm, _ = _setup("ur5e/configs", "obstacles")
+    q = workloads.sample_q(rm.model, 20000, seed=77)
+    monkeypatch.setenv("RAMP_B200_QUEUE_CAP", "100")
+    _compare_check(rm, q, lambda **kw: [record_property(k, v) for k, v in kw.items()])
