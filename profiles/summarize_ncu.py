@@ -2,6 +2,8 @@
 
     python profiles/summarize_ncu.py gpurun_out/prof_check.ncu-rep profiles/r01_check_ur5e
 
+    python profiles/summarize_ncu.py <rep> <out> gjk_queue      # source page of the first launch matching the name
+
 writes <out>_metrics.txt (raw-page counters of every captured launch) and <out>_source.txt
 (top source lines by warp-stall samples for the first captured launch; needs -lineinfo).
 """
@@ -33,7 +35,7 @@ def ncu(rep, page, extra=()):
     return subprocess.run(["ncu", "-i", rep, "--page", page, "--csv", *extra], capture_output=True, text=True).stdout
 
 
-def main(rep, out):
+def main(rep, out, kernel=None):
     rows = list(csv.reader(io.StringIO(ncu(rep, "raw"))))
     hdr, units = rows[0], rows[1]
     with open(out + "_metrics.txt", "w") as f:
@@ -42,7 +44,8 @@ def main(rep, out):
             for k in KEYS + [STALLS % s for s in STALL_NAMES]:
                 if k in hdr:
                     f.write(f"{k:86s} {r[hdr.index(k)]} {units[hdr.index(k)]}\n")
-    rows = list(csv.reader(io.StringIO(ncu(rep, "source", ("--print-source", "cuda,sass")))))
+    sel = ("-k", "regex:" + kernel, "-c", "1") if kernel else ()
+    rows = list(csv.reader(io.StringIO(ncu(rep, "source", ("--print-source", "cuda,sass", *sel)))))
     sections, cur = [], None
     for r in rows:
         if len(r) >= 2 and r[0] == "File Path":
@@ -74,7 +77,7 @@ def main(rep, out):
             if r[1] and k not in src:
                 src[k] = r[1]
     T, I = sum(samp.values()) or 1, sum(inst.values()) or 1
-    with open(out + "_source.txt", "w") as f:
+    with open(out + ("_source.txt" if not kernel else f"_source_{kernel}.txt"), "w") as f:
         f.write(f"total samples {T:.0f}, warp instructions {I:.0f}\n")
         f.write("file:line  samples%  inst%  threads/inst  no_inst% of samples  source\n")
         for k, v in samp.most_common(40):
@@ -82,4 +85,4 @@ def main(rep, out):
 
 
 if __name__ == "__main__":
-    main(sys.argv[1], sys.argv[2])
+    main(*sys.argv[1:4])

@@ -410,22 +410,15 @@ __device__ __forceinline__ void gjk_init(GjkLane& g, const Xf& rel, float rsum, 
 
 enum { GJK_CONTINUE = 0, GJK_HIT = 1, GJK_MISS = 2 };
 
-// One GJK iteration.  `exact`: run to convergence (distance output) instead of stopping at
-// the first proof of separation / overlap.  On GJK_MISS / GJK_HIT with exact, dist holds the
-// core distance minus the swept radii.
-__device__ __forceinline__ int gjk_step(GjkLane& g, const GjkShape& A, const GjkShape& B, bool exact, float& dist) {
+// The simplex half of one GJK iteration: sa, sb are the support points of A along -v and of B
+// along +v (each in its own frame).  `exact`: run to convergence (distance output) instead of
+// stopping at the first proof of separation / overlap.  On GJK_MISS / GJK_HIT with exact, dist
+// holds the core distance minus the swept radii.
+__device__ __forceinline__ int gjk_advance(GjkLane& g, V3 sa, V3 sb, bool exact, float& dist) {
   // |v| below 2e-5 m counts as touching: FP32 cannot resolve a simplex face through the origin
   // any better, and such a pair is inside the +-1e-4 m margin band either way
   const float EPS_REL = 1e-5f, TINY2 = 4e-10f;
   const float rs2 = g.rsum * g.rsum;
-  V3 sa = mk(0.f, 0.f, 0.f), sb = sa;
-#pragma unroll 1
-  for (int side = 0; side < 2; ++side) {
-    const GjkShape& S = side ? B : A;
-    const V3 d = side ? rot_t(g.rel, g.v) : -g.v;
-    const V3 r = support(S.type, S.p0, S.p1, S.p2, S.verts, S.vcnt, d);
-    if (side) sb = r; else sa = r;
-  }
   const V3 w = sa - apply(g.rel, sb);
   const float vw = dot(g.v, w);
   if (vw > 0.f) {
@@ -456,6 +449,19 @@ __device__ __forceinline__ int gjk_step(GjkLane& g, const GjkShape& A, const Gjk
   // a stalled iteration far from convergence: trust the proven lower bound
   if (d <= g.rsum && g.lower > g.rsum) { dist = g.lower - g.rsum; return GJK_MISS; }
   return d <= g.rsum ? GJK_HIT : GJK_MISS;
+}
+
+// One GJK iteration: both support scans, then the simplex update.
+__device__ __forceinline__ int gjk_step(GjkLane& g, const GjkShape& A, const GjkShape& B, bool exact, float& dist) {
+  V3 sa = mk(0.f, 0.f, 0.f), sb = sa;
+#pragma unroll 1
+  for (int side = 0; side < 2; ++side) {
+    const GjkShape& S = side ? B : A;
+    const V3 d = side ? rot_t(g.rel, g.v) : -g.v;
+    const V3 r = support(S.type, S.p0, S.p1, S.p2, S.verts, S.vcnt, d);
+    if (side) sb = r; else sa = r;
+  }
+  return gjk_advance(g, sa, sb, exact, dist);
 }
 
 // ------------------------------------------------------------------------------ EPA

@@ -684,7 +684,11 @@ __device__ __forceinline__ void narrow_phase(const Warp& w, bool stop_at_first, 
               A = load_shape(ga, w.t.verts);
               B = load_shape(gb, w.t.verts);
               const Xf rl = xf_inv_mul(geom_xf(w, ga->gslot, c), geom_xf(w, gb->gslot, c));
-              gjk_init(g, rl, swept_radius(ga) + swept_radius(gb), -trans(rl));
+              // same start as the queued items: the witness of the two inner capsule axes
+              const V3 zb = mk(rl.m[2], rl.m[6], rl.m[10]);
+              const V3 v0 = seg_seg_witness(mk(0.f, 0.f, -ga->s_in), mk(0.f, 0.f, 2.f * ga->s_in), trans(rl) - zb * gb->s_in,
+                                            zb * (2.f * gb->s_in));
+              gjk_init(g, rl, swept_radius(ga) + swept_radius(gb), v0);
               active = true;
             }
           }
@@ -992,7 +996,7 @@ struct GjkQueueArgs {
   const unsigned char* img;
   int32_t table_bytes;
   const GjkItem* items;
-  const uint32_t* count;
+  uint32_t* count;   // [0] items produced, [1] the consumers' cursor (both zeroed by the host)
   uint32_t capacity;
   uint8_t* hit;
   int32_t* first_pair;
@@ -1006,7 +1010,8 @@ struct GjkQueueArgs {
   int64_t n_edges;
 };
 
-constexpr int kQueueChunk = 64;  // consecutive items owned by one warp
+constexpr int kQueueChunk = 32;  // items a warp takes from the queue at a time
+constexpr int kFetchAttempts = 4;
 
 #ifdef RAMP_STATS
 __device__ unsigned long long g_stats[64];  // [0] items [1] iterations [2] hits [3] skipped, [8+it] histogram
@@ -1018,22 +1023,49 @@ __global__ void __launch_bounds__(256, 2) gjk_queue_kernel(const __grid_constant
   stage_tables(tbl, a.img, a.table_bytes, mbar);
   const Tables t = make_tables(tbl);
   const uint32_t total = min(*a.count, a.capacity);
-  const uint64_t W = static_cast<uint64_t>(gridDim.x) * (blockDim.x >> 5);
-  const uint64_t wg = static_cast<uint64_t>(blockIdx.x) * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  // Work is handed out dynamically: a warp takes kQueueChunk consecutive items at a time from a
+  // cursor next to the producers' counter, so every warp stays busy until the queue is empty
+  // (iteration counts per item vary from 1 to 48: a static split leaves long tails).
+  uint32_t* cursor = a.count + 1;
   const int l = threadIdx.x & 31;
   const unsigned FULL = 0xffffffffu;
-  uint32_t next = 0, row = 0, p = 0;
-  bool active = false;
+  uint32_t lo = 0, hi = 0, row = 0, p = 0;  // [lo, hi): items this warp holds but has not started
+  bool active = false, drained = false;
   GjkLane g;
   GjkShape A, B;
   A.type = B.type = 0; A.vcnt = B.vcnt = 0; A.p0 = A.p1 = A.p2 = B.p0 = B.p1 = B.p2 = 0.f; A.verts = B.verts = t.verts;
   g.s.n = 0; g.it = 0; g.vv = 1.f; g.rsum = 0.f; g.lower = 0.f; g.v = mk(1.f, 0.f, 0.f); g.rel = xf_identity();
-  auto global_index = [&](uint32_t i) { return (wg + static_cast<uint64_t>(i / kQueueChunk) * W) * kQueueChunk + (i % kQueueChunk); };
   while (true) {
-    const unsigned need = __ballot_sync(FULL, !active);
-    if (!active) {
-      const uint64_t gi = global_index(next + __popc(need & ((1u << l) - 1)));
-      if (gi < total) {
+    // Fill idle lanes.  In early-out mode many items are skipped on arrival (their
+    // configuration was hit meanwhile), so try a few times before running a trip.
+#pragma unroll 1
+    for (int attempt = 0; attempt < kFetchAttempts; ++attempt) {
+      const unsigned need = __ballot_sync(FULL, !active);
+      if (!need || (drained && lo == hi)) break;
+      uint32_t gi = 0xffffffffu;
+      {
+        const uint32_t rank = __popc(need & ((1u << l) - 1)), nneed = __popc(need), avail = hi - lo;
+        if (!active && rank < avail) gi = lo + rank;
+        if (nneed <= avail) {
+          lo += nneed;
+        } else {
+          lo = hi;
+          if (!drained) {
+            uint32_t base = 0;
+            if (l == 0) base = atomicAdd(cursor, static_cast<uint32_t>(kQueueChunk));
+            base = __shfl_sync(FULL, base, 0);
+            if (base >= total) {
+              drained = true;
+            } else {
+              hi = min(base + static_cast<uint32_t>(kQueueChunk), total);
+              const uint32_t r2 = rank - avail;
+              if (!active && rank >= avail && r2 < hi - base) gi = base + r2;
+              lo = min(base + (nneed - avail), hi);
+            }
+          }
+        }
+      }
+      if (gi != 0xffffffffu) {
         const float4* src = reinterpret_cast<const float4*>(a.items + gi);
         const float4 r0 = __ldcs(src), r1 = __ldcs(src + 1), r2 = __ldcs(src + 2), r3 = __ldcs(src + 3), r4 = __ldcs(src + 4);
         row = __float_as_uint(r3.w);
@@ -1055,9 +1087,8 @@ __global__ void __launch_bounds__(256, 2) gjk_queue_kernel(const __grid_constant
         }
       }
     }
-    next += __popc(need);
     if (!__any_sync(FULL, active)) {
-      if (global_index(next) >= total) break;
+      if (drained && lo == hi) break;
       continue;
     }
     if (active) {
