@@ -482,16 +482,22 @@ __device__ __forceinline__ bool closed_form_hit(int cls, const DGeom* ga, const 
   return closed_form_dist(cls, ga, gb, rel) <= 0.f;
 }
 
+// Early out (`stop_at_first`): pair p of a configuration is dropped once a pair with a smaller
+// list index has hit (the first-pair output needs nothing else), or -- `stop_any`, when only
+// the flag is wanted -- once any pair has hit.
 // `tw` / kTeam: this warp takes every kTeam-th chunk of `chunk_pairs` pairs (kTeam == 1: all of
 // them, in chunks of kChunkPairs -- a compile-time constant on the common path)
 template <int kTeam = 1>
-__device__ __forceinline__ void narrow_phase(const Warp& w, bool stop_at_first, bool want_mask, const GjkQueue& gq,
-                                             uint32_t row_base, int tw = 0, int chunk_pairs_rt = kChunkPairs) {
+__device__ __forceinline__ void narrow_phase(const Warp& w, bool stop_at_first, bool stop_any, bool want_mask,
+                                             const GjkQueue& gq, uint32_t row_base, int tw = 0,
+                                             int chunk_pairs_rt = kChunkPairs) {
   const int team = kTeam;
   const int chunk_pairs = kTeam == 1 ? kChunkPairs : chunk_pairs_rt;
   const ImgHeader* h = w.t.h;
   const int l = w.lane;
   const unsigned FULL = 0xffffffffu;
+  // decided already?  (first = smallest list index that hit so far, INT32_MAX if none)
+  auto dead = [&](int first, int orig) { return stop_at_first && first < (stop_any ? INT32_MAX : orig); };
   for (int chunk = tw * chunk_pairs; chunk < h->n_pairs; chunk += team * chunk_pairs) {
     const int chunk_end = min(chunk + chunk_pairs, h->n_pairs);
     const int my_first = w.first[l];
@@ -502,7 +508,7 @@ __device__ __forceinline__ void narrow_phase(const Warp& w, bool stop_at_first, 
     const float* T = S + w.geom_w + l + 6 * 32;   // translation rows of this lane's slab column
     const float* TS = S + w.stat_w + 6;           // translations of the static placements
     auto push = [&](int p, const DPair& pr, bool pass) {
-      pass = pass && pr.cls != kClsInactive && !(stop_at_first && my_first < pr.orig);
+      pass = pass && pr.cls != kClsInactive && !dead(my_first, pr.orig);
       if (pr.cls == kClsSphereSphere) {  // the sphere test was the decision itself
         if (pass) record_hit(w, l, pr.orig, want_mask);
         pass = false;
@@ -600,7 +606,13 @@ __device__ __forceinline__ void narrow_phase(const Warp& w, bool stop_at_first, 
       bool to_gjk = false;
       Xf rel = xf_identity();
       V3 v0 = mk(1.f, 0.f, 0.f);
-      if (live) {
+      int orig = 0;
+      bool go = live;
+      if (live) {  // a configuration settled by an earlier group needs no more work
+        orig = w.t.pairs[chunk + (item >> 5)].orig;
+        go = !dead(w.first[item & 31], orig);
+      }
+      if (go) {
         const int c = item & 31, p = chunk + (item >> 5);
         const DPair pr = w.t.pairs[p];
         const DGeom* ga = &w.t.geoms[pr.a];
@@ -632,6 +644,8 @@ __device__ __forceinline__ void narrow_phase(const Warp& w, bool stop_at_first, 
         }
       }
       __syncwarp();  // all lanes have read their item before the in-place compaction writes
+      // hits of this group may have settled configurations whose GJK items are still pending
+      if (to_gjk && dead(w.first[item & 31], orig)) to_gjk = false;
       if (gq.items != nullptr) {
         // reserve slots of the global queue for this group's survivors (one atomic per group)
         const unsigned gb_ = __ballot_sync(FULL, to_gjk);
@@ -678,7 +692,7 @@ __device__ __forceinline__ void narrow_phase(const Warp& w, bool stop_at_first, 
             // a configuration that was hit earlier (at a smaller list index) needs no later pair
             const DPair pr = w.t.pairs[p];
             p = pr.orig;  // results report the caller's index
-            if (!(stop_at_first && w.first[c] < p)) {
+            if (!dead(w.first[c], p)) {
               const DGeom* ga = &w.t.geoms[pr.a];
               const DGeom* gb = &w.t.geoms[pr.b];
               A = load_shape(ga, w.t.verts);
@@ -772,7 +786,8 @@ __global__ void __launch_bounds__(512, 1) check_kernel(const __grid_constant__ C
       fk_lane<0>(w);
     }
     team_sync();
-    narrow_phase<kTeam>(w, stop, want_mask, a.gq, static_cast<uint32_t>(row0), tw, a.L.chunk_pairs);
+    narrow_phase<kTeam>(w, stop, stop && a.first_pair == nullptr, want_mask, a.gq, static_cast<uint32_t>(row0), tw,
+                        a.L.chunk_pairs);
     team_sync();
     const int64_t row = row0 + w.lane;
     if (tw == 0 && row < a.n) {
@@ -1408,7 +1423,7 @@ __global__ void __launch_bounds__(512, 1) edge_check_kernel(const __grid_constan
     reset_results(w, 0);
     fk_lane<0>(w);
     __syncwarp();
-    narrow_phase(w, true, false, a.gq, static_cast<uint32_t>(tile << 5));
+    narrow_phase(w, true, true, false, a.gq, static_cast<uint32_t>(tile << 5));
     const bool invalid = w.first[l] != INT32_MAX || (a.sp.check_bounds && !in_bounds);
     if (!skip && invalid) atomicMin(&a.first_invalid[e], min(j, nd));
     __syncwarp();
