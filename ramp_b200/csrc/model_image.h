@@ -25,7 +25,7 @@ constexpr int kParentRunning = -2;   // parent is the previous joint: use the re
 // narrow-phase class of a pair (decided on the host from the two shape types)
 enum PairClass : int32_t {
   kClsInactive = 0,
-  kClsSphereSphere = 1,   // decided exactly by the bounding-sphere test
+  kClsSphereSphere = 1,   // classes 1..5: closed-form distance
   kClsSphereCapsule = 2,
   kClsSphereBox = 3,
   kClsSphereCylinder = 4,
@@ -69,16 +69,17 @@ static_assert(sizeof(DGeom) == 160, "DGeom");
 // ("DD"), then those of a joint-attached and a universe-attached one ("DS") -- each stage-1
 // loop then addresses placements with constant strides.  `orig` is the index in the caller's
 // list (GeometryModel.collisionPairs order), which is what every result reports.
-struct DPair {  // 12 words
-  int16_t d, s;       // stage 1: DD: slab slots of the two; DS: slab slot of one, static index of the other
-  int16_t cls, orig;  // narrow-phase class; index in the caller's pair list
-  float rs2;          // (bound_r(a)+bound_r(b))^2, inflated for culls, exact for sphere-sphere
+struct DPair {  // 12 words; the first four are everything stage 1 reads (one 16-byte load)
+  int32_t o1, o2;     // byte offsets of the two placement origins: into a lane's slab column
+                      // (joint-attached) or into the static table (universe-attached)
+  float rs2;          // (bound_r(a)+bound_r(b))^2, slightly inflated; -1 for an inactive pair
+  int16_t orig, cls;  // index in the caller's pair list; narrow-phase class
   float slack;        // widening of every conservative test: 1e-5 m + the pair's share of non-rigid placements
   int16_t a, b;       // geometry indices, ordered so that type(a) <= type(b)
   int16_t sa, sb;     // their gslot values (>= 0 slab slot, < 0 static placement)
   float ha_out, hb_out;  // outer capsules of a and b (GJK class): half lengths ...
   float rsum_out;        // ... and radius sum (+ slack)
-  int32_t pad[3];
+  int32_t pad[2];
 };
 static_assert(sizeof(DPair) == 48, "DPair");
 

@@ -502,33 +502,30 @@ __device__ __forceinline__ void narrow_phase(const Warp& w, bool stop_at_first, 
     const int chunk_end = min(chunk + chunk_pairs, h->n_pairs);
     const int my_first = w.first[l];
     int qn = 0;
-    // ---- stage 1: bounding spheres; lane = configuration, pair index uniform.  Two pairs per trip: their shared-memory loads and arithmetic are independent,
-    // which matters because only a few warps fit next to the slabs (latency, not issue, bound).
-    const float* S = reinterpret_cast<const float*>(g_smem);
-    const float* T = S + w.geom_w + l + 6 * 32;   // translation rows of this lane's slab column
-    const float* TS = S + w.stat_w + 6;           // translations of the static placements
-    auto push = [&](int p, const DPair& pr, bool pass) {
-      pass = pass && pr.cls != kClsInactive && !dead(my_first, pr.orig);
-      if (pr.cls == kClsSphereSphere) {  // the sphere test was the decision itself
-        if (pass) record_hit(w, l, pr.orig, want_mask);
-        pass = false;
-      }
+    // ---- stage 1: bounding spheres; lane = configuration, pair index uniform.  The first 16
+    // bytes of a DPair are all this stage reads (one vector load): two byte offsets of the
+    // placement origins, the squared radius sum (-1: inactive pair, never passes) and the
+    // caller's pair index for the early-out test.
+    const char* T = reinterpret_cast<const char*>(g_smem) + 4 * (w.geom_w + l + 6 * 32);  // origin rows of this lane's slab column
+    const char* TS = reinterpret_cast<const char*>(g_smem) + 4 * (w.stat_w + 6);          // origins of the static placements
+    const int4* rec = reinterpret_cast<const int4*>(w.t.pairs);  // 3 per DPair
+    const unsigned lt = (1u << l) - 1;
+    // dead(my_first, orig) as one LOP3 + compare: pass needs my_first >= (orig & lim_and) | lim_or
+    const int lim_and = (stop_at_first && !stop_any) ? 0xffff : 0;
+    const int lim_or = stop_at_first ? (stop_any ? INT32_MAX : 0) : INT32_MIN;
+    const int item0 = l - (chunk << 5);
+    auto push = [&](int p, const int4& r, bool pass) {
+      pass = pass && my_first >= ((r.w & lim_and) | lim_or);
       const unsigned b = __ballot_sync(FULL, pass);
-      if (pass) w.queue[qn + __popc(b & ((1u << l) - 1))] = static_cast<uint16_t>(((p - chunk) << 5) | l);
+      if (pass) w.queue[qn + __popc(b & lt)] = static_cast<uint16_t>((p << 5) + item0);
       qn += __popc(b);
     };
     // squared distance of the two placement origins against the bounding-sphere sum
-    auto dd_test = [&](const DPair& pr) {
-      const float* a = T + pr.d * (kGeomFloats * 32);
-      const float* b = T + pr.s * (kGeomFloats * 32);
-      const float dx = a[0] - b[0], dy = a[32] - b[32], dz = a[64] - b[64];
-      return fmaf(dx, dx, fmaf(dy, dy, dz * dz)) <= pr.rs2;
-    };
-    auto ds_test = [&](const DPair& pr) {
-      const float* a = T + pr.d * (kGeomFloats * 32);
-      const float* b = TS + pr.s * kStatFloats;
-      const float dx = a[0] - b[0], dy = a[32] - b[1], dz = a[64] - b[2];
-      return fmaf(dx, dx, fmaf(dy, dy, dz * dz)) <= pr.rs2;
+    auto near = [&](const int4& r, const char* base_a, const char* base_b, int stride_a, int stride_b) {
+      const float* a = reinterpret_cast<const float*>(base_a + r.x);
+      const float* b = reinterpret_cast<const float*>(base_b + r.y);
+      const float dx = a[0] - b[0], dy = a[stride_a] - b[stride_b], dz = a[2 * stride_a] - b[2 * stride_b];
+      return fmaf(dx, dx, fmaf(dy, dy, dz * dz)) <= __int_as_float(r.z);
     };
     const int dd_end = min(chunk_end, max(chunk, h->n_dd));
     // four pairs per trip: their loads are independent, which hides shared-memory latency
@@ -536,33 +533,28 @@ __device__ __forceinline__ void narrow_phase(const Warp& w, bool stop_at_first, 
 #pragma unroll 1
     for (int p = chunk; p < dd_end; p += 4) {
       const int last = dd_end - 1;
-      const DPair pr0 = w.t.pairs[p], pr1 = w.t.pairs[min(p + 1, last)], pr2 = w.t.pairs[min(p + 2, last)],
-                  pr3 = w.t.pairs[min(p + 3, last)];
-      const bool k0 = dd_test(pr0), k1 = dd_test(pr1), k2 = dd_test(pr2), k3 = dd_test(pr3);
-      push(p, pr0, k0);
-      if (p + 1 <= last) push(p + 1, pr1, k1);
-      if (p + 2 <= last) push(p + 2, pr2, k2);
-      if (p + 3 <= last) push(p + 3, pr3, k3);
+      const int4 r0 = rec[3 * p], r1 = rec[3 * min(p + 1, last)], r2 = rec[3 * min(p + 2, last)], r3 = rec[3 * min(p + 3, last)];
+      const bool k0 = near(r0, T, T, 32, 32), k1 = near(r1, T, T, 32, 32), k2 = near(r2, T, T, 32, 32), k3 = near(r3, T, T, 32, 32);
+      push(p, r0, k0);
+      push(p + 1, r1, k1 && p + 1 <= last);
+      push(p + 2, r2, k2 && p + 2 <= last);
+      push(p + 3, r3, k3 && p + 3 <= last);
     }
     const int ds_end = min(chunk_end, max(dd_end, h->ss_begin));
 #pragma unroll 1
     for (int p = dd_end; p < ds_end; p += 2) {
       const bool two = p + 1 < ds_end;
-      const DPair pr0 = w.t.pairs[p];
-      const DPair pr1 = w.t.pairs[two ? p + 1 : p];
-      const bool k0 = ds_test(pr0), k1 = ds_test(pr1);
-      push(p, pr0, k0);
-      if (two) push(p + 1, pr1, k1);
+      const int4 r0 = rec[3 * p], r1 = rec[3 * (two ? p + 1 : p)];
+      const bool k0 = near(r0, T, TS, 32, 1), k1 = near(r1, T, TS, 32, 1);
+      push(p, r0, k0);
+      push(p + 1, r1, k1 && two);
     }
     // two universe-attached geometries (a fixed base link against a scene object): the same
     // answer for every configuration, but it is part of the pair list
 #pragma unroll 1
     for (int p = ds_end; p < chunk_end; ++p) {
-      const DPair pr = w.t.pairs[p];
-      const float* a = TS + pr.d * kStatFloats;
-      const float* b = TS + pr.s * kStatFloats;
-      const float dx = a[0] - b[0], dy = a[1] - b[1], dz = a[2] - b[2];
-      push(p, pr, fmaf(dx, dx, fmaf(dy, dy, dz * dz)) <= pr.rs2);
+      const int4 r = rec[3 * p];
+      push(p, r, near(r, TS, TS, 1, 1));
     }
     __syncwarp();
     // ---- stage 1.5: OUTER capsules for the GJK class, on dense groups of 32 survivors of the
@@ -928,8 +920,7 @@ __device__ __forceinline__ int check_one_config(const SmallWarp& w, bool stop_at
       const Xf A = small_geom_xf(w, pr.sa), B = small_geom_xf(w, pr.sb);
       const V3 dc = trans(A) - trans(B);
       if (dot(dc, dc) <= pr.rs2) {
-        if (pr.cls == kClsSphereSphere) hit = true;
-        else {
+        {
           const Xf rel = xf_inv_mul(A, B);
           if (pr.cls < kClsBoxBox) hit = closed_form_hit(pr.cls, ga, gb, rel);
           else if (pr.cls == kClsBoxBox) hit = obb_overlap(mk(ga->p0, ga->p1, ga->p2), mk(gb->p0, gb->p1, gb->p2), rel, 0.f);
@@ -1981,14 +1972,16 @@ static int build_image(RampModel* m) {
     d.orig = static_cast<int16_t>(p);
     d.cls = static_cast<int16_t>(m->pair_active[p] ? pair_class(dg[a].type, dg[b].type) : kClsInactive);
     // stage-1 addressing: DD two slab slots; DS slab slot + static index; SS two static indices
-    if (k < n_dd) { d.d = d.sa; d.s = d.sb; }
-    else if (k >= ss_begin) { d.d = static_cast<int16_t>(-1 - dg[a].gslot); d.s = static_cast<int16_t>(-1 - dg[b].gslot); }
-    else if (dg[a].gslot >= 0) { d.d = d.sa; d.s = static_cast<int16_t>(-1 - dg[b].gslot); }
-    else { d.d = d.sb; d.s = static_cast<int16_t>(-1 - dg[a].gslot); }
+    const auto dyn_off = [](int gslot) { return gslot * kGeomFloats * 32 * 4; };     // bytes into a lane's slab column
+    const auto stat_off = [](int gslot) { return (-1 - gslot) * kStatFloats * 4; };  // bytes into the static table
+    if (k < n_dd) { d.o1 = dyn_off(d.sa); d.o2 = dyn_off(d.sb); }
+    else if (k >= ss_begin) { d.o1 = stat_off(d.sa); d.o2 = stat_off(d.sb); }
+    else if (dg[a].gslot >= 0) { d.o1 = dyn_off(d.sa); d.o2 = stat_off(d.sb); }
+    else { d.o1 = dyn_off(d.sb); d.o2 = stat_off(d.sa); }
     n_gjk += d.cls == kClsGjk;
     const double rs = static_cast<double>(dg[a].bound_r) + dg[b].bound_r;
-    // the sphere-sphere test is the decision itself; every other class uses it as a cull
-    d.rs2 = static_cast<float>(d.cls == kClsSphereSphere ? rs * rs : rs * rs * (1.0 + 1e-5) + 1e-9);
+    // stage 1 is a cull for every class (slightly inflated); an inactive pair never passes it
+    d.rs2 = d.cls == kClsInactive ? -1.f : static_cast<float>(rs * rs * (1.0 + 1e-5) + 1e-9);
     d.ha_out = dg[a].s_out; d.hb_out = dg[b].s_out;
     // Conservative tests are widened by 1e-5 m, plus -- when a placement is not a rigid
     // motion -- the amount by which lengths measured in its frame can be off
