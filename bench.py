@@ -338,15 +338,20 @@ def main() -> None:
         kt.append(a.elapsed_time(b))
     kernel_ms = statistics.mean(kt)
 
-    # end to end: the C-ABI host-buffer call (ramp_check_host): H2D of q, kernel, D2H of flags
-    q_pinned = batches[0].cpu().pin_memory()  # the step's inputs start in pinned host memory
-    q_host = q_pinned.numpy()
+    # end to end: the C-ABI host-buffer call (ramp_check_host): H2D of q, kernel, D2H of flags.
+    # The step's inputs start in page-locked host memory as plain [n, nq] rows (no padding).
+    from ramp_b200.engine import pinned_empty
+    nq = rm.model.nq
+    q_host = pinned_empty((n, nq), np.float32)
+    q_host[:] = batches[0][:, :nq].cpu().numpy()
+    hit_host = pinned_empty((n,), np.uint8)
     e2e_steps = max(3, min(args.steps, 10))
-    gpu.check_host(q_host)
+    gpu.check_host_into(q_host, hit_host)
+    assert np.array_equal(hit_host.astype(bool), gpu.check(batches[0])["hit"].cpu().numpy()), "e2e flags differ"
     barrier()
     t0 = time.perf_counter()
     for _ in range(e2e_steps):
-        gpu.check_host(q_host)
+        gpu.check_host_into(q_host, hit_host)
     barrier()
     e2e_s = time.perf_counter() - t0
     te = torch.tensor([e2e_s], dtype=torch.float64, device=dev)
@@ -396,8 +401,8 @@ def main() -> None:
                      "hbm": {"achieved": achieved_gbs, "peak": peaks["hbm_gbs"], "unit": "GB/s",
                              "frac": achieved_gbs / peaks["hbm_gbs"], "algorithmic_bytes_per_config": bytes_per_cfg,
                              "peak_source": peaks["_source"]}},
-        "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": n * ld * 4, "d2h_bytes_per_step": n,
-                "api": "ramp_check_host (C ABI, host buffers)", "steps": e2e_steps},
+        "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": n * nq * 4, "d2h_bytes_per_step": n,
+                "api": "ramp_check_host (C ABI, page-locked host buffers, rows of nq floats)", "steps": e2e_steps},
         "gpu_launches": launches,
         "clocks": clocks,
         "parity": {"checked": int(len(got)), "in_band": int((~outside).sum()),

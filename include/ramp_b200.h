@@ -29,6 +29,7 @@
 #ifndef RAMP_B200_H
 #define RAMP_B200_H
 
+#include <stddef.h>
 #include <stdint.h>
 
 #ifdef __cplusplus
@@ -290,6 +291,15 @@ int ramp_check_edges_host(const RampModel* m, const float* h_q0, const float* h_
 int ramp_check_host(const RampModel* m, const float* h_q, int64_t n, int32_t ld_q,
                     uint32_t flags, uint8_t* h_hit, int32_t* h_first_pair,
                     float* h_min_dist, uint32_t* h_pair_mask);
+
+/* Page-locked host memory for the h_* arguments of the host-buffer calls.
+ * ramp_check_host / ramp_check_edges_host copy straight from and to buffers
+ * that are page-locked (any allocator: they ask the driver per pointer) and go
+ * through an internal staging copy otherwise.  No reference counterpart (numpy
+ * arrays there); a convenience so that callers need no CUDA binding of their
+ * own.  ramp_host_alloc returns NULL on failure (see ramp_last_error). */
+void* ramp_host_alloc(size_t bytes);
+void ramp_host_free(void* p);
 
 /* Number of kernels this library has launched in this process (all models,
  * all threads) -- used by bench.py to report gpu_launches. */

@@ -159,17 +159,21 @@ __device__ __forceinline__ void load_rows(float* dst, const float* __restrict__ 
                                           int cols, int ld, int lane) {
   const int rows = static_cast<int>(imin64(32, n_rows - row0));
   const float* base = src + row0 * ld;
-  if (ld == cols && (cols & 3) == 0 && (reinterpret_cast<uintptr_t>(base) & 15) == 0) {
+  if (ld == cols && ((rows * cols) & 3) == 0 && (reinterpret_cast<uintptr_t>(base) & 15) == 0) {
+    // contiguous rows: the tile is rows * cols / 4 aligned float4 (one may straddle two rows)
     const int n4 = rows * cols / 4;
     const float4* b4 = reinterpret_cast<const float4*>(base);
-#pragma unroll 1
+    const float inv = 1.f / cols;  // floor(i / cols) == floor((i + 0.5) * inv) for i < 4096, cols <= 128
+#pragma unroll 2
     for (int e = lane; e < n4; e += 32) {
-      const float4 v = __ldg(b4 + e);
-      const int r = (4 * e) / cols, c = (4 * e) - r * cols;
-      dst[(c + 0) * 32 + r] = v.x;
-      dst[(c + 1) * 32 + r] = v.y;
-      dst[(c + 2) * 32 + r] = v.z;
-      dst[(c + 3) * 32 + r] = v.w;
+      const float4 q4 = __ldg(b4 + e);
+      int r = __float2int_rd((4 * e + 0.5f) * inv), c = 4 * e - r * cols;
+      const float v[4] = {q4.x, q4.y, q4.z, q4.w};
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        dst[c * 32 + r] = v[j];
+        if (++c == cols) { c = 0; ++r; }
+      }
     }
   } else {
     const int n = rows * cols;
@@ -195,7 +199,9 @@ __device__ __forceinline__ void load_rows(float* dst, const float* __restrict__ 
 // (long_scoreboard was the top stall of the FK kernel).  The next tile's float4s are fetched
 // into registers before the current tile's arithmetic and committed to shared memory after it.
 // kVec float4 per lane cover rows of up to 4 * kVec floats (8 in the FK kernels, 4 in the
-// register-tight validity kernel; wider rows fall back to the plain load)
+// register-tight validity kernel; wider rows fall back to the plain load).  Rows must be
+// contiguous (ld == cols, any width: a tile of 32 rows is then 8 * cols aligned float4, and one
+// float4 may straddle two rows).
 template <int kVec>
 struct RowPrefetch {
   float4 v[kVec];
@@ -204,7 +210,7 @@ struct RowPrefetch {
 
 template <int kVec>
 __device__ __forceinline__ bool rows_vectorisable(const float* base, int cols, int ld) {
-  return ld == cols && (cols & 3) == 0 && cols <= 4 * kVec && (reinterpret_cast<uintptr_t>(base) & 15) == 0;
+  return ld == cols && cols <= 4 * kVec && (reinterpret_cast<uintptr_t>(base) & 15) == 0;
 }
 
 template <int kVec>
@@ -214,8 +220,10 @@ __device__ __forceinline__ void prefetch_rows(RowPrefetch<kVec>& pf, const float
   if (row0 >= n_rows) return;
   const float* base = src + row0 * ld;
   if (!rows_vectorisable<kVec>(base, cols, ld)) return;
+  const int n_el = static_cast<int>(imin64(32, n_rows - row0)) * cols;
+  if (n_el & 3) return;  // a ragged last tile: plain load
   pf.valid = true;
-  const int n4 = static_cast<int>(imin64(32, n_rows - row0)) * cols / 4;
+  const int n4 = n_el / 4;
   const float4* b4 = reinterpret_cast<const float4*>(base);
 #pragma unroll
   for (int k = 0; k < kVec; ++k) {
@@ -233,15 +241,18 @@ __device__ __forceinline__ void commit_rows(const RowPrefetch<kVec>& pf, float* 
   }
   const int rows = static_cast<int>(imin64(32, n_rows - row0));
   const int n4 = rows * cols / 4;
+  const float inv = 1.f / cols;  // floor(i / cols) == floor((i + 0.5) * inv) for i < 4096, cols <= 128
 #pragma unroll
   for (int k = 0; k < kVec; ++k) {
     const int e = lane + 32 * k;
     if (e < n4) {
-      const int r = (4 * e) / cols, c = (4 * e) - r * cols;
-      dst[(c + 0) * 32 + r] = pf.v[k].x;
-      dst[(c + 1) * 32 + r] = pf.v[k].y;
-      dst[(c + 2) * 32 + r] = pf.v[k].z;
-      dst[(c + 3) * 32 + r] = pf.v[k].w;
+      int r = __float2int_rd((4 * e + 0.5f) * inv), c = 4 * e - r * cols;
+      const float v[4] = {pf.v[k].x, pf.v[k].y, pf.v[k].z, pf.v[k].w};
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        dst[c * 32 + r] = v[j];
+        if (++c == cols) { c = 0; ++r; }
+      }
     }
   }
   if (rows < 32) {
@@ -1018,6 +1029,10 @@ struct GjkQueueArgs {
 
 constexpr int kQueueChunk = 32;  // items a warp takes from the queue at a time
 constexpr int kFetchAttempts = 4;
+#ifndef RAMP_GJK_CTAS
+#define RAMP_GJK_CTAS 2
+#endif
+constexpr int kGjkCtasPerSm = RAMP_GJK_CTAS;
 
 #ifdef RAMP_STATS
 __device__ unsigned long long g_stats[64];  // [0] items [1] iterations [2] hits [3] skipped, [8+it] histogram
@@ -1079,6 +1094,10 @@ __global__ void __launch_bounds__(256, 2) gjk_queue_kernel(const __grid_constant
         p = static_cast<uint32_t>(pr.orig);  // results report the caller's index
         bool skip = false;
         if (a.stop && !a.offs) skip = a.first_pair ? static_cast<uint32_t>(a.first_pair[row]) < p : a.hit[row] != 0;
+#ifdef RAMP_STATS
+        atomicAdd(&g_stats[skip ? 3 : 4], 1ull);
+        if (!skip) { const int va = t.geoms[pr.a].vcnt, vb = t.geoms[pr.b].vcnt; atomicAdd(&g_stats[50 + (va > 16) + 2 * (vb > 16)], 1ull); }
+#endif
         if (!skip) {
           const DGeom* ga = &t.geoms[pr.a];
           const DGeom* gb = &t.geoms[pr.b];
@@ -1097,11 +1116,20 @@ __global__ void __launch_bounds__(256, 2) gjk_queue_kernel(const __grid_constant
       if (drained && lo == hi) break;
       continue;
     }
+    // Both support scans run with the whole warp converged (idle lanes scan zero vertices):
+    // left to itself the compiler lets lanes with a short vertex list run ahead into the next
+    // scan on their own, and the scans execute twice at partial width.
+    const V3 sa = support(A.type, A.p0, A.p1, A.p2, A.verts, active ? A.vcnt : 0, -g.v);
+    __syncwarp();
+    const V3 sb = support(B.type, B.p0, B.p1, B.p2, B.verts, active ? B.vcnt : 0, rot_t(g.rel, g.v));
+    __syncwarp();
     if (active) {
       float dist;
-      const int st = gjk_step(g, A, B, false, dist);
+      const int st = gjk_advance(g, sa, sb, false, dist);
 #ifdef RAMP_STATS
       atomicAdd(&g_stats[1], 1ull);
+      atomicAdd(&g_stats[5], static_cast<unsigned long long>(__popc(__activemask())));
+      atomicAdd(&g_stats[56 + min(g.s.n, 4)], 1ull);
       if (st != GJK_CONTINUE) { atomicAdd(&g_stats[0], 1ull); atomicAdd(&g_stats[2], st == GJK_HIT ? 1ull : 0ull); atomicAdd(&g_stats[8 + min(g.it, 40)], 1ull); }
 #endif
       if (st != GJK_CONTINUE) {
@@ -2203,7 +2231,7 @@ static int launch_check(const RampModel* m, const float* d_q, int64_t n, int32_t
     g_launches.fetch_add(1, std::memory_order_relaxed);
     if (use_queue) {
       b.hit = a.hit; b.first_pair = a.first_pair; b.pair_mask = a.pair_mask;
-      gjk_queue_kernel<<<m->sm_count * 2, 256, smem_b, st>>>(b);
+      gjk_queue_kernel<<<m->sm_count * kGjkCtasPerSm, 256, smem_b, st>>>(b);
       g_launches.fetch_add(1, std::memory_order_relaxed);
     }
   }
@@ -2500,7 +2528,7 @@ int ramp_check_batch_noalloc(const RampModel* m, const float* d_q, int64_t n, in
   b.items = a.gq.items; b.count = a.gq.count; b.capacity = kNoAllocQueueItems;
   b.hit = d_hit; b.first_pair = d_first_pair; b.pair_mask = d_pair_mask; b.mask_words = m->hdr.mask_words;
   b.stop = !(flags & RAMP_ALL_PAIRS) && d_pair_mask == nullptr;
-  gjk_queue_kernel<<<m->sm_count * 2, 256, smem_b, st>>>(b);
+  gjk_queue_kernel<<<m->sm_count * kGjkCtasPerSm, 256, smem_b, st>>>(b);
   g_launches.fetch_add(2, std::memory_order_relaxed);
   CUDA_TRY(cudaGetLastError());
   return RAMP_OK;
@@ -2643,7 +2671,7 @@ int ramp_check_edges(const RampModel* m, const float* d_q0, const float* d_q1, i
   edge_scan_kernel<<<1, 1024, 0, st>>>(a.offs, n_edges);
   // the number of states is only known on the device: size the grid for the SM count
   edge_check_kernel<<<m->sm_count, nwarps * 32, smem, st>>>(a);
-  if (use_queue) gjk_queue_kernel<<<m->sm_count * 2, 256, smem_b, st>>>(b);
+  if (use_queue) gjk_queue_kernel<<<m->sm_count * kGjkCtasPerSm, 256, smem_b, st>>>(b);
   edge_finish_kernel<<<eb, 256, 0, st>>>(a, d_first_invalid, d_nd);
   g_launches.fetch_add(use_queue ? 5 : 4, std::memory_order_relaxed);
   if (qmem) CUDA_TRY(cudaFreeAsync(qmem, st));
@@ -2702,10 +2730,26 @@ static bool is_pinned(const void* p) {
   return at.type == cudaMemoryTypeHost;
 }
 
+void* ramp_host_alloc(size_t bytes) {
+  void* p = nullptr;
+  if (cudaHostAlloc(&p, std::max<size_t>(bytes, 1), cudaHostAllocPortable) != cudaSuccess) {
+    cudaGetLastError();
+    fail(RAMP_ERR_ALLOC, "cudaHostAlloc(%zu) failed", bytes);
+    return nullptr;
+  }
+  return p;
+}
+
+void ramp_host_free(void* p) {
+  if (p) cudaFreeHost(p);
+}
+
 // Host-buffer check, pipelined: the batch moves in chunks over two streams so that the H2D
 // copy of chunk k+1, the kernels of chunk k and the D2H copy of chunk k-1 overlap.  Buffers
-// the caller already pinned (cudaHostAlloc / cudaHostRegister / torch pin_memory) are used for
-// DMA directly; pageable ones are staged through the model's pinned buffers.
+// the caller already pinned (ramp_host_alloc / cudaHostAlloc / cudaHostRegister / torch
+// pin_memory) are used for DMA directly; pageable ones are staged through the model's pinned
+// buffers.  (Reading a pinned q in place from the kernels was measured too: 35-46 GB/s over
+// PCIe against 55 GB/s for the copy engine, and slower end to end at every batch size.)
 int ramp_check_host(const RampModel* m, const float* h_q, int64_t n, int32_t ld, uint32_t flags, uint8_t* h_hit,
                     int32_t* h_first_pair, float* h_min_dist, uint32_t* h_pair_mask) {
   if (int rc = check_q_args(m, h_q, n, ld, flags)) return rc;
@@ -2722,7 +2766,8 @@ int ramp_check_host(const RampModel* m, const float* h_q, int64_t n, int32_t ld,
   if (int rc = ensure_scratch(m, 2 * per)) return rc;
   const bool pin_q = is_pinned(h_q), pin_hit = is_pinned(h_hit);
   const bool pin_first = !h_first_pair || is_pinned(h_first_pair), pin_mask = !h_pair_mask || is_pinned(h_pair_mask);
-  if (!(pin_q && pin_hit && pin_first && pin_mask) && 2 * per > m->pinned_cap) {
+  const bool staged = !(pin_q && pin_hit && pin_first && pin_mask);
+  if (staged && 2 * per > m->pinned_cap) {
     if (m->h_pinned) cudaFreeHost(m->h_pinned);
     m->h_pinned = nullptr; m->pinned_cap = 0;
     const size_t cap = std::max<size_t>(2 * per, 1 << 16);
@@ -2747,19 +2792,22 @@ int ramp_check_host(const RampModel* m, const float* h_q, int64_t n, int32_t ld,
     const int b = static_cast<int>(k & 1);
     cudaStream_t st = m->streams[b];
     const int64_t off = k * chunk, ns = std::min(chunk, n - off);
-    if (k >= 2) {  // the buffers of chunk k-2 are about to be reused
+    // Chunk k reuses the buffers of chunk k-2.  On the device the stream orders that by
+    // itself; only the host staging copies (pageable caller memory) make the host wait.
+    if (k >= 2 && staged) {
       CUDA_TRY(cudaStreamSynchronize(st));
       drain(k - 2);
     }
     unsigned char* Db = D + b * per;
     unsigned char* Hb = H + b * per;
     const float* src = h_q + off * ld;
+    const float* d_q = reinterpret_cast<const float*>(Db);
     if (!pin_q) { std::memcpy(Hb, src, sizeof(float) * ns * ld); src = reinterpret_cast<const float*>(Hb); }
     CUDA_TRY(cudaMemcpyAsync(Db, src, sizeof(float) * ns * ld, cudaMemcpyHostToDevice, st));
     uint8_t* d_hit = Db + b_q;
     int32_t* d_first = reinterpret_cast<int32_t*>(Db + b_q + b_hit);
     uint32_t* d_mask = reinterpret_cast<uint32_t*>(Db + b_q + b_hit + b_first);
-    if (int rc = launch_check(m, reinterpret_cast<const float*>(Db), ns, ld, flags, d_hit, h_first_pair ? d_first : nullptr,
+    if (int rc = launch_check(m, d_q, ns, ld, flags, d_hit, h_first_pair ? d_first : nullptr,
                               h_pair_mask ? d_mask : nullptr, st))
       return rc;
     CUDA_TRY(cudaMemcpyAsync(pin_hit ? h_hit + off : Hb + b_q, d_hit, ns, cudaMemcpyDeviceToHost, st));
@@ -2772,7 +2820,7 @@ int ramp_check_host(const RampModel* m, const float* h_q, int64_t n, int32_t ld,
   }
   for (int64_t k = std::max<int64_t>(0, nchunks - 2); k < nchunks; ++k) {
     CUDA_TRY(cudaStreamSynchronize(m->streams[k & 1]));
-    drain(k);
+    if (staged) drain(k);
   }
   return RAMP_OK;
 }

@@ -10,6 +10,7 @@ from __future__ import annotations
 
 import ctypes as C
 import os
+import weakref
 from pathlib import Path
 
 import numpy as np
@@ -54,6 +55,8 @@ def load_library():
         "ramp_check_edges": (C.c_int, [vp, vp, vp, i64, i32, C.POINTER(D.RampSpaceDesc), vp, vp, vp, vp]),
         "ramp_check_edges_host": (C.c_int, [vp, vp, vp, i64, i32, C.POINTER(D.RampSpaceDesc), vp, vp, vp]),
         "ramp_check_host": (C.c_int, [vp, vp, i64, i32, u32, vp, vp, vp, vp]),
+        "ramp_host_alloc": (vp, [C.c_size_t]),
+        "ramp_host_free": (None, [vp]),
     }
     for name, (res, args) in sig.items():
         fn = getattr(lib, name)  # AttributeError here = header and library disagree
@@ -72,6 +75,20 @@ def _check(rc: int, what: str):
 
 def launch_count() -> int:
     return int(load_library().ramp_launch_count())
+
+
+def pinned_empty(shape, dtype=np.float32) -> np.ndarray:
+    """A numpy array in page-locked host memory (ramp_host_alloc): the host-buffer calls copy
+    straight from / to such arrays instead of staging them.  Freed when the array is collected."""
+    lib = load_library()
+    dtype = np.dtype(dtype)
+    nbytes = int(np.prod(shape, dtype=np.int64)) * dtype.itemsize
+    ptr = lib.ramp_host_alloc(nbytes)
+    if not ptr:
+        raise RampGpuError("ramp_host_alloc failed: " + lib.ramp_last_error().decode(errors="replace"))
+    buf = (C.c_byte * max(nbytes, 1)).from_address(ptr)
+    weakref.finalize(buf, lib.ramp_host_free, ptr)
+    return np.frombuffer(buf, dtype=dtype, count=nbytes // dtype.itemsize).reshape(shape)
 
 
 def _stream_ptr(device: torch.device) -> int:
@@ -245,6 +262,17 @@ class GpuModel:
                                               C.byref(space.struct), valid.ctypes.data, first.ctypes.data, nd.ctypes.data),
                "ramp_check_edges_host")
         return {"valid": valid.astype(bool), "first_invalid": first, "nd": nd}
+
+    def check_host_into(self, q: np.ndarray, hit: np.ndarray, *, actuated: bool = False) -> None:
+        """ramp_check_host on caller-owned buffers, nothing allocated or converted: q float32
+        C-contiguous [n, ld], hit uint8 [n].  Page-locked arrays (``pinned_empty``) are copied
+        without staging."""
+        if q.dtype != np.float32 or not q.flags.c_contiguous or q.ndim != 2:
+            raise ValueError("q must be a C-contiguous float32 [n, ld] array")
+        if hit.dtype != np.uint8 or not hit.flags.c_contiguous or hit.size < len(q):
+            raise ValueError("hit must be a C-contiguous uint8 array of at least n elements")
+        _check(self.lib.ramp_check_host(self.handle, q.ctypes.data, len(q), q.shape[1], D.Q_ACTUATED if actuated else 0,
+                                        hit.ctypes.data, None, None, None), "ramp_check_host")
 
     def check_host(self, q: np.ndarray, *, actuated: bool = False, first_pair: bool = False,
                    pair_mask: bool = False) -> dict:

@@ -305,3 +305,28 @@ def test_queue_overflow_falls_back_to_in_kernel_gjk(built, monkeypatch, record_p
     q = workloads.sample_q(rm.model, 20000, seed=77)
     monkeypatch.setenv("RAMP_B200_QUEUE_CAP", "100")
     _compare_check(rm, q, lambda **kw: [record_property(k, v) for k, v in kw.items()])
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name,scene", [("ur5e/configs", "obstacles"), ("panda/configs", "capsule"), ("rrr/floating_configs", "capsule")])
+def test_unpadded_rows_and_page_locked_host_buffers(built, name, scene):
+    """Rows of exactly nq floats (nq not a multiple of 4: a float4 of the tile load straddles two
+    rows) give the same flags as padded rows, on the device and through ramp_check_host with
+    buffers from ramp_host_alloc; ragged batch sizes exercise the plain-load tail."""
+    from ramp_b200 import workloads
+    from ramp_b200.engine import pinned_empty
+
+    rm, _ = _setup(name, scene)
+    nq = rm.model.nq
+    for n in (1, 31, 32, 33, 4097, 300001):
+        qp = workloads.sample_q(rm.model, n, seed=5 + n)  # padded rows
+        ref = rm.gpu.check(torch.from_numpy(qp).cuda(), first_pair=True)
+        tight = np.ascontiguousarray(qp[:, :nq])
+        got = rm.gpu.check(torch.from_numpy(tight).cuda(), first_pair=True)
+        assert torch.equal(got["hit"], ref["hit"]) and torch.equal(got["first_pair"], ref["first_pair"])
+        qh = pinned_empty((n, nq), np.float32)
+        qh[:] = tight
+        hh = pinned_empty((n,), np.uint8)
+        hh[:] = 7
+        rm.gpu.check_host_into(qh, hh)
+        assert np.array_equal(hh.astype(bool), ref["hit"].cpu().numpy())
