@@ -218,6 +218,14 @@ def run_edges(args, wl, rm, desc, dev) -> None:
     torch.cuda.synchronize()
     ms = a.elapsed_time(b) / args.steps
     launches = engine.launch_count() - l0
+    # end to end: host end points in, host verdicts out (ramp_check_edges_host)
+    h0, h1 = q0.astype(np.float32), q1.astype(np.float32)
+    gpu.check_edges_host(h0, h1, planner.space)
+    e2e_steps = max(3, min(args.steps, 10))
+    t0 = time.perf_counter()
+    for _ in range(e2e_steps):
+        gpu.check_edges_host(h0, h1, planner.space)
+    e2e_value = states * e2e_steps / (time.perf_counter() - t0)
     t0 = time.perf_counter()
     path = planner.plan(start, [0.0, 0.25, 0.0, -1.25, 0.0, 1.5, 0.0], timeout=5.0)
     plan_s = time.perf_counter() - t0
@@ -227,6 +235,8 @@ def run_edges(args, wl, rm, desc, dev) -> None:
         "config": {"workload": wl.name, "robot": wl.robot, "scene": wl.scene, "note": wl.note, "model": "stand-in",
                    "edges": E, "states": states, "mean_nd": states / E, "edges_per_s": E / (ms * 1e-3),
                    "valid_edge_fraction": float(res["valid"].float().mean().item())},
+        "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(h0.nbytes + h1.nbytes), "d2h_bytes_per_step": 9 * E,
+                "api": "ramp_check_edges_host (C ABI, host buffers)", "steps": e2e_steps},
         "gpu_launches": launches,
         "planning": {"planner": "built-in RRTConnect over GpuMotionValidator", "found": path is not None,
                      "seconds": plan_s, "waypoints": 0 if path is None else len(path),

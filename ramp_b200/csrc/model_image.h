@@ -69,17 +69,21 @@ static_assert(sizeof(DGeom) == 160, "DGeom");
 // ("DD"), then those of a joint-attached and a universe-attached one ("DS") -- each stage-1
 // loop then addresses placements with constant strides.  `orig` is the index in the caller's
 // list (GeometryModel.collisionPairs order), which is what every result reports.
-struct DPair {  // 12 words; the first four are everything stage 1 reads (one 16-byte load)
+struct DPair {  // 12 words = three 16-byte records
+  // record 0: everything stage 1 reads
   int32_t o1, o2;     // byte offsets of the two placement origins: into a lane's slab column
                       // (joint-attached) or into the static table (universe-attached)
   float rs2;          // (bound_r(a)+bound_r(b))^2, slightly inflated; -1 for an inactive pair
   int16_t orig, cls;  // index in the caller's pair list; narrow-phase class
+  // record 1: stage 1.5, the outer capsules of the geometries at o1 / o2 (GJK class)
+  float h1_out, h2_out;  // half lengths
+  float rsum_out;        // radius sum (+ slack); +inf for the other classes, which always pass
+  int32_t kind;          // 0: o1 and o2 address the slab, 1: o1 slab / o2 static, 2: both static
+  // record 2
   float slack;        // widening of every conservative test: 1e-5 m + the pair's share of non-rigid placements
   int16_t a, b;       // geometry indices, ordered so that type(a) <= type(b)
   int16_t sa, sb;     // their gslot values (>= 0 slab slot, < 0 static placement)
-  float ha_out, hb_out;  // outer capsules of a and b (GJK class): half lengths ...
-  float rsum_out;        // ... and radius sum (+ slack)
-  int32_t pad[2];
+  int32_t pad;
 };
 static_assert(sizeof(DPair) == 48, "DPair");
 

@@ -579,18 +579,20 @@ __device__ __forceinline__ void narrow_phase(const Warp& w, bool stop_at_first, 
         const int item = live ? w.queue[base + l] : 0;
         bool keep = live;
         if (live) {
-          const int c = item & 31;
-          const DPair pr = w.t.pairs[chunk + (item >> 5)];
-          if (pr.cls == kClsGjk) {
-            const float* S = reinterpret_cast<const float*>(g_smem);
-            const float* pa = S + (pr.sa >= 0 ? w.geom_w + pr.sa * (kGeomFloats * 32) + c : w.stat_w - (pr.sa + 1) * kStatFloats);
-            const float* pb = S + (pr.sb >= 0 ? w.geom_w + pr.sb * (kGeomFloats * 32) + c : w.stat_w - (pr.sb + 1) * kStatFloats);
-            const int sta = pr.sa >= 0 ? 32 : 1, stb = pr.sb >= 0 ? 32 : 1;
-            const V3 za = mk(pa[3 * sta], pa[4 * sta], pa[5 * sta]), ta = mk(pa[6 * sta], pa[7 * sta], pa[8 * sta]);
-            const V3 zb = mk(pb[3 * stb], pb[4 * stb], pb[5 * stb]), tb = mk(pb[6 * stb], pb[7 * stb], pb[8 * stb]);
-            const V3 wv = seg_seg_witness(ta - za * pr.ha_out, za * (2.f * pr.ha_out), tb - zb * pr.hb_out, zb * (2.f * pr.hb_out));
-            keep = dot(wv, wv) <= pr.rsum_out * pr.rsum_out;
-          }
+          // record 1 of the pair: outer capsules in o1 / o2 order (rsum_out = inf: not the GJK class)
+          const int pidx = chunk + (item >> 5);
+          const int4 r0 = rec[3 * pidx];
+          const float4 r1 = reinterpret_cast<const float4*>(rec)[3 * pidx + 1];
+          const int kind = __float_as_int(r1.w);
+          const char* col = T + 4 * ((item & 31) - l);  // origin rows of the item's configuration
+          const char* pa = (kind < 2 ? col : TS) + r0.x;
+          const char* pb = (kind < 1 ? col : TS) + r0.y;
+          const int sa = kind < 2 ? 128 : 4, sb = kind < 1 ? 128 : 4;  // row strides in bytes
+          auto f = [](const char* p) { return *reinterpret_cast<const float*>(p); };
+          const V3 za = mk(f(pa - 3 * sa), f(pa - 2 * sa), f(pa - sa)), ta = mk(f(pa), f(pa + sa), f(pa + 2 * sa));
+          const V3 zb = mk(f(pb - 3 * sb), f(pb - 2 * sb), f(pb - sb)), tb = mk(f(pb), f(pb + sb), f(pb + 2 * sb));
+          const V3 wv = seg_seg_witness(ta - za * r1.x, za * (2.f * r1.x), tb - zb * r1.y, zb * (2.f * r1.y));
+          keep = dot(wv, wv) <= r1.z * r1.z;
         }
         __syncwarp();  // every lane has read its item before the in-place compaction writes
         const unsigned b = __ballot_sync(FULL, keep);
@@ -2002,20 +2004,21 @@ static int build_image(RampModel* m) {
     // stage-1 addressing: DD two slab slots; DS slab slot + static index; SS two static indices
     const auto dyn_off = [](int gslot) { return gslot * kGeomFloats * 32 * 4; };     // bytes into a lane's slab column
     const auto stat_off = [](int gslot) { return (-1 - gslot) * kStatFloats * 4; };  // bytes into the static table
-    if (k < n_dd) { d.o1 = dyn_off(d.sa); d.o2 = dyn_off(d.sb); }
-    else if (k >= ss_begin) { d.o1 = stat_off(d.sa); d.o2 = stat_off(d.sb); }
-    else if (dg[a].gslot >= 0) { d.o1 = dyn_off(d.sa); d.o2 = stat_off(d.sb); }
-    else { d.o1 = dyn_off(d.sb); d.o2 = stat_off(d.sa); }
+    int g1 = a, g2 = b;  // the geometries o1 / o2 address
+    if (k < n_dd) { d.o1 = dyn_off(d.sa); d.o2 = dyn_off(d.sb); d.kind = 0; }
+    else if (k >= ss_begin) { d.o1 = stat_off(d.sa); d.o2 = stat_off(d.sb); d.kind = 2; }
+    else if (dg[a].gslot >= 0) { d.o1 = dyn_off(d.sa); d.o2 = stat_off(d.sb); d.kind = 1; }
+    else { d.o1 = dyn_off(d.sb); d.o2 = stat_off(d.sa); d.kind = 1; g1 = b; g2 = a; }
     n_gjk += d.cls == kClsGjk;
     const double rs = static_cast<double>(dg[a].bound_r) + dg[b].bound_r;
     // stage 1 is a cull for every class (slightly inflated); an inactive pair never passes it
     d.rs2 = d.cls == kClsInactive ? -1.f : static_cast<float>(rs * rs * (1.0 + 1e-5) + 1e-9);
-    d.ha_out = dg[a].s_out; d.hb_out = dg[b].s_out;
+    d.h1_out = dg[g1].s_out; d.h2_out = dg[g2].s_out;
     // Conservative tests are widened by 1e-5 m, plus -- when a placement is not a rigid
     // motion -- the amount by which lengths measured in its frame can be off
     const double nr = nonrigid[a] + nonrigid[b];
     d.slack = static_cast<float>(1e-5 + (nr > 1e-6 ? 2.0 * nr * rs : 0.0));
-    d.rsum_out = dg[a].r_out + dg[b].r_out + d.slack;
+    d.rsum_out = d.cls == kClsGjk ? dg[a].r_out + dg[b].r_out + d.slack : INFINITY;
   }
   // q map
   std::vector<DMimic> dm(m->mimic_dst.size());
