@@ -16,6 +16,9 @@ constexpr int kMaxNq = 128;
 constexpr int kMaxSubspaces = 48;
 constexpr int kLanes = 32;             // configurations per warp tile
 constexpr int kChunkPairs = 32;        // pairs culled per queue round
+// FK plan table (int32): [kPlanTeam2 .. +2] and [kPlanTeam4 .. +4] are entry ranges of the warps of
+// a team of 2 / 4, entries start at kPlanEntries; an entry is joint | (places its geometries << 16)
+constexpr int kPlanTeam2 = 0, kPlanTeam4 = 3, kPlanEntries = 8;
 constexpr int kQueueCap = kChunkPairs * kLanes;
 
 // parent_code of a joint
@@ -38,7 +41,7 @@ struct ImgHeader {  // 32 words
   int32_t total_bytes, nq, n_joints, n_geoms, n_dyn, n_static, n_pairs, n_verts;
   int32_t n_act, n_mimic, n_cont, n_save, mask_words, n_robot_geoms, n_robot_pairs, n_dd;  // n_dd: DD pairs
   int32_t off_joints, off_geoms, off_pairs, off_verts, off_static, off_dyn, off_act, off_mimic;
-  int32_t off_cont, off_refq, ss_begin, reserved1[5];  // ss_begin: first pair of two universe-attached geometries
+  int32_t off_cont, off_refq, ss_begin, off_plan, reserved1[4];  // ss_begin: first pair of two universe-attached geometries
 };
 static_assert(sizeof(ImgHeader) == 128, "header is 32 words");
 

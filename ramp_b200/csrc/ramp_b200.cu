@@ -48,6 +48,7 @@ struct Tables {
   const DMimic* mimic;
   const int32_t* cont;
   const float* refq;
+  const int32_t* plan;  // FK plans for teams of warps (see build_image)
 };
 
 __device__ __forceinline__ Tables make_tables(const unsigned char* base) {
@@ -63,6 +64,7 @@ __device__ __forceinline__ Tables make_tables(const unsigned char* base) {
   t.mimic = reinterpret_cast<const DMimic*>(base + t.h->off_mimic);
   t.cont = reinterpret_cast<const int32_t*>(base + t.h->off_cont);
   t.refq = reinterpret_cast<const float*>(base + t.h->off_refq);
+  t.plan = reinterpret_cast<const int32_t*>(base + t.h->off_plan);
   return t;
 }
 
@@ -394,32 +396,51 @@ __device__ __forceinline__ void stage_xf(const Warp& w, int slot, const Xf& x) {
 // updateGeometryPlacements).  kStage: 0 = geometry placements to the slab (validity path),
 // 1 = stage the oMi rows, 2 = stage the oMg rows (output kernels).
 template <int kStage>
-__device__ __forceinline__ void fk_lane(const Warp& w) {
-  const ImgHeader* h = w.t.h;
+__device__ __forceinline__ void fk_joint(const Warp& w, int i, Xf& cur, bool emit) {
   const int l = w.lane;
+  const DJoint* j = &w.t.joints[i];
+  float qv[7];
+  const int n = joint_nq(j->type);
+#pragma unroll
+  for (int k = 0; k < 7; ++k) qv[k] = k < n ? w.q[(j->idx_q + k) * 32 + l] : 0.f;
+  const Xf loc = local_xf(j, qv);
+  const int pc = j->parent_code;
+  if (pc == kParentUniverse) cur = loc;
+  else if (pc == kParentRunning) cur = xf_mul(cur, loc);
+  else cur = xf_mul(load_slab_xf(w.save, pc, l), loc);
+  if (j->save_slot >= 0) store_slab_xf(w.save, j->save_slot, l, cur);
+  if (kStage == 1) stage_xf(w, i, cur);
+  const int gend = (kStage == 1 || !emit) ? j->gfirst : j->gfirst + j->gcount;
+#pragma unroll 1
+  for (int s = j->gfirst; s < gend; ++s) {
+    const int gi = w.t.dyn[s];
+    const Xf og = xf_mul(cur, load_table_xf(kStage == 2 ? w.t.geoms[gi].opl : w.t.geoms[gi].pl));
+    if (kStage == 2) stage_xf(w, gi, og);
+    else store_geom_xf(w.geom, s, l, og);
+  }
+}
+
+template <int kStage>
+__device__ __forceinline__ void fk_lane(const Warp& w) {
   Xf cur = xf_identity();
 #pragma unroll 1
-  for (int i = 0; i < h->n_joints; ++i) {
-    const DJoint* j = &w.t.joints[i];
-    float qv[7];
-    const int n = joint_nq(j->type);
-#pragma unroll
-    for (int k = 0; k < 7; ++k) qv[k] = k < n ? w.q[(j->idx_q + k) * 32 + l] : 0.f;
-    const Xf loc = local_xf(j, qv);
-    const int pc = j->parent_code;
-    if (pc == kParentUniverse) cur = loc;
-    else if (pc == kParentRunning) cur = xf_mul(cur, loc);
-    else cur = xf_mul(load_slab_xf(w.save, pc, l), loc);
-    if (j->save_slot >= 0) store_slab_xf(w.save, j->save_slot, l, cur);
-    if (kStage == 1) stage_xf(w, i, cur);
-    const int gend = kStage == 1 ? j->gfirst : j->gfirst + j->gcount;
+  for (int i = 0; i < w.t.h->n_joints; ++i) fk_joint<kStage>(w, i, cur, true);
+}
+
+// The same for a team of kTeam warps sharing one slab: warp `tw` walks its FK plan -- a
+// contiguous run of the joint order whose geometries it places, preceded by the ancestors of
+// that run (recomputed, not placed) -- so the kinematic tree is split between the warps
+// instead of one of them doing all of it while the others wait.
+template <int kTeam>
+__device__ __forceinline__ void fk_team(const Warp& w, int tw) {
+  const int32_t* plan = w.t.plan;
+  const int base = kTeam == 2 ? kPlanTeam2 : kPlanTeam4;
+  const int e = plan[base + tw + 1];
+  Xf cur = xf_identity();
 #pragma unroll 1
-    for (int s = j->gfirst; s < gend; ++s) {
-      const int gi = w.t.dyn[s];
-      const Xf og = xf_mul(cur, load_table_xf(kStage == 2 ? w.t.geoms[gi].opl : w.t.geoms[gi].pl));
-      if (kStage == 2) stage_xf(w, gi, og);
-      else store_geom_xf(w.geom, s, l, og);
-    }
+  for (int k = plan[base + tw]; k < e; ++k) {
+    const int ent = plan[kPlanEntries + k];
+    fk_joint<0>(w, ent & 0xffff, cur, (ent >> 16) != 0);
   }
 }
 
@@ -788,7 +809,11 @@ __global__ void __launch_bounds__(512, 1) check_kernel(const __grid_constant__ C
       prefetch_rows(pf, a.q, (tile + tile_step) << 5, a.n, cols, a.ld, w.lane);
       if (actuated) expand_q(w);
       reset_results(w, want_mask ? t.h->mask_words : 0);
-      fk_lane<0>(w);
+      if (kTeam == 1) fk_lane<0>(w);
+    }
+    if (kTeam > 1) {  // every warp of the team runs its share of the kinematic tree
+      team_sync();
+      fk_team<kTeam>(w, tw);
     }
     team_sync();
     narrow_phase<kTeam>(w, stop, stop && a.first_pair == nullptr, want_mask, a.gq, static_cast<uint32_t>(row0), tw,
@@ -2027,6 +2052,57 @@ static int build_image(RampModel* m) {
   std::vector<float> refq(m->nq, 0.f);
   if (m->has_qmap) for (int k = 0; k < m->nq; ++k) refq[k] = static_cast<float>(m->ref_q[k]);
 
+  // FK plans for teams of 2 and 4 warps.  Warp k of a team owns a contiguous run [c_k, c_k+1)
+  // of the joint order (it places their geometries) and first recomputes the ancestors of that
+  // run.  A plan is a sub-sequence of the joint order closed under "parent of", so the
+  // running / saved parent codes of the joints stay valid inside it.  The cuts minimise the
+  // largest per-warp cost (1 per joint computed, 0.75 per geometry placed).
+  std::vector<int32_t> plan(kPlanEntries, 0);
+  {
+    std::vector<std::vector<double>> cost(nj + 1, std::vector<double>(nj + 1, 0.0));
+    std::vector<char> anc(std::max(nj, 1));
+    auto mark_ancestors = [&](int s0, int e0) {
+      std::fill(anc.begin(), anc.end(), 0);
+      int na = 0;
+      for (int i = s0; i < e0; ++i)
+        for (int p = m->joints[i].parent; p >= 0 && !anc[p]; p = m->joints[p].parent) { anc[p] = 1; na += p < s0; }
+      return na;
+    };
+    for (int s0 = 0; s0 <= nj; ++s0)
+      for (int e0 = s0; e0 <= nj; ++e0) {
+        if (e0 == s0) continue;
+        double c = mark_ancestors(s0, e0) + (e0 - s0);
+        for (int i = s0; i < e0; ++i) c += 0.75 * dj[i].gcount;
+        cost[s0][e0] = c;
+      }
+    auto emit_plan = [&](int base, const std::vector<int>& cuts) {  // cuts: T+1 joint indices
+      for (size_t k = 0; k + 1 < cuts.size(); ++k) {
+        plan[base + k] = static_cast<int32_t>(plan.size()) - kPlanEntries;
+        mark_ancestors(cuts[k], cuts[k + 1]);
+        for (int i = 0; i < cuts[k]; ++i)
+          if (anc[i]) plan.push_back(i);
+        for (int i = cuts[k]; i < cuts[k + 1]; ++i) plan.push_back(i | (1 << 16));
+      }
+      plan[base + cuts.size() - 1] = static_cast<int32_t>(plan.size()) - kPlanEntries;
+    };
+    int best2 = 0;
+    double b2 = 1e300;
+    for (int c = 0; c <= nj; ++c) {
+      const double v = std::max(cost[0][c], cost[c][nj]);
+      if (v < b2) { b2 = v; best2 = c; }
+    }
+    emit_plan(kPlanTeam2, {0, best2, nj});
+    std::vector<int> best4{0, 0, 0, 0, nj};
+    double b4 = 1e300;
+    for (int c1 = 0; c1 <= nj; ++c1)
+      for (int c2 = c1; c2 <= nj; ++c2)
+        for (int c3 = c2; c3 <= nj; ++c3) {
+          const double v = std::max(std::max(cost[0][c1], cost[c1][c2]), std::max(cost[c2][c3], cost[c3][nj]));
+          if (v < b4) { b4 = v; best4 = {0, c1, c2, c3, nj}; }
+        }
+    emit_plan(kPlanTeam4, best4);
+  }
+
   ImgHeader h;
   std::memset(&h, 0, sizeof h);
   size_t off = sizeof(ImgHeader);
@@ -2041,6 +2117,7 @@ static int build_image(RampModel* m) {
   h.off_mimic = place(dm.size() * sizeof(DMimic));
   h.off_cont = place(m->cont_slot.size() * sizeof(int32_t));
   h.off_refq = place(refq.size() * sizeof(float));
+  h.off_plan = place(plan.size() * sizeof(int32_t));
   h.total_bytes = static_cast<int32_t>(off);
   h.nq = m->nq; h.n_joints = nj; h.n_geoms = ng; h.n_dyn = static_cast<int32_t>(dyn.size());
   h.n_static = n_static; h.n_pairs = np; h.n_verts = static_cast<int32_t>(verts4.size() / 4);
@@ -2062,6 +2139,7 @@ static int build_image(RampModel* m) {
   put(h.off_mimic, dm.data(), dm.size() * sizeof(DMimic));
   put(h.off_cont, m->cont_slot.data(), m->cont_slot.size() * sizeof(int32_t));
   put(h.off_refq, refq.data(), refq.size() * sizeof(float));
+  put(h.off_plan, plan.data(), plan.size() * sizeof(int32_t));
   m->hdr = h;
   m->n_gjk_pairs = n_gjk;
 
@@ -2185,10 +2263,20 @@ static int launch_check(const RampModel* m, const float* d_q, int64_t n, int32_t
   a.img = m->d_image; a.ld = ld; a.flags = flags;
   int nwarps; size_t smem;
   if (int rc = plan_slabs(m, 0, m->hdr.n_act, &a.L, &nwarps, &smem, ld)) return rc;
-  // Few slabs fit (a robot with many geometries): let pairs of warps share each slab and split
-  // the pair list (measured on the 20-geometry H1 stand-in: +17 %; teams of 4 lose it again to
-  // the FK that only one warp of the team runs, and robots whose slabs fit 12+ times lose ~20 %).
-  int team = nwarps < 12 ? 2 : 1;
+  // Few slabs fit (a robot with many geometries): let teams of 2 or 4 warps share each slab and
+  // split the kinematic tree and the pair list between them -- whichever team size puts the most
+  // warps on an SM (H1 stand-in, 20 hulls: 6 slabs -> 6 / 12 / 16 warps: 4.6e8 / 7.6e8 / 8.1e8
+  // configurations/s).  Robots whose slabs fit 12+ times are ~20 % faster without teams.
+  int team = 1;
+  if (nwarps < 12) {
+    SlabLayout L2, L4;
+    int w2 = 0, w4 = 0;
+    size_t s2 = 0, s4 = 0;
+    const bool ok2 = plan_slabs(m, 0, m->hdr.n_act, &L2, &w2, &s2, ld, 2) == RAMP_OK;
+    const bool ok4 = plan_slabs(m, 0, m->hdr.n_act, &L4, &w4, &s4, ld, 4) == RAMP_OK;
+    if (ok2 && w2 > nwarps) team = 2;
+    if (ok4 && w4 > (team == 2 ? w2 : nwarps)) team = 4;
+  }
   if (const char* e = std::getenv("RAMP_B200_TEAM")) { team = std::atoi(e); team = team >= 4 ? 4 : (team >= 2 ? 2 : 1); }  // experiments
   if (team > 1 && plan_slabs(m, 0, m->hdr.n_act, &a.L, &nwarps, &smem, ld, team) != RAMP_OK) return RAMP_ERR_LIMIT;
   if (int rc = team == 2 ? set_smem(check_kernel<2>, smem) : (team == 4 ? set_smem(check_kernel<4>, smem) : set_smem(check_kernel<1>, smem))) return rc;

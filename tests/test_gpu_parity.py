@@ -330,3 +330,22 @@ def test_unpadded_rows_and_page_locked_host_buffers(built, name, scene):
         hh[:] = 7
         rm.gpu.check_host_into(qh, hh)
         assert np.array_equal(hh.astype(bool), ref["hit"].cpu().numpy())
+
+
+@pytest.mark.parametrize("name,scene", [("unitree_h1/configs", None), ("panda/configs", "capsule"), ("ur5e/configs", "obstacles"),
+                                        ("rrr/floating_configs", "capsule"), ("rrr/configs", None)])
+def test_team_fk_plans_give_the_same_answers(built, monkeypatch, name, scene):
+    """Teams of 2 and 4 warps split the kinematic tree between them (FK plans: a run of the joint
+    order plus its recomputed ancestors per warp).  Flags, first pairs and pair masks must be
+    identical to the one-warp-per-slab kernel, whatever the tree shape."""
+    from ramp_b200 import workloads
+
+    rm, _ = _setup(name, scene)
+    q = torch.from_numpy(workloads.sample_q(rm.model, 40000, seed=11)).cuda()
+    monkeypatch.setenv("RAMP_B200_TEAM", "1")
+    ref = rm.gpu.check(q, first_pair=True, pair_mask=True)
+    for team in ("2", "4"):
+        monkeypatch.setenv("RAMP_B200_TEAM", team)
+        got = rm.gpu.check(q, first_pair=True, pair_mask=True)
+        for k in ("hit", "first_pair", "pair_mask"):
+            assert torch.equal(got[k], ref[k]), (team, k)
