@@ -302,13 +302,27 @@ def main() -> None:
     ld = workloads.padded_nq(rm.model)
     # N_ROTATE distinct batches: 8 x n x ld x 4 B is well above the 126 MB L2 for n >= 2^20
     batches = [workloads.sample_q_torch(rm.model, n, seed=0xB200 + 97 * rank + 13 * i, device=dev) for i in range(N_ROTATE)]
-    hit = torch.empty(n, dtype=torch.uint8, device=dev)
-    gathered = torch.empty(n * world, dtype=torch.uint8, device=dev) if world > 1 else None
+    # Two result buffers: the NCCL all-gather of step i's flags runs on NCCL's stream while the
+    # kernels of step i+1 fill the other buffer; step i+2 waits for it before reusing the buffer.
+    hits = [torch.empty(n, dtype=torch.uint8, device=dev) for _ in range(2)]
+    hit = hits[0]
+    gathered = [torch.empty(n * world, dtype=torch.uint8, device=dev) for _ in range(2)] if world > 1 else None
+    pending = [None, None]
 
     def step(i: int):
-        gpu.check_raw(batches[i % N_ROTATE], hit)
+        b = i & 1
+        if pending[b] is not None:
+            pending[b].wait()  # stream-side wait: the gather that read hits[b] is done
+            pending[b] = None
+        gpu.check_raw(batches[i % N_ROTATE], hits[b])
         if world > 1:
-            dist.all_gather_into_tensor(gathered, hit)
+            pending[b] = dist.all_gather_into_tensor(gathered[b], hits[b], async_op=True)
+
+    def drain():
+        for b in range(2):
+            if pending[b] is not None:
+                pending[b].wait()
+                pending[b] = None
 
     def barrier():
         if world > 1:
@@ -317,6 +331,7 @@ def main() -> None:
 
     for i in range(args.warmup):
         step(i)
+    drain()
     barrier()
     sampler = ClockSampler(local_rank)
     sampler.start()
@@ -326,6 +341,8 @@ def main() -> None:
     ev[0].record()
     for i in range(args.steps):
         step(i)
+        if i + 1 == args.steps:
+            drain()  # every step's gather has completed before the last event
         ev[i + 1].record()
     barrier()
     launches = engine.launch_count() - launches0
@@ -400,7 +417,7 @@ def main() -> None:
                    "n_per_gpu": n, "pairs": desc.n_pairs, "geoms": desc.n_geoms, "ld_q": ld,
                    "colliding_fraction": colliding,
                    "l2": f"{N_ROTATE} rotating input batches of {n * ld * 4 / 2**20:.0f} MiB each (inputs > 126 MB L2)",
-                   "parallelism": f"config shards x{world}, geometry replicated"
+                   "parallelism": f"config shards x{world}, geometry replicated, flags all-gathered per step (NCCL, overlapped with the next step)"
                                   + (", NCCL all_gather of flags per step" if world > 1 else "")},
         "roofline": {"bound": "fp32", "achieved": achieved_tf, "peak": fp32_peak, "unit": "TFLOP/s",
                      "frac": achieved_tf / fp32_peak, "traffic": traffic,
