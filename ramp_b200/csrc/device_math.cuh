@@ -469,6 +469,7 @@ __device__ __forceinline__ int gjk_step(GjkLane& g, const GjkShape& A, const Gjk
 // distance output (ramp_distance_batch) uses it; the boolean paths never do.  The polytope lives
 // in per-thread local memory.
 constexpr int kEpaMaxV = 68, kEpaMaxF = 160, kEpaIters = 64;
+constexpr float kEpaTol = 1e-5f;  // relative gap at which the expansion stops
 
 struct EpaFace {
   unsigned char a, b, c, alive;
@@ -548,7 +549,8 @@ __device__ __noinline__ float epa_depth(const GjkShape& A, const GjkShape& B, co
     if (bi < 0) break;
     best = bd;
     const V3 w = mink_support(A, B, rel, fc[bi].n);
-    if (dot(fc[bi].n, w) - bd <= 1e-6f * (1.f + bd) || nv >= kEpaMaxV) break;
+    // FP32: face normals and plane offsets carry ~1e-6 of noise, a tighter test never fires
+    if (dot(fc[bi].n, w) - bd <= kEpaTol * (1.f + bd) || nv >= kEpaMaxV) break;
     // drop the faces that see w, keep the horizon
     unsigned char eh[96][2];
     int ne = 0;
@@ -571,7 +573,14 @@ __device__ __noinline__ float epa_depth(const GjkShape& A, const GjkShape& B, co
       int slot = -1;
       for (int i = 0; i < nf; ++i) if (!fc[i].alive) { slot = i; break; }
       if (slot < 0) { if (nf >= kEpaMaxF) { ok = false; break; } slot = nf++; }
-      epa_face(vt, eh[e][0], eh[e][1], nv, fc[slot]);
+      // Expanding the polytope can only move its faces outwards.  A new face that is a sliver,
+      // or lies closer to the origin than the face it replaces, is rounding noise (w almost in
+      // the plane of the old face): the polytope would be corrupt from here on, so stop with
+      // the depth reached -- by then it is within the noise of the converged value.
+      // (bd < 0: GJK handed over a simplex that does not hold the origin -- a false "enclosed" on
+      // a sliver tetrahedron of two shapes a few mm apart; the expansion then walks to the face
+      // the origin lies beyond, and its negative offset is the separation.  Leave that alone.)
+      if (!epa_face(vt, eh[e][0], eh[e][1], nv, fc[slot]) || (bd > 0.f && fc[slot].d < bd - kEpaTol * (1.f + bd))) ok = false;
     }
     ++nv;
     if (!ok) break;

@@ -349,3 +349,80 @@ def test_team_fk_plans_give_the_same_answers(built, monkeypatch, name, scene):
         got = rm.gpu.check(q, first_pair=True, pair_mask=True)
         for k in ("hit", "first_pair", "pair_mask"):
             assert torch.equal(got[k], ref[k]), (team, k)
+
+
+def _shape_zoo():
+    from ramp_b200.shapes import Box, Capsule, Convex, Cylinder, Ellipsoid, Sphere
+
+    rng = np.random.default_rng(42)
+    hull = rng.normal(size=(24, 3)) * np.array([0.12, 0.08, 0.1])
+    return [("sphere", Sphere(0.09)), ("capsule", Capsule(0.05, 0.2)), ("box", Box(0.16, 0.1, 0.22)),
+            ("cylinder", Cylinder(0.07, 0.18)), ("ellipsoid", Ellipsoid(0.12, 0.07, 0.05)), ("convex", Convex(hull))]
+
+
+def _shape_zoo_robot():
+    """A free-flying body carrying one geometry of each type, in a scene holding one of each."""
+    from ramp_b200.kinematics import GeometryObject
+    from ramp_b200.robot_model import create_geometry_object, load_robot_model
+    from ramp_b200.robot_state import RobotState
+    from ramp_b200.se3 import SE3, Quaternion
+
+    rng = np.random.default_rng(7)
+
+    def pose(t):
+        v = rng.normal(size=4)
+        v /= np.linalg.norm(v)
+        return SE3(Quaternion(*v).matrix(), np.asarray(t, dtype=np.float64))
+
+    rm = load_robot_model("zoo::floating")
+    cm = rm.collision_model
+    n0 = cm.ngeoms
+    for k, (name, shape) in enumerate(_shape_zoo()):  # on the free-flyer joint, 0.3 m apart along x
+        cm.addGeometryObject(GeometryObject("body_" + name, 1, pose((0.3 * (k - 2.5), 0.0, 0.0)), shape))
+    rs = RobotState(rm)
+    for k, (name, shape) in enumerate(_shape_zoo()):  # scene: a ring of radius 0.45 m
+        a = 2 * np.pi * k / 6
+        rs.add_object(create_geometry_object("scene_" + name, shape, pose((0.45 * np.cos(a), 0.45 * np.sin(a), 0.0))))
+    assert len(cm.collisionPairs) >= 36 and cm.ngeoms == n0 + 12
+    return rm, rs
+
+
+def test_every_pairing_of_shape_types(built, record_property):
+    """every shape RAMP can produce against every other -- sphere, capsule, box,
+    cylinder, ellipsoid, convex hull: 36 pairings, random body poses, per-pair decisions against
+    the oracle outside the margin band."""
+    rm, _ = _shape_zoo_robot()
+    q = workloads_sample(rm.model, 60000, seed=3, bound=0.6)
+    _compare_check(rm, q, lambda **kw: [record_property(k, v) for k, v in kw.items()])
+
+
+def test_signed_distance_of_every_pairing_of_shape_types(built):
+    """The same scenario through ramp_distance_batch: separations to 5e-5 (1 + d) m, depths to
+    1e-3 m + 2 % (tolerances of test_signed_distance_matches_oracle), sign = collision flag."""
+    from oracle import oracle
+    from ramp_b200.desc import ModelDesc
+
+    rm, _ = _shape_zoo_robot()
+    q = workloads_sample(rm.model, 20000, seed=4, bound=0.6)
+    got = rm.gpu.distance(torch.from_numpy(q).cuda()).cpu().numpy().astype(np.float64)
+    oracle.set_params(1e-8, 128, 1e-8, 255)
+    try:
+        ref = oracle.check(ModelDesc(rm.model, rm.collision_model), q[:, : rm.model.nq].astype(np.float64))["pair_dist"]
+    finally:
+        oracle.set_params()
+    sep, pen = ref > 1e-4, ref < -1e-4
+    assert sep.sum() > 1000 and pen.sum() > 200
+    err_sep = (np.abs(got - ref) / (1.0 + np.abs(ref)))
+    err_pen = (np.abs(got - ref) / (1e-3 + 0.02 * np.abs(ref)))
+    worst_sep, worst_pen = err_sep[:, :][sep].max(), err_pen[pen].max()
+    per_pair_pen = [float(np.where(pen[:, k], err_pen[:, k], 0).max()) for k in range(ref.shape[1])]
+    print(dict(separated=int(sep.sum()), penetrating=int(pen.sum()), err_sep=worst_sep, err_pen=worst_pen,
+               worst_pair=int(np.argmax(per_pair_pen))))
+    assert worst_sep < 5e-5 and worst_pen < 1.0
+    assert ((got <= 0) == (ref <= 0))[sep | pen].all()
+
+
+def workloads_sample(model, n, seed, bound):
+    from ramp_b200 import workloads
+
+    return workloads.sample_q(model, n, seed=seed, position_bound=bound)
