@@ -148,7 +148,7 @@ __device__ __forceinline__ Xf joint_xf(int type, float ax, float ay, float az, c
   return o;
 }
 
-__device__ __forceinline__ int joint_nq(int type) {
+__host__ __device__ __forceinline__ int joint_nq(int type) {
   switch (type) {
     case 5: case 6: case 7: case 8: return 2;
     case 13: return 4;

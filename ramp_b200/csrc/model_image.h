@@ -49,7 +49,9 @@ struct DJoint {  // 24 words
   int32_t type, parent_code, idx_q, save_slot;
   float ax, ay, az;
   int32_t gfirst, gcount;  // range in the dyn-geometry order list
-  int32_t pad[3];
+  int32_t parent;          // plain parent index (-1: universe)
+  int32_t nq;              // q entries the joint reads
+  int32_t pad;
   float pl[12];
 };
 static_assert(sizeof(DJoint) == 96, "DJoint");

@@ -400,9 +400,15 @@ __device__ __forceinline__ void fk_joint(const Warp& w, int i, Xf& cur, bool emi
   const int l = w.lane;
   const DJoint* j = &w.t.joints[i];
   float qv[7];
-  const int n = joint_nq(j->type);
+  const float* qj = w.q + j->idx_q * 32 + l;
+  qv[0] = qj[0];
+  const int n = j->nq;  // 1 for all but a few joints of a robot: skip the other six loads
 #pragma unroll
-  for (int k = 0; k < 7; ++k) qv[k] = k < n ? w.q[(j->idx_q + k) * 32 + l] : 0.f;
+  for (int k = 1; k < 7; ++k) qv[k] = 0.f;
+  if (n > 1) {
+#pragma unroll
+    for (int k = 1; k < 7; ++k) qv[k] = k < n ? qj[k * 32] : 0.f;
+  }
   const Xf loc = local_xf(j, qv);
   const int pc = j->parent_code;
   if (pc == kParentUniverse) cur = loc;
@@ -919,7 +925,7 @@ __device__ __forceinline__ int check_one_config(const SmallWarp& w, bool stop_at
       else {  // parent published earlier (its index is recoverable from the geometry-free table: stored per joint)
         Xf par;
 #pragma unroll
-        for (int k = 0; k < 12; ++k) par.m[k] = w.omi[j->pad[0] * 12 + k];
+        for (int k = 0; k < 12; ++k) par.m[k] = w.omi[j->parent * 12 + k];
         cur = xf_mul(par, loc);
       }
       if ((i & 31) == l) {
@@ -1830,7 +1836,8 @@ static int build_image(RampModel* m) {
     d.idx_q = j.idx_q;
     d.parent_code = j.parent < 0 ? kParentUniverse : (j.parent == i - 1 ? kParentRunning : save_slot[j.parent]);
     d.save_slot = save_slot[i];
-    d.pad[0] = j.parent;  // plain parent index, for the one-warp-per-configuration kernel
+    d.parent = j.parent;  // plain parent index, for the one-warp-per-configuration kernel
+    d.nq = joint_nq(j.type);
     d.ax = static_cast<float>(j.axis[0]); d.ay = static_cast<float>(j.axis[1]); d.az = static_cast<float>(j.axis[2]);
     for (int k = 0; k < 12; ++k) d.pl[k] = static_cast<float>(j.placement[k]);
   }
