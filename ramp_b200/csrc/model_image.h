@@ -5,6 +5,7 @@
 // table reads on the hot path are shared-memory broadcasts.  Shared by the host packer
 // and the kernels in ramp_b200.cu.
 #pragma once
+#include <stddef.h>
 #include <stdint.h>
 
 namespace ramp {
@@ -69,6 +70,8 @@ struct DGeom {  // 40 words
   float opl[12];  // the caller's placement, before re-framing: what ramp_placements_batch reports
 };
 static_assert(sizeof(DGeom) == 160, "DGeom");
+static_assert(offsetof(DJoint, pl) % 16 == 0 && offsetof(DGeom, pl) % 16 == 0 && offsetof(DGeom, opl) % 16 == 0,
+              "placements are read as float4");
 
 // Pairs are stored in PROCESSING order: first the pairs of two joint-attached geometries
 // ("DD"), then those of a joint-attached and a universe-attached one ("DS") -- each stage-1

@@ -291,10 +291,14 @@ __device__ __forceinline__ void expand_q(const Warp& w) {
   }
 }
 
+// a 3x4 placement of the model image (DJoint::pl, DGeom::pl / opl: all 16-byte aligned)
 __device__ __forceinline__ Xf load_table_xf(const float* p) {
+  const float4* p4 = reinterpret_cast<const float4*>(p);
+  const float4 r0 = p4[0], r1 = p4[1], r2 = p4[2];
   Xf o;
-#pragma unroll
-  for (int k = 0; k < 12; ++k) o.m[k] = p[k];
+  o.m[0] = r0.x; o.m[1] = r0.y; o.m[2] = r0.z; o.m[3] = r0.w;
+  o.m[4] = r1.x; o.m[5] = r1.y; o.m[6] = r1.z; o.m[7] = r1.w;
+  o.m[8] = r2.x; o.m[9] = r2.y; o.m[10] = r2.z; o.m[11] = r2.w;
   return o;
 }
 
