@@ -642,41 +642,45 @@ __device__ __forceinline__ void narrow_phase(const Warp& w, bool stop_at_first, 
       bool to_gjk = false;
       Xf rel = xf_identity();
       V3 v0 = mk(1.f, 0.f, 0.f);
-      int orig = 0;
+      int orig = 0, cls = 0, p = 0;
       bool go = live;
       if (live) {  // a configuration settled by an earlier group needs no more work
-        orig = w.t.pairs[chunk + (item >> 5)].orig;
+        p = chunk + (item >> 5);
+        const int oc = rec[3 * p].w;  // orig | cls << 16
+        orig = oc & 0xffff;
+        cls = oc >> 16;
         go = !dead(w.first[item & 31], orig);
       }
       if (go) {
-        const int c = item & 31, p = chunk + (item >> 5);
-        const DPair pr = w.t.pairs[p];
-        const DGeom* ga = &w.t.geoms[pr.a];
-        const DGeom* gb = &w.t.geoms[pr.b];
-        rel = xf_inv_mul(geom_xf(w, ga->gslot, c), geom_xf(w, gb->gslot, c));
-        if (pr.cls >= kClsBoxBox) {
+        const int c = item & 31;
+        const int4 r2 = rec[3 * p + 2];  // slack, a | b << 16, sa | sb << 16
+        const float slack = __int_as_float(r2.x);
+        const DGeom* ga = &w.t.geoms[r2.y & 0xffff];
+        const DGeom* gb = &w.t.geoms[r2.y >> 16];
+        rel = xf_inv_mul(geom_xf(w, static_cast<int16_t>(r2.z & 0xffff), c), geom_xf(w, r2.z >> 16, c));
+        if (cls >= kClsBoxBox) {
           // one SAT instance: exact decision on the boxes themselves, or a cull on the
-          // local bounding boxes of two GJK shapes
-          const bool bb = pr.cls == kClsBoxBox;
-          const V3 ha = bb ? mk(ga->p0, ga->p1, ga->p2) : mk(ga->hx, ga->hy, ga->hz);
-          const V3 hb = bb ? mk(gb->p0, gb->p1, gb->p2) : mk(gb->hx, gb->hy, gb->hz);
+          // local bounding boxes of two GJK shapes (DGeom words 4-7: the box, 8-10: the bounds)
+          const bool bb = cls == kClsBoxBox;
+          const float4 ha4 = reinterpret_cast<const float4*>(ga)[bb ? 1 : 2], hb4 = reinterpret_cast<const float4*>(gb)[bb ? 1 : 2];
+          const V3 ha = mk(ha4.x, ha4.y, ha4.z), hb = mk(hb4.x, hb4.y, hb4.z);
           // GJK class: overlapping INNER capsules prove the collision (the outer ones were
           // tested in stage 1); only the shell in between goes on to the OBB cull and GJK.
           bool decided = false;
           if (!bb) {
+            const float4 ca = reinterpret_cast<const float4*>(ga)[6], cb = reinterpret_cast<const float4*>(gb)[6];  // s_out r_out s_in r_in
             const V3 zb = mk(rel.m[2], rel.m[6], rel.m[10]);
-            v0 = seg_seg_witness(mk(0.f, 0.f, -ga->s_in), mk(0.f, 0.f, 2.f * ga->s_in), trans(rel) - zb * gb->s_in,
-                                 zb * (2.f * gb->s_in));
-            const float rin = ga->r_in + gb->r_in - pr.slack;
-            if (rin > 0.f && dot(v0, v0) < rin * rin) { record_hit(w, c, pr.orig, want_mask); decided = true; }
+            v0 = seg_seg_witness(mk(0.f, 0.f, -ca.z), mk(0.f, 0.f, 2.f * ca.z), trans(rel) - zb * cb.z, zb * (2.f * cb.z));
+            const float rin = ca.w + cb.w - slack;
+            if (rin > 0.f && dot(v0, v0) < rin * rin) { record_hit(w, c, orig, want_mask); decided = true; }
           }
           if (!decided) {
-            const bool ov = obb_overlap(ha, hb, rel, bb ? 0.f : pr.slack);
-            if (ov && bb) record_hit(w, c, pr.orig, want_mask);
+            const bool ov = obb_overlap(ha, hb, rel, bb ? 0.f : slack);
+            if (ov && bb) record_hit(w, c, orig, want_mask);
             to_gjk = ov && !bb;
           }
-        } else if (closed_form_hit(pr.cls, ga, gb, rel)) {
-          record_hit(w, c, pr.orig, want_mask);
+        } else if (closed_form_hit(cls, ga, gb, rel)) {
+          record_hit(w, c, orig, want_mask);
         }
       }
       __syncwarp();  // all lanes have read their item before the in-place compaction writes
