@@ -86,6 +86,7 @@ struct SlabLayout {
   int32_t team;         // warps sharing one slab (1, 2 or 4): they split the pair list of a tile
   int32_t chunk_pairs;  // pairs per queue round of one warp
   int32_t queue_words;  // per-warp queue size
+  int32_t raw_cols;     // validity kernels: widest input row (floats) the TMA row prefetch takes; 0 = off
 };
 
 __device__ __forceinline__ int64_t imin64(int64_t a, int64_t b) { return a < b ? a : b; }
@@ -264,6 +265,73 @@ __device__ __forceinline__ void commit_rows(const RowPrefetch<kVec>& pf, float* 
       for (int c = 0; c < cols; ++c) dst[c * 32 + lane] = dst[c * 32];
     }
   }
+  __syncwarp();
+}
+
+// ---- TMA prefetch of the NEXT tile's rows (validity kernels).  The 32 rows of a tile are one
+// contiguous, 16-byte aligned block when ld == cols; a single cp.async.bulk lands it in the
+// slab's `save` region -- dead between the end of FK and the next tile's FK -- behind a
+// per-slab mbarrier, so the copy costs no registers and runs under the whole narrow phase.
+// The mbarrier sits in the 16 bytes in front of the region (never written by FK).
+struct TileFetch {
+  uint32_t bar, raw;  // shared-space addresses
+  uint32_t phase;
+  bool pending;       // a copy for the tile about to be committed is in flight
+};
+
+__device__ __forceinline__ void tile_fetch_init(TileFetch& tf, float* region, int lane) {
+  tf.bar = smem_u32(region - 4);
+  tf.raw = smem_u32(region);
+  tf.phase = 0;
+  tf.pending = false;
+  if (lane == 0) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(tf.bar));
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncwarp();
+}
+
+// Start the copy of tile `row0` if it is a full, contiguous, aligned tile that fits; otherwise
+// leave it to the plain load at commit time.  Warp-uniform.
+__device__ __forceinline__ void tile_fetch_issue(TileFetch& tf, const float* __restrict__ src, int64_t row0, int64_t n_rows,
+                                                 int cols, int ld, int raw_cols, int lane) {
+  tf.pending = false;
+  if (row0 + 32 > n_rows || ld != cols || cols > raw_cols) return;
+  const float* base = src + row0 * ld;
+  if (reinterpret_cast<uintptr_t>(base) & 15) return;
+  tf.pending = true;
+  __syncwarp();  // every lane is done reading the region (previous commit / FK saves)
+  if (lane == 0) {
+    const uint32_t bytes = 128u * cols;
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(tf.bar), "r"(bytes) : "memory");
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(tf.raw),
+                 "l"(base), "r"(bytes), "r"(tf.bar)
+                 : "memory");
+  }
+}
+
+// Rows of the tile into slot-major dst[col * 32 + row]: from the landed copy (lane = row), or
+// with the plain load.
+__device__ __forceinline__ void tile_fetch_commit(TileFetch& tf, float* dst, const float* region, const float* __restrict__ src,
+                                                  int64_t row0, int64_t n_rows, int cols, int ld, int lane) {
+  if (!tf.pending) {
+    load_rows(dst, src, row0, n_rows, cols, ld, lane);
+    return;
+  }
+  uint32_t done = 0;
+  while (!done) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(done)
+        : "r"(tf.bar), "r"(tf.phase)
+        : "memory");
+  }
+  tf.phase ^= 1;
+  const float* raw = region + lane * cols;
+#pragma unroll 4
+  for (int c = 0; c < cols; ++c) dst[c * 32 + lane] = raw[c];
   __syncwarp();
 }
 
@@ -813,14 +881,14 @@ __global__ void __launch_bounds__(512, 1) check_kernel(const __grid_constant__ C
   const int64_t ntiles = (a.n + 31) >> 5;
   const int64_t tile_step = static_cast<int64_t>(gridDim.x) * nteams;
   const int64_t tile0 = static_cast<int64_t>(blockIdx.x) * nteams + tid;
-  RowPrefetch<4> pf;
-  pf.valid = false;
-  if (tw == 0) prefetch_rows(pf, a.q, tile0 << 5, a.n, cols, a.ld, w.lane);
+  TileFetch tf;
+  if (tw == 0) {
+    tile_fetch_init(tf, w.save, w.lane);  // the first tile takes the plain load: nothing to hide a copy behind
+  }
   for (int64_t tile = tile0; tile < ntiles; tile += tile_step) {
     const int64_t row0 = tile << 5;
     if (tw == 0) {
-      commit_rows(pf, actuated ? w.act : w.q, a.q, row0, a.n, cols, a.ld, w.lane);
-      prefetch_rows(pf, a.q, (tile + tile_step) << 5, a.n, cols, a.ld, w.lane);
+      tile_fetch_commit(tf, actuated ? w.act : w.q, w.save, a.q, row0, a.n, cols, a.ld, w.lane);
       if (actuated) expand_q(w);
       reset_results(w, want_mask ? t.h->mask_words : 0);
       if (kTeam == 1) fk_lane<0>(w);
@@ -830,6 +898,8 @@ __global__ void __launch_bounds__(512, 1) check_kernel(const __grid_constant__ C
       fk_team<kTeam>(w, tw);
     }
     team_sync();
+    // FK is done with the saved transforms: their region takes the next tile's rows
+    if (tw == 0) tile_fetch_issue(tf, a.q, (tile + tile_step) << 5, a.n, cols, a.ld, a.L.raw_cols, w.lane);
     narrow_phase<kTeam>(w, stop, stop && a.first_pair == nullptr, want_mask, a.gq, static_cast<uint32_t>(row0), tw,
                         a.L.chunk_pairs);
     team_sync();
@@ -2192,7 +2262,12 @@ static int plan_slabs(const RampModel* m, int stage_row_floats, int act_cols, Sl
   L->off_act = region0 + q_words;
   const bool fk_only = stage_row_floats > 0;  // the FK kernels need no slab, queue or result rows
   L->off_geom = take(fk_only ? 0 : std::max(h.n_dyn, 1) * kGeomFloats * 32);
-  L->off_save = take(std::max(h.n_save, 1) * 12 * 32);
+  // the saved transforms share their region with the TMA row prefetch of the validity kernels
+  // (mbarrier + 32 raw rows); rows wider than 35 floats are loaded the plain way
+  const int in_cols = std::max(q_words, act_words) / 32;
+  L->raw_cols = (!fk_only && in_cols <= 35) ? in_cols : 0;
+  take(4);  // the prefetch mbarrier, in front of the shared region
+  L->off_save = take(std::max(std::max(h.n_save, 1) * 12 * 32, 32 * L->raw_cols));
   L->off_queue = region0;
   L->off_mask = take(fk_only ? 0 : std::max(h.mask_words, 1) * 32);
   L->off_first = take(fk_only ? 0 : 32);
