@@ -535,11 +535,21 @@ struct __align__(16) GjkItem {
 };
 static_assert(sizeof(GjkItem) == 80, "GjkItem");
 
+// The queue has two regions.  Items whose inner capsules are still far apart compared with the
+// shell between inner and outer capsule almost always end after one GJK iteration ("easy");
+// the others take 4-5 ("hard").  Hard items go to the front region and are handed out first,
+// so the consumer kernel drains on one-iteration items and its warps finish together.
 struct GjkQueue {
-  GjkItem* items;    // nullptr: no queue, GJK runs inside the validity kernel
-  uint32_t* count;   // items reserved so far (may exceed capacity: overflow stays in-kernel)
-  uint32_t capacity;
+  GjkItem* items;     // nullptr: no queue, GJK runs inside the validity kernel
+  uint32_t* count;    // [0] hard, [1] easy items reserved so far (may exceed the regions: the
+                      // overflow stays in-kernel), [2] the consumer's cursor; zeroed by the host
+  uint32_t capacity;  // items: hard region [0, cap_hard), easy region [cap_hard, capacity)
+  uint32_t cap_hard;
 };
+
+__host__ __device__ constexpr uint32_t queue_cap_hard(uint32_t capacity) { return capacity / 3; }
+// hard: |witness of the inner capsule axes| below inner radii + 7/8 of the shell
+constexpr float kHardShell = 0.875f;
 
 __device__ __forceinline__ void record_hit(const Warp& w, int c, int p, bool want_mask) {
   atomicMin(&w.first[c], p);
@@ -707,7 +717,7 @@ __device__ __forceinline__ void narrow_phase(const Warp& w, bool stop_at_first, 
     for (int base = 0; base < qn; base += 32) {
       const bool live = base + l < qn;
       const int item = live ? w.queue[base + l] : 0;
-      bool to_gjk = false;
+      bool to_gjk = false, hard = false;
       Xf rel = xf_identity();
       V3 v0 = mk(1.f, 0.f, 0.f);
       int orig = 0, cls = 0, p = 0;
@@ -740,7 +750,10 @@ __device__ __forceinline__ void narrow_phase(const Warp& w, bool stop_at_first, 
             const V3 zb = mk(rel.m[2], rel.m[6], rel.m[10]);
             v0 = seg_seg_witness(mk(0.f, 0.f, -ca.z), mk(0.f, 0.f, 2.f * ca.z), trans(rel) - zb * cb.z, zb * (2.f * cb.z));
             const float rin = ca.w + cb.w - slack;
-            if (rin > 0.f && dot(v0, v0) < rin * rin) { record_hit(w, c, orig, want_mask); decided = true; }
+            const float vv0 = dot(v0, v0);
+            if (rin > 0.f && vv0 < rin * rin) { record_hit(w, c, orig, want_mask); decided = true; }
+            const float thr = fmaf(kHardShell, ca.y + cb.y - (ca.w + cb.w), ca.w + cb.w);  // r_out, r_in sums
+            hard = vv0 < thr * thr;
           }
           if (!decided) {
             const bool ov = obb_overlap(ha, hb, rel, bb ? 0.f : slack);
@@ -755,14 +768,20 @@ __device__ __forceinline__ void narrow_phase(const Warp& w, bool stop_at_first, 
       // hits of this group may have settled configurations whose GJK items are still pending
       if (to_gjk && dead(w.first[item & 31], orig)) to_gjk = false;
       if (gq.items != nullptr) {
-        // reserve slots of the global queue for this group's survivors (one atomic per group)
-        const unsigned gb_ = __ballot_sync(FULL, to_gjk);
-        if (gb_) {
-          uint32_t base_slot = 0;
-          if (l == __ffs(gb_) - 1) base_slot = atomicAdd(gq.count, static_cast<uint32_t>(__popc(gb_)));
-          base_slot = __shfl_sync(FULL, base_slot, __ffs(gb_) - 1);
-          const uint32_t slot = base_slot + __popc(gb_ & ((1u << l) - 1));
-          if (to_gjk && slot < gq.capacity) {
+        // reserve slots of the two queue regions for this group's survivors (one 64-bit atomic
+        // per group: hard count in the low word, easy count in the high word)
+        const unsigned mh = __ballot_sync(FULL, to_gjk && hard), me = __ballot_sync(FULL, to_gjk && !hard);
+        if (mh | me) {
+          const int leader = __ffs(mh | me) - 1;
+          unsigned long long base = 0;
+          if (l == leader)
+            base = atomicAdd(reinterpret_cast<unsigned long long*>(gq.count),
+                             static_cast<unsigned long long>(__popc(mh)) | (static_cast<unsigned long long>(__popc(me)) << 32));
+          base = __shfl_sync(FULL, base, leader);
+          const uint32_t lt_l = (1u << l) - 1;
+          const uint32_t slot = hard ? static_cast<uint32_t>(base) + __popc(mh & lt_l)
+                                     : gq.cap_hard + static_cast<uint32_t>(base >> 32) + __popc(me & lt_l);
+          if (to_gjk && slot < (hard ? gq.cap_hard : gq.capacity)) {
             const uint32_t c = item & 31, p = chunk + (item >> 5);
             float4* dst = reinterpret_cast<float4*>(gq.items + slot);
             dst[0] = make_float4(rel.m[0], rel.m[1], rel.m[2], rel.m[3]);
@@ -1125,7 +1144,7 @@ struct GjkQueueArgs {
   int32_t table_bytes;
   const GjkItem* items;
   uint32_t* count;   // [0] items produced, [1] the consumers' cursor (both zeroed by the host)
-  uint32_t capacity;
+  uint32_t capacity, cap_hard;
   uint8_t* hit;
   int32_t* first_pair;
   uint32_t* pair_mask;
@@ -1145,6 +1164,37 @@ constexpr int kFetchAttempts = 4;
 #endif
 constexpr int kGjkCtasPerSm = RAMP_GJK_CTAS;
 
+// Support scan of the few items left in a draining warp, shared between lanes: the k-th active
+// lane owns item k; lanes [k * kG, (k + 1) * kG) each scan 1/kG of its vertex list and a
+// butterfly picks the best.  Closed-form shapes (no vertex list) are left to their owner.
+template <int kG>
+__device__ __forceinline__ V3 coop_support(unsigned am, bool active, const GjkShape& S, V3 d, const float4* verts0) {
+  const unsigned FULL = 0xffffffffu;
+  const int l = threadIdx.x & 31;
+  const int grp = l / kG, sub = l % kG;
+  const int owner = __fns(am, 0, grp + 1) & 31;  // lane of the grp-th active item (any lane if there is none)
+  const bool has = grp < __popc(am);
+  const bool listed = S.type != SH_CYLINDER && S.type != SH_ELLIPSOID;
+  const int o_cnt = __shfl_sync(FULL, active && listed ? S.vcnt : 0, owner);
+  const int o_off = __shfl_sync(FULL, static_cast<int>(S.verts - verts0), owner);
+  const V3 od = mk(__shfl_sync(FULL, d.x, owner), __shfl_sync(FULL, d.y, owner), __shfl_sync(FULL, d.z, owner));
+  const int per = (o_cnt + kG - 1) / kG;
+  const int begin = sub * per, cnt = has ? max(min(per, o_cnt - begin), 0) : 0;
+  V3 r = support(SH_CONVEX, 0.f, 0.f, 0.f, verts0 + o_off + begin, cnt, od);
+  float val = cnt > 0 ? dot(r, od) : -3.0e38f;
+#pragma unroll
+  for (int m = 1; m < kG; m <<= 1) {
+    const float ov = __shfl_xor_sync(FULL, val, m);
+    const V3 orr = mk(__shfl_xor_sync(FULL, r.x, m), __shfl_xor_sync(FULL, r.y, m), __shfl_xor_sync(FULL, r.z, m));
+    if (ov > val) { val = ov; r = orr; }
+  }
+  // back to the owners: active lane with rank k reads the result of group k
+  const int src = (__popc(am & ((1u << l) - 1)) * kG) & 31;
+  V3 res = mk(__shfl_sync(FULL, r.x, src), __shfl_sync(FULL, r.y, src), __shfl_sync(FULL, r.z, src));
+  if (active && !listed) res = support(S.type, S.p0, S.p1, S.p2, S.verts, S.vcnt, d);
+  return res;
+}
+
 #ifdef RAMP_STATS
 __device__ unsigned long long g_stats[64];  // [0] items [1] iterations [2] hits [3] skipped, [8+it] histogram
 #endif
@@ -1154,11 +1204,13 @@ __global__ void __launch_bounds__(256, 2) gjk_queue_kernel(const __grid_constant
   unsigned char* tbl = g_smem + 16;
   stage_tables(tbl, a.img, a.table_bytes, mbar);
   const Tables t = make_tables(tbl);
-  const uint32_t total = min(*a.count, a.capacity);
+  // hard items first (see GjkQueue): virtual index i -> slot i, or cap_hard + (i - n_hard)
+  const uint32_t n_hard = min(a.count[0], a.cap_hard);
+  const uint32_t total = n_hard + min(a.count[1], a.capacity - a.cap_hard);
   // Work is handed out dynamically: a warp takes kQueueChunk consecutive items at a time from a
   // cursor next to the producers' counter, so every warp stays busy until the queue is empty
   // (iteration counts per item vary from 1 to 48: a static split leaves long tails).
-  uint32_t* cursor = a.count + 1;
+  uint32_t* cursor = a.count + 2;
   const int l = threadIdx.x & 31;
   const unsigned FULL = 0xffffffffu;
   uint32_t lo = 0, hi = 0, row = 0, p = 0;  // [lo, hi): items this warp holds but has not started
@@ -1198,7 +1250,7 @@ __global__ void __launch_bounds__(256, 2) gjk_queue_kernel(const __grid_constant
         }
       }
       if (gi != 0xffffffffu) {
-        const float4* src = reinterpret_cast<const float4*>(a.items + gi);
+        const float4* src = reinterpret_cast<const float4*>(a.items + (gi < n_hard ? gi : a.cap_hard + (gi - n_hard)));
         const float4 r0 = __ldcs(src), r1 = __ldcs(src + 1), r2 = __ldcs(src + 2), r3 = __ldcs(src + 3), r4 = __ldcs(src + 4);
         row = __float_as_uint(r3.w);
         const DPair pr = t.pairs[__float_as_uint(r4.x)];
@@ -1230,10 +1282,21 @@ __global__ void __launch_bounds__(256, 2) gjk_queue_kernel(const __grid_constant
     // Both support scans run with the whole warp converged (idle lanes scan zero vertices):
     // left to itself the compiler lets lanes with a short vertex list run ahead into the next
     // scan on their own, and the scans execute twice at partial width.
-    const V3 sa = support(A.type, A.p0, A.p1, A.p2, A.verts, active ? A.vcnt : 0, -g.v);
-    __syncwarp();
-    const V3 sb = support(B.type, B.p0, B.p1, B.p2, B.verts, active ? B.vcnt : 0, rot_t(g.rel, g.v));
-    __syncwarp();
+    // Once the queue is empty a warp is left with a few long-running items (38 % of the trips
+    // of a UR5 batch ran with 7 of 32 lanes busy): then the idle lanes help with the scans.
+    const unsigned am = __ballot_sync(FULL, active);
+    const int na = __popc(am);
+    V3 sa, sb;
+    if (drained && lo == hi && na <= 8) {
+      const V3 da = -g.v, db = rot_t(g.rel, g.v);
+      if (na <= 4) { sa = coop_support<8>(am, active, A, da, t.verts); sb = coop_support<8>(am, active, B, db, t.verts); }
+      else { sa = coop_support<4>(am, active, A, da, t.verts); sb = coop_support<4>(am, active, B, db, t.verts); }
+    } else {
+      sa = support(A.type, A.p0, A.p1, A.p2, A.verts, active ? A.vcnt : 0, -g.v);
+      __syncwarp();
+      sb = support(B.type, B.p0, B.p1, B.p2, B.verts, active ? B.vcnt : 0, rot_t(g.rel, g.v));
+      __syncwarp();
+    }
     if (active) {
       float dist;
       const int st = gjk_advance(g, sa, sb, false, dist);
@@ -2311,7 +2374,7 @@ static int check_q_args(const RampModel* m, const void* d_q, int64_t n, int32_t 
 
 // Rows are processed in slices so the GJK work queue has a bounded size.
 constexpr int64_t kSliceRows = 1 << 21;
-constexpr int64_t kQueueItemsPerRow = 2;   // capacity; overflow is handled inside check_kernel
+constexpr int64_t kQueueItemsPerRow = 3;   // capacity (1 hard + 2 easy per row); overflow is handled inside check_kernel
 constexpr int64_t kQueueMinRows = 1024;    // below this a second launch costs more than it saves
 
 constexpr int64_t kSmallRows = 8192;  // up to here one warp per configuration is faster than 32 per warp
@@ -2388,7 +2451,7 @@ static int launch_check(const RampModel* m, const float* d_q, int64_t n, int32_t
     if (int rc = set_smem(gjk_queue_kernel, smem_b)) return rc;
     b.img = m->d_image; b.table_bytes = a.L.table_bytes;
     b.items = reinterpret_cast<GjkItem*>(scratch + 256); b.count = reinterpret_cast<uint32_t*>(scratch);
-    b.capacity = cap_items; b.mask_words = m->hdr.mask_words;
+    b.capacity = cap_items; b.cap_hard = queue_cap_hard(cap_items); b.mask_words = m->hdr.mask_words;
     b.stop = !(flags & RAMP_ALL_PAIRS) && d_mask == nullptr;
   }
   const int64_t step = use_queue ? kSliceRows : n;
@@ -2398,10 +2461,10 @@ static int launch_check(const RampModel* m, const float* d_q, int64_t n, int32_t
     a.hit = d_hit + off;
     a.first_pair = d_first ? d_first + off : nullptr;
     a.pair_mask = d_mask ? d_mask + off * m->hdr.mask_words : nullptr;
-    a.gq = GjkQueue{nullptr, nullptr, 0u};
+    a.gq = GjkQueue{nullptr, nullptr, 0u, 0u};
     if (use_queue) {
       CUDA_TRY(cudaMemsetAsync(scratch, 0, 16, st));
-      a.gq = GjkQueue{reinterpret_cast<GjkItem*>(scratch + 256), reinterpret_cast<uint32_t*>(scratch), cap_items};
+      a.gq = GjkQueue{reinterpret_cast<GjkItem*>(scratch + 256), reinterpret_cast<uint32_t*>(scratch), cap_items, queue_cap_hard(cap_items)};
     }
     {
       const int grid = grid_for(m, (ns + 31) / 32, nwarps / a.L.team);
@@ -2653,7 +2716,7 @@ int ramp_check_batch(const RampModel* m, const float* d_q, int64_t n, int32_t ld
 // kNoAllocQueueBytes (about 5.6 MB) until the process exits, whether or not the entry point
 // is ever used.  That is why the limit is modest.
 constexpr int64_t kNoAllocMaxRows = RAMP_NOALLOC_MAX_ROWS;
-constexpr uint32_t kNoAllocQueueItems = static_cast<uint32_t>(kNoAllocMaxRows * kQueueItemsPerRow + 4096);
+constexpr uint32_t kNoAllocQueueItems = static_cast<uint32_t>(kNoAllocMaxRows * 2 + 4096);
 constexpr size_t kNoAllocQueueBytes = 256 + static_cast<size_t>(kNoAllocQueueItems) * sizeof(GjkItem);
 static __device__ __align__(256) unsigned char g_noalloc_queue[kNoAllocQueueBytes];
 
@@ -2702,11 +2765,11 @@ int ramp_check_batch_noalloc(const RampModel* m, const float* d_q, int64_t n, in
   // the array still holds the previous call's counter and items: only the counter has to
   // start from zero, the items below it are rewritten before they are read
   CUDA_TRY(cudaMemsetAsync(scratch, 0, 16, st));
-  a.gq = GjkQueue{reinterpret_cast<GjkItem*>(scratch + 256), reinterpret_cast<uint32_t*>(scratch), kNoAllocQueueItems};
+  a.gq = GjkQueue{reinterpret_cast<GjkItem*>(scratch + 256), reinterpret_cast<uint32_t*>(scratch), kNoAllocQueueItems, queue_cap_hard(kNoAllocQueueItems)};
   check_kernel<1><<<grid_for(m, (n + 31) / 32, nwarps), nwarps * 32, smem, st>>>(a);
   GjkQueueArgs b{};
   b.img = m->d_image; b.table_bytes = a.L.table_bytes;
-  b.items = a.gq.items; b.count = a.gq.count; b.capacity = kNoAllocQueueItems;
+  b.items = a.gq.items; b.count = a.gq.count; b.capacity = kNoAllocQueueItems; b.cap_hard = a.gq.cap_hard;
   b.hit = d_hit; b.first_pair = d_first_pair; b.pair_mask = d_pair_mask; b.mask_words = m->hdr.mask_words;
   b.stop = !(flags & RAMP_ALL_PAIRS) && d_pair_mask == nullptr;
   gjk_queue_kernel<<<m->sm_count * kGjkCtasPerSm, 256, smem_b, st>>>(b);
@@ -2828,7 +2891,7 @@ int ramp_check_edges(const RampModel* m, const float* d_q0, const float* d_q1, i
   if (int rc = plan_slabs(m, 0, n_cols, &a.L, &nwarps, &smem)) return rc;
   if (int rc = set_smem(edge_check_kernel, smem)) return rc;
   // GJK work queue (only worth a launch when there are enough edges to fill warps)
-  a.gq = GjkQueue{nullptr, nullptr, 0u};
+  a.gq = GjkQueue{nullptr, nullptr, 0u, 0u};
   unsigned char* qmem = nullptr;
   const bool use_queue = m->pool != nullptr && m->n_gjk_pairs > 0 && n_edges >= 64;
   GjkQueueArgs b{};
@@ -2841,10 +2904,10 @@ int ramp_check_edges(const RampModel* m, const float* d_q0, const float* d_q1, i
       return fail(RAMP_ERR_ALLOC, "cudaMallocFromPoolAsync(%zu) for the GJK queue failed", bytes);
     }
     CUDA_TRY(cudaMemsetAsync(qmem, 0, 16, st));
-    a.gq = GjkQueue{reinterpret_cast<GjkItem*>(qmem + 256), reinterpret_cast<uint32_t*>(qmem), cap};
+    a.gq = GjkQueue{reinterpret_cast<GjkItem*>(qmem + 256), reinterpret_cast<uint32_t*>(qmem), cap, queue_cap_hard(cap)};
     smem_b = 16 + a.L.table_bytes;
     if (int rc = set_smem(gjk_queue_kernel, smem_b)) return rc;
-    b.img = m->d_image; b.table_bytes = a.L.table_bytes; b.items = a.gq.items; b.count = a.gq.count; b.capacity = cap;
+    b.img = m->d_image; b.table_bytes = a.L.table_bytes; b.items = a.gq.items; b.count = a.gq.count; b.capacity = cap; b.cap_hard = a.gq.cap_hard;
     b.offs = a.offs; b.nd = a.nd; b.first_invalid = a.first_invalid; b.n_edges = n_edges;
   }
   const int eb = static_cast<int>((n_edges + 255) / 256);
