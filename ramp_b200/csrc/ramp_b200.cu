@@ -3022,11 +3022,20 @@ int ramp_check_host(const RampModel* m, const float* h_q, int64_t n, int32_t ld,
     if (!m->streams[k]) CUDA_TRY(cudaStreamCreateWithFlags(&m->streams[k], cudaStreamNonBlocking));
   unsigned char* D = static_cast<unsigned char*>(m->d_scratch);
   unsigned char* H = static_cast<unsigned char*>(m->h_pinned);
-  const int64_t nchunks = (n + chunk - 1) / chunk;
+  // Chunk boundaries.  The kernels of chunk 0 cannot start before its copy has landed and
+  // nothing hides that copy, so chunk 0 is shorter (n/8, at least 2^16 rows: smaller chunks
+  // cost more in kernel tails than they save); the rest are full chunks.
+  std::vector<int64_t> start{0};
+  {
+    const int64_t first = std::min<int64_t>(chunk, std::max<int64_t>(1 << 16, (n / 8 + 31) & ~int64_t{31}));
+    if (first < n) start.push_back(first);
+    while (start.back() < n) start.push_back(std::min(n, start.back() + chunk));
+  }
+  const int64_t nchunks = static_cast<int64_t>(start.size()) - 1;
   // results of a chunk that went through the pinned staging are copied out once its stream is done
   auto drain = [&](int64_t k) {
     const int b = static_cast<int>(k & 1);
-    const int64_t off = k * chunk, ns = std::min(chunk, n - off);
+    const int64_t off = start[k], ns = start[k + 1] - off;
     unsigned char* Hb = H + b * per;
     if (!pin_hit) std::memcpy(h_hit + off, Hb + b_q, ns);
     if (h_first_pair && !pin_first) std::memcpy(h_first_pair + off, Hb + b_q + b_hit, sizeof(int32_t) * ns);
@@ -3035,7 +3044,7 @@ int ramp_check_host(const RampModel* m, const float* h_q, int64_t n, int32_t ld,
   for (int64_t k = 0; k < nchunks; ++k) {
     const int b = static_cast<int>(k & 1);
     cudaStream_t st = m->streams[b];
-    const int64_t off = k * chunk, ns = std::min(chunk, n - off);
+    const int64_t off = start[k], ns = start[k + 1] - off;
     // Chunk k reuses the buffers of chunk k-2.  On the device the stream orders that by
     // itself; only the host staging copies (pageable caller memory) make the host wait.
     if (k >= 2 && staged) {
