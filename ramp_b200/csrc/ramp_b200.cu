@@ -869,6 +869,7 @@ struct CheckArgs {
   int32_t* first_pair;
   uint32_t* pair_mask;
   GjkQueue gq;
+  uint32_t row_offset;  // added to the row index of queued items: several launches can feed one queue
   SlabLayout L;
 };
 
@@ -919,7 +920,7 @@ __global__ void __launch_bounds__(512, 1) check_kernel(const __grid_constant__ C
     team_sync();
     // FK is done with the saved transforms: their region takes the next tile's rows
     if (tw == 0) tile_fetch_issue(tf, a.q, (tile + tile_step) << 5, a.n, cols, a.ld, a.L.raw_cols, w.lane);
-    narrow_phase<kTeam>(w, stop, stop && a.first_pair == nullptr, want_mask, a.gq, static_cast<uint32_t>(row0), tw,
+    narrow_phase<kTeam>(w, stop, stop && a.first_pair == nullptr, want_mask, a.gq, static_cast<uint32_t>(row0) + a.row_offset, tw,
                         a.L.chunk_pairs);
     team_sync();
     const int64_t row = row0 + w.lane;
@@ -1800,7 +1801,8 @@ struct RampModel {
   mutable size_t scratch_cap = 0;
   mutable void* h_pinned = nullptr;
   mutable size_t pinned_cap = 0;
-  mutable cudaStream_t streams[2] = {nullptr, nullptr};  // ramp_check_host pipeline
+  mutable cudaStream_t streams[3] = {nullptr, nullptr, nullptr};  // ramp_check_host pipeline: two for chunks, one for the queue kernel + D2H
+  mutable cudaEvent_t events[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};  // queue ready, tiles done x2, results copied x2
   mutable void* d_edge_stage = nullptr;  // ramp_check_edges_host staging (device / pinned host)
   mutable void* h_edge_stage = nullptr;
   mutable size_t edge_stage_cap = 0;
@@ -2409,11 +2411,21 @@ static int launch_check_small(const RampModel* m, const float* d_q, int64_t n, i
   return RAMP_OK;
 }
 
-static int launch_check(const RampModel* m, const float* d_q, int64_t n, int32_t ld, uint32_t flags, uint8_t* d_hit,
-                        int32_t* d_first, uint32_t* d_mask, cudaStream_t st) {
-  if (n <= kSmallRows) return launch_check_small(m, d_q, n, ld, flags, d_hit, d_first, d_mask, st);
-  CheckArgs a;
-  a.img = m->d_image; a.ld = ld; a.flags = flags;
+// One ramp_check_batch is: plan (slab layout, team size, shared-memory opt-in), a GJK queue from
+// the model's pool, then per slice the tile kernel and the queue kernel.  The pieces are
+// separate because ramp_check_host feeds ONE queue from the tile kernels of several chunks and
+// runs the queue kernel once behind them.
+struct CheckPlan {
+  CheckArgs a;  // img, ld, flags, L; the per-launch fields are filled by launch_tiles
+  int nwarps, team;
+  size_t smem, smem_b;
+  bool use_queue;
+};
+
+static int plan_check(const RampModel* m, int32_t ld, uint32_t flags, int64_t n, CheckPlan* P) {
+  CheckArgs& a = P->a;
+  a.img = m->d_image; a.ld = ld; a.flags = flags; a.row_offset = 0;
+  a.gq = GjkQueue{nullptr, nullptr, 0u, 0u};
   int nwarps; size_t smem;
   if (int rc = plan_slabs(m, 0, m->hdr.n_act, &a.L, &nwarps, &smem, ld)) return rc;
   // Few slabs fit (a robot with many geometries): let teams of 2 or 4 warps share each slab and
@@ -2433,51 +2445,71 @@ static int launch_check(const RampModel* m, const float* d_q, int64_t n, int32_t
   if (const char* e = std::getenv("RAMP_B200_TEAM")) { team = std::atoi(e); team = team >= 4 ? 4 : (team >= 2 ? 2 : 1); }  // experiments
   if (team > 1 && plan_slabs(m, 0, m->hdr.n_act, &a.L, &nwarps, &smem, ld, team) != RAMP_OK) return RAMP_ERR_LIMIT;
   if (int rc = team == 2 ? set_smem(check_kernel<2>, smem) : (team == 4 ? set_smem(check_kernel<4>, smem) : set_smem(check_kernel<1>, smem))) return rc;
-  const bool use_queue = m->pool != nullptr && m->n_gjk_pairs > 0 && n >= kQueueMinRows;
-  unsigned char* scratch = nullptr;
-  uint32_t cap_items = 0;
-  GjkQueueArgs b{};
-  size_t smem_b = 0;
-  if (use_queue) {
-    cap_items = static_cast<uint32_t>(std::min<int64_t>(n, kSliceRows) * kQueueItemsPerRow + 4096);
-    // test hook: a tiny queue forces the overflow path (GJK inside check_kernel)
-    if (const char* e = std::getenv("RAMP_B200_QUEUE_CAP")) cap_items = static_cast<uint32_t>(std::max(1, std::atoi(e)));
-    const size_t bytes = 256 + static_cast<size_t>(cap_items) * sizeof(GjkItem);
-    if (cudaMallocFromPoolAsync(reinterpret_cast<void**>(&scratch), bytes, m->pool, st) != cudaSuccess) {
-      cudaGetLastError();
-      return fail(RAMP_ERR_ALLOC, "cudaMallocFromPoolAsync(%zu) for the GJK queue failed", bytes);
-    }
-    smem_b = 16 + a.L.table_bytes;
-    if (int rc = set_smem(gjk_queue_kernel, smem_b)) return rc;
-    b.img = m->d_image; b.table_bytes = a.L.table_bytes;
-    b.items = reinterpret_cast<GjkItem*>(scratch + 256); b.count = reinterpret_cast<uint32_t*>(scratch);
-    b.capacity = cap_items; b.cap_hard = queue_cap_hard(cap_items); b.mask_words = m->hdr.mask_words;
-    b.stop = !(flags & RAMP_ALL_PAIRS) && d_mask == nullptr;
+  P->nwarps = nwarps; P->team = team; P->smem = smem;
+  P->use_queue = m->pool != nullptr && m->n_gjk_pairs > 0 && n >= kQueueMinRows;
+  P->smem_b = 16 + a.L.table_bytes;
+  if (P->use_queue)
+    if (int rc = set_smem(gjk_queue_kernel, P->smem_b)) return rc;
+  return RAMP_OK;
+}
+
+// a queue for up to `rows` configurations, from the model's pool, in stream order
+static int queue_alloc(const RampModel* m, int64_t rows, cudaStream_t st, unsigned char** scratch, GjkQueue* gq) {
+  uint32_t cap_items = static_cast<uint32_t>(rows * kQueueItemsPerRow + 4096);
+  // test hook: a tiny queue forces the overflow path (GJK inside check_kernel)
+  if (const char* e = std::getenv("RAMP_B200_QUEUE_CAP")) cap_items = static_cast<uint32_t>(std::max(1, std::atoi(e)));
+  const size_t bytes = 256 + static_cast<size_t>(cap_items) * sizeof(GjkItem);
+  if (cudaMallocFromPoolAsync(reinterpret_cast<void**>(scratch), bytes, m->pool, st) != cudaSuccess) {
+    cudaGetLastError();
+    return fail(RAMP_ERR_ALLOC, "cudaMallocFromPoolAsync(%zu) for the GJK queue failed", bytes);
   }
-  const int64_t step = use_queue ? kSliceRows : n;
+  *gq = GjkQueue{reinterpret_cast<GjkItem*>(*scratch + 256), reinterpret_cast<uint32_t*>(*scratch), cap_items, queue_cap_hard(cap_items)};
+  return RAMP_OK;
+}
+
+// tile kernel over ns rows; queued items carry row_offset + their row, results go to hit/first/mask
+static void launch_tiles(const RampModel* m, const CheckPlan& P, const float* d_q, int64_t ns, uint32_t row_offset, uint8_t* hit,
+                         int32_t* first, uint32_t* mask, const GjkQueue& gq, cudaStream_t st) {
+  CheckArgs a = P.a;
+  a.q = d_q; a.n = ns; a.hit = hit; a.first_pair = first; a.pair_mask = mask; a.gq = gq; a.row_offset = row_offset;
+  const int grid = grid_for(m, (ns + 31) / 32, P.nwarps / a.L.team);
+  if (P.team == 2) check_kernel<2><<<grid, P.nwarps * 32, P.smem, st>>>(a);
+  else if (P.team == 4) check_kernel<4><<<grid, P.nwarps * 32, P.smem, st>>>(a);
+  else check_kernel<1><<<grid, P.nwarps * 32, P.smem, st>>>(a);
+  g_launches.fetch_add(1, std::memory_order_relaxed);
+}
+
+// queue kernel; hit/first/mask are the arrays the items' row indices refer to
+static void launch_queue(const RampModel* m, const CheckPlan& P, const GjkQueue& gq, uint8_t* hit, int32_t* first, uint32_t* mask,
+                         cudaStream_t st) {
+  GjkQueueArgs b{};
+  b.img = m->d_image; b.table_bytes = P.a.L.table_bytes;
+  b.items = gq.items; b.count = gq.count; b.capacity = gq.capacity; b.cap_hard = gq.cap_hard;
+  b.mask_words = m->hdr.mask_words;
+  b.stop = !(P.a.flags & RAMP_ALL_PAIRS) && mask == nullptr;
+  b.hit = hit; b.first_pair = first; b.pair_mask = mask;
+  gjk_queue_kernel<<<m->sm_count * kGjkCtasPerSm, 256, P.smem_b, st>>>(b);
+  g_launches.fetch_add(1, std::memory_order_relaxed);
+}
+
+static int launch_check(const RampModel* m, const float* d_q, int64_t n, int32_t ld, uint32_t flags, uint8_t* d_hit,
+                        int32_t* d_first, uint32_t* d_mask, cudaStream_t st) {
+  if (n <= kSmallRows) return launch_check_small(m, d_q, n, ld, flags, d_hit, d_first, d_mask, st);
+  CheckPlan P;
+  if (int rc = plan_check(m, ld, flags, n, &P)) return rc;
+  unsigned char* scratch = nullptr;
+  GjkQueue gq{nullptr, nullptr, 0u, 0u};
+  if (P.use_queue)
+    if (int rc = queue_alloc(m, std::min<int64_t>(n, kSliceRows), st, &scratch, &gq)) return rc;
+  const int64_t step = P.use_queue ? kSliceRows : n;
   for (int64_t off = 0; off < n; off += step) {
     const int64_t ns = std::min(step, n - off);
-    a.q = d_q + off * ld; a.n = ns;
-    a.hit = d_hit + off;
-    a.first_pair = d_first ? d_first + off : nullptr;
-    a.pair_mask = d_mask ? d_mask + off * m->hdr.mask_words : nullptr;
-    a.gq = GjkQueue{nullptr, nullptr, 0u, 0u};
-    if (use_queue) {
-      CUDA_TRY(cudaMemsetAsync(scratch, 0, 16, st));
-      a.gq = GjkQueue{reinterpret_cast<GjkItem*>(scratch + 256), reinterpret_cast<uint32_t*>(scratch), cap_items, queue_cap_hard(cap_items)};
-    }
-    {
-      const int grid = grid_for(m, (ns + 31) / 32, nwarps / a.L.team);
-      if (team == 2) check_kernel<2><<<grid, nwarps * 32, smem, st>>>(a);
-      else if (team == 4) check_kernel<4><<<grid, nwarps * 32, smem, st>>>(a);
-      else check_kernel<1><<<grid, nwarps * 32, smem, st>>>(a);
-    }
-    g_launches.fetch_add(1, std::memory_order_relaxed);
-    if (use_queue) {
-      b.hit = a.hit; b.first_pair = a.first_pair; b.pair_mask = a.pair_mask;
-      gjk_queue_kernel<<<m->sm_count * kGjkCtasPerSm, 256, smem_b, st>>>(b);
-      g_launches.fetch_add(1, std::memory_order_relaxed);
-    }
+    uint8_t* hit = d_hit + off;
+    int32_t* first = d_first ? d_first + off : nullptr;
+    uint32_t* mask = d_mask ? d_mask + off * m->hdr.mask_words : nullptr;
+    if (P.use_queue) CUDA_TRY(cudaMemsetAsync(scratch, 0, 16, st));
+    launch_tiles(m, P, d_q + off * ld, ns, 0u, hit, first, mask, gq, st);
+    if (P.use_queue) launch_queue(m, P, gq, hit, first, mask, st);
   }
   if (scratch) CUDA_TRY(cudaFreeAsync(scratch, st));
   CUDA_TRY(cudaGetLastError());
@@ -2645,6 +2677,7 @@ void ramp_model_destroy(RampModel* m) {
   if (m->d_scratch) cudaFree(m->d_scratch);
   if (m->pool) cudaMemPoolDestroy(m->pool);
   for (cudaStream_t st : m->streams) if (st) cudaStreamDestroy(st);
+  for (cudaEvent_t ev : m->events) if (ev) cudaEventDestroy(ev);
   if (m->h_pinned) cudaFreeHost(m->h_pinned);
   if (m->d_edge_stage) cudaFree(m->d_edge_stage);
   if (m->h_edge_stage) cudaFreeHost(m->h_edge_stage);
@@ -2755,6 +2788,7 @@ int ramp_check_batch_noalloc(const RampModel* m, const float* d_q, int64_t n, in
   if (int rc = noalloc_queue_for(m->device, &scratch)) return rc;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   CheckArgs a;
+  a.row_offset = 0;
   a.img = m->d_image; a.q = d_q; a.n = n; a.ld = ld; a.flags = flags;
   a.hit = d_hit; a.first_pair = d_first_pair; a.pair_mask = d_pair_mask;
   int nwarps; size_t smem;
@@ -2988,8 +3022,11 @@ void ramp_host_free(void* p) {
   if (p) cudaFreeHost(p);
 }
 
-// Host-buffer check, pipelined: the batch moves in chunks over two streams so that the H2D
-// copy of chunk k+1, the kernels of chunk k and the D2H copy of chunk k-1 overlap.  Buffers
+// Host-buffer check, pipelined.  The rows move to the device in chunks on two streams, so the
+// H2D copy of chunk k+1 runs under the tile kernel of chunk k.  The tile kernels of all chunks
+// of a section (up to 2^21 rows) feed ONE GJK queue; a third stream runs the queue kernel once
+// behind them and copies the section's results home -- a queue kernel per chunk would pay its
+// drain (warps finishing their last long items at low occupancy) every 2^18 rows.  Buffers
 // the caller already pinned (ramp_host_alloc / cudaHostAlloc / cudaHostRegister / torch
 // pin_memory) are used for DMA directly; pageable ones are staged through the model's pinned
 // buffers.  (Reading a pinned q in place from the kernels was measured too: 35-46 GB/s over
@@ -3003,78 +3040,111 @@ int ramp_check_host(const RampModel* m, const float* h_q, int64_t n, int32_t ld,
   CUDA_TRY(cudaSetDevice(m->device));
   std::lock_guard<std::mutex> lk(m->mu);
   const int mw = std::max(m->hdr.mask_words, 1);
-  const int64_t chunk = std::min<int64_t>(n, 1 << 18);
-  const size_t b_q = align16(sizeof(float) * chunk * ld), b_hit = align16(chunk), b_first = align16(sizeof(int32_t) * chunk),
-               b_mask = align16(sizeof(uint32_t) * chunk * mw);
-  const size_t per = b_q + b_hit + b_first + b_mask;
-  if (int rc = ensure_scratch(m, 2 * per)) return rc;
+  // A SECTION is what one queue kernel covers (up to kSliceRows rows); its rows arrive in CHUNKS.
+  const int64_t chunk = std::min<int64_t>(n, 1 << 18), section = std::min<int64_t>(n, kSliceRows);
+  CheckPlan P;
+  const bool tiled = n > kSmallRows;
+  if (tiled)
+    if (int rc = plan_check(m, ld, flags, n, &P)) return rc;
+  const bool queued = tiled && P.use_queue;
+  // device: two q chunks, then two sets of result arrays (one per section parity)
+  const size_t b_q = align16(sizeof(float) * chunk * ld), b_hit = align16(section), b_first = align16(sizeof(int32_t) * section),
+               b_mask = align16(sizeof(uint32_t) * section * mw);
+  const size_t b_out = b_hit + b_first + b_mask, total = 2 * b_q + 2 * b_out;
+  if (int rc = ensure_scratch(m, total)) return rc;
   const bool pin_q = is_pinned(h_q), pin_hit = is_pinned(h_hit);
   const bool pin_first = !h_first_pair || is_pinned(h_first_pair), pin_mask = !h_pair_mask || is_pinned(h_pair_mask);
   const bool staged = !(pin_q && pin_hit && pin_first && pin_mask);
-  if (staged && 2 * per > m->pinned_cap) {
+  if (staged && total > m->pinned_cap) {
     if (m->h_pinned) cudaFreeHost(m->h_pinned);
     m->h_pinned = nullptr; m->pinned_cap = 0;
-    const size_t cap = std::max<size_t>(2 * per, 1 << 16);
+    const size_t cap = std::max<size_t>(total, 1 << 16);
     if (cudaMallocHost(&m->h_pinned, cap) != cudaSuccess) return fail(RAMP_ERR_ALLOC, "cudaMallocHost(%zu) failed", cap);
     m->pinned_cap = cap;
   }
-  for (int k = 0; k < 2; ++k)
-    if (!m->streams[k]) CUDA_TRY(cudaStreamCreateWithFlags(&m->streams[k], cudaStreamNonBlocking));
+  for (auto& st : m->streams)
+    if (!st) CUDA_TRY(cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking));
+  for (auto& ev : m->events)
+    if (!ev) CUDA_TRY(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
+  cudaStream_t s_tail = m->streams[2];
+  cudaEvent_t ev_queue = m->events[0], ev_tiles[2] = {m->events[1], m->events[2]}, ev_out[2] = {m->events[3], m->events[4]};
   unsigned char* D = static_cast<unsigned char*>(m->d_scratch);
   unsigned char* H = static_cast<unsigned char*>(m->h_pinned);
-  // Chunk boundaries.  The kernels of chunk 0 cannot start before its copy has landed and
-  // nothing hides that copy, so chunk 0 is shorter (n/8, at least 2^16 rows: smaller chunks
-  // cost more in kernel tails than they save); the rest are full chunks.
-  std::vector<int64_t> start{0};
-  {
-    const int64_t first = std::min<int64_t>(chunk, std::max<int64_t>(1 << 16, (n / 8 + 31) & ~int64_t{31}));
-    if (first < n) start.push_back(first);
-    while (start.back() < n) start.push_back(std::min(n, start.back() + chunk));
-  }
-  const int64_t nchunks = static_cast<int64_t>(start.size()) - 1;
-  // results of a chunk that went through the pinned staging are copied out once its stream is done
-  auto drain = [&](int64_t k) {
-    const int b = static_cast<int>(k & 1);
-    const int64_t off = start[k], ns = start[k + 1] - off;
-    unsigned char* Hb = H + b * per;
-    if (!pin_hit) std::memcpy(h_hit + off, Hb + b_q, ns);
-    if (h_first_pair && !pin_first) std::memcpy(h_first_pair + off, Hb + b_q + b_hit, sizeof(int32_t) * ns);
-    if (h_pair_mask && !pin_mask) std::memcpy(h_pair_mask + off * mw, Hb + b_q + b_hit + b_first, sizeof(uint32_t) * ns * mw);
-  };
-  for (int64_t k = 0; k < nchunks; ++k) {
-    const int b = static_cast<int>(k & 1);
-    cudaStream_t st = m->streams[b];
-    const int64_t off = start[k], ns = start[k + 1] - off;
-    // Chunk k reuses the buffers of chunk k-2.  On the device the stream orders that by
-    // itself; only the host staging copies (pageable caller memory) make the host wait.
-    if (k >= 2 && staged) {
-      CUDA_TRY(cudaStreamSynchronize(st));
-      drain(k - 2);
+  int64_t k = 0;  // chunk counter over the whole call: picks the stream and the q buffer
+  int64_t nsec = 0;
+  for (int64_t s0 = 0; s0 < n; s0 += section, ++nsec) {
+    const int64_t s1 = std::min(n, s0 + section), rows = s1 - s0;
+    const int par = static_cast<int>(nsec & 1);
+    unsigned char* Dout = D + 2 * b_q + par * b_out;
+    uint8_t* d_hit = Dout;
+    int32_t* d_first = h_first_pair ? reinterpret_cast<int32_t*>(Dout + b_hit) : nullptr;
+    uint32_t* d_mask = h_pair_mask ? reinterpret_cast<uint32_t*>(Dout + b_hit + b_first) : nullptr;
+    // the result arrays of this parity were last copied out by section nsec - 2
+    if (nsec >= 2)
+      for (int i = 0; i < 2; ++i) CUDA_TRY(cudaStreamWaitEvent(m->streams[i], ev_out[par], 0));
+    unsigned char* qmem = nullptr;
+    GjkQueue gq{nullptr, nullptr, 0u, 0u};
+    if (queued) {
+      if (int rc = queue_alloc(m, rows, m->streams[0], &qmem, &gq)) return rc;
+      CUDA_TRY(cudaMemsetAsync(qmem, 0, 16, m->streams[0]));
+      CUDA_TRY(cudaEventRecord(ev_queue, m->streams[0]));
+      CUDA_TRY(cudaStreamWaitEvent(m->streams[1], ev_queue, 0));
     }
-    unsigned char* Db = D + b * per;
-    unsigned char* Hb = H + b * per;
-    const float* src = h_q + off * ld;
-    const float* d_q = reinterpret_cast<const float*>(Db);
-    if (!pin_q) { std::memcpy(Hb, src, sizeof(float) * ns * ld); src = reinterpret_cast<const float*>(Hb); }
-    CUDA_TRY(cudaMemcpyAsync(Db, src, sizeof(float) * ns * ld, cudaMemcpyHostToDevice, st));
-    uint8_t* d_hit = Db + b_q;
-    int32_t* d_first = reinterpret_cast<int32_t*>(Db + b_q + b_hit);
-    uint32_t* d_mask = reinterpret_cast<uint32_t*>(Db + b_q + b_hit + b_first);
-    if (int rc = launch_check(m, d_q, ns, ld, flags, d_hit, h_first_pair ? d_first : nullptr,
-                              h_pair_mask ? d_mask : nullptr, st))
-      return rc;
-    CUDA_TRY(cudaMemcpyAsync(pin_hit ? h_hit + off : Hb + b_q, d_hit, ns, cudaMemcpyDeviceToHost, st));
+    // Chunk boundaries.  The kernels of the very first chunk cannot start before its copy has
+    // landed and nothing hides that copy, so it is shorter (n/8, at least 2^16 rows: smaller
+    // chunks cost more in kernel tails than they save); the rest are full chunks.
+    std::vector<int64_t> start{s0};
+    if (s0 == 0) {
+      const int64_t first = std::min<int64_t>(chunk, std::max<int64_t>(1 << 16, (n / 8 + 31) & ~int64_t{31}));
+      if (first < rows) start.push_back(first);
+    }
+    while (start.back() < s1) start.push_back(std::min(s1, start.back() + chunk));
+    for (size_t c = 0; c + 1 < start.size(); ++c, ++k) {
+      const int b = static_cast<int>(k & 1);
+      cudaStream_t st = m->streams[b];
+      const int64_t off = start[c], ns = start[c + 1] - off, rel = off - s0;
+      float* d_q = reinterpret_cast<float*>(D + b * b_q);
+      const float* src = h_q + off * ld;
+      if (!pin_q) {  // pageable q: through the pinned staging buffer the copy of chunk k - 2 read
+        if (k >= 2) CUDA_TRY(cudaStreamSynchronize(st));
+        std::memcpy(H + b * b_q, src, sizeof(float) * ns * ld);
+        src = reinterpret_cast<const float*>(H + b * b_q);
+      }
+      CUDA_TRY(cudaMemcpyAsync(d_q, src, sizeof(float) * ns * ld, cudaMemcpyHostToDevice, st));
+      uint8_t* c_hit = d_hit + rel;
+      int32_t* c_first = d_first ? d_first + rel : nullptr;
+      uint32_t* c_mask = d_mask ? d_mask + rel * mw : nullptr;
+      if (tiled) launch_tiles(m, P, d_q, ns, static_cast<uint32_t>(rel), c_hit, c_first, c_mask, gq, st);
+      else if (int rc = launch_check(m, d_q, ns, ld, flags, c_hit, c_first, c_mask, st)) return rc;
+    }
+    // tail of the section, behind the tile kernels of both chunk streams: ONE queue kernel for
+    // all its chunks, then the results go home
+    for (int i = 0; i < 2; ++i) {
+      CUDA_TRY(cudaEventRecord(ev_tiles[i], m->streams[i]));
+      CUDA_TRY(cudaStreamWaitEvent(s_tail, ev_tiles[i], 0));
+    }
+    if (queued) {
+      launch_queue(m, P, gq, d_hit, d_first, d_mask, s_tail);
+      CUDA_TRY(cudaFreeAsync(qmem, s_tail));
+    }
+    unsigned char* Hout = staged ? H + 2 * b_q + par * b_out : nullptr;
+    CUDA_TRY(cudaMemcpyAsync(pin_hit ? h_hit + s0 : Hout, d_hit, rows, cudaMemcpyDeviceToHost, s_tail));
     if (h_first_pair)
-      CUDA_TRY(cudaMemcpyAsync(pin_first ? reinterpret_cast<unsigned char*>(h_first_pair + off) : Hb + b_q + b_hit, d_first,
-                               sizeof(int32_t) * ns, cudaMemcpyDeviceToHost, st));
+      CUDA_TRY(cudaMemcpyAsync(pin_first ? reinterpret_cast<unsigned char*>(h_first_pair + s0) : Hout + b_hit, d_first,
+                               sizeof(int32_t) * rows, cudaMemcpyDeviceToHost, s_tail));
     if (h_pair_mask)
-      CUDA_TRY(cudaMemcpyAsync(pin_mask ? reinterpret_cast<unsigned char*>(h_pair_mask + off * mw) : Hb + b_q + b_hit + b_first,
-                               d_mask, sizeof(uint32_t) * ns * mw, cudaMemcpyDeviceToHost, st));
+      CUDA_TRY(cudaMemcpyAsync(pin_mask ? reinterpret_cast<unsigned char*>(h_pair_mask + s0 * mw) : Hout + b_hit + b_first, d_mask,
+                               sizeof(uint32_t) * rows * mw, cudaMemcpyDeviceToHost, s_tail));
+    CUDA_TRY(cudaEventRecord(ev_out[par], s_tail));
+    if (staged) {  // pageable results: wait and copy them out of the staging buffer
+      CUDA_TRY(cudaStreamSynchronize(s_tail));
+      if (!pin_hit) std::memcpy(h_hit + s0, Hout, rows);
+      if (h_first_pair && !pin_first) std::memcpy(h_first_pair + s0, Hout + b_hit, sizeof(int32_t) * rows);
+      if (h_pair_mask && !pin_mask) std::memcpy(h_pair_mask + s0 * mw, Hout + b_hit + b_first, sizeof(uint32_t) * rows * mw);
+    }
   }
-  for (int64_t k = std::max<int64_t>(0, nchunks - 2); k < nchunks; ++k) {
-    CUDA_TRY(cudaStreamSynchronize(m->streams[k & 1]));
-    if (staged) drain(k);
-  }
+  CUDA_TRY(cudaStreamSynchronize(s_tail));
+  CUDA_TRY(cudaGetLastError());
   return RAMP_OK;
 }
 

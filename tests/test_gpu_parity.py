@@ -426,3 +426,32 @@ def workloads_sample(model, n, seed, bound):
     from ramp_b200 import workloads
 
     return workloads.sample_q(model, n, seed=seed, position_bound=bound)
+
+
+def test_host_buffer_call_sections_and_staging(built):
+    """ramp_check_host at sizes that span several chunks (2^18 rows) and two sections (2^21 rows:
+    one GJK queue and one queue kernel each), with page-locked and with pageable buffers, flags /
+    first pair / pair mask: identical to the device-buffer call."""
+    from ramp_b200 import workloads
+    from ramp_b200.engine import pinned_empty
+
+    rm, _ = _setup("ur5e/configs", "obstacles")
+    nq = rm.model.nq
+    n = (1 << 21) + 300001
+    q = workloads.sample_q(rm.model, n, seed=21)
+    ref = rm.gpu.check(torch.from_numpy(q).cuda(), first_pair=True)
+    ref_hit, ref_first = ref["hit"].cpu().numpy(), ref["first_pair"].cpu().numpy()
+    qh = pinned_empty((n, nq), np.float32)
+    qh[:] = q[:, :nq]
+    hh = pinned_empty((n,), np.uint8)
+    hh[:] = 9
+    rm.gpu.check_host_into(qh, hh)
+    assert np.array_equal(hh.astype(bool), ref_hit)
+    # pageable numpy arrays, all three outputs (a smaller batch: the pair mask is n x pairs)
+    m = 600000
+    got = rm.gpu.check_host(q[:m, :nq].copy(), first_pair=True, pair_mask=True)
+    refm = rm.gpu.check(torch.from_numpy(q[:m]).cuda(), first_pair=True, pair_mask=True)
+    assert np.array_equal(got["hit"], ref_hit[:m])
+    assert np.array_equal(got["first_pair"], refm["first_pair"].cpu().numpy())
+    assert np.array_equal(got["pair_mask"], refm["pair_mask"].cpu().numpy())
+    assert np.array_equal(refm["first_pair"].cpu().numpy(), ref_first[:m])
