@@ -133,6 +133,17 @@ def host_threads() -> int:
         return os.cpu_count() or 1
 
 
+def reference_wheels() -> str:
+    """BASELINE.md section 3 probe: are Pinocchio / coal / OMPL (the reference's own arithmetic)
+    importable on this box?  They are not vendored; when absent the CPU arm is the oracle port."""
+    import importlib.util
+
+    found = [m for m in ("pinocchio", "hppfcl", "coal", "ompl") if importlib.util.find_spec(m) is not None]
+    ref = os.path.isdir(os.path.join(os.path.dirname(os.path.abspath(__file__)), "baseline", "_ref"))
+    return ("importable: " + ",".join(found) if found else "pinocchio/hppfcl/coal/ompl not importable") + (
+        "; baseline/_ref present" if ref else "; no baseline/_ref") + " -> CPU arm = oracle port"
+
+
 def cpu_baseline(desc, q_host, target_seconds: float = 12.0) -> dict:
     """The CPU oracle (boolean, stop at first collision, all host threads) on a bounded sample."""
     from oracle import oracle
@@ -146,7 +157,7 @@ def cpu_baseline(desc, q_host, target_seconds: float = 12.0) -> dict:
     t0 = time.perf_counter()
     oracle.check_f32(desc, q_host[:n], cores)
     dt = time.perf_counter() - t0
-    return {"value": n / dt, "unit": UNIT, "cores": cores, "kind": "port",
+    return {"value": n / dt, "unit": UNIT, "cores": cores, "kind": "port", "reference_wheels": reference_wheels(),
             "sample": f"first {n} configurations of the step's batch, boolean stop-at-first, OpenMP {cores} threads, {dt:.1f} s"}
 
 
@@ -180,7 +191,8 @@ def run_reference(args, wl, rm, desc) -> None:
         "vs_baseline": None, "dtype": "f64", "data": "synthetic",
         "config": {"workload": wl.name, "robot": wl.robot, "scene": wl.scene, "note": wl.note,
                    "model": "stand-in" if "stand-in" in wl.note else "in-tree"},
-        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample,
+                         "reference_wheels": reference_wheels()},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "reference_note": "Pinocchio 3.7.0 / coal 3.0.1 are not installable offline; this is the repo's FP64 "
                           "restatement of that path (oracle/ramp_oracle.c)",
