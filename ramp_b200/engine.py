@@ -232,6 +232,14 @@ class GpuModel:
                                             sel, n_sel, out.data_ptr(), _stream_ptr(self.device)), "ramp_distance_batch")
         return out
 
+    def clearance(self, q, *, actuated: bool = False) -> torch.Tensor:
+        """Smallest signed distance over the enabled pairs, float32[N] (+inf without pairs): the
+        quantity the reference's PathClearanceObjective integrates (src/ramp/motion_planner.py:165-206)."""
+        d = self.distance(q, actuated=actuated)
+        if d.shape[1] == 0:
+            return torch.full((d.shape[0],), float("inf"), dtype=torch.float32, device=self.device)
+        return d.min(dim=1).values
+
     def check_raw(self, q: torch.Tensor, hit: torch.Tensor, flags: int = 0) -> None:
         """Zero-overhead variant for benchmarks: caller-owned contiguous tensors, no allocations."""
         _check(self.lib.ramp_check_batch(self.handle, q.data_ptr(), q.shape[0], q.shape[1], flags, hit.data_ptr(),

@@ -202,6 +202,14 @@ class MotionPlanner:
         res = self.validator.check_edges(np.asarray(path[:-1], dtype=np.float32), np.asarray(path[1:], dtype=np.float32))
         return bool(res["valid"].all().item())
 
+    def path_clearance(self, path: list) -> np.ndarray:
+        """Clearance (smallest signed distance over the enabled pairs) at every interpolated state
+        of the path, one batched call -- the state cost of the reference's PathClearanceObjective
+        (src/ramp/motion_planner.py:165-206, dead code there because it is never installed)."""
+        self._sync_gpu()
+        states = np.asarray(self._interpolate_path(path), dtype=np.float32)
+        return self._robot_model.gpu.clearance(states, actuated=True).cpu().numpy()
+
     def plan(self, start_state: RobotState, group_goal_qpos, timeout: float = 1.0,
              planner: str | None = None) -> list[RobotState] | None:
         """reference :509-610.  ``planner`` accepts None / "RRTConnect" (the built-in)."""

@@ -146,3 +146,23 @@ def test_projection_batch_matches_frame_pose(built):
     for i in (0, 17, 63):
         rs.set_group_qpos("arm", states[i])
         assert np.allclose(got[i], rs.get_frame_pose("panda_hand_tcp").translation, atol=2e-5)
+
+
+def test_path_clearance_matches_oracle(built):
+    """clearance along a planned path (state cost of the reference's
+    PathClearanceObjective) = smallest signed pair distance per interpolated state, one batched
+    call; against the oracle's min_dist."""
+    from ramp_b200 import MotionPlanner, RobotState, load_robot_model, workloads
+
+    rm = load_robot_model("zoo::rrr/configs")
+    start = RobotState.from_named_state(rm, "arm", "home")
+    start.add_object(workloads.reference_capsule())
+    planner = MotionPlanner(rm, "arm")
+    path = planner.plan(start, [0.0, 2.0, 1.4], timeout=5.0)
+    assert path is not None
+    states = [planner.as_state(s) for s in path]
+    clr = planner.path_clearance(states)
+    res, _ = _oracle_path_valid(rm, planner, path)
+    assert len(clr) >= len(path) and clr.min() > -1e-4
+    # the planned path is already interpolated, so the states coincide with the waypoints
+    assert np.allclose(np.sort(clr)[:3], np.sort(res["min_dist"])[:3], atol=5e-5)
