@@ -937,6 +937,37 @@ __global__ void __launch_bounds__(512, 1) check_kernel(const __grid_constant__ C
 }
 
 
+// Support scan of the few items left in a draining warp, shared between lanes: the k-th active
+// lane owns item k; lanes [k * kG, (k + 1) * kG) each scan 1/kG of its vertex list and a
+// butterfly picks the best.  Closed-form shapes (no vertex list) are left to their owner.
+template <int kG>
+__device__ __forceinline__ V3 coop_support(unsigned am, bool active, const GjkShape& S, V3 d, const float4* verts0) {
+  const unsigned FULL = 0xffffffffu;
+  const int l = threadIdx.x & 31;
+  const int grp = l / kG, sub = l % kG;
+  const int owner = __fns(am, 0, grp + 1) & 31;  // lane of the grp-th active item (any lane if there is none)
+  const bool has = grp < __popc(am);
+  const bool listed = S.type != SH_CYLINDER && S.type != SH_ELLIPSOID;
+  const int o_cnt = __shfl_sync(FULL, active && listed ? S.vcnt : 0, owner);
+  const int o_off = __shfl_sync(FULL, static_cast<int>(S.verts - verts0), owner);
+  const V3 od = mk(__shfl_sync(FULL, d.x, owner), __shfl_sync(FULL, d.y, owner), __shfl_sync(FULL, d.z, owner));
+  const int per = (o_cnt + kG - 1) / kG;
+  const int begin = sub * per, cnt = has ? max(min(per, o_cnt - begin), 0) : 0;
+  V3 r = support(SH_CONVEX, 0.f, 0.f, 0.f, verts0 + o_off + begin, cnt, od);
+  float val = cnt > 0 ? dot(r, od) : -3.0e38f;
+#pragma unroll
+  for (int m = 1; m < kG; m <<= 1) {
+    const float ov = __shfl_xor_sync(FULL, val, m);
+    const V3 orr = mk(__shfl_xor_sync(FULL, r.x, m), __shfl_xor_sync(FULL, r.y, m), __shfl_xor_sync(FULL, r.z, m));
+    if (ov > val) { val = ov; r = orr; }
+  }
+  // back to the owners: active lane with rank k reads the result of group k
+  const int src = (__popc(am & ((1u << l) - 1)) * kG) & 31;
+  V3 res = mk(__shfl_sync(FULL, r.x, src), __shfl_sync(FULL, r.y, src), __shfl_sync(FULL, r.z, src));
+  if (active && !listed) res = support(S.type, S.p0, S.p1, S.p2, S.verts, S.vcnt, d);
+  return res;
+}
+
 // ------------------------------------------------- kernel: validity, one warp per configuration
 // Latency mode for small batches (a few thousand configurations, the states of one planner
 // edge): the tile kernel above needs 32 configurations per warp and tens of thousands of them
@@ -1052,7 +1083,11 @@ __device__ __forceinline__ int check_one_config(const SmallWarp& w, bool stop_at
 #pragma unroll 1
   for (int base = 0; base < h->n_pairs; base += 32) {
     const int p = base + l;
-    bool hit = false;
+    bool hit = false, need_gjk = false;
+    GjkLane g;
+    GjkShape SA, SB;
+    SA.type = SB.type = 0; SA.vcnt = SB.vcnt = 0; SA.p0 = SA.p1 = SA.p2 = SB.p0 = SB.p1 = SB.p2 = 0.f; SA.verts = SB.verts = w.t.verts;
+    g.s.n = 0; g.it = 0; g.vv = 1.f; g.rsum = 0.f; g.lower = 0.f; g.v = mk(1.f, 0.f, 0.f); g.rel = xf_identity();
     DPair pr;
     pr.cls = kClsInactive; pr.orig = 0;
     if (p < h->n_pairs) pr = w.t.pairs[p];
@@ -1074,18 +1109,33 @@ __device__ __forceinline__ int check_one_config(const SmallWarp& w, bool stop_at
               const float rin = ga->r_in + gb->r_in - pr.slack;
               if (rin > 0.f && dot(v0, v0) < rin * rin) hit = true;
               else if (obb_overlap(mk(ga->hx, ga->hy, ga->hz), mk(gb->hx, gb->hy, gb->hz), rel, pr.slack)) {
-                GjkLane g;
                 gjk_init(g, rel, swept_radius(ga) + swept_radius(gb), v0);
-                const GjkShape SA = load_shape(ga, w.t.verts), SB = load_shape(gb, w.t.verts);
-                float dist;
-                int st;
-                do { st = gjk_step(g, SA, SB, false, dist); } while (st == GJK_CONTINUE);
-                hit = st == GJK_HIT;
+                SA = load_shape(ga, w.t.verts);
+                SB = load_shape(gb, w.t.verts);
+                need_gjk = true;
               }
             }
           }
         }
       }
+    }
+    // GJK for the few pairs that got this far, one after the other with the WHOLE warp on each:
+    // every lane scans two vertices of a 64-vertex hull and a butterfly picks the support
+    // point, the owner lane runs the simplex update (this kernel is about latency, and a
+    // configuration rarely has more than one or two such pairs).
+    for (unsigned gm = __ballot_sync(FULL, need_gjk); gm; gm &= gm - 1) {
+      const int owner = __ffs(gm) - 1;
+      const bool mine = l == owner;
+      int st = GJK_CONTINUE;
+      while (st == GJK_CONTINUE) {
+        const V3 sa = coop_support<32>(1u << owner, mine, SA, -g.v, w.t.verts);
+        const V3 sb = coop_support<32>(1u << owner, mine, SB, rot_t(g.rel, g.v), w.t.verts);
+        float dist;
+        if (mine) st = gjk_advance(g, sa, sb, false, dist);
+        st = __shfl_sync(FULL, st, owner);
+        if (stop_at_first && __any_sync(FULL, hit)) st = GJK_MISS;  // settled already by another pair
+      }
+      if (mine) hit = hit || st == GJK_HIT;
     }
     if (hit) {
       first = min(first, static_cast<int>(pr.orig));
@@ -1164,37 +1214,6 @@ constexpr int kFetchAttempts = 4;
 #define RAMP_GJK_CTAS 2
 #endif
 constexpr int kGjkCtasPerSm = RAMP_GJK_CTAS;
-
-// Support scan of the few items left in a draining warp, shared between lanes: the k-th active
-// lane owns item k; lanes [k * kG, (k + 1) * kG) each scan 1/kG of its vertex list and a
-// butterfly picks the best.  Closed-form shapes (no vertex list) are left to their owner.
-template <int kG>
-__device__ __forceinline__ V3 coop_support(unsigned am, bool active, const GjkShape& S, V3 d, const float4* verts0) {
-  const unsigned FULL = 0xffffffffu;
-  const int l = threadIdx.x & 31;
-  const int grp = l / kG, sub = l % kG;
-  const int owner = __fns(am, 0, grp + 1) & 31;  // lane of the grp-th active item (any lane if there is none)
-  const bool has = grp < __popc(am);
-  const bool listed = S.type != SH_CYLINDER && S.type != SH_ELLIPSOID;
-  const int o_cnt = __shfl_sync(FULL, active && listed ? S.vcnt : 0, owner);
-  const int o_off = __shfl_sync(FULL, static_cast<int>(S.verts - verts0), owner);
-  const V3 od = mk(__shfl_sync(FULL, d.x, owner), __shfl_sync(FULL, d.y, owner), __shfl_sync(FULL, d.z, owner));
-  const int per = (o_cnt + kG - 1) / kG;
-  const int begin = sub * per, cnt = has ? max(min(per, o_cnt - begin), 0) : 0;
-  V3 r = support(SH_CONVEX, 0.f, 0.f, 0.f, verts0 + o_off + begin, cnt, od);
-  float val = cnt > 0 ? dot(r, od) : -3.0e38f;
-#pragma unroll
-  for (int m = 1; m < kG; m <<= 1) {
-    const float ov = __shfl_xor_sync(FULL, val, m);
-    const V3 orr = mk(__shfl_xor_sync(FULL, r.x, m), __shfl_xor_sync(FULL, r.y, m), __shfl_xor_sync(FULL, r.z, m));
-    if (ov > val) { val = ov; r = orr; }
-  }
-  // back to the owners: active lane with rank k reads the result of group k
-  const int src = (__popc(am & ((1u << l) - 1)) * kG) & 31;
-  V3 res = mk(__shfl_sync(FULL, r.x, src), __shfl_sync(FULL, r.y, src), __shfl_sync(FULL, r.z, src));
-  if (active && !listed) res = support(S.type, S.p0, S.p1, S.p2, S.verts, S.vcnt, d);
-  return res;
-}
 
 #ifdef RAMP_STATS
 __device__ unsigned long long g_stats[64];  // [0] items [1] iterations [2] hits [3] skipped, [8+it] histogram
