@@ -955,6 +955,17 @@ __device__ __forceinline__ V3 coop_support(unsigned am, bool active, const GjkSh
   const int begin = sub * per, cnt = has ? max(min(per, o_cnt - begin), 0) : 0;
   V3 r = support(SH_CONVEX, 0.f, 0.f, 0.f, verts0 + o_off + begin, cnt, od);
   float val = cnt > 0 ? dot(r, od) : -3.0e38f;
+  if (kG == 32) {
+    // whole warp on one item: one integer max-reduction on an order-preserving key, then the
+    // winning lane hands out its vertex (5 dependent steps instead of a 20-shuffle butterfly)
+    int key = __float_as_int(val);
+    key ^= (key >> 31) & 0x7fffffff;
+    const int best = __reduce_max_sync(FULL, key);
+    const int win = __ffs(__ballot_sync(FULL, key == best)) - 1;
+    V3 res = mk(__shfl_sync(FULL, r.x, win), __shfl_sync(FULL, r.y, win), __shfl_sync(FULL, r.z, win));
+    if (active && !listed) res = support(S.type, S.p0, S.p1, S.p2, S.verts, S.vcnt, d);
+    return res;
+  }
 #pragma unroll
   for (int m = 1; m < kG; m <<= 1) {
     const float ov = __shfl_xor_sync(FULL, val, m);
@@ -1157,7 +1168,7 @@ __device__ __forceinline__ SmallWarp make_small_warp(const Tables& t, float* sla
   return w;
 }
 
-__global__ void __launch_bounds__(128) check_warp_kernel(const __grid_constant__ SmallArgs a) {
+__global__ void __launch_bounds__(128, 4) check_warp_kernel(const __grid_constant__ SmallArgs a) {
   uint64_t* mbar = reinterpret_cast<uint64_t*>(g_smem);
   unsigned char* tbl = g_smem + 16;
   stage_tables(tbl, a.img, a.table_bytes, mbar);
