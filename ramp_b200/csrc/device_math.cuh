@@ -527,7 +527,11 @@ __device__ __noinline__ bool epa_enclose(const GjkShape& A, const GjkShape& B, c
   return true;
 }
 
-__device__ __noinline__ float epa_depth(const GjkShape& A, const GjkShape& B, const Xf& rel, Simplex s) {
+// `restart`: when given and the starting tetrahedron does NOT hold the origin (GJK's exact mode
+// can report a false "enclosed" on a sliver tetrahedron of two shapes a few mm apart), nothing
+// is expanded: *restart receives the point of the offending face plane nearest to the origin --
+// a good place to start GJK again from -- and the result is -1.
+__device__ __noinline__ float epa_depth(const GjkShape& A, const GjkShape& B, const Xf& rel, Simplex s, V3* restart) {
   V3 vt[kEpaMaxV];
   EpaFace fc[kEpaMaxF];
   int nv = 0, nf = 0;
@@ -539,6 +543,12 @@ __device__ __noinline__ float epa_depth(const GjkShape& A, const GjkShape& B, co
     const V3 n = cross(vt[b] - vt[a], vt[c] - vt[a]);
     if (dot(n, vt[opp] - vt[a]) > 0.f) { const int t = b; b = c; c = t; }
     if (!epa_face(vt, a, b, c, fc[nf++])) return 0.f;
+  }
+  if (restart) {
+    int worst = 0;
+    for (int i = 1; i < 4; ++i)
+      if (fc[i].d < fc[worst].d) worst = i;
+    if (fc[worst].d < -1e-6f) { *restart = fc[worst].n * fc[worst].d; return -1.f; }
   }
   float best = 0.f;
   for (int it = 0; it < kEpaIters; ++it) {
@@ -591,12 +601,23 @@ __device__ __noinline__ float epa_depth(const GjkShape& A, const GjkShape& B, co
 // Signed distance of two shapes through GJK (+ EPA when the cores overlap).
 __device__ __forceinline__ float gjk_signed_distance(const GjkShape& A, const GjkShape& B, const Xf& rel, float rsum) {
   GjkLane g;
-  gjk_init(g, rel, rsum, -trans(rel));
-  float dist = 0.f;
-  int st = GJK_CONTINUE;
-  while (st == GJK_CONTINUE) st = gjk_step(g, A, B, true, dist);
-  if (st == GJK_MISS || g.vv > 0.f) return dist;  // cores apart: |v| - radii (negative if the sweeps overlap)
-  return -epa_depth(A, B, rel, g.s) - rsum;
+  V3 v0 = -trans(rel);
+#pragma unroll 1
+  for (int attempt = 0;; ++attempt) {
+    gjk_init(g, rel, rsum, v0);
+    float dist = 0.f;
+    int st = GJK_CONTINUE;
+    while (st == GJK_CONTINUE) st = gjk_step(g, A, B, true, dist);
+    if (st == GJK_MISS || g.vv > 0.f) return dist;  // cores apart: |v| - radii (negative if the sweeps overlap)
+    // "enclosed": believed only if the simplex really holds the origin; else start over from
+    // the face the origin lies beyond (twice at most, then take EPA's walk to that face)
+    V3 from;
+    const bool last = attempt >= 2;
+    const float depth = epa_depth(A, B, rel, g.s, last ? nullptr : &from);
+    // (on the last attempt a negative "depth" is the offset of the face EPA walked to)
+    if (last || depth != -1.f) return -depth - rsum;
+    v0 = from;
+  }
 }
 
 }  // namespace ramp

@@ -955,7 +955,7 @@ __device__ __forceinline__ V3 coop_support(unsigned am, bool active, const GjkSh
   const int begin = sub * per, cnt = has ? max(min(per, o_cnt - begin), 0) : 0;
   V3 r = support(SH_CONVEX, 0.f, 0.f, 0.f, verts0 + o_off + begin, cnt, od);
   float val = cnt > 0 ? dot(r, od) : -3.0e38f;
-  if (kG == 32) {
+  if constexpr (kG == 32) {
     // whole warp on one item: one integer max-reduction on an order-preserving key, then the
     // winning lane hands out its vertex (5 dependent steps instead of a 20-shuffle butterfly)
     int key = __float_as_int(val);
@@ -965,18 +965,19 @@ __device__ __forceinline__ V3 coop_support(unsigned am, bool active, const GjkSh
     V3 res = mk(__shfl_sync(FULL, r.x, win), __shfl_sync(FULL, r.y, win), __shfl_sync(FULL, r.z, win));
     if (active && !listed) res = support(S.type, S.p0, S.p1, S.p2, S.verts, S.vcnt, d);
     return res;
-  }
+  } else {
 #pragma unroll
-  for (int m = 1; m < kG; m <<= 1) {
-    const float ov = __shfl_xor_sync(FULL, val, m);
-    const V3 orr = mk(__shfl_xor_sync(FULL, r.x, m), __shfl_xor_sync(FULL, r.y, m), __shfl_xor_sync(FULL, r.z, m));
-    if (ov > val) { val = ov; r = orr; }
+    for (int m = 1; m < kG; m <<= 1) {
+      const float ov = __shfl_xor_sync(FULL, val, m);
+      const V3 orr = mk(__shfl_xor_sync(FULL, r.x, m), __shfl_xor_sync(FULL, r.y, m), __shfl_xor_sync(FULL, r.z, m));
+      if (ov > val) { val = ov; r = orr; }
+    }
+    // back to the owners: active lane with rank k reads the result of group k
+    const int src = (__popc(am & ((1u << l) - 1)) * kG) & 31;
+    V3 res = mk(__shfl_sync(FULL, r.x, src), __shfl_sync(FULL, r.y, src), __shfl_sync(FULL, r.z, src));
+    if (active && !listed) res = support(S.type, S.p0, S.p1, S.p2, S.verts, S.vcnt, d);
+    return res;
   }
-  // back to the owners: active lane with rank k reads the result of group k
-  const int src = (__popc(am & ((1u << l) - 1)) * kG) & 31;
-  V3 res = mk(__shfl_sync(FULL, r.x, src), __shfl_sync(FULL, r.y, src), __shfl_sync(FULL, r.z, src));
-  if (active && !listed) res = support(S.type, S.p0, S.p1, S.p2, S.verts, S.vcnt, d);
-  return res;
 }
 
 // ------------------------------------------------- kernel: validity, one warp per configuration
