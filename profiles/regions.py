@@ -14,21 +14,22 @@ for r in rows:
         cur["hdr"] = r
     elif cur and cur["hdr"] and not (len(r) >= 2 and r[0] == "Function Name"):
         cur["rows"].append(r)
-# region boundaries: marker comments in the source
-src = open("ramp_b200/csrc/ramp_b200.cu").read().splitlines()
-marks = [("rows / expand_q", "// ---- coalesced load of a"), ("fk", "// Geometry placements are kept as 9 floats"),
-         ("narrow: helpers", "// ---- narrow phase over the pair list"), ("stage 1", "// ---- stage 1: bounding spheres"),
+# region boundaries: marker comments inside narrow_phase.cuh; the other files are one region each
+src = open("ramp_b200/csrc/narrow_phase.cuh").read().splitlines()
+marks = [("narrow: helpers", "// ---- narrow phase over the pair list"), ("stage 1", "// ---- stage 1: bounding spheres"),
          ("stage 1.5", "// ---- stage 1.5"), ("stage 2", "// ---- stage 2"), ("stage 3 (overflow)", "// ---- stage 3"),
-         ("kernel body", "__device__ __forceinline__ void reset_results"), ("after", "// ------------------------------------------------- kernel: validity, one warp")]
+         ("kernel body", "__device__ __forceinline__ void reset_results")]
 bounds = []
 for name, m in marks:
     ln = next(i + 1 for i, t in enumerate(src) if m in t)
     bounds.append((ln, name))
 def region(ln):
-    name = "prologue"
+    name = "narrow: helpers"
     for b, n in bounds:
         if ln >= b: name = n
     return name
+tile_src = open("ramp_b200/csrc/tile.cuh").read().splitlines()
+fk_line = next(i + 1 for i, t in enumerate(tile_src) if "// Geometry placements are kept as 9 floats" in t)
 dm = [(0, "dm: xf / vectors"), (100, "dm: sincos / joints"), (162, "dm: support"), (208, "dm: closed forms / seg-seg"), (262, "dm: obb"), (295, "dm: simplex / gjk")]
 inst, samp = collections.Counter(), collections.Counter()
 num = lambda x: float(x) if x.replace(".", "", 1).isdigit() else 0.0
@@ -38,7 +39,8 @@ for s in sections:
     for r in s["rows"]:
         if not r[0].isdigit(): continue
         ln = int(r[0])
-        if fn == "ramp_b200.cu": name = region(ln)
+        if fn == "narrow_phase.cuh": name = region(ln)
+        elif fn == "tile.cuh": name = "fk" if ln >= fk_line else "rows / expand_q / tables"
         elif fn == "device_math.cuh": name = [n for b, n in dm if ln >= b][-1]
         else: name = fn
         inst[name] += num(r[iI]); samp[name] += num(r[iS])

@@ -1,4 +1,8 @@
-// ramp_b200.cu -- sm_100a kernels and the C ABI of libramp_b200.so (include/ramp_b200.h).
+// ramp_b200.cu -- the one translation unit of libramp_b200.so (include/ramp_b200.h): this file
+// holds the host side (model packing, launch logic, the C ABI); the sm_100a device code lives in
+// the headers it includes: device_math.cuh (SE(3), shapes, closed forms, GJK / EPA), tile.cuh
+// (tables, slabs, row loads, FK), narrow_phase.cuh (check_kernel), small_batch.cuh
+// (check_warp_kernel), gjk_queue.cuh, fk_distance.cuh, edges.cuh.
 //
 // Execution model (DESIGN.md has the full account):
 //   * one persistent CTA per SM; the packed model image is staged into shared memory once
@@ -33,1752 +37,15 @@
 #include "device_math.cuh"
 #include "model_image.h"
 
+// device code, in dependency order
+#include "tile.cuh"
+#include "narrow_phase.cuh"
+#include "small_batch.cuh"
+#include "gjk_queue.cuh"
+#include "fk_distance.cuh"
+#include "edges.cuh"
+
 namespace ramp {
-
-// =============================================================================== device
-struct Tables {
-  const ImgHeader* h;
-  const DJoint* joints;
-  const DGeom* geoms;
-  const DPair* pairs;
-  const float4* verts;
-  const float* stat;  // [n_static][12]: x axis, z axis, translation, y axis
-  const int32_t* dyn; // slot -> geometry index
-  const int32_t* act;
-  const DMimic* mimic;
-  const int32_t* cont;
-  const float* refq;
-  const int32_t* plan;  // FK plans for teams of warps (see build_image)
-};
-
-__device__ __forceinline__ Tables make_tables(const unsigned char* base) {
-  Tables t;
-  t.h = reinterpret_cast<const ImgHeader*>(base);
-  t.joints = reinterpret_cast<const DJoint*>(base + t.h->off_joints);
-  t.geoms = reinterpret_cast<const DGeom*>(base + t.h->off_geoms);
-  t.pairs = reinterpret_cast<const DPair*>(base + t.h->off_pairs);
-  t.verts = reinterpret_cast<const float4*>(base + t.h->off_verts);
-  t.stat = reinterpret_cast<const float*>(base + t.h->off_static);
-  t.dyn = reinterpret_cast<const int32_t*>(base + t.h->off_dyn);
-  t.act = reinterpret_cast<const int32_t*>(base + t.h->off_act);
-  t.mimic = reinterpret_cast<const DMimic*>(base + t.h->off_mimic);
-  t.cont = reinterpret_cast<const int32_t*>(base + t.h->off_cont);
-  t.refq = reinterpret_cast<const float*>(base + t.h->off_refq);
-  t.plan = reinterpret_cast<const int32_t*>(base + t.h->off_plan);
-  return t;
-}
-
-extern __shared__ __align__(128) unsigned char g_smem[];
-
-// Per-warp shared-memory slab (offsets in 4-byte words from the slab base).
-struct SlabLayout {
-  int32_t words;      // slab size
-  int32_t off_q;      // [nq][32]   Pinocchio q, slot-major
-  int32_t off_act;    // [n_cols][32] raw actuated input
-  int32_t off_geom;   // [n_dyn][12][32] geometry placements
-  int32_t off_save;   // [n_save][12][32] transforms of branching joints
-  int32_t off_queue;  // uint16[kQueueCap]
-  int32_t off_mask;   // uint32[mask_words][32]
-  int32_t off_first;  // int32[32] first colliding pair per configuration
-  int32_t off_stage;  // [32][stage_stride] output staging of the FK kernels
-  int32_t stage_stride;
-  int32_t table_bytes;  // image size rounded up to 16
-  int32_t team;         // warps sharing one slab (1, 2 or 4): they split the pair list of a tile
-  int32_t chunk_pairs;  // pairs per queue round of one warp
-  int32_t queue_words;  // per-warp queue size
-  int32_t raw_cols;     // validity kernels: widest input row (floats) the TMA row prefetch takes; 0 = off
-};
-
-__device__ __forceinline__ int64_t imin64(int64_t a, int64_t b) { return a < b ? a : b; }
-
-// ---- TMA bulk copy of the model image into shared memory
-__device__ __forceinline__ uint32_t smem_u32(const void* p) { return static_cast<uint32_t>(__cvta_generic_to_shared(p)); }
-
-__device__ __forceinline__ void stage_tables(unsigned char* dst, const unsigned char* __restrict__ src, int bytes,
-                                             uint64_t* mbar) {
-  const uint32_t bar = smem_u32(mbar);
-  if (threadIdx.x == 0) {
-    asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar));
-    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-  }
-  __syncthreads();
-  if (threadIdx.x == 0) {
-    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
-    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
-                     smem_u32(dst)),
-                 "l"(src), "r"(bytes), "r"(bar)
-                 : "memory");
-  }
-  uint32_t done = 0;
-  while (!done) {
-    asm volatile(
-        "{\n\t.reg .pred p;\n\t"
-        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], 0;\n\t"
-        "selp.u32 %0, 1, 0, p;\n\t}"
-        : "=r"(done)
-        : "r"(bar)
-        : "memory");
-  }
-}
-
-struct Warp {
-  Tables t;
-  float* q;
-  float* act;
-  float* geom;
-  float* save;
-  uint16_t* queue;
-  uint32_t* mask;
-  int32_t* first;
-  float* stage;
-  int stage_stride;
-  int lane;
-  // 32-bit word offsets into the CTA's shared memory (g_smem) of this warp's geometry slab and of
-  // the static placements: placement addressing in the pair loops is plain integer arithmetic
-  int geom_w, stat_w;
-};
-
-__device__ __forceinline__ Warp make_warp(const Tables& t, float* slab, const SlabLayout& L) {
-  Warp w;
-  w.t = t;
-  w.q = slab + L.off_q;
-  w.act = slab + L.off_act;
-  w.geom = slab + L.off_geom;
-  w.save = slab + L.off_save;
-  w.queue = reinterpret_cast<uint16_t*>(slab + L.off_queue + ((threadIdx.x >> 5) % L.team) * L.queue_words);
-  w.mask = reinterpret_cast<uint32_t*>(slab + L.off_mask);
-  w.first = reinterpret_cast<int32_t*>(slab + L.off_first);
-  w.stage = slab + L.off_stage;
-  w.stage_stride = L.stage_stride;
-  w.lane = threadIdx.x & 31;
-  w.geom_w = static_cast<int>(w.geom - reinterpret_cast<const float*>(g_smem));
-  w.stat_w = static_cast<int>(t.stat - reinterpret_cast<const float*>(g_smem));
-  return w;
-}
-
-// ---- coalesced load of a [rows<=32][cols] float tile into slot-major shared memory
-// dst[col*32 + row].  Vectorised float4 path when the tile is 16-byte aligned.
-__device__ __forceinline__ void load_rows(float* dst, const float* __restrict__ src, int64_t row0, int64_t n_rows,
-                                          int cols, int ld, int lane) {
-  const int rows = static_cast<int>(imin64(32, n_rows - row0));
-  const float* base = src + row0 * ld;
-  if (ld == cols && ((rows * cols) & 3) == 0 && (reinterpret_cast<uintptr_t>(base) & 15) == 0) {
-    // contiguous rows: the tile is rows * cols / 4 aligned float4 (one may straddle two rows)
-    const int n4 = rows * cols / 4;
-    const float4* b4 = reinterpret_cast<const float4*>(base);
-    const float inv = 1.f / cols;  // floor(i / cols) == floor((i + 0.5) * inv) for i < 4096, cols <= 128
-#pragma unroll 2
-    for (int e = lane; e < n4; e += 32) {
-      const float4 q4 = __ldg(b4 + e);
-      int r = __float2int_rd((4 * e + 0.5f) * inv), c = 4 * e - r * cols;
-      const float v[4] = {q4.x, q4.y, q4.z, q4.w};
-#pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        dst[c * 32 + r] = v[j];
-        if (++c == cols) { c = 0; ++r; }
-      }
-    }
-  } else {
-    const int n = rows * cols;
-#pragma unroll 1
-    for (int e = lane; e < n; e += 32) {
-      const int r = e / cols, c = e - r * cols;
-      dst[c * 32 + r] = __ldg(base + static_cast<int64_t>(r) * ld + c);
-    }
-  }
-  // lanes past the end of the batch replay row 0 so every lane does well-defined work
-  if (rows < 32) {
-    __syncwarp();
-    if (lane >= rows) {
-#pragma unroll 1
-      for (int c = 0; c < cols; ++c) dst[c * 32 + lane] = dst[c * 32];
-    }
-  }
-  __syncwarp();
-}
-
-// ---- software prefetch of the NEXT tile's rows.  Each warp works through load -> FK ->
-// store on its own, so without this the global-load latency of every tile is exposed
-// (long_scoreboard was the top stall of the FK kernel).  The next tile's float4s are fetched
-// into registers before the current tile's arithmetic and committed to shared memory after it.
-// kVec float4 per lane cover rows of up to 4 * kVec floats (8 in the FK kernels, 4 in the
-// register-tight validity kernel; wider rows fall back to the plain load).  Rows must be
-// contiguous (ld == cols, any width: a tile of 32 rows is then 8 * cols aligned float4, and one
-// float4 may straddle two rows).
-template <int kVec>
-struct RowPrefetch {
-  float4 v[kVec];
-  bool valid;  // the vector path applied (else commit falls back to load_rows)
-};
-
-template <int kVec>
-__device__ __forceinline__ bool rows_vectorisable(const float* base, int cols, int ld) {
-  return ld == cols && cols <= 4 * kVec && (reinterpret_cast<uintptr_t>(base) & 15) == 0;
-}
-
-template <int kVec>
-__device__ __forceinline__ void prefetch_rows(RowPrefetch<kVec>& pf, const float* __restrict__ src, int64_t row0, int64_t n_rows,
-                                              int cols, int ld, int lane) {
-  pf.valid = false;
-  if (row0 >= n_rows) return;
-  const float* base = src + row0 * ld;
-  if (!rows_vectorisable<kVec>(base, cols, ld)) return;
-  const int n_el = static_cast<int>(imin64(32, n_rows - row0)) * cols;
-  if (n_el & 3) return;  // a ragged last tile: plain load
-  pf.valid = true;
-  const int n4 = n_el / 4;
-  const float4* b4 = reinterpret_cast<const float4*>(base);
-#pragma unroll
-  for (int k = 0; k < kVec; ++k) {
-    const int e = lane + 32 * k;
-    if (e < n4) pf.v[k] = __ldg(b4 + e);
-  }
-}
-
-template <int kVec>
-__device__ __forceinline__ void commit_rows(const RowPrefetch<kVec>& pf, float* dst, const float* __restrict__ src, int64_t row0,
-                                            int64_t n_rows, int cols, int ld, int lane) {
-  if (!pf.valid) {
-    load_rows(dst, src, row0, n_rows, cols, ld, lane);
-    return;
-  }
-  const int rows = static_cast<int>(imin64(32, n_rows - row0));
-  const int n4 = rows * cols / 4;
-  const float inv = 1.f / cols;  // floor(i / cols) == floor((i + 0.5) * inv) for i < 4096, cols <= 128
-#pragma unroll
-  for (int k = 0; k < kVec; ++k) {
-    const int e = lane + 32 * k;
-    if (e < n4) {
-      int r = __float2int_rd((4 * e + 0.5f) * inv), c = 4 * e - r * cols;
-      const float v[4] = {pf.v[k].x, pf.v[k].y, pf.v[k].z, pf.v[k].w};
-#pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        dst[c * 32 + r] = v[j];
-        if (++c == cols) { c = 0; ++r; }
-      }
-    }
-  }
-  if (rows < 32) {
-    __syncwarp();
-    if (lane >= rows) {
-#pragma unroll 1
-      for (int c = 0; c < cols; ++c) dst[c * 32 + lane] = dst[c * 32];
-    }
-  }
-  __syncwarp();
-}
-
-// ---- TMA prefetch of the NEXT tile's rows (validity kernels).  The 32 rows of a tile are one
-// contiguous, 16-byte aligned block when ld == cols; a single cp.async.bulk lands it in the
-// slab's `save` region -- dead between the end of FK and the next tile's FK -- behind a
-// per-slab mbarrier, so the copy costs no registers and runs under the whole narrow phase.
-// The mbarrier sits in the 16 bytes in front of the region (never written by FK).
-struct TileFetch {
-  uint32_t bar, raw;  // shared-space addresses
-  uint32_t phase;
-  bool pending;       // a copy for the tile about to be committed is in flight
-};
-
-__device__ __forceinline__ void tile_fetch_init(TileFetch& tf, float* region, int lane) {
-  tf.bar = smem_u32(region - 4);
-  tf.raw = smem_u32(region);
-  tf.phase = 0;
-  tf.pending = false;
-  if (lane == 0) {
-    asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(tf.bar));
-    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-  }
-  __syncwarp();
-}
-
-// Start the copy of tile `row0` if it is a full, contiguous, aligned tile that fits; otherwise
-// leave it to the plain load at commit time.  Warp-uniform.
-__device__ __forceinline__ void tile_fetch_issue(TileFetch& tf, const float* __restrict__ src, int64_t row0, int64_t n_rows,
-                                                 int cols, int ld, int raw_cols, int lane) {
-  tf.pending = false;
-  if (row0 + 32 > n_rows || ld != cols || cols > raw_cols) return;
-  const float* base = src + row0 * ld;
-  if (reinterpret_cast<uintptr_t>(base) & 15) return;
-  tf.pending = true;
-  __syncwarp();  // every lane is done reading the region (previous commit / FK saves)
-  if (lane == 0) {
-    const uint32_t bytes = 128u * cols;
-    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(tf.bar), "r"(bytes) : "memory");
-    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(tf.raw),
-                 "l"(base), "r"(bytes), "r"(tf.bar)
-                 : "memory");
-  }
-}
-
-// Rows of the tile into slot-major dst[col * 32 + row]: from the landed copy (lane = row), or
-// with the plain load.
-__device__ __forceinline__ void tile_fetch_commit(TileFetch& tf, float* dst, const float* region, const float* __restrict__ src,
-                                                  int64_t row0, int64_t n_rows, int cols, int ld, int lane) {
-  if (!tf.pending) {
-    load_rows(dst, src, row0, n_rows, cols, ld, lane);
-    return;
-  }
-  uint32_t done = 0;
-  while (!done) {
-    asm volatile(
-        "{\n\t.reg .pred p;\n\t"
-        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
-        "selp.u32 %0, 1, 0, p;\n\t}"
-        : "=r"(done)
-        : "r"(tf.bar), "r"(tf.phase)
-        : "memory");
-  }
-  tf.phase ^= 1;
-  const float* raw = region + lane * cols;
-#pragma unroll 4
-  for (int c = 0; c < cols; ++c) dst[c * 32 + lane] = raw[c];
-  __syncwarp();
-}
-
-// ---- actuated values -> Pinocchio q (reference robot_state.py:117-119: scatter, mimic,
-// then continuous).  Lane-private columns of shared memory, no cross-lane traffic.
-__device__ __forceinline__ void expand_q(const Warp& w) {
-  const ImgHeader* h = w.t.h;
-  const int l = w.lane;
-#pragma unroll 1
-  for (int s = 0; s < h->nq; ++s) w.q[s * 32 + l] = w.t.refq[s];
-#pragma unroll 1
-  for (int k = 0; k < h->n_act; ++k) w.q[w.t.act[k] * 32 + l] = w.act[k * 32 + l];
-#pragma unroll 1
-  for (int k = 0; k < h->n_mimic; ++k) {
-    const DMimic m = w.t.mimic[k];
-    w.q[m.dst * 32 + l] = fmaf(w.q[m.src * 32 + l], m.mult, m.off);
-  }
-#pragma unroll 1
-  for (int k = 0; k < h->n_cont; ++k) {
-    const int c = w.t.cont[k];
-    float s, co;
-    sincos_small(w.q[c * 32 + l], &s, &co);
-    w.q[c * 32 + l] = co;
-    w.q[(c + 1) * 32 + l] = s;
-  }
-}
-
-// a 3x4 placement of the model image (DJoint::pl, DGeom::pl / opl: all 16-byte aligned)
-__device__ __forceinline__ Xf load_table_xf(const float* p) {
-  const float4* p4 = reinterpret_cast<const float4*>(p);
-  const float4 r0 = p4[0], r1 = p4[1], r2 = p4[2];
-  Xf o;
-  o.m[0] = r0.x; o.m[1] = r0.y; o.m[2] = r0.z; o.m[3] = r0.w;
-  o.m[4] = r1.x; o.m[5] = r1.y; o.m[6] = r1.z; o.m[7] = r1.w;
-  o.m[8] = r2.x; o.m[9] = r2.y; o.m[10] = r2.z; o.m[11] = r2.w;
-  return o;
-}
-
-__device__ __forceinline__ void store_slab_xf(float* slab, int slot, int lane, const Xf& x) {
-#pragma unroll
-  for (int k = 0; k < 12; ++k) slab[(slot * 12 + k) * 32 + lane] = x.m[k];
-}
-
-__device__ __forceinline__ Xf load_slab_xf(const float* slab, int slot, int lane) {
-  Xf o;
-#pragma unroll
-  for (int k = 0; k < 12; ++k) o.m[k] = slab[(slot * 12 + k) * 32 + lane];
-  return o;
-}
-
-// Geometry placements are kept as 9 floats -- x axis, z axis, translation -- in the slab
-// (and in the static table): the y axis is z cross x.  A quarter less shared memory per warp
-// means more resident warps, and stage 1 only ever reads z and t.
-constexpr int kGeomFloats = 9;
-// static placements keep their own y axis too (x, z, t, y): a scene object may carry a rotation
-// that is not orthonormal (the reference builds poses from un-normalised quaternions)
-constexpr int kStatFloats = 12;
-
-__device__ __forceinline__ void store_geom_xf(float* slab, int slot, int lane, const Xf& x) {
-  float* p = slab + slot * kGeomFloats * 32 + lane;
-  p[0 * 32] = x.m[0]; p[1 * 32] = x.m[4]; p[2 * 32] = x.m[8];
-  p[3 * 32] = x.m[2]; p[4 * 32] = x.m[6]; p[5 * 32] = x.m[10];
-  p[6 * 32] = x.m[3]; p[7 * 32] = x.m[7]; p[8 * 32] = x.m[11];
-}
-
-// World placement of geometry g for configuration c (lane-divergent g and c allowed).
-__device__ __forceinline__ Xf geom_xf(const Warp& w, int gslot, int c) {
-  const float* S = reinterpret_cast<const float*>(g_smem);
-  const float* p = S + (gslot >= 0 ? w.geom_w + gslot * (kGeomFloats * 32) + c : w.stat_w - (gslot + 1) * kStatFloats);
-  const int st = gslot >= 0 ? 32 : 1;
-  const V3 x = mk(p[0], p[st], p[2 * st]), z = mk(p[3 * st], p[4 * st], p[5 * st]);
-  const V3 y = gslot >= 0 ? cross(z, x) : mk(p[9], p[10], p[11]);
-  Xf o;
-  o.m[0] = x.x; o.m[1] = y.x; o.m[2] = z.x; o.m[3] = p[6 * st];
-  o.m[4] = x.y; o.m[5] = y.y; o.m[6] = z.y; o.m[7] = p[7 * st];
-  o.m[8] = x.z; o.m[9] = y.z; o.m[10] = z.z; o.m[11] = p[8 * st];
-  return o;
-}
-
-// ---- forward kinematics for this lane's configuration (pinocchio::forwardKinematics +
-// updateGeometryPlacements).  kStage: 0 = placements to the slab only, 1 = also stage oMi
-// rows, 2 = also stage oMg rows (output kernels).
-// liMi = placement * M(q).  The aligned revolute / prismatic joints -- all but a handful in
-// practice -- only mix two columns of the placement's rotation (or slide along one), a third of
-// the arithmetic of a general 3x4 product.
-template <int A, int B>
-__device__ __forceinline__ void mix_columns(Xf& o, float c, float s) {  // columns A, B of R times a plane rotation
-#pragma unroll
-  for (int r = 0; r < 3; ++r) {
-    const float ua = o.m[4 * r + A], ub = o.m[4 * r + B];
-    o.m[4 * r + A] = fmaf(c, ua, s * ub);
-    o.m[4 * r + B] = fmaf(c, ub, -s * ua);
-  }
-}
-
-template <int A>
-__device__ __forceinline__ void slide_column(Xf& o, float d) {
-#pragma unroll
-  for (int r = 0; r < 3; ++r) o.m[4 * r + 3] = fmaf(d, o.m[4 * r + A], o.m[4 * r + 3]);
-}
-
-__device__ __forceinline__ Xf local_xf(const DJoint* j, const float* qv) {
-  Xf o = load_table_xf(j->pl);
-  const int type = j->type;
-  if (type <= 3) {  // RX / RY / RZ
-    float s, c;
-    sincos_small(qv[0], &s, &c);
-    if (type == 1) mix_columns<1, 2>(o, c, s);
-    else if (type == 2) mix_columns<2, 0>(o, c, s);
-    else mix_columns<0, 1>(o, c, s);
-    return o;
-  }
-  if (type >= 9 && type <= 11) {  // PX / PY / PZ
-    if (type == 9) slide_column<0>(o, qv[0]);
-    else if (type == 10) slide_column<1>(o, qv[0]);
-    else slide_column<2>(o, qv[0]);
-    return o;
-  }
-  return xf_mul(o, joint_xf(type, j->ax, j->ay, j->az, qv));
-}
-
-// Staging of output rows for the FK kernels: row l (this lane's configuration) holds its 3x4
-// matrices as float4 triples.  The row pitch (in float4) is odd, so the 32 lanes' STS.128 of
-// one matrix row land in distinct bank groups; an odd pitch that equals the row length makes
-// the tile in shared memory the exact image of the tile in global memory.
-__device__ __forceinline__ void stage_xf(const Warp& w, int slot, const Xf& x) {
-  float4* p = reinterpret_cast<float4*>(w.stage) + w.lane * w.stage_stride + slot * 3;
-  p[0] = make_float4(x.m[0], x.m[1], x.m[2], x.m[3]);
-  p[1] = make_float4(x.m[4], x.m[5], x.m[6], x.m[7]);
-  p[2] = make_float4(x.m[8], x.m[9], x.m[10], x.m[11]);
-}
-
-// ---- forward kinematics for this lane's configuration (pinocchio::forwardKinematics +
-// updateGeometryPlacements).  kStage: 0 = geometry placements to the slab (validity path),
-// 1 = stage the oMi rows, 2 = stage the oMg rows (output kernels).
-template <int kStage>
-__device__ __forceinline__ void fk_joint(const Warp& w, int i, Xf& cur, bool emit) {
-  const int l = w.lane;
-  const DJoint* j = &w.t.joints[i];
-  float qv[7];
-  const float* qj = w.q + j->idx_q * 32 + l;
-  qv[0] = qj[0];
-  const int n = j->nq;  // 1 for all but a few joints of a robot: skip the other six loads
-#pragma unroll
-  for (int k = 1; k < 7; ++k) qv[k] = 0.f;
-  if (n > 1) {
-#pragma unroll
-    for (int k = 1; k < 7; ++k) qv[k] = k < n ? qj[k * 32] : 0.f;
-  }
-  const Xf loc = local_xf(j, qv);
-  const int pc = j->parent_code;
-  if (pc == kParentUniverse) cur = loc;
-  else if (pc == kParentRunning) cur = xf_mul(cur, loc);
-  else cur = xf_mul(load_slab_xf(w.save, pc, l), loc);
-  if (j->save_slot >= 0) store_slab_xf(w.save, j->save_slot, l, cur);
-  if (kStage == 1) stage_xf(w, i, cur);
-  const int gend = (kStage == 1 || !emit) ? j->gfirst : j->gfirst + j->gcount;
-#pragma unroll 1
-  for (int s = j->gfirst; s < gend; ++s) {
-    const int gi = w.t.dyn[s];
-    const Xf og = xf_mul(cur, load_table_xf(kStage == 2 ? w.t.geoms[gi].opl : w.t.geoms[gi].pl));
-    if (kStage == 2) stage_xf(w, gi, og);
-    else store_geom_xf(w.geom, s, l, og);
-  }
-}
-
-template <int kStage>
-__device__ __forceinline__ void fk_lane(const Warp& w) {
-  Xf cur = xf_identity();
-#pragma unroll 1
-  for (int i = 0; i < w.t.h->n_joints; ++i) fk_joint<kStage>(w, i, cur, true);
-}
-
-// The same for a team of kTeam warps sharing one slab: warp `tw` walks its FK plan -- a
-// contiguous run of the joint order whose geometries it places, preceded by the ancestors of
-// that run (recomputed, not placed) -- so the kinematic tree is split between the warps
-// instead of one of them doing all of it while the others wait.
-template <int kTeam>
-__device__ __forceinline__ void fk_team(const Warp& w, int tw) {
-  const int32_t* plan = w.t.plan;
-  const int base = kTeam == 2 ? kPlanTeam2 : kPlanTeam4;
-  const int e = plan[base + tw + 1];
-  Xf cur = xf_identity();
-#pragma unroll 1
-  for (int k = plan[base + tw]; k < e; ++k) {
-    const int ent = plan[kPlanEntries + k];
-    fk_joint<0>(w, ent & 0xffff, cur, (ent >> 16) != 0);
-  }
-}
-
-// ---- narrow phase over the pair list for the 32 configurations of the tile.
-// A (configuration, pair) work item that survived every cull and needs GJK.  The validity
-// kernel appends such items to a global queue; gjk_queue_kernel drains it with full warps and
-// far more resident warps than the slab-bound validity kernel can have.
-struct __align__(16) GjkItem {
-  float rel[12];   // pose of shape b in shape a's frame
-  float v0[3];     // starting point for GJK: witness vector of the two inner capsules
-  uint32_t row;    // configuration index inside the launch's slice / flat state index (edges)
-  uint32_t p;      // pair index
-  uint32_t pad[3];
-};
-static_assert(sizeof(GjkItem) == 80, "GjkItem");
-
-// The queue has two regions.  Items whose inner capsules are still far apart compared with the
-// shell between inner and outer capsule almost always end after one GJK iteration ("easy");
-// the others take 4-5 ("hard").  Hard items go to the front region and are handed out first,
-// so the consumer kernel drains on one-iteration items and its warps finish together.
-struct GjkQueue {
-  GjkItem* items;     // nullptr: no queue, GJK runs inside the validity kernel
-  uint32_t* count;    // [0] hard, [1] easy items reserved so far (may exceed the regions: the
-                      // overflow stays in-kernel), [2] the consumer's cursor; zeroed by the host
-  uint32_t capacity;  // items: hard region [0, cap_hard), easy region [cap_hard, capacity)
-  uint32_t cap_hard;
-};
-
-__host__ __device__ constexpr uint32_t queue_cap_hard(uint32_t capacity) { return capacity / 3; }
-// hard: |witness of the inner capsule axes| below inner radii + 7/8 of the shell
-constexpr float kHardShell = 0.875f;
-
-__device__ __forceinline__ void record_hit(const Warp& w, int c, int p, bool want_mask) {
-  atomicMin(&w.first[c], p);
-  if (want_mask) atomicOr(&w.mask[(p >> 5) * 32 + c], 1u << (p & 31));
-}
-
-__device__ __forceinline__ GjkShape load_shape(const DGeom* g, const float4* verts) {
-  GjkShape s;
-  s.type = g->type; s.vcnt = g->vcnt; s.p0 = g->p0; s.p1 = g->p1; s.p2 = g->p2; s.verts = verts + g->voff;
-  return s;
-}
-
-__device__ __forceinline__ float swept_radius(const DGeom* g) {
-  return (g->type == SH_SPHERE || g->type == SH_CAPSULE) ? g->p0 : 0.f;
-}
-
-__device__ __forceinline__ int pair_class_of(int ta, int tb) {  // ta <= tb (pairs are stored ordered)
-  if (ta == SH_SPHERE && tb <= SH_CYLINDER) return kClsSphereSphere + tb;
-  if (ta == SH_CAPSULE && tb == SH_CAPSULE) return kClsCapsuleCapsule;
-  if (ta == SH_BOX && tb == SH_BOX) return kClsBoxBox;
-  return kClsGjk;
-}
-
-// exact closed-form signed distance of the primitive classes; rel = pose of b in a's frame
-__device__ __forceinline__ float closed_form_dist(int cls, const DGeom* ga, const DGeom* gb, const Xf& rel) {
-  switch (cls) {
-    case kClsSphereSphere: return sqrtf(dot(trans(rel), trans(rel))) - ga->p0 - gb->p0;
-    case kClsSphereCapsule: {  // a sphere, b capsule: sphere centre in b's frame
-      const V3 c = rot_t(rel, -trans(rel));
-      return point_zseg_dist(c, gb->p1) - ga->p0 - gb->p0;
-    }
-    case kClsSphereBox: {
-      const V3 c = rot_t(rel, -trans(rel));
-      return sphere_box_dist(c, gb->p0, gb->p1, gb->p2, ga->p0);
-    }
-    case kClsSphereCylinder: {
-      const V3 c = rot_t(rel, -trans(rel));
-      return sphere_cyl_dist(c, gb->p0, gb->p1, ga->p0);
-    }
-    case kClsCapsuleCapsule: {
-      const V3 zb = mk(rel.m[2], rel.m[6], rel.m[10]);
-      const V3 p2 = trans(rel) - zb * gb->p1;
-      return seg_seg_dist(mk(0.f, 0.f, -ga->p1), mk(0.f, 0.f, 2.f * ga->p1), p2, zb * (2.f * gb->p1)) - ga->p0 - gb->p0;
-    }
-    default: return 3.0e38f;
-  }
-}
-
-__device__ __forceinline__ bool closed_form_hit(int cls, const DGeom* ga, const DGeom* gb, const Xf& rel) {
-  return closed_form_dist(cls, ga, gb, rel) <= 0.f;
-}
-
-// Early out (`stop_at_first`): pair p of a configuration is dropped once a pair with a smaller
-// list index has hit (the first-pair output needs nothing else), or -- `stop_any`, when only
-// the flag is wanted -- once any pair has hit.
-// `tw` / kTeam: this warp takes every kTeam-th chunk of `chunk_pairs` pairs (kTeam == 1: all of
-// them, in chunks of kChunkPairs -- a compile-time constant on the common path)
-template <int kTeam = 1>
-__device__ __forceinline__ void narrow_phase(const Warp& w, bool stop_at_first, bool stop_any, bool want_mask,
-                                             const GjkQueue& gq, uint32_t row_base, int tw = 0,
-                                             int chunk_pairs_rt = kChunkPairs) {
-  const int team = kTeam;
-  const int chunk_pairs = kTeam == 1 ? kChunkPairs : chunk_pairs_rt;
-  const ImgHeader* h = w.t.h;
-  const int l = w.lane;
-  const unsigned FULL = 0xffffffffu;
-  // decided already?  (first = smallest list index that hit so far, INT32_MAX if none)
-  auto dead = [&](int first, int orig) { return stop_at_first && first < (stop_any ? INT32_MAX : orig); };
-  for (int chunk = tw * chunk_pairs; chunk < h->n_pairs; chunk += team * chunk_pairs) {
-    const int chunk_end = min(chunk + chunk_pairs, h->n_pairs);
-    const int my_first = w.first[l];
-    int qn = 0;
-    // ---- stage 1: bounding spheres; lane = configuration, pair index uniform.  The first 16
-    // bytes of a DPair are all this stage reads (one vector load): two byte offsets of the
-    // placement origins, the squared radius sum (-1: inactive pair, never passes) and the
-    // caller's pair index for the early-out test.
-    const char* T = reinterpret_cast<const char*>(g_smem) + 4 * (w.geom_w + l + 6 * 32);  // origin rows of this lane's slab column
-    const char* TS = reinterpret_cast<const char*>(g_smem) + 4 * (w.stat_w + 6);          // origins of the static placements
-    const int4* rec = reinterpret_cast<const int4*>(w.t.pairs);  // 3 per DPair
-    const unsigned lt = (1u << l) - 1;
-    // dead(my_first, orig) as one LOP3 + compare: pass needs my_first >= (orig & lim_and) | lim_or
-    const int lim_and = (stop_at_first && !stop_any) ? 0xffff : 0;
-    const int lim_or = stop_at_first ? (stop_any ? INT32_MAX : 0) : INT32_MIN;
-    const int item0 = l - (chunk << 5);
-    auto push = [&](int p, const int4& r, bool pass) {
-      pass = pass && my_first >= ((r.w & lim_and) | lim_or);
-      const unsigned b = __ballot_sync(FULL, pass);
-      if (pass) w.queue[qn + __popc(b & lt)] = static_cast<uint16_t>((p << 5) + item0);
-      qn += __popc(b);
-    };
-    // squared distance of the two placement origins against the bounding-sphere sum
-    auto near = [&](const int4& r, const char* base_a, const char* base_b, int stride_a, int stride_b) {
-      const float* a = reinterpret_cast<const float*>(base_a + r.x);
-      const float* b = reinterpret_cast<const float*>(base_b + r.y);
-      const float dx = a[0] - b[0], dy = a[stride_a] - b[stride_b], dz = a[2 * stride_a] - b[2 * stride_b];
-      return fmaf(dx, dx, fmaf(dy, dy, dz * dz)) <= __int_as_float(r.z);
-    };
-    const int dd_end = min(chunk_end, max(chunk, h->n_dd));
-    // four pairs per trip: their loads are independent, which hides shared-memory latency
-    // when few warps fit next to the slabs (20-geometry robots: 6 warps per SM)
-#pragma unroll 1
-    for (int p = chunk; p < dd_end; p += 4) {
-      const int last = dd_end - 1;
-      const int4 r0 = rec[3 * p], r1 = rec[3 * min(p + 1, last)], r2 = rec[3 * min(p + 2, last)], r3 = rec[3 * min(p + 3, last)];
-      const bool k0 = near(r0, T, T, 32, 32), k1 = near(r1, T, T, 32, 32), k2 = near(r2, T, T, 32, 32), k3 = near(r3, T, T, 32, 32);
-      push(p, r0, k0);
-      push(p + 1, r1, k1 && p + 1 <= last);
-      push(p + 2, r2, k2 && p + 2 <= last);
-      push(p + 3, r3, k3 && p + 3 <= last);
-    }
-    const int ds_end = min(chunk_end, max(dd_end, h->ss_begin));
-#pragma unroll 1
-    for (int p = dd_end; p < ds_end; p += 2) {
-      const bool two = p + 1 < ds_end;
-      const int4 r0 = rec[3 * p], r1 = rec[3 * (two ? p + 1 : p)];
-      const bool k0 = near(r0, T, TS, 32, 1), k1 = near(r1, T, TS, 32, 1);
-      push(p, r0, k0);
-      push(p + 1, r1, k1 && two);
-    }
-    // two universe-attached geometries (a fixed base link against a scene object): the same
-    // answer for every configuration, but it is part of the pair list
-#pragma unroll 1
-    for (int p = ds_end; p < chunk_end; ++p) {
-      const int4 r = rec[3 * p];
-      push(p, r, near(r, TS, TS, 1, 1));
-    }
-    __syncwarp();
-    // ---- stage 1.5: OUTER capsules for the GJK class, on dense groups of 32 survivors of the
-    // sphere test (only ~20 % of the lanes pass it, so testing capsules per lane in stage 1
-    // would waste four lanes in five).  Needs just the z axis and the origin of each placement.
-    {
-      int kept = 0;
-#pragma unroll 1
-      for (int base = 0; base < qn; base += 32) {
-        const bool live = base + l < qn;
-        const int item = live ? w.queue[base + l] : 0;
-        bool keep = live;
-        if (live) {
-          // record 1 of the pair: outer capsules in o1 / o2 order (rsum_out = inf: not the GJK class)
-          const int pidx = chunk + (item >> 5);
-          const int4 r0 = rec[3 * pidx];
-          const float4 r1 = reinterpret_cast<const float4*>(rec)[3 * pidx + 1];
-          const int kind = __float_as_int(r1.w);
-          const char* col = T + 4 * ((item & 31) - l);  // origin rows of the item's configuration
-          const char* pa = (kind < 2 ? col : TS) + r0.x;
-          const char* pb = (kind < 1 ? col : TS) + r0.y;
-          const int sa = kind < 2 ? 128 : 4, sb = kind < 1 ? 128 : 4;  // row strides in bytes
-          auto f = [](const char* p) { return *reinterpret_cast<const float*>(p); };
-          const V3 za = mk(f(pa - 3 * sa), f(pa - 2 * sa), f(pa - sa)), ta = mk(f(pa), f(pa + sa), f(pa + 2 * sa));
-          const V3 zb = mk(f(pb - 3 * sb), f(pb - 2 * sb), f(pb - sb)), tb = mk(f(pb), f(pb + sb), f(pb + 2 * sb));
-          const V3 wv = seg_seg_witness(ta - za * r1.x, za * (2.f * r1.x), tb - zb * r1.y, zb * (2.f * r1.y));
-          keep = dot(wv, wv) <= r1.z * r1.z;
-        }
-        __syncwarp();  // every lane has read its item before the in-place compaction writes
-        const unsigned b = __ballot_sync(FULL, keep);
-        if (keep) w.queue[kept + __popc(b & ((1u << l) - 1))] = static_cast<uint16_t>(item);
-        kept += __popc(b);
-        __syncwarp();
-      }
-      qn = kept;
-    }
-    // ---- stage 2: closed forms, exact box-box, OBB cull; survivors re-compacted in place
-    int gn = 0;
-#pragma unroll 1
-    for (int base = 0; base < qn; base += 32) {
-      const bool live = base + l < qn;
-      const int item = live ? w.queue[base + l] : 0;
-      bool to_gjk = false, hard = false;
-      Xf rel = xf_identity();
-      V3 v0 = mk(1.f, 0.f, 0.f);
-      int orig = 0, cls = 0, p = 0;
-      bool go = live;
-      if (live) {  // a configuration settled by an earlier group needs no more work
-        p = chunk + (item >> 5);
-        const int oc = rec[3 * p].w;  // orig | cls << 16
-        orig = oc & 0xffff;
-        cls = oc >> 16;
-        go = !dead(w.first[item & 31], orig);
-      }
-      if (go) {
-        const int c = item & 31;
-        const int4 r2 = rec[3 * p + 2];  // slack, a | b << 16, sa | sb << 16
-        const float slack = __int_as_float(r2.x);
-        const DGeom* ga = &w.t.geoms[r2.y & 0xffff];
-        const DGeom* gb = &w.t.geoms[r2.y >> 16];
-        rel = xf_inv_mul(geom_xf(w, static_cast<int16_t>(r2.z & 0xffff), c), geom_xf(w, r2.z >> 16, c));
-        if (cls >= kClsBoxBox) {
-          // one SAT instance: exact decision on the boxes themselves, or a cull on the
-          // local bounding boxes of two GJK shapes (DGeom words 4-7: the box, 8-10: the bounds)
-          const bool bb = cls == kClsBoxBox;
-          const float4 ha4 = reinterpret_cast<const float4*>(ga)[bb ? 1 : 2], hb4 = reinterpret_cast<const float4*>(gb)[bb ? 1 : 2];
-          const V3 ha = mk(ha4.x, ha4.y, ha4.z), hb = mk(hb4.x, hb4.y, hb4.z);
-          // GJK class: overlapping INNER capsules prove the collision (the outer ones were
-          // tested in stage 1); only the shell in between goes on to the OBB cull and GJK.
-          bool decided = false;
-          if (!bb) {
-            const float4 ca = reinterpret_cast<const float4*>(ga)[6], cb = reinterpret_cast<const float4*>(gb)[6];  // s_out r_out s_in r_in
-            const V3 zb = mk(rel.m[2], rel.m[6], rel.m[10]);
-            v0 = seg_seg_witness(mk(0.f, 0.f, -ca.z), mk(0.f, 0.f, 2.f * ca.z), trans(rel) - zb * cb.z, zb * (2.f * cb.z));
-            const float rin = ca.w + cb.w - slack;
-            const float vv0 = dot(v0, v0);
-            if (rin > 0.f && vv0 < rin * rin) { record_hit(w, c, orig, want_mask); decided = true; }
-            const float thr = fmaf(kHardShell, ca.y + cb.y - (ca.w + cb.w), ca.w + cb.w);  // r_out, r_in sums
-            hard = vv0 < thr * thr;
-          }
-          if (!decided) {
-            const bool ov = obb_overlap(ha, hb, rel, bb ? 0.f : slack);
-            if (ov && bb) record_hit(w, c, orig, want_mask);
-            to_gjk = ov && !bb;
-          }
-        } else if (closed_form_hit(cls, ga, gb, rel)) {
-          record_hit(w, c, orig, want_mask);
-        }
-      }
-      __syncwarp();  // all lanes have read their item before the in-place compaction writes
-      // hits of this group may have settled configurations whose GJK items are still pending
-      if (to_gjk && dead(w.first[item & 31], orig)) to_gjk = false;
-      if (gq.items != nullptr) {
-        // reserve slots of the two queue regions for this group's survivors (one 64-bit atomic
-        // per group: hard count in the low word, easy count in the high word)
-        const unsigned mh = __ballot_sync(FULL, to_gjk && hard), me = __ballot_sync(FULL, to_gjk && !hard);
-        if (mh | me) {
-          const int leader = __ffs(mh | me) - 1;
-          unsigned long long base = 0;
-          if (l == leader)
-            base = atomicAdd(reinterpret_cast<unsigned long long*>(gq.count),
-                             static_cast<unsigned long long>(__popc(mh)) | (static_cast<unsigned long long>(__popc(me)) << 32));
-          base = __shfl_sync(FULL, base, leader);
-          const uint32_t lt_l = (1u << l) - 1;
-          const uint32_t slot = hard ? static_cast<uint32_t>(base) + __popc(mh & lt_l)
-                                     : gq.cap_hard + static_cast<uint32_t>(base >> 32) + __popc(me & lt_l);
-          if (to_gjk && slot < (hard ? gq.cap_hard : gq.capacity)) {
-            const uint32_t c = item & 31, p = chunk + (item >> 5);
-            float4* dst = reinterpret_cast<float4*>(gq.items + slot);
-            dst[0] = make_float4(rel.m[0], rel.m[1], rel.m[2], rel.m[3]);
-            dst[1] = make_float4(rel.m[4], rel.m[5], rel.m[6], rel.m[7]);
-            dst[2] = make_float4(rel.m[8], rel.m[9], rel.m[10], rel.m[11]);
-            dst[3] = make_float4(v0.x, v0.y, v0.z, __uint_as_float(row_base + c));
-            dst[4] = make_float4(__uint_as_float(p), 0.f, 0.f, 0.f);
-            to_gjk = false;  // queued; anything past the capacity stays for the in-kernel loop
-          }
-        }
-      }
-      const unsigned b = __ballot_sync(FULL, to_gjk);
-      if (to_gjk) w.queue[gn + __popc(b & ((1u << l) - 1))] = static_cast<uint16_t>(item);
-      gn += __popc(b);
-      __syncwarp();
-    }
-    // ---- stage 3: GJK.  Each lane owns one work item and advances it one iteration per
-    // trip; lanes whose item finished fetch the next one from the queue, so lanes stay busy
-    // although iteration counts differ per item.
-    if (gn > 0) {
-      int next = 0, c = 0, p = 0;
-      bool active = false;
-      GjkLane g;
-      GjkShape A, B;
-      A.type = B.type = 0; A.vcnt = B.vcnt = 0; A.p0 = A.p1 = A.p2 = B.p0 = B.p1 = B.p2 = 0.f; A.verts = B.verts = w.t.verts;
-      g.s.n = 0; g.it = 0; g.vv = 1.f; g.rsum = 0.f; g.lower = 0.f; g.v = mk(1.f, 0.f, 0.f); g.rel = xf_identity();
-      while (true) {
-        const unsigned need = __ballot_sync(FULL, !active);
-        if (!active) {
-          const int idx = next + __popc(need & ((1u << l) - 1));
-          if (idx < gn) {
-            const int item = w.queue[idx];
-            c = item & 31;
-            p = chunk + (item >> 5);
-            // a configuration that was hit earlier (at a smaller list index) needs no later pair
-            const DPair pr = w.t.pairs[p];
-            p = pr.orig;  // results report the caller's index
-            if (!dead(w.first[c], p)) {
-              const DGeom* ga = &w.t.geoms[pr.a];
-              const DGeom* gb = &w.t.geoms[pr.b];
-              A = load_shape(ga, w.t.verts);
-              B = load_shape(gb, w.t.verts);
-              const Xf rl = xf_inv_mul(geom_xf(w, ga->gslot, c), geom_xf(w, gb->gslot, c));
-              // same start as the queued items: the witness of the two inner capsule axes
-              const V3 zb = mk(rl.m[2], rl.m[6], rl.m[10]);
-              const V3 v0 = seg_seg_witness(mk(0.f, 0.f, -ga->s_in), mk(0.f, 0.f, 2.f * ga->s_in), trans(rl) - zb * gb->s_in,
-                                            zb * (2.f * gb->s_in));
-              gjk_init(g, rl, swept_radius(ga) + swept_radius(gb), v0);
-              active = true;
-            }
-          }
-        }
-        next += __popc(need);
-        if (!__any_sync(FULL, active)) {
-          if (next >= gn) break;
-          continue;
-        }
-        if (active) {
-          float dist;
-          const int st = gjk_step(g, A, B, false, dist);
-          if (st != GJK_CONTINUE) {
-            if (st == GJK_HIT) record_hit(w, c, p, want_mask);
-            active = false;
-          }
-        }
-      }
-    }
-    __syncwarp();
-  }
-}
-
-__device__ __forceinline__ void reset_results(const Warp& w, int mask_words) {
-  w.first[w.lane] = INT32_MAX;
-  for (int k = 0; k < mask_words; ++k) w.mask[k * 32 + w.lane] = 0u;
-  __syncwarp();
-}
-
-struct CheckArgs {
-  const unsigned char* img;
-  const float* q;
-  int64_t n;
-  int32_t ld;
-  uint32_t flags;
-  uint8_t* hit;
-  int32_t* first_pair;
-  uint32_t* pair_mask;
-  GjkQueue gq;
-  uint32_t row_offset;  // added to the row index of queued items: several launches can feed one queue
-  SlabLayout L;
-};
-
-// ------------------------------------------------------------------ kernel: validity
-template <int kTeam>
-__global__ void __launch_bounds__(512, 1) check_kernel(const __grid_constant__ CheckArgs a) {
-  uint64_t* mbar = reinterpret_cast<uint64_t*>(g_smem);
-  unsigned char* tbl = g_smem + 16;
-  stage_tables(tbl, a.img, a.L.table_bytes, mbar);
-  const Tables t = make_tables(tbl);
-  const int nwarps = blockDim.x >> 5, wid = threadIdx.x >> 5;
-  // Teams: `team` warps share one slab and one tile.  Warp 0 of the team loads the rows and
-  // runs FK, then all of them split the pair list; a named barrier per team orders the phases.
-  // More warps per slab is what lets robots with many geometries (large slabs) and small
-  // batches (few tiles) keep the schedulers busy.
-  constexpr int team = kTeam;
-  const int tid = wid / team, tw = wid - tid * team, nteams = nwarps / team;
-  float* slab = reinterpret_cast<float*>(tbl + a.L.table_bytes) + static_cast<size_t>(tid) * a.L.words;
-  const Warp w = make_warp(t, slab, a.L);
-  auto team_sync = [&]() {
-    if (team == 1) __syncwarp();
-    else asm volatile("bar.sync %0, %1;" ::"r"(1 + tid), "r"(team * 32) : "memory");
-  };
-  const bool actuated = a.flags & RAMP_Q_ACTUATED;
-  const bool want_mask = a.pair_mask != nullptr;
-  const bool stop = !(a.flags & RAMP_ALL_PAIRS) && !want_mask;
-  int cols = actuated ? t.h->n_act : t.h->nq;
-  if ((a.ld & 3) == 0 && a.ld <= cols + 3) cols = a.ld;  // padded rows: take the float4 path
-  const int64_t ntiles = (a.n + 31) >> 5;
-  const int64_t tile_step = static_cast<int64_t>(gridDim.x) * nteams;
-  const int64_t tile0 = static_cast<int64_t>(blockIdx.x) * nteams + tid;
-  TileFetch tf;
-  if (tw == 0) {
-    tile_fetch_init(tf, w.save, w.lane);  // the first tile takes the plain load: nothing to hide a copy behind
-  }
-  for (int64_t tile = tile0; tile < ntiles; tile += tile_step) {
-    const int64_t row0 = tile << 5;
-    if (tw == 0) {
-      tile_fetch_commit(tf, actuated ? w.act : w.q, w.save, a.q, row0, a.n, cols, a.ld, w.lane);
-      if (actuated) expand_q(w);
-      reset_results(w, want_mask ? t.h->mask_words : 0);
-      if (kTeam == 1) fk_lane<0>(w);
-    }
-    if (kTeam > 1) {  // every warp of the team runs its share of the kinematic tree
-      team_sync();
-      fk_team<kTeam>(w, tw);
-    }
-    team_sync();
-    // FK is done with the saved transforms: their region takes the next tile's rows
-    if (tw == 0) tile_fetch_issue(tf, a.q, (tile + tile_step) << 5, a.n, cols, a.ld, a.L.raw_cols, w.lane);
-    narrow_phase<kTeam>(w, stop, stop && a.first_pair == nullptr, want_mask, a.gq, static_cast<uint32_t>(row0) + a.row_offset, tw,
-                        a.L.chunk_pairs);
-    team_sync();
-    const int64_t row = row0 + w.lane;
-    if (tw == 0 && row < a.n) {
-      const int f = w.first[w.lane];
-      a.hit[row] = f != INT32_MAX;
-      if (a.first_pair) a.first_pair[row] = f != INT32_MAX ? f : -1;
-      if (want_mask)
-        for (int k = 0; k < t.h->mask_words; ++k) a.pair_mask[row * t.h->mask_words + k] = w.mask[k * 32 + w.lane];
-    }
-    // the next trip's rows overwrite the region the team's queues live in
-    team_sync();
-  }
-}
-
-
-// Support scan of the few items left in a draining warp, shared between lanes: the k-th active
-// lane owns item k; lanes [k * kG, (k + 1) * kG) each scan 1/kG of its vertex list and a
-// butterfly picks the best.  Closed-form shapes (no vertex list) are left to their owner.
-template <int kG>
-__device__ __forceinline__ V3 coop_support(unsigned am, bool active, const GjkShape& S, V3 d, const float4* verts0) {
-  const unsigned FULL = 0xffffffffu;
-  const int l = threadIdx.x & 31;
-  const int grp = l / kG, sub = l % kG;
-  const int owner = __fns(am, 0, grp + 1) & 31;  // lane of the grp-th active item (any lane if there is none)
-  const bool has = grp < __popc(am);
-  const bool listed = S.type != SH_CYLINDER && S.type != SH_ELLIPSOID;
-  const int o_cnt = __shfl_sync(FULL, active && listed ? S.vcnt : 0, owner);
-  const int o_off = __shfl_sync(FULL, static_cast<int>(S.verts - verts0), owner);
-  const V3 od = mk(__shfl_sync(FULL, d.x, owner), __shfl_sync(FULL, d.y, owner), __shfl_sync(FULL, d.z, owner));
-  const int per = (o_cnt + kG - 1) / kG;
-  const int begin = sub * per, cnt = has ? max(min(per, o_cnt - begin), 0) : 0;
-  V3 r = support(SH_CONVEX, 0.f, 0.f, 0.f, verts0 + o_off + begin, cnt, od);
-  float val = cnt > 0 ? dot(r, od) : -3.0e38f;
-  if constexpr (kG == 32) {
-    // whole warp on one item: one integer max-reduction on an order-preserving key, then the
-    // winning lane hands out its vertex (5 dependent steps instead of a 20-shuffle butterfly)
-    int key = __float_as_int(val);
-    key ^= (key >> 31) & 0x7fffffff;
-    const int best = __reduce_max_sync(FULL, key);
-    const int win = __ffs(__ballot_sync(FULL, key == best)) - 1;
-    V3 res = mk(__shfl_sync(FULL, r.x, win), __shfl_sync(FULL, r.y, win), __shfl_sync(FULL, r.z, win));
-    if (active && !listed) res = support(S.type, S.p0, S.p1, S.p2, S.verts, S.vcnt, d);
-    return res;
-  } else {
-#pragma unroll
-    for (int m = 1; m < kG; m <<= 1) {
-      const float ov = __shfl_xor_sync(FULL, val, m);
-      const V3 orr = mk(__shfl_xor_sync(FULL, r.x, m), __shfl_xor_sync(FULL, r.y, m), __shfl_xor_sync(FULL, r.z, m));
-      if (ov > val) { val = ov; r = orr; }
-    }
-    // back to the owners: active lane with rank k reads the result of group k
-    const int src = (__popc(am & ((1u << l) - 1)) * kG) & 31;
-    V3 res = mk(__shfl_sync(FULL, r.x, src), __shfl_sync(FULL, r.y, src), __shfl_sync(FULL, r.z, src));
-    if (active && !listed) res = support(S.type, S.p0, S.p1, S.p2, S.verts, S.vcnt, d);
-    return res;
-  }
-}
-
-// ------------------------------------------------- kernel: validity, one warp per configuration
-// Latency mode for small batches (a few thousand configurations, the states of one planner
-// edge): the tile kernel above needs 32 configurations per warp and tens of thousands of them
-// to fill the machine; here every configuration gets its own warp.  All lanes run the (cheap)
-// forward kinematics redundantly, lane g places geometry g, lane p tests pair p -- spheres,
-// capsules, closed forms / SAT, and GJK in the lane -- and the warp reduces the first hit.
-struct WarpSlab {  // per-warp shared memory, in words
-  int32_t words, off_q, off_act, off_omi, off_geom, off_mask;
-};
-
-struct SmallArgs {
-  const unsigned char* img;
-  int32_t table_bytes;
-  const float* q;
-  int64_t n;
-  int32_t ld;
-  uint32_t flags;
-  uint8_t* hit;
-  int32_t* first_pair;
-  uint32_t* pair_mask;
-  WarpSlab L;
-};
-
-struct SmallWarp {
-  Tables t;
-  float *q, *act, *omi, *geom;
-  uint32_t* mask;
-  int lane;
-};
-
-// actuated values (already in w.act) -> Pinocchio q, cooperatively
-__device__ __forceinline__ void expand_q_warp(const SmallWarp& w) {
-  const ImgHeader* h = w.t.h;
-  for (int s = w.lane; s < h->nq; s += 32) w.q[s] = w.t.refq[s];
-  __syncwarp();
-  for (int k = w.lane; k < h->n_act; k += 32) w.q[w.t.act[k]] = w.act[k];
-  __syncwarp();
-  if (w.lane == 0)  // in list order: a mimic source may itself be a mimic target
-    for (int k = 0; k < h->n_mimic; ++k) {
-      const DMimic m = w.t.mimic[k];
-      w.q[m.dst] = fmaf(w.q[m.src], m.mult, m.off);
-    }
-  __syncwarp();
-  for (int k = w.lane; k < h->n_cont; k += 32) {
-    const int c = w.t.cont[k];
-    float sn, cs;
-    sincos_small(w.q[c], &sn, &cs);
-    w.q[c] = cs;
-    w.q[c + 1] = sn;
-  }
-  __syncwarp();
-}
-
-__device__ __forceinline__ Xf small_geom_xf(const SmallWarp& w, int gslot) {
-  const float* p = gslot >= 0 ? w.geom + gslot * kStatFloats : w.t.stat + (-1 - gslot) * kStatFloats;
-  Xf o;
-  o.m[0] = p[0]; o.m[4] = p[1]; o.m[8] = p[2];
-  o.m[2] = p[3]; o.m[6] = p[4]; o.m[10] = p[5];
-  o.m[3] = p[6]; o.m[7] = p[7]; o.m[11] = p[8];
-  o.m[1] = p[9]; o.m[5] = p[10]; o.m[9] = p[11];
-  return o;
-}
-
-// FK + placements + every pair for ONE configuration whose q is in w.q.  Returns the smallest
-// colliding pair index (caller's numbering) or INT32_MAX; sets mask bits when asked.
-__device__ __forceinline__ int check_one_config(const SmallWarp& w, bool stop_at_first, bool want_mask) {
-  const ImgHeader* h = w.t.h;
-  const int l = w.lane;
-  const unsigned FULL = 0xffffffffu;
-  // every lane walks the whole chain (identical values); lane i % 32 publishes joint i
-  {
-    Xf cur = xf_identity();
-#pragma unroll 1
-    for (int i = 0; i < h->n_joints; ++i) {
-      const DJoint* j = &w.t.joints[i];
-      float qv[7];
-      const int n = joint_nq(j->type);
-#pragma unroll
-      for (int k = 0; k < 7; ++k) qv[k] = k < n ? w.q[j->idx_q + k] : 0.f;
-      const Xf loc = local_xf(j, qv);
-      const int pc = j->parent_code;
-      if (pc == kParentUniverse) cur = loc;
-      else if (pc == kParentRunning) cur = xf_mul(cur, loc);
-      else {  // parent published earlier (its index is recoverable from the geometry-free table: stored per joint)
-        Xf par;
-#pragma unroll
-        for (int k = 0; k < 12; ++k) par.m[k] = w.omi[j->parent * 12 + k];
-        cur = xf_mul(par, loc);
-      }
-      if ((i & 31) == l) {
-#pragma unroll
-        for (int k = 0; k < 12; ++k) w.omi[i * 12 + k] = cur.m[k];
-      }
-      __syncwarp();
-    }
-  }
-  // lane s places geometry s (x, z, t, y layout of the static table)
-  for (int s = l; s < h->n_dyn; s += 32) {
-    const DGeom* g = &w.t.geoms[w.t.dyn[s]];
-    Xf par;
-#pragma unroll
-    for (int k = 0; k < 12; ++k) par.m[k] = w.omi[g->parent * 12 + k];
-    const Xf og = xf_mul(par, load_table_xf(g->pl));
-    float* p = w.geom + s * kStatFloats;
-    p[0] = og.m[0]; p[1] = og.m[4]; p[2] = og.m[8];
-    p[3] = og.m[2]; p[4] = og.m[6]; p[5] = og.m[10];
-    p[6] = og.m[3]; p[7] = og.m[7]; p[8] = og.m[11];
-    p[9] = og.m[1]; p[10] = og.m[5]; p[11] = og.m[9];
-  }
-  for (int k = l; k < h->mask_words; k += 32) w.mask[k] = 0u;
-  __syncwarp();
-  int first = INT32_MAX;
-#pragma unroll 1
-  for (int base = 0; base < h->n_pairs; base += 32) {
-    const int p = base + l;
-    bool hit = false, need_gjk = false;
-    GjkLane g;
-    GjkShape SA, SB;
-    SA.type = SB.type = 0; SA.vcnt = SB.vcnt = 0; SA.p0 = SA.p1 = SA.p2 = SB.p0 = SB.p1 = SB.p2 = 0.f; SA.verts = SB.verts = w.t.verts;
-    g.s.n = 0; g.it = 0; g.vv = 1.f; g.rsum = 0.f; g.lower = 0.f; g.v = mk(1.f, 0.f, 0.f); g.rel = xf_identity();
-    DPair pr;
-    pr.cls = kClsInactive; pr.orig = 0;
-    if (p < h->n_pairs) pr = w.t.pairs[p];
-    if (pr.cls != kClsInactive) {
-      const DGeom* ga = &w.t.geoms[pr.a];
-      const DGeom* gb = &w.t.geoms[pr.b];
-      const Xf A = small_geom_xf(w, pr.sa), B = small_geom_xf(w, pr.sb);
-      const V3 dc = trans(A) - trans(B);
-      if (dot(dc, dc) <= pr.rs2) {
-        {
-          const Xf rel = xf_inv_mul(A, B);
-          if (pr.cls < kClsBoxBox) hit = closed_form_hit(pr.cls, ga, gb, rel);
-          else if (pr.cls == kClsBoxBox) hit = obb_overlap(mk(ga->p0, ga->p1, ga->p2), mk(gb->p0, gb->p1, gb->p2), rel, 0.f);
-          else {
-            const V3 zb = mk(rel.m[2], rel.m[6], rel.m[10]), tb = trans(rel);
-            const V3 wo = seg_seg_witness(mk(0.f, 0.f, -ga->s_out), mk(0.f, 0.f, 2.f * ga->s_out), tb - zb * gb->s_out, zb * (2.f * gb->s_out));
-            if (dot(wo, wo) <= pr.rsum_out * pr.rsum_out) {
-              const V3 v0 = seg_seg_witness(mk(0.f, 0.f, -ga->s_in), mk(0.f, 0.f, 2.f * ga->s_in), tb - zb * gb->s_in, zb * (2.f * gb->s_in));
-              const float rin = ga->r_in + gb->r_in - pr.slack;
-              if (rin > 0.f && dot(v0, v0) < rin * rin) hit = true;
-              else if (obb_overlap(mk(ga->hx, ga->hy, ga->hz), mk(gb->hx, gb->hy, gb->hz), rel, pr.slack)) {
-                gjk_init(g, rel, swept_radius(ga) + swept_radius(gb), v0);
-                SA = load_shape(ga, w.t.verts);
-                SB = load_shape(gb, w.t.verts);
-                need_gjk = true;
-              }
-            }
-          }
-        }
-      }
-    }
-    // GJK for the few pairs that got this far, one after the other with the WHOLE warp on each:
-    // every lane scans two vertices of a 64-vertex hull and a butterfly picks the support
-    // point, the owner lane runs the simplex update (this kernel is about latency, and a
-    // configuration rarely has more than one or two such pairs).
-    for (unsigned gm = __ballot_sync(FULL, need_gjk); gm; gm &= gm - 1) {
-      const int owner = __ffs(gm) - 1;
-      const bool mine = l == owner;
-      int st = GJK_CONTINUE;
-      while (st == GJK_CONTINUE) {
-        const V3 sa = coop_support<32>(1u << owner, mine, SA, -g.v, w.t.verts);
-        const V3 sb = coop_support<32>(1u << owner, mine, SB, rot_t(g.rel, g.v), w.t.verts);
-        float dist;
-        if (mine) st = gjk_advance(g, sa, sb, false, dist);
-        st = __shfl_sync(FULL, st, owner);
-        if (stop_at_first && __any_sync(FULL, hit)) st = GJK_MISS;  // settled already by another pair
-      }
-      if (mine) hit = hit || st == GJK_HIT;
-    }
-    if (hit) {
-      first = min(first, static_cast<int>(pr.orig));
-      if (want_mask) atomicOr(&w.mask[pr.orig >> 5], 1u << (pr.orig & 31));
-    }
-    // without a first-pair / mask request any hit settles the configuration
-    if (stop_at_first && __any_sync(FULL, hit)) break;
-  }
-  __syncwarp();
-  return __reduce_min_sync(FULL, first);
-}
-
-__device__ __forceinline__ SmallWarp make_small_warp(const Tables& t, float* slab, const WarpSlab& L) {
-  SmallWarp w;
-  w.t = t;
-  w.q = slab + L.off_q; w.act = slab + L.off_act; w.omi = slab + L.off_omi; w.geom = slab + L.off_geom;
-  w.mask = reinterpret_cast<uint32_t*>(slab + L.off_mask);
-  w.lane = threadIdx.x & 31;
-  return w;
-}
-
-__global__ void __launch_bounds__(128, 4) check_warp_kernel(const __grid_constant__ SmallArgs a) {
-  uint64_t* mbar = reinterpret_cast<uint64_t*>(g_smem);
-  unsigned char* tbl = g_smem + 16;
-  stage_tables(tbl, a.img, a.table_bytes, mbar);
-  const Tables t = make_tables(tbl);
-  const int nwarps = blockDim.x >> 5, wid = threadIdx.x >> 5;
-  float* slab = reinterpret_cast<float*>(tbl + a.table_bytes) + static_cast<size_t>(wid) * a.L.words;
-  const SmallWarp w = make_small_warp(t, slab, a.L);
-  const bool actuated = a.flags & RAMP_Q_ACTUATED;
-  const bool want_mask = a.pair_mask != nullptr;
-  // early-out only when nobody asked which pair came first
-  const bool stop = !(a.flags & RAMP_ALL_PAIRS) && !want_mask && a.first_pair == nullptr;
-  const int cols = actuated ? t.h->n_act : t.h->nq;
-  for (int64_t row = static_cast<int64_t>(blockIdx.x) * nwarps + wid; row < a.n; row += static_cast<int64_t>(gridDim.x) * nwarps) {
-    const float* src = a.q + row * a.ld;
-    for (int k = w.lane; k < cols; k += 32) (actuated ? w.act : w.q)[k] = __ldg(src + k);
-    __syncwarp();
-    if (actuated) expand_q_warp(w);
-    const int f = check_one_config(w, stop, want_mask);
-    if (w.lane == 0) {
-      a.hit[row] = f != INT32_MAX;
-      if (a.first_pair) a.first_pair[row] = f != INT32_MAX ? f : -1;
-    }
-    if (want_mask)
-      for (int k = w.lane; k < t.h->mask_words; k += 32) a.pair_mask[row * t.h->mask_words + k] = w.mask[k];
-    __syncwarp();
-  }
-}
-
-// ------------------------------------------------------------- kernel: GJK work queue
-// Drains the queue the validity kernel filled.  Only the tables live in shared memory, so many
-// more warps are resident than in the validity kernel; every lane owns one item and advances
-// it one GJK iteration per trip, fetching the next item of its warp's share when it finishes.
-struct GjkQueueArgs {
-  const unsigned char* img;
-  int32_t table_bytes;
-  const GjkItem* items;
-  uint32_t* count;   // [0] items produced, [1] the consumers' cursor (both zeroed by the host)
-  uint32_t capacity, cap_hard;
-  uint8_t* hit;
-  int32_t* first_pair;
-  uint32_t* pair_mask;
-  int32_t mask_words;
-  int32_t stop;  // early-out semantics: a configuration already hit by an earlier pair is skipped
-  // edge mode (offs != nullptr): `row` is a flat state index; a hit lowers first_invalid[edge]
-  const int64_t* offs;
-  const int32_t* nd;
-  int32_t* first_invalid;
-  int64_t n_edges;
-};
-
-constexpr int kQueueChunk = 32;  // items a warp takes from the queue at a time
-constexpr int kFetchAttempts = 4;
-#ifndef RAMP_GJK_CTAS
-#define RAMP_GJK_CTAS 2
-#endif
-constexpr int kGjkCtasPerSm = RAMP_GJK_CTAS;
-
-#ifdef RAMP_STATS
-__device__ unsigned long long g_stats[64];  // [0] items [1] iterations [2] hits [3] skipped, [8+it] histogram
-#endif
-
-__global__ void __launch_bounds__(256, 2) gjk_queue_kernel(const __grid_constant__ GjkQueueArgs a) {
-  uint64_t* mbar = reinterpret_cast<uint64_t*>(g_smem);
-  unsigned char* tbl = g_smem + 16;
-  stage_tables(tbl, a.img, a.table_bytes, mbar);
-  const Tables t = make_tables(tbl);
-  // hard items first (see GjkQueue): virtual index i -> slot i, or cap_hard + (i - n_hard)
-  const uint32_t n_hard = min(a.count[0], a.cap_hard);
-  const uint32_t total = n_hard + min(a.count[1], a.capacity - a.cap_hard);
-  // Work is handed out dynamically: a warp takes kQueueChunk consecutive items at a time from a
-  // cursor next to the producers' counter, so every warp stays busy until the queue is empty
-  // (iteration counts per item vary from 1 to 48: a static split leaves long tails).
-  uint32_t* cursor = a.count + 2;
-  const int l = threadIdx.x & 31;
-  const unsigned FULL = 0xffffffffu;
-  uint32_t lo = 0, hi = 0, row = 0, p = 0;  // [lo, hi): items this warp holds but has not started
-  bool active = false, drained = false;
-  GjkLane g;
-  GjkShape A, B;
-  A.type = B.type = 0; A.vcnt = B.vcnt = 0; A.p0 = A.p1 = A.p2 = B.p0 = B.p1 = B.p2 = 0.f; A.verts = B.verts = t.verts;
-  g.s.n = 0; g.it = 0; g.vv = 1.f; g.rsum = 0.f; g.lower = 0.f; g.v = mk(1.f, 0.f, 0.f); g.rel = xf_identity();
-  while (true) {
-    // Fill idle lanes.  In early-out mode many items are skipped on arrival (their
-    // configuration was hit meanwhile), so try a few times before running a trip.
-#pragma unroll 1
-    for (int attempt = 0; attempt < kFetchAttempts; ++attempt) {
-      const unsigned need = __ballot_sync(FULL, !active);
-      if (!need || (drained && lo == hi)) break;
-      uint32_t gi = 0xffffffffu;
-      {
-        const uint32_t rank = __popc(need & ((1u << l) - 1)), nneed = __popc(need), avail = hi - lo;
-        if (!active && rank < avail) gi = lo + rank;
-        if (nneed <= avail) {
-          lo += nneed;
-        } else {
-          lo = hi;
-          if (!drained) {
-            uint32_t base = 0;
-            if (l == 0) base = atomicAdd(cursor, static_cast<uint32_t>(kQueueChunk));
-            base = __shfl_sync(FULL, base, 0);
-            if (base >= total) {
-              drained = true;
-            } else {
-              hi = min(base + static_cast<uint32_t>(kQueueChunk), total);
-              const uint32_t r2 = rank - avail;
-              if (!active && rank >= avail && r2 < hi - base) gi = base + r2;
-              lo = min(base + (nneed - avail), hi);
-            }
-          }
-        }
-      }
-      if (gi != 0xffffffffu) {
-        const float4* src = reinterpret_cast<const float4*>(a.items + (gi < n_hard ? gi : a.cap_hard + (gi - n_hard)));
-        const float4 r0 = __ldcs(src), r1 = __ldcs(src + 1), r2 = __ldcs(src + 2), r3 = __ldcs(src + 3), r4 = __ldcs(src + 4);
-        row = __float_as_uint(r3.w);
-        const DPair pr = t.pairs[__float_as_uint(r4.x)];
-        p = static_cast<uint32_t>(pr.orig);  // results report the caller's index
-        bool skip = false;
-        if (a.stop && !a.offs) skip = a.first_pair ? static_cast<uint32_t>(a.first_pair[row]) < p : a.hit[row] != 0;
-#ifdef RAMP_STATS
-        atomicAdd(&g_stats[skip ? 3 : 4], 1ull);
-        if (!skip) { const int va = t.geoms[pr.a].vcnt, vb = t.geoms[pr.b].vcnt; atomicAdd(&g_stats[50 + (va > 16) + 2 * (vb > 16)], 1ull); }
-#endif
-        if (!skip) {
-          const DGeom* ga = &t.geoms[pr.a];
-          const DGeom* gb = &t.geoms[pr.b];
-          A = load_shape(ga, t.verts);
-          B = load_shape(gb, t.verts);
-          Xf rel;
-          rel.m[0] = r0.x; rel.m[1] = r0.y; rel.m[2] = r0.z; rel.m[3] = r0.w;
-          rel.m[4] = r1.x; rel.m[5] = r1.y; rel.m[6] = r1.z; rel.m[7] = r1.w;
-          rel.m[8] = r2.x; rel.m[9] = r2.y; rel.m[10] = r2.z; rel.m[11] = r2.w;
-          gjk_init(g, rel, swept_radius(ga) + swept_radius(gb), mk(r3.x, r3.y, r3.z));
-          active = true;
-        }
-      }
-    }
-    if (!__any_sync(FULL, active)) {
-      if (drained && lo == hi) break;
-      continue;
-    }
-    // Both support scans run with the whole warp converged (idle lanes scan zero vertices):
-    // left to itself the compiler lets lanes with a short vertex list run ahead into the next
-    // scan on their own, and the scans execute twice at partial width.
-    // Once the queue is empty a warp is left with a few long-running items (38 % of the trips
-    // of a UR5 batch ran with 7 of 32 lanes busy): then the idle lanes help with the scans.
-    const unsigned am = __ballot_sync(FULL, active);
-    const int na = __popc(am);
-    V3 sa, sb;
-    if (drained && lo == hi && na <= 8) {
-      const V3 da = -g.v, db = rot_t(g.rel, g.v);
-      if (na <= 4) { sa = coop_support<8>(am, active, A, da, t.verts); sb = coop_support<8>(am, active, B, db, t.verts); }
-      else { sa = coop_support<4>(am, active, A, da, t.verts); sb = coop_support<4>(am, active, B, db, t.verts); }
-    } else {
-      sa = support(A.type, A.p0, A.p1, A.p2, A.verts, active ? A.vcnt : 0, -g.v);
-      __syncwarp();
-      sb = support(B.type, B.p0, B.p1, B.p2, B.verts, active ? B.vcnt : 0, rot_t(g.rel, g.v));
-      __syncwarp();
-    }
-    if (active) {
-      float dist;
-      const int st = gjk_advance(g, sa, sb, false, dist);
-#ifdef RAMP_STATS
-      atomicAdd(&g_stats[1], 1ull);
-      atomicAdd(&g_stats[5], static_cast<unsigned long long>(__popc(__activemask())));
-      atomicAdd(&g_stats[56 + min(g.s.n, 4)], 1ull);
-      if (st != GJK_CONTINUE) { atomicAdd(&g_stats[0], 1ull); atomicAdd(&g_stats[2], st == GJK_HIT ? 1ull : 0ull); atomicAdd(&g_stats[8 + min(g.it, 40)], 1ull); }
-#endif
-      if (st != GJK_CONTINUE) {
-        if (st == GJK_HIT && a.offs) {
-          // edge of flat state `row`: last e with offs[e] <= row; its 1-based index j
-          int64_t lo = 0, hi = a.n_edges - 1;
-          while (lo < hi) {
-            const int64_t mid = (lo + hi + 1) >> 1;
-            if (a.offs[mid] <= static_cast<int64_t>(row)) lo = mid; else hi = mid - 1;
-          }
-          const int j = static_cast<int>(static_cast<int64_t>(row) - a.offs[lo]) + 1;
-          atomicMin(&a.first_invalid[lo], min(j, a.nd[lo]));
-        } else if (st == GJK_HIT) {
-          a.hit[row] = 1;
-          // -1 ("none") is the largest unsigned value, so an unsigned min keeps list order
-          if (a.first_pair) atomicMin(reinterpret_cast<uint32_t*>(a.first_pair) + row, p);
-          if (a.pair_mask) atomicOr(a.pair_mask + static_cast<size_t>(row) * a.mask_words + (p >> 5), 1u << (p & 31));
-        }
-        active = false;
-      }
-    }
-  }
-}
-
-// --------------------------------------------------------------- kernel: FK / placements
-struct FkArgs {
-  const unsigned char* img;
-  const float* q;
-  int64_t n;
-  int32_t ld;
-  uint32_t flags;
-  float* out;
-  int32_t row_floats;  // n_joints*12 or n_geoms*12
-  SlabLayout L;
-};
-
-template <int kWhat>  // 1 = oMi, 2 = oMg
-__global__ void __launch_bounds__(512, 1) fk_kernel(const __grid_constant__ FkArgs a) {
-  uint64_t* mbar = reinterpret_cast<uint64_t*>(g_smem);
-  unsigned char* tbl = g_smem + 16;
-  stage_tables(tbl, a.img, a.L.table_bytes, mbar);
-  const Tables t = make_tables(tbl);
-  const int nwarps = blockDim.x >> 5, wid = threadIdx.x >> 5;
-  float* slab = reinterpret_cast<float*>(tbl + a.L.table_bytes) + static_cast<size_t>(wid) * a.L.words;
-  const Warp w = make_warp(t, slab, a.L);
-  const bool actuated = a.flags & RAMP_Q_ACTUATED;
-  int cols = actuated ? t.h->n_act : t.h->nq;
-  if ((a.ld & 3) == 0 && a.ld <= cols + 3) cols = a.ld;  // padded rows: take the float4 path
-  const int64_t ntiles = (a.n + 31) >> 5;
-  const int64_t tile_step = static_cast<int64_t>(gridDim.x) * nwarps;
-  RowPrefetch<8> pf;
-  prefetch_rows(pf, a.q, (static_cast<int64_t>(blockIdx.x) * nwarps + wid) << 5, a.n, cols, a.ld, w.lane);
-  for (int64_t tile = static_cast<int64_t>(blockIdx.x) * nwarps + wid; tile < ntiles; tile += tile_step) {
-    const int64_t row0 = tile << 5;
-    commit_rows(pf, actuated ? w.act : w.q, a.q, row0, a.n, cols, a.ld, w.lane);
-    prefetch_rows(pf, a.q, (tile + tile_step) << 5, a.n, cols, a.ld, w.lane);
-    if (actuated) expand_q(w);
-    // the bulk stores of the previous tile must have finished READING the staging rows
-    asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
-    __syncwarp();
-    fk_lane<kWhat>(w);
-    if (kWhat == 2) {  // universe-attached geometries have constant placements
-      for (int g = 0; g < t.h->n_geoms; ++g)
-        if (t.geoms[g].gslot < 0) stage_xf(w, g, load_table_xf(t.geoms[g].opl));
-    }
-    // make the generic-proxy writes to shared memory visible to the async (TMA) proxy
-    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-    __syncwarp();
-    // the tile's rows are contiguous in the output: one TMA bulk store for the whole tile when
-    // the staging pitch equals the row length, else one per row (cp.async.bulk, SASS UBLKCP)
-    const int rows = static_cast<int>(imin64(32, a.n - row0));
-    float* dst = a.out + row0 * a.row_floats;
-    const uint32_t row_bytes = static_cast<uint32_t>(a.row_floats) * 4u;
-    if (w.stage_stride * 4 == a.row_floats) {
-      if (w.lane == 0)
-        asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(dst), "r"(smem_u32(w.stage)),
-                     "r"(row_bytes * rows)
-                     : "memory");
-    } else if (w.lane < rows) {
-      asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(dst + static_cast<size_t>(w.lane) * a.row_floats),
-                   "r"(smem_u32(reinterpret_cast<float4*>(w.stage) + w.lane * w.stage_stride)), "r"(row_bytes)
-                   : "memory");
-    }
-    asm volatile("cp.async.bulk.commit_group;" ::: "memory");
-  }
-  asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
-}
-
-// ------------------------------------------------------------- kernel: signed distances
-struct DistArgs {
-  const unsigned char* img;
-  const float* q;
-  int64_t n;
-  int32_t ld;
-  uint32_t flags;
-  const int32_t* sel;  // [n_sel] pair indices (device); nullptr = every pair
-  int32_t n_sel;
-  float* out;          // [n][n_sel]
-  SlabLayout L;
-};
-
-// pinocchio::computeDistance for selected pairs: FK per configuration, then lane l walks the
-// selected pairs of ITS configuration (closed forms, or GJK to convergence + EPA).  Not a
-// throughput kernel: lanes diverge in GJK/EPA and the EPA polytope sits in local memory.
-__global__ void __launch_bounds__(256, 1) distance_kernel(const __grid_constant__ DistArgs a) {
-  uint64_t* mbar = reinterpret_cast<uint64_t*>(g_smem);
-  unsigned char* tbl = g_smem + 16;
-  stage_tables(tbl, a.img, a.L.table_bytes, mbar);
-  const Tables t = make_tables(tbl);
-  const int nwarps = blockDim.x >> 5, wid = threadIdx.x >> 5;
-  float* slab = reinterpret_cast<float*>(tbl + a.L.table_bytes) + static_cast<size_t>(wid) * a.L.words;
-  const Warp w = make_warp(t, slab, a.L);
-  const bool actuated = a.flags & RAMP_Q_ACTUATED;
-  int cols = actuated ? t.h->n_act : t.h->nq;
-  if ((a.ld & 3) == 0 && a.ld <= cols + 3) cols = a.ld;
-  const int64_t ntiles = (a.n + 31) >> 5;
-  for (int64_t tile = static_cast<int64_t>(blockIdx.x) * nwarps + wid; tile < ntiles;
-       tile += static_cast<int64_t>(gridDim.x) * nwarps) {
-    const int64_t row0 = tile << 5;
-    load_rows(actuated ? w.act : w.q, a.q, row0, a.n, cols, a.ld, w.lane);
-    if (actuated) expand_q(w);
-    fk_lane<0>(w);
-    __syncwarp();
-    const int64_t row = row0 + w.lane;
-    for (int k = 0; k < a.n_sel; ++k) {
-      const DPair pr = t.pairs[a.sel ? a.sel[k] : k];  // sel holds processing indices
-      const int col = a.sel ? k : pr.orig;
-      const DGeom* ga = &t.geoms[pr.a];
-      const DGeom* gb = &t.geoms[pr.b];
-      const Xf rel = xf_inv_mul(geom_xf(w, ga->gslot, w.lane), geom_xf(w, gb->gslot, w.lane));
-      const int cls = pair_class_of(ga->type, gb->type);  // also for inactive pairs
-      float d = cls < kClsBoxBox ? closed_form_dist(cls, ga, gb, rel)
-                                 : gjk_signed_distance(load_shape(ga, t.verts), load_shape(gb, t.verts), rel,
-                                                       swept_radius(ga) + swept_radius(gb));
-      if (row < a.n) a.out[row * a.n_sel + col] = d;
-    }
-    __syncwarp();
-  }
-}
-
-// ------------------------------------------------------------------ kernels: edges
-// OMPL state-space maths in FP32 (reference: OMPL RealVector/SO2/SO3 spaces).
-#define RAMP_PI_F 3.14159265358979323846f
-
-__device__ __forceinline__ float so2_dist(float a, float b) {
-  const float d = fabsf(a - b);
-  return d > RAMP_PI_F ? 2.f * RAMP_PI_F - d : d;
-}
-
-__device__ __forceinline__ float so2_interp(float from, float to, float t) {
-  float diff = to - from, v;
-  if (fabsf(diff) <= RAMP_PI_F) v = fmaf(diff, t, from);
-  else {
-    diff = diff > 0.f ? 2.f * RAMP_PI_F - diff : -2.f * RAMP_PI_F - diff;
-    v = from - diff * t;
-    if (v > RAMP_PI_F) v -= 2.f * RAMP_PI_F;
-    else if (v < -RAMP_PI_F) v += 2.f * RAMP_PI_F;
-  }
-  return v;
-}
-
-__device__ __forceinline__ float so3_arc(const float* a, const float* b, int st) {
-  const float dq = fabsf(a[0] * b[0] + a[st] * b[st] + a[2 * st] * b[2 * st] + a[3 * st] * b[3 * st]);
-  return dq > 1.f - 1e-7f ? 0.f : acosf(dq);
-}
-
-__device__ __forceinline__ int seg_count(float dist, float inv_lvs) { return static_cast<int>(ceilf(dist * inv_lvs)); }
-
-// validSegmentCount of one edge; q0/q1 are the edge's rows in global memory
-__device__ __forceinline__ int edge_nd(const DSpace& sp, const float* __restrict__ q0, const float* __restrict__ q1) {
-  int nd = 0;
-  for (int i = 0; i < sp.n_sub; ++i) {
-    const DSub& s = sp.sub[i];
-    const float* a = q0 + s.col;
-    const float* b = q1 + s.col;
-    int c = 0;
-    const int nreal = s.type == RAMP_SPACE_REAL ? s.dim : (s.type == RAMP_SPACE_SE2 ? 2 : (s.type == RAMP_SPACE_SE3 ? 3 : 0));
-    if (nreal) {
-      float e = 0.f;
-      for (int k = 0; k < nreal; ++k) { const float d = a[k] - b[k]; e = fmaf(d, d, e); }
-      c = seg_count(sqrtf(e), s.inv_lvs_real);
-    }
-    if (s.type == RAMP_SPACE_SO2) c = seg_count(so2_dist(a[0], b[0]), s.inv_lvs_rot);
-    else if (s.type == RAMP_SPACE_SE2) c = max(c, seg_count(so2_dist(a[2], b[2]), s.inv_lvs_rot));
-    else if (s.type == RAMP_SPACE_SE3) c = max(c, seg_count(so3_arc(a + 3, b + 3, 1), s.inv_lvs_rot));
-    else if (s.type == RAMP_SPACE_SO3) c = seg_count(so3_arc(a, b, 1), s.inv_lvs_rot);
-    nd = max(nd, c);
-  }
-  return nd;
-}
-
-struct EdgeArgs {
-  const unsigned char* img;
-  const float* q0;
-  const float* q1;
-  int64_t n_edges;
-  int32_t ld;
-  uint8_t* valid;
-  int32_t* first_invalid;  // always non-null inside the library (scratch when the caller passes none)
-  int32_t* nd;             // idem
-  int64_t* offs;           // [n_edges+1] exclusive prefix of per-edge state counts (scratch)
-  GjkQueue gq;
-  SlabLayout L;
-  DSpace sp;
-};
-
-// pass 1: nd per edge, number of states to check per edge (nd interior+end states, >= 1)
-__global__ void edge_count_kernel(const __grid_constant__ EdgeArgs a) {
-  const int64_t e = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
-  if (e >= a.n_edges) return;
-  const int nd = edge_nd(a.sp, a.q0 + e * a.ld, a.q1 + e * a.ld);
-  a.nd[e] = nd;
-  a.first_invalid[e] = INT32_MAX;
-  a.offs[e + 1] = max(nd, 1);
-}
-
-// pass 2: in-place inclusive scan of offs[1..n] by one CTA (offs[0] = 0)
-__global__ void __launch_bounds__(1024) edge_scan_kernel(int64_t* offs, int64_t n) {
-  __shared__ int64_t part[1024];
-  const int t = threadIdx.x;
-  const int64_t per = (n + 1023) / 1024, lo = imin64(n, t * per), hi = imin64(n, lo + per);
-  int64_t s = 0;
-  for (int64_t i = lo; i < hi; ++i) s += offs[i + 1];
-  part[t] = s;
-  __syncthreads();
-  for (int d = 1; d < 1024; d <<= 1) {
-    const int64_t v = t >= d ? part[t - d] : 0;
-    __syncthreads();
-    part[t] += v;
-    __syncthreads();
-  }
-  int64_t run = t ? part[t - 1] : 0;
-  if (t == 0) offs[0] = 0;
-  for (int64_t i = lo; i < hi; ++i) {
-    run += offs[i + 1];
-    offs[i + 1] = run;
-  }
-}
-
-// pass 3: every warp tile is 32 consecutive (edge, j) states of the flattened list
-__global__ void __launch_bounds__(512, 1) edge_check_kernel(const __grid_constant__ EdgeArgs a) {
-  uint64_t* mbar = reinterpret_cast<uint64_t*>(g_smem);
-  unsigned char* tbl = g_smem + 16;
-  stage_tables(tbl, a.img, a.L.table_bytes, mbar);
-  const Tables t = make_tables(tbl);
-  const int nwarps = blockDim.x >> 5, wid = threadIdx.x >> 5;
-  float* slab = reinterpret_cast<float*>(tbl + a.L.table_bytes) + static_cast<size_t>(wid) * a.L.words;
-  const Warp w = make_warp(t, slab, a.L);
-  const int l = w.lane;
-  const int64_t total = a.offs[a.n_edges];
-  const int64_t ntiles = (total + 31) >> 5;
-  for (int64_t tile = static_cast<int64_t>(blockIdx.x) * nwarps + wid; tile < ntiles;
-       tile += static_cast<int64_t>(gridDim.x) * nwarps) {
-    const int64_t s = (tile << 5) + l;
-    const bool live = s < total;
-    // edge of state s: last e with offs[e] <= s
-    int64_t lo = 0, hi = a.n_edges - 1;
-    const int64_t ss = live ? s : total - 1;
-    while (lo < hi) {
-      const int64_t mid = (lo + hi + 1) >> 1;
-      if (a.offs[mid] <= ss) lo = mid; else hi = mid - 1;
-    }
-    const int64_t e = lo;
-    const int nd = a.nd[e];
-    const int j = static_cast<int>(ss - a.offs[e]) + 1;  // 1..max(nd,1); j >= nd means q1 itself
-    const float* r0 = a.q0 + e * a.ld;
-    const float* r1 = a.q1 + e * a.ld;
-    const bool is_end = j >= nd;
-    const float tt = is_end ? 1.f : static_cast<float>(j) / static_cast<float>(nd);
-    // an edge already known to be invalid at a smaller j needs no further states
-    bool skip = !live || a.first_invalid[e] < min(j, nd);
-    bool in_bounds = true;
-    for (int i = 0; i < a.sp.n_sub; ++i) {
-      const DSub& sb = a.sp.sub[i];
-      const float* p0 = r0 + sb.col;
-      const float* p1 = r1 + sb.col;
-      float* o = w.act + sb.col * 32 + l;
-      const int nreal = sb.type == RAMP_SPACE_REAL ? sb.dim : (sb.type == RAMP_SPACE_SE2 ? 2 : (sb.type == RAMP_SPACE_SE3 ? 3 : 0));
-      for (int k = 0; k < nreal; ++k) {
-        const float v = is_end ? p1[k] : fmaf(p1[k] - p0[k], tt, p0[k]);
-        o[k * 32] = v;
-        in_bounds = in_bounds && v <= sb.hi[k] && v >= sb.lo[k];
-      }
-      if (sb.type == RAMP_SPACE_SO2 || sb.type == RAMP_SPACE_SE2) {
-        const int k = sb.type == RAMP_SPACE_SE2 ? 2 : 0;
-        const float v = is_end ? p1[k] : so2_interp(p0[k], p1[k], tt);
-        o[k * 32] = v;
-        in_bounds = in_bounds && v <= RAMP_PI_F && v >= -RAMP_PI_F;
-      } else if (sb.type == RAMP_SPACE_SE3 || sb.type == RAMP_SPACE_SO3) {
-        const int k0 = sb.type == RAMP_SPACE_SE3 ? 3 : 0;
-        const float* qa = p0 + k0;
-        const float* qb = p1 + k0;
-        float out[4] = {qb[0], qb[1], qb[2], qb[3]};
-        if (!is_end) {
-          const float th = so3_arc(qa, qb, 1);
-          if (th > 1e-7f) {
-            const float d = 1.f / sinf(th), s0 = sinf((1.f - tt) * th);
-            float s1 = sinf(tt * th);
-            if (qa[0] * qb[0] + qa[1] * qb[1] + qa[2] * qb[2] + qa[3] * qb[3] < 0.f) s1 = -s1;
-            for (int k = 0; k < 4; ++k) out[k] = (qa[k] * s0 + qb[k] * s1) * d;
-          } else {
-            for (int k = 0; k < 4; ++k) out[k] = qa[k];
-          }
-        }
-        for (int k = 0; k < 4; ++k) o[(k0 + k) * 32] = out[k];
-      }
-    }
-    __syncwarp();
-    expand_q(w);
-    reset_results(w, 0);
-    fk_lane<0>(w);
-    __syncwarp();
-    narrow_phase(w, true, true, false, a.gq, static_cast<uint32_t>(tile << 5));
-    const bool invalid = w.first[l] != INT32_MAX || (a.sp.check_bounds && !in_bounds);
-    if (!skip && invalid) atomicMin(&a.first_invalid[e], min(j, nd));
-    __syncwarp();
-  }
-}
-
-// ---- latency mode for a handful of edges (one planner query calls checkMotion edge by
-// edge): ONE launch, one warp per interpolated state.  Every warp recomputes the (tiny) segment
-// counts of all edges, picks its states, and the last warp to finish folds the per-edge minima
-// into the outputs.  `work` = 33 ints pre-set to 0x7f7f7f7f: [e] smallest invalid j, [32] a
-// counter of finished states.
-constexpr int kSmallEdges = 32;
-constexpr int32_t kWorkInit = 0x7f7f7f7f;
-
-struct EdgeSmallArgs {
-  const unsigned char* img;
-  int32_t table_bytes;
-  const float* q0;
-  const float* q1;
-  int32_t n_edges;
-  int32_t ld;
-  uint8_t* valid;
-  int32_t* first_invalid;  // nullable
-  int32_t* nd;             // nullable
-  int32_t* work;
-  WarpSlab L;
-  DSpace sp;
-};
-
-__global__ void __launch_bounds__(128) edge_warp_kernel(const __grid_constant__ EdgeSmallArgs a) {
-  uint64_t* mbar = reinterpret_cast<uint64_t*>(g_smem);
-  unsigned char* tbl = g_smem + 16;
-  stage_tables(tbl, a.img, a.table_bytes, mbar);
-  const Tables t = make_tables(tbl);
-  const int nwarps = blockDim.x >> 5, wid = threadIdx.x >> 5;
-  float* slab = reinterpret_cast<float*>(tbl + a.table_bytes) + static_cast<size_t>(wid) * a.L.words;
-  const SmallWarp w = make_small_warp(t, slab, a.L);
-  const int l = w.lane;
-  const unsigned FULL = 0xffffffffu;
-  // lane e: segment count of edge e, then an inclusive scan of the states per edge
-  const int my_nd = l < a.n_edges ? edge_nd(a.sp, a.q0 + static_cast<int64_t>(l) * a.ld, a.q1 + static_cast<int64_t>(l) * a.ld) : 0;
-  int incl = l < a.n_edges ? max(my_nd, 1) : 0;
-#pragma unroll
-  for (int d = 1; d < 32; d <<= 1) {
-    const int v = __shfl_up_sync(FULL, incl, d);
-    if (l >= d) incl += v;
-  }
-  const int total = __shfl_sync(FULL, incl, 31);
-  const int gw = blockIdx.x * nwarps + wid, gstep = gridDim.x * nwarps;
-  int done = 0;
-  for (int s = gw; s < total; s += gstep, ++done) {
-    const int e = __popc(__ballot_sync(FULL, l < a.n_edges && incl <= s));
-    const int excl = __shfl_sync(FULL, incl, e) - max(__shfl_sync(FULL, my_nd, e), 1);
-    const int nd = __shfl_sync(FULL, my_nd, e);
-    const int j = s - excl + 1;  // 1 .. max(nd, 1); j >= nd is the end state itself
-    const int jj = min(j, nd);
-    if (*reinterpret_cast<volatile int32_t*>(a.work + e) < jj) continue;  // an earlier state already failed
-    const float* r0 = a.q0 + static_cast<int64_t>(e) * a.ld;
-    const float* r1 = a.q1 + static_cast<int64_t>(e) * a.ld;
-    const bool is_end = j >= nd;
-    const float tt = is_end ? 1.f : static_cast<float>(j) / static_cast<float>(nd);
-    bool in_bounds = true;
-    for (int i = l; i < a.sp.n_sub; i += 32) {  // lane i interpolates subspace i
-      const DSub& sb = a.sp.sub[i];
-      const float* p0 = r0 + sb.col;
-      const float* p1 = r1 + sb.col;
-      float* o = w.act + sb.col;
-      const int nreal = sb.type == RAMP_SPACE_REAL ? sb.dim : (sb.type == RAMP_SPACE_SE2 ? 2 : (sb.type == RAMP_SPACE_SE3 ? 3 : 0));
-      for (int k = 0; k < nreal; ++k) {
-        const float v = is_end ? p1[k] : fmaf(p1[k] - p0[k], tt, p0[k]);
-        o[k] = v;
-        in_bounds = in_bounds && v <= sb.hi[k] && v >= sb.lo[k];
-      }
-      if (sb.type == RAMP_SPACE_SO2 || sb.type == RAMP_SPACE_SE2) {
-        const int k = sb.type == RAMP_SPACE_SE2 ? 2 : 0;
-        const float v = is_end ? p1[k] : so2_interp(p0[k], p1[k], tt);
-        o[k] = v;
-        in_bounds = in_bounds && v <= RAMP_PI_F && v >= -RAMP_PI_F;
-      } else if (sb.type == RAMP_SPACE_SE3 || sb.type == RAMP_SPACE_SO3) {
-        const int k0 = sb.type == RAMP_SPACE_SE3 ? 3 : 0;
-        const float* qa = p0 + k0;
-        const float* qb = p1 + k0;
-        float out[4] = {qb[0], qb[1], qb[2], qb[3]};
-        if (!is_end) {
-          const float th = so3_arc(qa, qb, 1);
-          if (th > 1e-7f) {
-            const float dn = 1.f / sinf(th), s0 = sinf((1.f - tt) * th);
-            float s1 = sinf(tt * th);
-            if (qa[0] * qb[0] + qa[1] * qb[1] + qa[2] * qb[2] + qa[3] * qb[3] < 0.f) s1 = -s1;
-            for (int k = 0; k < 4; ++k) out[k] = (qa[k] * s0 + qb[k] * s1) * dn;
-          } else {
-            for (int k = 0; k < 4; ++k) out[k] = qa[k];
-          }
-        }
-        for (int k = 0; k < 4; ++k) o[k0 + k] = out[k];
-      }
-    }
-    in_bounds = __all_sync(FULL, in_bounds);
-    __syncwarp();
-    expand_q_warp(w);
-    bool invalid = a.sp.check_bounds && !in_bounds;
-    if (!invalid) invalid = check_one_config(w, true, false) != INT32_MAX;
-    if (invalid && l == 0) atomicMin(a.work + e, jj);
-    __syncwarp();
-  }
-  // the last warp to hand in its states folds the minima into the outputs
-  __threadfence();
-  unsigned fin = 0;
-  if (l == 0) fin = atomicAdd(reinterpret_cast<unsigned*>(a.work + kSmallEdges), static_cast<unsigned>(done)) + done;
-  fin = __shfl_sync(FULL, fin, 0);
-  if (fin == static_cast<unsigned>(kWorkInit) + static_cast<unsigned>(total) && done > 0 || (total == 0 && gw == 0)) {
-    __threadfence();
-    if (l < a.n_edges) {
-      const int32_t f = *reinterpret_cast<volatile int32_t*>(a.work + l);
-      a.valid[l] = f == kWorkInit;
-      if (a.first_invalid) a.first_invalid[l] = f == kWorkInit ? -1 : f;
-      if (a.nd) a.nd[l] = my_nd;
-    }
-  }
-}
-
-// pass 4: fold the per-edge minimum into the caller's outputs
-__global__ void edge_finish_kernel(const __grid_constant__ EdgeArgs a, int32_t* out_first, int32_t* out_nd) {
-  const int64_t e = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
-  if (e >= a.n_edges) return;
-  const int f = a.first_invalid[e];
-  a.valid[e] = f == INT32_MAX;
-  if (out_first) out_first[e] = f == INT32_MAX ? -1 : f;
-  if (out_nd && out_nd != a.nd) out_nd[e] = a.nd[e];
-}
 
 // ================================================================================= host
 static thread_local char g_err[512] = "";

@@ -111,7 +111,7 @@ def sample_uniform(space: D.SpaceDesc, n: int, rng: np.random.Generator, positio
 # ----------------------------------------------------------------------------------------
 # Host-side (numpy, FP64) statement of the OMPL state-space maths the planner loop needs
 # between validator calls: distance, interpolation, bounds.  The batched
-# validator itself runs these in FP32 on the device (csrc/ramp_b200.cu edge kernels).
+# validator itself runs these in FP32 on the device (csrc/edges.cuh).
 def _so2_dist(a: float, b: float) -> float:
     d = abs(a - b)
     return 2 * np.pi - d if d > np.pi else d
