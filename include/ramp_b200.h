@@ -219,8 +219,10 @@ int ramp_placements_batch(const RampModel* m, const float* d_q, int64_t n,
  *   d_hit[n]        1 if any active pair collides (required)
  *   d_first_pair[n] index of the first colliding pair in list order, -1 if
  *                   none (nullable) == GeometryData.collisionPairIndex
- *   d_min_dist[n]   min over active pairs of the signed distance (nullable;
- *                   implies RAMP_ALL_PAIRS)
+ *   d_min_dist[n]   min over active pairs of the signed distance (nullable).
+ *                   Computed by a second kernel that runs every active pair
+ *                   to convergence (GJK / EPA): correct, but 100x slower than
+ *                   the flags -- ask for it only where clearance is needed
  *   d_pair_mask[n, ceil(n_pairs/32)] bit p set iff pair p collides (nullable;
  *                   implies RAMP_ALL_PAIRS) == collisionResults[p].isCollision()
  * Replaces pinocchio.computeCollisions at src/ramp/robot_state.py:379-392 and

@@ -78,6 +78,7 @@ struct DistArgs {
   const int32_t* sel;  // [n_sel] pair indices (device); nullptr = every pair
   int32_t n_sel;
   float* out;          // [n][n_sel]
+  float* min_out;      // when set: [n] smallest distance over the ACTIVE pairs instead of `out`
   SlabLayout L;
 };
 
@@ -104,9 +105,11 @@ __global__ void __launch_bounds__(256, 1) distance_kernel(const __grid_constant_
     fk_lane<0>(w);
     __syncwarp();
     const int64_t row = row0 + w.lane;
+    float dmin = 3.0e38f;
     for (int k = 0; k < a.n_sel; ++k) {
       const DPair pr = t.pairs[a.sel ? a.sel[k] : k];  // sel holds processing indices
       const int col = a.sel ? k : pr.orig;
+      if (a.min_out && pr.cls == kClsInactive) continue;
       const DGeom* ga = &t.geoms[pr.a];
       const DGeom* gb = &t.geoms[pr.b];
       const Xf rel = xf_inv_mul(geom_xf(w, ga->gslot, w.lane), geom_xf(w, gb->gslot, w.lane));
@@ -114,8 +117,10 @@ __global__ void __launch_bounds__(256, 1) distance_kernel(const __grid_constant_
       float d = cls < kClsBoxBox ? closed_form_dist(cls, ga, gb, rel)
                                  : gjk_signed_distance(load_shape(ga, t.verts), load_shape(gb, t.verts), rel,
                                                        swept_radius(ga) + swept_radius(gb));
-      if (row < a.n) a.out[row * a.n_sel + col] = d;
+      if (a.min_out) dmin = fminf(dmin, d);
+      else if (row < a.n) a.out[row * a.n_sel + col] = d;
     }
+    if (a.min_out && row < a.n) a.min_out[row] = dmin;
     __syncwarp();
   }
 }

@@ -824,6 +824,9 @@ static int ensure_scratch(const RampModel* m, size_t bytes) {
   return RAMP_OK;
 }
 
+static int launch_min_distance(const RampModel* m, const float* d_q, int64_t n, int32_t ld, uint32_t flags, float* d_min,
+                               cudaStream_t st);
+
 }  // namespace ramp
 
 using namespace ramp;
@@ -1029,9 +1032,9 @@ int ramp_check_batch(const RampModel* m, const float* d_q, int64_t n, int32_t ld
   if (int rc = check_q_args(m, d_q, n, ld, flags)) return rc;
   if (n == 0) return RAMP_OK;
   if (!d_hit) return fail(RAMP_ERR_INVALID, "null d_hit");
-  if (d_min_dist) return fail(RAMP_ERR_INVALID, "d_min_dist: use ramp_distance_batch");
   CUDA_TRY(cudaSetDevice(m->device));
-  return launch_check(m, d_q, n, ld, flags, d_hit, d_first_pair, d_pair_mask, static_cast<cudaStream_t>(stream));
+  if (int rc = launch_check(m, d_q, n, ld, flags, d_hit, d_first_pair, d_pair_mask, static_cast<cudaStream_t>(stream))) return rc;
+  return d_min_dist ? launch_min_distance(m, d_q, n, ld, flags, d_min_dist, static_cast<cudaStream_t>(stream)) : RAMP_OK;
 }
 
 // ---- ramp_check_batch_noalloc: the validity check for callers that must not allocate.
@@ -1110,6 +1113,30 @@ int ramp_check_batch_noalloc(const RampModel* m, const float* d_q, int64_t n, in
   return RAMP_OK;
 }
 
+}  // extern "C"
+
+namespace ramp {
+// smallest signed distance over the active pairs per configuration (the d_min_dist output):
+// the distance kernel in reduce mode -- every pair to convergence, so far slower than the flags
+static int launch_min_distance(const RampModel* m, const float* d_q, int64_t n, int32_t ld, uint32_t flags, float* d_min,
+                               cudaStream_t st) {
+  DistArgs a;
+  a.img = m->d_image; a.q = d_q; a.n = n; a.ld = ld; a.flags = flags; a.n_sel = m->hdr.n_pairs; a.out = nullptr; a.sel = nullptr;
+  a.min_out = d_min;
+  int nwarps; size_t smem;
+  if (int rc = plan_slabs(m, 0, m->hdr.n_act, &a.L, &nwarps, &smem, ld)) return rc;
+  nwarps = std::min(nwarps, 8);
+  smem = 16 + a.L.table_bytes + static_cast<size_t>(a.L.words) * 4 * nwarps;
+  if (int rc = set_smem(distance_kernel, smem)) return rc;
+  distance_kernel<<<grid_for(m, (n + 31) / 32, nwarps), nwarps * 32, smem, st>>>(a);
+  g_launches.fetch_add(1, std::memory_order_relaxed);
+  CUDA_TRY(cudaGetLastError());
+  return RAMP_OK;
+}
+}  // namespace ramp
+
+extern "C" {
+
 int ramp_distance_batch(const RampModel* m, const float* d_q, int64_t n, int32_t ld, uint32_t flags, const int32_t* h_pair_idx,
                         int32_t n_sel, float* d_dist, void* stream) {
   if (int rc = check_q_args(m, d_q, n, ld, flags)) return rc;
@@ -1125,6 +1152,7 @@ int ramp_distance_batch(const RampModel* m, const float* d_q, int64_t n, int32_t
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   DistArgs a;
   a.img = m->d_image; a.q = d_q; a.n = n; a.ld = ld; a.flags = flags; a.n_sel = n_sel; a.out = d_dist; a.sel = nullptr;
+  a.min_out = nullptr;
   int32_t* d_sel = nullptr;
   if (h_pair_idx) {
     if (!m->pool) return fail(RAMP_ERR_ALLOC, "no memory pool for the pair selection");
@@ -1334,7 +1362,7 @@ int ramp_check_host(const RampModel* m, const float* h_q, int64_t n, int32_t ld,
   if (int rc = check_q_args(m, h_q, n, ld, flags)) return rc;
   if (n == 0) return RAMP_OK;
   if (!h_hit) return fail(RAMP_ERR_INVALID, "null h_hit");
-  if (h_min_dist) return fail(RAMP_ERR_INVALID, "h_min_dist: use ramp_distance_batch");
+  if (h_min_dist && !m->pool) return fail(RAMP_ERR_ALLOC, "no memory pool for the distance output");
   CUDA_TRY(cudaSetDevice(m->device));
   std::lock_guard<std::mutex> lk(m->mu);
   const int mw = std::max(m->hdr.mask_words, 1);
@@ -1442,6 +1470,23 @@ int ramp_check_host(const RampModel* m, const float* h_q, int64_t n, int32_t ld,
     }
   }
   CUDA_TRY(cudaStreamSynchronize(s_tail));
+  if (h_min_dist) {
+    // smallest signed distance per configuration: the (slow, every pair to convergence) distance
+    // kernel in reduce mode, chunk by chunk through the first q buffer
+    float* d_min = nullptr;
+    if (cudaMallocFromPoolAsync(reinterpret_cast<void**>(&d_min), sizeof(float) * chunk, m->pool, s_tail) != cudaSuccess) {
+      cudaGetLastError();
+      return fail(RAMP_ERR_ALLOC, "cudaMallocFromPoolAsync for the distance output failed");
+    }
+    for (int64_t off = 0; off < n; off += chunk) {
+      const int64_t ns = std::min(chunk, n - off);
+      CUDA_TRY(cudaMemcpyAsync(D, h_q + off * ld, sizeof(float) * ns * ld, cudaMemcpyHostToDevice, s_tail));
+      if (int rc = launch_min_distance(m, reinterpret_cast<const float*>(D), ns, ld, flags, d_min, s_tail)) return rc;
+      CUDA_TRY(cudaMemcpyAsync(h_min_dist + off, d_min, sizeof(float) * ns, cudaMemcpyDeviceToHost, s_tail));
+      CUDA_TRY(cudaStreamSynchronize(s_tail));
+    }
+    CUDA_TRY(cudaFreeAsync(d_min, s_tail));
+  }
   CUDA_TRY(cudaGetLastError());
   return RAMP_OK;
 }

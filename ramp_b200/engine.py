@@ -196,9 +196,10 @@ class GpuModel:
         return out
 
     def check(self, q, *, actuated: bool = False, first_pair: bool = False, pair_mask: bool = False,
-              all_pairs: bool = False, out_hit: torch.Tensor | None = None) -> dict:
+              all_pairs: bool = False, min_dist: bool = False, out_hit: torch.Tensor | None = None) -> dict:
         """Batched computeCollisions (ramp_check_batch).  Returns ``hit`` (bool[N]) and, on
-        request, ``first_pair`` (int32[N], -1 = none) and ``pair_mask`` (bool[N, P])."""
+        request, ``first_pair`` (int32[N], -1 = none), ``pair_mask`` (bool[N, P]) and ``min_dist``
+        (float32[N], smallest signed distance over the active pairs; a much slower kernel)."""
         q = self._q(q)
         n = q.shape[0]
         npairs = self.info()["n_pairs"]
@@ -207,9 +208,12 @@ class GpuModel:
         words = (npairs + 31) // 32
         mask = torch.zeros((n, max(words, 1)), dtype=torch.int32, device=self.device) if pair_mask else None
         flags = (D.Q_ACTUATED if actuated else 0) | (D.ALL_PAIRS if all_pairs or pair_mask else 0)
+        dmin = torch.empty(n, dtype=torch.float32, device=self.device) if min_dist else None
         _check(self.lib.ramp_check_batch(self.handle, q.data_ptr(), n, q.shape[1], flags, hit.data_ptr(), _ptr(first),
-                                         None, _ptr(mask), _stream_ptr(self.device)), "ramp_check_batch")
+                                         _ptr(dmin), _ptr(mask), _stream_ptr(self.device)), "ramp_check_batch")
         res = {"hit": hit.bool()}
+        if dmin is not None:
+            res["min_dist"] = dmin
         if first is not None:
             res["first_pair"] = first
         if mask is not None:
@@ -283,7 +287,7 @@ class GpuModel:
                                         hit.ctypes.data, None, None, None), "ramp_check_host")
 
     def check_host(self, q: np.ndarray, *, actuated: bool = False, first_pair: bool = False,
-                   pair_mask: bool = False) -> dict:
+                   pair_mask: bool = False, min_dist: bool = False) -> dict:
         """Host-buffer call (ramp_check_host): numpy in, numpy out, copies inside the library."""
         q = np.ascontiguousarray(np.atleast_2d(q), dtype=np.float32)
         n = len(q)
@@ -293,10 +297,13 @@ class GpuModel:
         first = np.zeros(n, dtype=np.int32) if first_pair else None
         mask = np.zeros((n, words), dtype=np.uint32) if pair_mask else None
         flags = (D.Q_ACTUATED if actuated else 0) | (D.ALL_PAIRS if pair_mask else 0)
+        dmin = np.zeros(n, dtype=np.float32) if min_dist else None
         vp = lambda a: None if a is None else a.ctypes.data  # noqa: E731
         _check(self.lib.ramp_check_host(self.handle, q.ctypes.data, n, q.shape[1], flags, hit.ctypes.data, vp(first),
-                                        None, vp(mask)), "ramp_check_host")
+                                        vp(dmin), vp(mask)), "ramp_check_host")
         res = {"hit": hit.astype(bool)}
+        if dmin is not None:
+            res["min_dist"] = dmin
         if first is not None:
             res["first_pair"] = first
         if mask is not None:

@@ -455,3 +455,28 @@ def test_host_buffer_call_sections_and_staging(built):
     assert np.array_equal(got["first_pair"], refm["first_pair"].cpu().numpy())
     assert np.array_equal(got["pair_mask"], refm["pair_mask"].cpu().numpy())
     assert np.array_equal(refm["first_pair"].cpu().numpy(), ref_first[:m])
+
+
+def test_min_distance_output(built):
+    """The optional d_min_dist / h_min_dist output of ramp_check_batch / ramp_check_host: smallest
+    signed distance over the ACTIVE pairs (a disabled pair does not count), against the oracle."""
+    from oracle import oracle
+    from ramp_b200 import workloads
+    from ramp_b200.desc import ModelDesc
+
+    rm, _ = _setup("ur5e/configs", "obstacles")
+    q = workloads.sample_q(rm.model, 3000, seed=31)
+    rm.gpu.set_pair_active(3, False)
+    try:
+        got = rm.gpu.check(torch.from_numpy(q).cuda(), min_dist=True)
+        goth = rm.gpu.check_host(q[:, : rm.model.nq].copy(), min_dist=True)
+    finally:
+        rm.gpu.set_pair_active(3, True)
+    pd = oracle.check(ModelDesc(rm.model, rm.collision_model), q[:, : rm.model.nq].astype(np.float64))["pair_dist"]
+    ref = np.delete(pd, 3, axis=1).min(axis=1)
+    d = got["min_dist"].cpu().numpy().astype(np.float64)
+    sep, pen = ref > 1e-4, ref < -1e-4
+    assert (np.abs(d - ref) / (1.0 + np.abs(ref)))[sep].max() < 5e-5
+    assert (np.abs(d - ref) / (1e-3 + 0.02 * np.abs(ref)))[pen].max() < 1.0
+    assert np.array_equal(goth["min_dist"], got["min_dist"].cpu().numpy())
+    assert np.array_equal(goth["hit"], got["hit"].cpu().numpy())
