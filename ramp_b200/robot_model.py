@@ -159,6 +159,29 @@ class RobotModel:
         return self._gpu[0]
 
 
+    # ------------------------------------------------------------------ batched entry points
+    # (SURVEY section 8b "added": the calls a user of the reference makes once per state, for a
+    # whole batch; q rows are Pinocchio configurations, float32 [N, nq] on the host or the device)
+    def check_collisions(self, q):
+        """bool[N]: any enabled pair in collision (batched RobotState.check_collision)."""
+        return self.gpu.check(q)["hit"]
+
+    def forward_kinematics(self, q):
+        """float32[N, J, 3, 4]: oMi of every movable joint (batched pinocchio.forwardKinematics)."""
+        return self.gpu.forward_kinematics(q)
+
+    def check_edges(self, group_name: str, q0, q1, reference_state=None):
+        """(valid bool[E], first_invalid int32[E]): OMPL's DiscreteMotionValidator over E edges
+        between ACTUATED states of ``group_name``; q slots outside the group come from
+        ``reference_state`` (default: the neutral configuration)."""
+        from ramp_b200 import spaces
+
+        ref = None if reference_state is None else reference_state.qpos
+        self.gpu.set_qmap(spaces.make_qmap(self, group_name, ref))
+        res = self.gpu.check_edges(q0, q1, spaces.make_space(self, group_name))
+        return res["valid"], res["first_invalid"]
+
+
 def make_groups(model: Model, configs: dict) -> dict[str, GroupModel]:
     """reference src/ramp/robot_model.py:187-246."""
     groups = {}

@@ -166,3 +166,27 @@ def test_path_clearance_matches_oracle(built):
     assert len(clr) >= len(path) and clr.min() > -1e-4
     # the planned path is already interpolated, so the states coincide with the waypoints
     assert np.allclose(np.sort(clr)[:3], np.sort(res["min_dist"])[:3], atol=5e-5)
+
+
+def test_robot_model_batch_entry_points(built):
+    """RobotModel.check_collisions / forward_kinematics / check_edges (SURVEY 8b "added") agree
+    with the per-state reference-shaped calls."""
+    from ramp_b200 import MotionPlanner, RobotState, load_robot_model, workloads
+
+    rm = load_robot_model("zoo::rrr/configs")
+    start = RobotState.from_named_state(rm, "arm", "home")
+    start.add_object(workloads.reference_capsule())
+    q = workloads.sample_q(rm.model, 64, seed=2)
+    hit = rm.check_collisions(q).cpu().numpy()
+    for i in range(0, 64, 8):
+        s = start.clone()
+        s.qpos = q[i, : rm.model.nq].astype(np.float64)
+        assert s.check_collision() == bool(hit[i])
+    assert tuple(rm.forward_kinematics(q).shape) == (64, rm.model.njoints - 1, 3, 4)
+    planner = MotionPlanner(rm, "arm")
+    planner.set_reference_state(start)
+    rng = np.random.default_rng(0)
+    a, b = rng.uniform(-1.5, 1.5, (32, 3)), rng.uniform(-1.5, 1.5, (32, 3))
+    valid, first = rm.check_edges("arm", a, b, start)
+    for i in range(0, 32, 4):
+        assert planner.validator.checkMotion(a[i], b[i]) == bool(valid[i])
