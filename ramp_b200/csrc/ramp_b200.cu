@@ -645,7 +645,7 @@ static int plan_slabs(const RampModel* m, int stage_row_floats, int act_cols, Sl
   if (fixed + per_warp > static_cast<size_t>(m->max_smem))
     return fail(RAMP_ERR_LIMIT, "model needs %zu B of shared memory per CTA, device allows %d", fixed + per_warp, m->max_smem);
   const int fit = static_cast<int>((m->max_smem - fixed) / per_warp);  // slabs (= teams) that fit
-  const int teams = std::min(std::min(16 / team, 15), fit);
+  const int teams = std::min(16 / team, fit);
   *nwarps = teams * team;
   *smem_bytes = fixed + per_warp * teams;
   return RAMP_OK;
