@@ -724,8 +724,10 @@ static int plan_check(const RampModel* m, int32_t ld, uint32_t flags, int64_t n,
   CheckArgs& a = P->a;
   a.img = m->d_image; a.ld = ld; a.flags = flags; a.row_offset = 0;
   a.gq = GjkQueue{nullptr, nullptr, 0u, 0u};
+  // no actuated rows in this call: their part of the slab is not reserved (one more warp on Panda-sized robots)
+  const int act_cols = (flags & RAMP_Q_ACTUATED) ? m->hdr.n_act : 0;
   int nwarps; size_t smem;
-  if (int rc = plan_slabs(m, 0, m->hdr.n_act, &a.L, &nwarps, &smem, ld)) return rc;
+  if (int rc = plan_slabs(m, 0, act_cols, &a.L, &nwarps, &smem, ld)) return rc;
   // Few slabs fit (a robot with many geometries): let teams of 2 or 4 warps share each slab and
   // split the kinematic tree and the pair list between them -- whichever team size puts the most
   // warps on an SM (H1 stand-in, 20 hulls: 6 slabs -> 6 / 12 / 16 warps: 4.6e8 / 7.6e8 / 8.1e8
@@ -735,13 +737,13 @@ static int plan_check(const RampModel* m, int32_t ld, uint32_t flags, int64_t n,
     SlabLayout L2, L4;
     int w2 = 0, w4 = 0;
     size_t s2 = 0, s4 = 0;
-    const bool ok2 = plan_slabs(m, 0, m->hdr.n_act, &L2, &w2, &s2, ld, 2) == RAMP_OK;
-    const bool ok4 = plan_slabs(m, 0, m->hdr.n_act, &L4, &w4, &s4, ld, 4) == RAMP_OK;
+    const bool ok2 = plan_slabs(m, 0, act_cols, &L2, &w2, &s2, ld, 2) == RAMP_OK;
+    const bool ok4 = plan_slabs(m, 0, act_cols, &L4, &w4, &s4, ld, 4) == RAMP_OK;
     if (ok2 && w2 > nwarps) team = 2;
     if (ok4 && w4 > (team == 2 ? w2 : nwarps)) team = 4;
   }
   if (const char* e = std::getenv("RAMP_B200_TEAM")) { team = std::atoi(e); team = team >= 4 ? 4 : (team >= 2 ? 2 : 1); }  // experiments
-  if (team > 1 && plan_slabs(m, 0, m->hdr.n_act, &a.L, &nwarps, &smem, ld, team) != RAMP_OK) return RAMP_ERR_LIMIT;
+  if (team > 1 && plan_slabs(m, 0, act_cols, &a.L, &nwarps, &smem, ld, team) != RAMP_OK) return RAMP_ERR_LIMIT;
   if (int rc = team == 2 ? set_smem(check_kernel<2>, smem) : (team == 4 ? set_smem(check_kernel<4>, smem) : set_smem(check_kernel<1>, smem))) return rc;
   P->nwarps = nwarps; P->team = team; P->smem = smem;
   P->use_queue = m->pool != nullptr && m->n_gjk_pairs > 0 && n >= kQueueMinRows;
