@@ -100,7 +100,17 @@ __device__ __forceinline__ void narrow_phase(const Warp& w, bool stop_at_first, 
   const unsigned FULL = 0xffffffffu;
   // decided already?  (first = smallest list index that hit so far, INT32_MAX if none)
   auto dead = [&](int first, int orig) { return stop_at_first && first < (stop_any ? INT32_MAX : orig); };
-  for (int chunk = tw * chunk_pairs; chunk < h->n_pairs; chunk += team * chunk_pairs) {
+  // kTeam == 1: the chunks in order.  Teams: every warp takes the next chunk from a counter in
+  // the slab (the word behind the prefetch mbarrier, reset with the results), so a warp that
+  // drew cheap chunks takes more of them -- chunk costs differ by the share of pairs that
+  // survive to stage 2.
+  int* next_chunk = reinterpret_cast<int*>(w.save) - 2;
+  auto take_chunk = [&]() {
+    int c = 0;
+    if (l == 0) c = atomicAdd(next_chunk, chunk_pairs);
+    return __shfl_sync(FULL, c, 0);
+  };
+  for (int chunk = kTeam == 1 ? 0 : take_chunk(); chunk < h->n_pairs; chunk = kTeam == 1 ? chunk + chunk_pairs : take_chunk()) {
     const int chunk_end = min(chunk + chunk_pairs, h->n_pairs);
     const int my_first = w.first[l];
     int qn = 0;
@@ -337,6 +347,7 @@ __device__ __forceinline__ void narrow_phase(const Warp& w, bool stop_at_first, 
 
 __device__ __forceinline__ void reset_results(const Warp& w, int mask_words) {
   w.first[w.lane] = INT32_MAX;
+  if (w.lane == 0) reinterpret_cast<int*>(w.save)[-2] = 0;  // the team's chunk counter
   for (int k = 0; k < mask_words; ++k) w.mask[k * 32 + w.lane] = 0u;
   __syncwarp();
 }

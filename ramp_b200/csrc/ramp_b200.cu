@@ -619,6 +619,7 @@ static int plan_slabs(const RampModel* m, int stage_row_floats, int act_cols, Sl
   const int rounds = std::max(1, (h.n_pairs + team * kChunkPairs - 1) / (team * kChunkPairs));
   L->team = team;
   L->chunk_pairs = team == 1 ? kChunkPairs : std::min(kChunkPairs, std::max(4, ((h.n_pairs + team * rounds - 1) / (team * rounds) + 3) & ~3));
+  if (const char* e = std::getenv("RAMP_B200_TEAM_CHUNK")) if (team > 1) L->chunk_pairs = std::min(kChunkPairs, std::max(4, std::atoi(e) & ~3));  // experiments
   L->queue_words = L->chunk_pairs * kLanes / 2;
   const int region0 = take(std::max(q_words + act_words, stage_row_floats > 0 ? 0 : team * L->queue_words));
   L->off_q = region0;
