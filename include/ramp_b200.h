@@ -286,10 +286,13 @@ int ramp_check_edges_host(const RampModel* m, const float* h_q0, const float* h_
                           int64_t n_edges, int32_t ld, const RampSpaceDesc* h_space,
                           uint8_t* h_valid, int32_t* h_first_invalid, int32_t* h_nd);
 
-/* Host-buffer convenience for the single-state call sites
- * (RobotState.check_collision, src/ramp/robot_state.py:366): copies n rows of
- * h_q to the device, runs ramp_check_batch and copies the results back,
- * synchronously.  Output pointers follow ramp_check_batch (host memory). */
+/* Host-buffer form of ramp_check_batch: the call of the single-state call sites
+ * (RobotState.check_collision, src/ramp/robot_state.py:366) and of callers whose
+ * batches live in host memory.  Rows move to the device in chunks of 2^18 on two
+ * streams while earlier chunks are being checked; results are copied back; the
+ * call returns when everything is done.  Page-locked buffers (ramp_host_alloc)
+ * are used in place, pageable ones are staged.  Output pointers follow
+ * ramp_check_batch (host memory). */
 int ramp_check_host(const RampModel* m, const float* h_q, int64_t n, int32_t ld_q,
                     uint32_t flags, uint8_t* h_hit, int32_t* h_first_pair,
                     float* h_min_dist, uint32_t* h_pair_mask);
