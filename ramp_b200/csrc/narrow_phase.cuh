@@ -93,7 +93,6 @@ template <int kTeam = 1>
 __device__ __forceinline__ void narrow_phase(const Warp& w, bool stop_at_first, bool stop_any, bool want_mask,
                                              const GjkQueue& gq, uint32_t row_base, int tw = 0,
                                              int chunk_pairs_rt = kChunkPairs) {
-  const int team = kTeam;
   const int chunk_pairs = kTeam == 1 ? kChunkPairs : chunk_pairs_rt;
   const ImgHeader* h = w.t.h;
   const int l = w.lane;
