@@ -7,12 +7,13 @@ namespace ramp {
 // ------------------------------------------------------------- kernel: GJK work queue
 // Drains the queue the validity kernel filled.  Only the tables live in shared memory, so many
 // more warps are resident than in the validity kernel; every lane owns one item and advances
-// it one GJK iteration per trip, fetching the next item of its warp's share when it finishes.
+// it one GJK iteration per trip, fetching the next item (from the chunk of 32 its warp last drew
+// from the queue's cursor, hard region first) when it finishes.
 struct GjkQueueArgs {
   const unsigned char* img;
   int32_t table_bytes;
   const GjkItem* items;
-  uint32_t* count;   // [0] items produced, [1] the consumers' cursor (both zeroed by the host)
+  uint32_t* count;   // [0] hard, [1] easy items produced, [2] the consumers' cursor (zeroed by the host)
   uint32_t capacity, cap_hard;
   uint8_t* hit;
   int32_t* first_pair;
