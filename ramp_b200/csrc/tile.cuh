@@ -166,12 +166,12 @@ __device__ __forceinline__ void load_rows(float* dst, const float* __restrict__ 
   __syncwarp();
 }
 
-// ---- software prefetch of the NEXT tile's rows.  Each warp works through load -> FK ->
-// store on its own, so without this the global-load latency of every tile is exposed
-// (long_scoreboard was the top stall of the FK kernel).  The next tile's float4s are fetched
-// into registers before the current tile's arithmetic and committed to shared memory after it.
-// kVec float4 per lane cover rows of up to 4 * kVec floats (8 in the FK kernels, 4 in the
-// register-tight validity kernel; wider rows fall back to the plain load).  Rows must be
+// ---- software prefetch of the NEXT tile's rows (FK kernels; the validity kernels use the TMA
+// prefetch below, which costs no registers).  Each warp works through load -> FK -> store on
+// its own, so without this the global-load latency of every tile is exposed (long_scoreboard
+// was the top stall of the FK kernel).  The next tile's float4s are fetched into registers
+// before the current tile's arithmetic and committed to shared memory after it.  kVec float4
+// per lane cover rows of up to 4 * kVec floats; wider rows take the plain load.  Rows must be
 // contiguous (ld == cols, any width: a tile of 32 rows is then 8 * cols aligned float4, and one
 // float4 may straddle two rows).
 template <int kVec>
