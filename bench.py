@@ -307,7 +307,7 @@ def main() -> None:
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="ur5e_1m")
-    ap.add_argument("--n", type=int, default=0, help="override configurations per step per GPU")
+    ap.add_argument("--n", "--rows", dest="n", type=int, default=0, help="override configurations per step per GPU (--rows under torchrun, whose own parser claims --n)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--kernel", default="check", choices=["check", "fk"], help="fk: time ramp_fk_batch (poses stored)")
     args = ap.parse_args()
