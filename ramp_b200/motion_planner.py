@@ -108,7 +108,7 @@ class MotionPlanner:
         """Batched ``is_state_valid`` on actuated vectors [N, n_act]."""
         self._sync_gpu()
         states = np.atleast_2d(np.asarray(states, dtype=np.float64))
-        inb = np.array([spaces.satisfies_bounds(self.space, s) for s in states])
+        inb = spaces.satisfies_bounds_batch(self.space, states)
         hit = self._robot_model.gpu.check(states.astype(np.float32), actuated=True)["hit"].cpu().numpy()
         return inb & ~hit
 

@@ -223,6 +223,21 @@ def satisfies_bounds(space: D.SpaceDesc, a) -> bool:
     return True
 
 
+def satisfies_bounds_batch(space: D.SpaceDesc, states) -> np.ndarray:
+    """``satisfies_bounds`` for every row of ``states`` [N, n_cols] at once (bool[N])."""
+    a = np.atleast_2d(np.asarray(states, dtype=np.float64))
+    eps = np.finfo(float).eps
+    ok = np.ones(len(a), dtype=bool)
+    for s in space.subspaces:
+        c = s["col"]
+        nreal, rot, off = _parts(s)
+        for k in range(nreal):
+            ok &= (a[:, c + k] - eps <= s["hi"][k]) & (a[:, c + k] + eps >= s["lo"][k])
+        if rot == "so2":
+            ok &= (a[:, c + off] >= -np.pi - eps) & (a[:, c + off] <= np.pi + eps)
+    return ok
+
+
 def maximum_extent(space: D.SpaceDesc) -> float:
     ext = 0.0
     for s in space.subspaces:

@@ -123,3 +123,23 @@ def test_first_invalid_index_implies_both_ompl_overloads():
         assert ok == (first < 0)
         if not ok and nd > 0:
             assert t == pytest.approx((first - 1) / nd)
+
+
+def test_batched_bounds_equal_the_per_state_rule():
+    """spaces.satisfies_bounds_batch is the vectorised form of satisfies_bounds (StateSpace::
+    satisfiesBounds per subspace), including values exactly on a bound."""
+    from ramp_b200 import spaces
+    from ramp_b200.robot_model import load_robot_model
+
+    rng = np.random.default_rng(5)
+    for cfg, group in (("rrr/configs", "arm"), ("rrr/planar_configs", "arm"), ("rrr/floating_configs", "arm")):
+        rm = load_robot_model("zoo::" + cfg)
+        space = spaces.make_space(rm, group)
+        a = spaces.sample_uniform(space, 400, rng)
+        a[::7] *= 1.5  # push some rows out of bounds
+        for s in space.subspaces:  # and some exactly onto a bound
+            if len(s["hi"]) and np.isfinite(s["hi"][0]):
+                a[3, s["col"]] = s["hi"][0]
+        want = np.array([spaces.satisfies_bounds(space, row) for row in a])
+        assert np.array_equal(spaces.satisfies_bounds_batch(space, a), want)
+        assert want.any() and not want.all()
