@@ -190,3 +190,24 @@ def test_robot_model_batch_entry_points(built):
     valid, first = rm.check_edges("arm", a, b, start)
     for i in range(0, 32, 4):
         assert planner.validator.checkMotion(a[i], b[i]) == bool(valid[i])
+
+
+def test_are_states_valid_matches_is_state_valid(built):
+    """MotionPlanner.are_states_valid (vectorised bounds + one batched check) equals
+    is_state_valid state by state (reference src/ramp/motion_planner.py:612-625)."""
+    from ramp_b200 import MotionPlanner, RobotState, load_robot_model, spaces, workloads
+
+    rm = load_robot_model("zoo::rrr/configs")
+    start = RobotState.from_named_state(rm, "arm", "home")
+    start.add_object(workloads.reference_capsule())
+    planner = MotionPlanner(rm, "arm")
+    planner.set_reference_state(start)
+    rng = np.random.default_rng(3)
+    states = spaces.sample_uniform(planner.space, 64, rng)
+    states[::9] *= 3.0  # some out of bounds
+    got = planner.are_states_valid(states)
+    for i in range(0, 64, 3):
+        s = start.clone()
+        s.set_group_qpos("arm", states[i])
+        assert planner.is_state_valid(s) == bool(got[i]), i
+    assert got.any() and not got.all()
