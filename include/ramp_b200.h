@@ -19,10 +19,18 @@
  *     pointers named h_* are caller-owned HOST pointers;
  *   - `stream` is a cudaStream_t passed as void* (0 = the legacy default
  *     stream); d_* calls are asynchronous on it;
- *   - a RampModel is bound to the device it was created on.  It is read-only
- *     during the compute calls (safe from several host threads / streams);
- *     ramp_model_set_scene / ramp_model_set_qmap mutate it and must be
- *     serialised against compute calls by the caller;
+ *   - a RampModel is bound to the device it was created on.  The d_* compute
+ *     calls only read it and take their scratch per call, in stream order,
+ *     from the model's memory pool: they may be issued from several host
+ *     threads and on several streams at once.  The host-buffer calls
+ *     (ramp_check_host, ramp_check_edges_host) share the model's staging
+ *     buffers and take a per-model lock for their whole duration: concurrent
+ *     ones on one model run one after the other.  ramp_model_set_scene /
+ *     ramp_model_set_qmap / ramp_model_set_pair_active mutate the model and
+ *     must be serialised against all compute calls by the caller;
+ *   - the pool keeps what it has handed out once (the GJK work queue of a
+ *     2^21-row slice is the largest block) until ramp_model_trim or
+ *     ramp_model_destroy;
  *   - there is no CPU fallback: without a CUDA device every compute call
  *     fails with RAMP_ERR_CUDA.
  */
@@ -199,6 +207,11 @@ int ramp_model_set_pair_active(RampModel* m, int32_t pair_index, int32_t active)
 
 void ramp_model_destroy(RampModel* m);
 
+/* Give the memory the model's scratch pool holds back to the device (it is kept
+ * between calls so that steady-state calls allocate nothing).  Waits for the
+ * device to go idle first.  No reference counterpart. */
+int ramp_model_trim(RampModel* m);
+
 /* Sizes of the live model: out[0]=nq, [1]=n_joints, [2]=n_geoms (robot+scene),
  * [3]=n_pairs (robot+scene), [4]=n_act (0 if no qmap), [5]=device. */
 int ramp_model_info(const RampModel* m, int32_t out[6]);
@@ -271,6 +284,9 @@ int ramp_distance_batch(const RampModel* m, const float* d_q, int64_t n, int32_t
  *   d_valid[e]         1 iff every checked state is valid (required)
  *   d_first_invalid[e] smallest invalid j, -1 if none (nullable)
  *   d_nd[e]            nd (nullable)
+ * Edges are processed 2^22 at a time.  Should such a slice hold more than
+ * 2^32 - 1 interpolated states (end points far outside the bounds), none of it
+ * is checked and all its edges come back with d_valid = 0, d_first_invalid = -2.
  * Replaces OMPL's implicit DiscreteMotionValidator::checkMotion driving
  * is_ompl_state_valid, src/ramp/motion_planner.py:366,469-483,612-625. */
 int ramp_check_edges(const RampModel* m, const float* d_q0, const float* d_q1,

@@ -96,7 +96,9 @@ __global__ void __launch_bounds__(1024) edge_scan_kernel(int64_t* offs, int64_t 
     __syncthreads();
   }
   int64_t run = t ? part[t - 1] : 0;
-  if (t == 0) offs[0] = 0;
+  // more states than a 32-bit flat index can name: offs[0] = -1 tells the check kernel to do
+  // nothing and the finish kernel to report every edge of the slice as unchecked (-2)
+  if (t == 0) offs[0] = part[1023] > 0xffffffffll ? -1 : 0;
   for (int64_t i = lo; i < hi; ++i) {
     run += offs[i + 1];
     offs[i + 1] = run;
@@ -113,7 +115,7 @@ __global__ void __launch_bounds__(512, 1) edge_check_kernel(const __grid_constan
   float* slab = reinterpret_cast<float*>(tbl + a.L.table_bytes) + static_cast<size_t>(wid) * a.L.words;
   const Warp w = make_warp(t, slab, a.L);
   const int l = w.lane;
-  const int64_t total = a.offs[a.n_edges];
+  const int64_t total = a.offs[0] < 0 ? 0 : a.offs[a.n_edges];
   const int64_t ntiles = (total + 31) >> 5;
   for (int64_t tile = static_cast<int64_t>(blockIdx.x) * nwarps + wid; tile < ntiles;
        tile += static_cast<int64_t>(gridDim.x) * nwarps) {
@@ -176,7 +178,7 @@ __global__ void __launch_bounds__(512, 1) edge_check_kernel(const __grid_constan
     reset_results(w, 0);
     fk_lane<0>(w);
     __syncwarp();
-    narrow_phase(w, true, true, false, a.gq, static_cast<uint32_t>(tile << 5));
+    narrow_phase(w, true, true, false, a.gq, static_cast<uint32_t>(tile << 5), static_cast<int>(imin64(32, total - (tile << 5))));
     const bool invalid = w.first[l] != INT32_MAX || (a.sp.check_bounds && !in_bounds);
     if (!skip && invalid) atomicMin(&a.first_invalid[e], min(j, nd));
     __syncwarp();
@@ -302,7 +304,8 @@ __global__ void __launch_bounds__(128) edge_warp_kernel(const __grid_constant__ 
 __global__ void edge_finish_kernel(const __grid_constant__ EdgeArgs a, int32_t* out_first, int32_t* out_nd) {
   const int64_t e = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
   if (e >= a.n_edges) return;
-  const int f = a.first_invalid[e];
+  const bool unchecked = a.offs[0] < 0;  // the slice held more than 2^32 - 1 states
+  const int f = unchecked ? -2 : a.first_invalid[e];
   a.valid[e] = f == INT32_MAX;
   if (out_first) out_first[e] = f == INT32_MAX ? -1 : f;
   if (out_nd && out_nd != a.nd) out_nd[e] = a.nd[e];

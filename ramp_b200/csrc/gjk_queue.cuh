@@ -20,6 +20,8 @@ struct GjkQueueArgs {
   uint32_t* pair_mask;
   int32_t mask_words;
   int32_t stop;  // early-out semantics: a configuration already hit by an earlier pair is skipped
+  uint32_t n_rows;  // rows of the result arrays: an item whose row lies beyond them is dropped (second line of
+                    // defence; the producers never queue one).  Edge mode: unused
   // edge mode (offs != nullptr): `row` is a flat state index; a hit lowers first_invalid[edge]
   const int64_t* offs;
   const int32_t* nd;
@@ -94,8 +96,8 @@ __global__ void __launch_bounds__(256, 2) gjk_queue_kernel(const __grid_constant
         row = __float_as_uint(r3.w);
         const DPair pr = t.pairs[__float_as_uint(r4.x)];
         p = static_cast<uint32_t>(pr.orig);  // results report the caller's index
-        bool skip = false;
-        if (a.stop && !a.offs) skip = a.first_pair ? static_cast<uint32_t>(a.first_pair[row]) < p : a.hit[row] != 0;
+        bool skip = !a.offs && row >= a.n_rows;
+        if (!skip && a.stop && !a.offs) skip = a.first_pair ? static_cast<uint32_t>(a.first_pair[row]) < p : a.hit[row] != 0;
 #ifdef RAMP_STATS
         atomicAdd(&g_stats[skip ? 3 : 4], 1ull);
         if (!skip) { const int va = t.geoms[pr.a].vcnt, vb = t.geoms[pr.b].vcnt; atomicAdd(&g_stats[50 + (va > 16) + 2 * (vb > 16)], 1ull); }

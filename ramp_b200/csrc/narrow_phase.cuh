@@ -91,7 +91,7 @@ __device__ __forceinline__ bool closed_form_hit(int cls, const DGeom* ga, const 
 // them, in chunks of kChunkPairs -- a compile-time constant on the common path)
 template <int kTeam = 1>
 __device__ __forceinline__ void narrow_phase(const Warp& w, bool stop_at_first, bool stop_any, bool want_mask,
-                                             const GjkQueue& gq, uint32_t row_base, int tw = 0,
+                                             const GjkQueue& gq, uint32_t row_base, int live_rows, int tw = 0,
                                              int chunk_pairs_rt = kChunkPairs) {
   const int chunk_pairs = kTeam == 1 ? kChunkPairs : chunk_pairs_rt;
   const ImgHeader* h = w.t.h;
@@ -111,7 +111,10 @@ __device__ __forceinline__ void narrow_phase(const Warp& w, bool stop_at_first, 
   };
   for (int chunk = kTeam == 1 ? 0 : take_chunk(); chunk < h->n_pairs; chunk = kTeam == 1 ? chunk + chunk_pairs : take_chunk()) {
     const int chunk_end = min(chunk + chunk_pairs, h->n_pairs);
-    const int my_first = w.first[l];
+    // Lanes past the end of the batch hold a replayed row (load_rows): they must never produce
+    // work, or their results and queued GJK items would land behind the caller's arrays.  A
+    // "first hit" of INT32_MIN fails the test in push() in every mode, at no cost in the loop.
+    const int my_first = l < live_rows ? w.first[l] : INT32_MIN;
     int qn = 0;
     // ---- stage 1: bounding spheres; lane = configuration, pair index uniform.  The first 16
     // bytes of a DPair are all this stage reads (one vector load): two byte offsets of the
@@ -123,7 +126,7 @@ __device__ __forceinline__ void narrow_phase(const Warp& w, bool stop_at_first, 
     const unsigned lt = (1u << l) - 1;
     // dead(my_first, orig) as one LOP3 + compare: pass needs my_first >= (orig & lim_and) | lim_or
     const int lim_and = (stop_at_first && !stop_any) ? 0xffff : 0;
-    const int lim_or = stop_at_first ? (stop_any ? INT32_MAX : 0) : INT32_MIN;
+    const int lim_or = stop_at_first ? (stop_any ? INT32_MAX : 0) : INT32_MIN + 1;
     const int item0 = l - (chunk << 5);
     auto push = [&](int p, const int4& r, bool pass) {
       pass = pass && my_first >= ((r.w & lim_and) | lim_or);
@@ -412,8 +415,8 @@ __global__ void __launch_bounds__(512, 1) check_kernel(const __grid_constant__ C
     team_sync();
     // FK is done with the saved transforms: their region takes the next tile's rows
     if (tw == 0) tile_fetch_issue(tf, a.q, (tile + tile_step) << 5, a.n, cols, a.ld, a.L.raw_cols, w.lane);
-    narrow_phase<kTeam>(w, stop, stop && a.first_pair == nullptr, want_mask, a.gq, static_cast<uint32_t>(row0) + a.row_offset, tw,
-                        a.L.chunk_pairs);
+    narrow_phase<kTeam>(w, stop, stop && a.first_pair == nullptr, want_mask, a.gq, static_cast<uint32_t>(row0) + a.row_offset,
+                        static_cast<int>(imin64(32, a.n - row0)), tw, a.L.chunk_pairs);
     team_sync();
     const int64_t row = row0 + w.lane;
     if (tw == 0 && row < a.n) {

@@ -652,9 +652,34 @@ static int plan_slabs(const RampModel* m, int stage_row_floats, int act_cols, Sl
   return RAMP_OK;
 }
 
+// Every kernel that takes dynamic shared memory is opted in to the device maximum ONCE per device,
+// when the first model is created there: launches then only pass their own size, and host threads
+// launching with different sizes cannot race on the attribute.
+constexpr int kMaxDevices = 64;
+static std::mutex g_attr_mu;
+static bool g_attr_done[kMaxDevices] = {};
+
 template <typename K>
-static int set_smem(K kernel, size_t bytes) {
-  CUDA_TRY(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(bytes)));
+static cudaError_t opt_in_smem(K kernel, int bytes) {
+  return cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+}
+
+static int init_kernel_attrs(int device, int max_smem) {
+  if (device < 0 || device >= kMaxDevices) return fail(RAMP_ERR_LIMIT, "device %d: only %d devices supported", device, kMaxDevices);
+  std::lock_guard<std::mutex> lk(g_attr_mu);
+  if (g_attr_done[device]) return RAMP_OK;
+  CUDA_TRY(cudaSetDevice(device));
+  CUDA_TRY(opt_in_smem(check_kernel<1>, max_smem));
+  CUDA_TRY(opt_in_smem(check_kernel<2>, max_smem));
+  CUDA_TRY(opt_in_smem(check_kernel<4>, max_smem));
+  CUDA_TRY(opt_in_smem(gjk_queue_kernel, max_smem));
+  CUDA_TRY(opt_in_smem(check_warp_kernel, max_smem));
+  CUDA_TRY(opt_in_smem(fk_kernel<1>, max_smem));
+  CUDA_TRY(opt_in_smem(fk_kernel<2>, max_smem));
+  CUDA_TRY(opt_in_smem(distance_kernel, max_smem));
+  CUDA_TRY(opt_in_smem(edge_check_kernel, max_smem));
+  CUDA_TRY(opt_in_smem(edge_warp_kernel, max_smem));
+  g_attr_done[device] = true;
   return RAMP_OK;
 }
 
@@ -678,6 +703,7 @@ constexpr int64_t kSliceRows = 1 << 21;
 constexpr int64_t kQueueItemsPerRow = 3;   // capacity (1 hard + 2 easy per row); overflow is handled inside check_kernel
 constexpr int64_t kQueueMinRows = 1024;    // below this a second launch costs more than it saves
 
+constexpr int64_t kEdgeSliceEdges = 1 << 22;  // edges per launch group of ramp_check_edges
 constexpr int64_t kSmallRows = 8192;  // up to here one warp per configuration is faster than 32 per warp
 
 static void plan_warp_slab(const RampModel* m, int cols, WarpSlab* L) {
@@ -701,7 +727,6 @@ static int launch_check_small(const RampModel* m, const float* d_q, int64_t n, i
   const int nwarps = 4;
   const size_t smem = 16 + a.table_bytes + static_cast<size_t>(a.L.words) * 4 * nwarps;
   if (smem > static_cast<size_t>(m->max_smem)) return fail(RAMP_ERR_LIMIT, "model needs %zu B of shared memory per CTA", smem);
-  if (int rc = set_smem(check_warp_kernel, smem)) return rc;
   const int per_sm = static_cast<int>(std::max<size_t>(1, std::min<size_t>(8, (static_cast<size_t>(m->max_smem) + 1024) / (smem + 1024))));
   const int64_t blocks = std::min<int64_t>((n + nwarps - 1) / nwarps, static_cast<int64_t>(m->sm_count) * per_sm);
   check_warp_kernel<<<static_cast<int>(blocks), nwarps * 32, smem, st>>>(a);
@@ -745,12 +770,9 @@ static int plan_check(const RampModel* m, int32_t ld, uint32_t flags, int64_t n,
   }
   if (const char* e = std::getenv("RAMP_B200_TEAM")) { team = std::atoi(e); team = team >= 4 ? 4 : (team >= 2 ? 2 : 1); }  // experiments
   if (team > 1 && plan_slabs(m, 0, act_cols, &a.L, &nwarps, &smem, ld, team) != RAMP_OK) return RAMP_ERR_LIMIT;
-  if (int rc = team == 2 ? set_smem(check_kernel<2>, smem) : (team == 4 ? set_smem(check_kernel<4>, smem) : set_smem(check_kernel<1>, smem))) return rc;
   P->nwarps = nwarps; P->team = team; P->smem = smem;
   P->use_queue = m->pool != nullptr && m->n_gjk_pairs > 0 && n >= kQueueMinRows;
   P->smem_b = 16 + a.L.table_bytes;
-  if (P->use_queue)
-    if (int rc = set_smem(gjk_queue_kernel, P->smem_b)) return rc;
   return RAMP_OK;
 }
 
@@ -782,13 +804,13 @@ static void launch_tiles(const RampModel* m, const CheckPlan& P, const float* d_
 
 // queue kernel; hit/first/mask are the arrays the items' row indices refer to
 static void launch_queue(const RampModel* m, const CheckPlan& P, const GjkQueue& gq, uint8_t* hit, int32_t* first, uint32_t* mask,
-                         cudaStream_t st) {
+                         int64_t rows, cudaStream_t st) {
   GjkQueueArgs b{};
   b.img = m->d_image; b.table_bytes = P.a.L.table_bytes;
   b.items = gq.items; b.count = gq.count; b.capacity = gq.capacity; b.cap_hard = gq.cap_hard;
   b.mask_words = m->hdr.mask_words;
   b.stop = !(P.a.flags & RAMP_ALL_PAIRS) && mask == nullptr;
-  b.hit = hit; b.first_pair = first; b.pair_mask = mask;
+  b.hit = hit; b.first_pair = first; b.pair_mask = mask; b.n_rows = static_cast<uint32_t>(rows);
   gjk_queue_kernel<<<m->sm_count * kGjkCtasPerSm, 256, P.smem_b, st>>>(b);
   g_launches.fetch_add(1, std::memory_order_relaxed);
 }
@@ -810,7 +832,7 @@ static int launch_check(const RampModel* m, const float* d_q, int64_t n, int32_t
     uint32_t* mask = d_mask ? d_mask + off * m->hdr.mask_words : nullptr;
     if (P.use_queue) CUDA_TRY(cudaMemsetAsync(scratch, 0, 16, st));
     launch_tiles(m, P, d_q + off * ld, ns, 0u, hit, first, mask, gq, st);
-    if (P.use_queue) launch_queue(m, P, gq, hit, first, mask, st);
+    if (P.use_queue) launch_queue(m, P, gq, hit, first, mask, ns, st);
   }
   if (scratch) CUDA_TRY(cudaFreeAsync(scratch, st));
   CUDA_TRY(cudaGetLastError());
@@ -824,6 +846,19 @@ static int ensure_scratch(const RampModel* m, size_t bytes) {
   const size_t cap = std::max<size_t>(bytes, 1 << 20);
   if (cudaMalloc(&m->d_scratch, cap) != cudaSuccess) return fail(RAMP_ERR_ALLOC, "cudaMalloc(%zu) for scratch failed", cap);
   m->scratch_cap = cap;
+  return RAMP_OK;
+}
+
+// Per-call scratch in stream order: from the model's pool (kept between calls, so no driver
+// allocation after the first call of a size), else from the device's default pool.  Calls on
+// different streams or host threads get different blocks -- nothing here is shared.
+static int pool_alloc(const RampModel* m, size_t bytes, cudaStream_t st, void** out) {
+  const cudaError_t e = m->pool ? cudaMallocFromPoolAsync(out, bytes, m->pool, st) : cudaMallocAsync(out, bytes, st);
+  if (e != cudaSuccess) {
+    cudaGetLastError();
+    *out = nullptr;
+    return fail(RAMP_ERR_ALLOC, "stream-ordered allocation of %zu B failed: %s", bytes, cudaGetErrorString(e));
+  }
   return RAMP_OK;
 }
 
@@ -906,6 +941,7 @@ int ramp_model_create(const RampModelDesc* d, int device, RampModel** out) {
   if (cudaGetDeviceProperties(&prop, device) != cudaSuccess) { delete m; return fail(RAMP_ERR_CUDA, "cudaGetDeviceProperties failed"); }
   m->sm_count = prop.multiProcessorCount;
   m->max_smem = static_cast<int>(prop.sharedMemPerBlockOptin);
+  if (int rc = init_kernel_attrs(device, m->max_smem)) { delete m; return rc; }
   {  // a private stream-ordered pool that keeps its memory between calls
     cudaMemPoolProps pp{};
     pp.allocType = cudaMemAllocationTypePinned;
@@ -936,12 +972,14 @@ int ramp_model_create(const RampModelDesc* d, int device, RampModel** out) {
 int ramp_model_set_scene(RampModel* m, const RampGeom* geoms, int32_t n_geoms, const int32_t* pairs, int32_t n_pairs,
                          const double* verts, int32_t n_verts) {
   if (!m || n_geoms < 0 || n_pairs < 0 || n_verts < 0) return fail(RAMP_ERR_INVALID, "bad argument");
+  if ((n_geoms > 0 && !geoms) || (n_pairs > 0 && !pairs) || (n_verts > 0 && !verts)) return fail(RAMP_ERR_INVALID, "null array");
+  // validate before touching the model: a rejected scene leaves the previous one in place
+  for (int32_t g = 0; g < n_geoms; ++g)
+    if (geoms[g].parent_joint != -1) return fail(RAMP_ERR_INVALID, "scene objects must be attached to the universe");
   std::lock_guard<std::mutex> lk(m->mu);
   m->scene_geoms.assign(geoms, geoms + n_geoms);
   m->scene_pairs.assign(pairs, pairs + 2 * static_cast<size_t>(n_pairs));
   m->scene_verts.assign(verts, verts + 3 * static_cast<size_t>(n_verts));
-  for (auto& g : m->scene_geoms)
-    if (g.parent_joint != -1) return fail(RAMP_ERR_INVALID, "scene objects must be attached to the universe");
   m->pair_active.resize(m->robot_pairs.size() / 2);  // scene pairs start active
   return build_image(m);
 }
@@ -988,6 +1026,14 @@ void ramp_model_destroy(RampModel* m) {
   delete m;
 }
 
+int ramp_model_trim(RampModel* m) {
+  if (!m) return fail(RAMP_ERR_INVALID, "null model");
+  CUDA_TRY(cudaSetDevice(m->device));
+  CUDA_TRY(cudaDeviceSynchronize());
+  if (m->pool) CUDA_TRY(cudaMemPoolTrimTo(m->pool, 0));
+  return RAMP_OK;
+}
+
 int ramp_model_info(const RampModel* m, int32_t out[6]) {
   if (!m || !out) return fail(RAMP_ERR_INVALID, "null argument");
   out[0] = m->hdr.nq; out[1] = m->hdr.n_joints; out[2] = m->hdr.n_geoms; out[3] = m->hdr.n_pairs;
@@ -1010,10 +1056,8 @@ static int fk_common(const RampModel* m, const float* d_q, int64_t n, int32_t ld
   const int grid = grid_for(m, (n + 31) / 32, nwarps);
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   if (what == 1) {
-    if (int rc = set_smem(fk_kernel<1>, smem)) return rc;
     fk_kernel<1><<<grid, nwarps * 32, smem, st>>>(a);
   } else {
-    if (int rc = set_smem(fk_kernel<2>, smem)) return rc;
     fk_kernel<2><<<grid, nwarps * 32, smem, st>>>(a);
   }
   g_launches.fetch_add(1, std::memory_order_relaxed);
@@ -1060,7 +1104,6 @@ static __device__ __align__(256) unsigned char g_noalloc_queue[kNoAllocQueueByte
 // In host code `g_noalloc_queue` is only a handle for the symbol, not an address a kernel
 // could use: the device address differs per GPU and has to be asked for, once per device,
 // with that device current.
-constexpr int kMaxDevices = 64;
 static unsigned char* g_noalloc_ptr[kMaxDevices] = {};
 static std::mutex g_noalloc_mu;
 
@@ -1097,9 +1140,7 @@ int ramp_check_batch_noalloc(const RampModel* m, const float* d_q, int64_t n, in
   a.hit = d_hit; a.first_pair = d_first_pair; a.pair_mask = d_pair_mask;
   int nwarps; size_t smem;
   if (int rc = plan_slabs(m, 0, m->hdr.n_act, &a.L, &nwarps, &smem, ld)) return rc;
-  if (int rc = set_smem(check_kernel<1>, smem)) return rc;
   const size_t smem_b = 16 + a.L.table_bytes;
-  if (int rc = set_smem(gjk_queue_kernel, smem_b)) return rc;
   // the array still holds the previous call's counter and items: only the counter has to
   // start from zero, the items below it are rewritten before they are read
   CUDA_TRY(cudaMemsetAsync(scratch, 0, 16, st));
@@ -1110,6 +1151,7 @@ int ramp_check_batch_noalloc(const RampModel* m, const float* d_q, int64_t n, in
   b.items = a.gq.items; b.count = a.gq.count; b.capacity = kNoAllocQueueItems; b.cap_hard = a.gq.cap_hard;
   b.hit = d_hit; b.first_pair = d_first_pair; b.pair_mask = d_pair_mask; b.mask_words = m->hdr.mask_words;
   b.stop = !(flags & RAMP_ALL_PAIRS) && d_pair_mask == nullptr;
+  b.n_rows = static_cast<uint32_t>(n);
   gjk_queue_kernel<<<m->sm_count * kGjkCtasPerSm, 256, smem_b, st>>>(b);
   g_launches.fetch_add(2, std::memory_order_relaxed);
   CUDA_TRY(cudaGetLastError());
@@ -1130,7 +1172,6 @@ static int launch_min_distance(const RampModel* m, const float* d_q, int64_t n, 
   if (int rc = plan_slabs(m, 0, m->hdr.n_act, &a.L, &nwarps, &smem, ld)) return rc;
   nwarps = std::min(nwarps, 8);
   smem = 16 + a.L.table_bytes + static_cast<size_t>(a.L.words) * 4 * nwarps;
-  if (int rc = set_smem(distance_kernel, smem)) return rc;
   distance_kernel<<<grid_for(m, (n + 31) / 32, nwarps), nwarps * 32, smem, st>>>(a);
   g_launches.fetch_add(1, std::memory_order_relaxed);
   CUDA_TRY(cudaGetLastError());
@@ -1173,7 +1214,6 @@ int ramp_distance_batch(const RampModel* m, const float* d_q, int64_t n, int32_t
   if (int rc = plan_slabs(m, 0, m->hdr.n_act, &a.L, &nwarps, &smem, ld)) return rc;
   nwarps = std::min(nwarps, 8);
   smem = 16 + a.L.table_bytes + static_cast<size_t>(a.L.words) * 4 * nwarps;
-  if (int rc = set_smem(distance_kernel, smem)) return rc;
   distance_kernel<<<grid_for(m, (n + 31) / 32, nwarps), nwarps * 32, smem, st>>>(a);
   g_launches.fetch_add(1, std::memory_order_relaxed);
   if (d_sel) CUDA_TRY(cudaFreeAsync(d_sel, st));
@@ -1220,68 +1260,80 @@ int ramp_check_edges(const RampModel* m, const float* d_q0, const float* d_q1, i
   a.sp.n_sub = sp->n_sub; a.sp.check_bounds = sp->check_bounds; a.sp.n_cols = n_cols;
   CUDA_TRY(cudaSetDevice(m->device));
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  std::lock_guard<std::mutex> lk(m->mu);
   if (n_edges <= kSmallEdges) {  // a planner's edge-by-edge calls: one launch
-    if (int rc = ensure_scratch(m, 256)) return rc;
+    void* work = nullptr;
+    if (int rc = pool_alloc(m, 256, st, &work)) return rc;
     EdgeSmallArgs b;
     b.img = m->d_image; b.table_bytes = static_cast<int32_t>(align16(m->hdr.total_bytes));
     b.q0 = d_q0; b.q1 = d_q1; b.n_edges = static_cast<int32_t>(n_edges); b.ld = ld;
     b.valid = d_valid; b.first_invalid = d_first_invalid; b.nd = d_nd;
-    b.work = static_cast<int32_t*>(m->d_scratch);
+    b.work = static_cast<int32_t*>(work);
     b.sp = a.sp;
     plan_warp_slab(m, n_cols, &b.L);
     const int nw = 4;
     const size_t smem = 16 + b.table_bytes + static_cast<size_t>(b.L.words) * 4 * nw;
     if (smem > static_cast<size_t>(m->max_smem)) return fail(RAMP_ERR_LIMIT, "model needs %zu B of shared memory per CTA", smem);
-    if (int rc = set_smem(edge_warp_kernel, smem)) return rc;
     CUDA_TRY(cudaMemsetAsync(b.work, 0x7f, (kSmallEdges + 1) * sizeof(int32_t), st));
     // enough warps for a few hundred states at once; every warp loops over its share
     edge_warp_kernel<<<std::min(m->sm_count, 128), nw * 32, smem, st>>>(b);
     g_launches.fetch_add(1, std::memory_order_relaxed);
+    CUDA_TRY(cudaFreeAsync(work, st));
     CUDA_TRY(cudaGetLastError());
     return RAMP_OK;
   }
-  // scratch: offs int64[n+1] | nd int32[n] | first int32[n]
-  const size_t off_nd = align16(sizeof(int64_t) * (n_edges + 1));
-  const size_t off_first = off_nd + align16(sizeof(int32_t) * n_edges);
-  if (int rc = ensure_scratch(m, off_first + align16(sizeof(int32_t) * n_edges))) return rc;
-  unsigned char* S = static_cast<unsigned char*>(m->d_scratch);
-  a.img = m->d_image; a.q0 = d_q0; a.q1 = d_q1; a.n_edges = n_edges; a.ld = ld; a.valid = d_valid;
-  a.offs = reinterpret_cast<int64_t*>(S);
-  a.nd = d_nd ? d_nd : reinterpret_cast<int32_t*>(S + off_nd);
-  a.first_invalid = reinterpret_cast<int32_t*>(S + off_first);
+  // Edges are processed in slices: the flat index of an interpolated state travels as 32 bits in
+  // the GJK work items, and a slice of 2^22 edges stays below 2^32 states for any mean segment
+  // count up to 1023 (edges with both ends inside the bounds have at most ~101).  A slice that
+  // still exceeds it is not checked at all: every one of its edges is reported invalid with
+  // first_invalid = -2 (edge_scan_kernel / edge_finish_kernel), which no valid result can be.
   int nwarps; size_t smem;
   if (int rc = plan_slabs(m, 0, n_cols, &a.L, &nwarps, &smem)) return rc;
-  if (int rc = set_smem(edge_check_kernel, smem)) return rc;
+  const size_t smem_b = 16 + a.L.table_bytes;
+  const int64_t slice = std::min<int64_t>(n_edges, kEdgeSliceEdges);
+  // scratch: offs int64[n+1] | nd int32[n] | first int32[n]
+  const size_t off_nd = align16(sizeof(int64_t) * (slice + 1));
+  const size_t off_first = off_nd + align16(sizeof(int32_t) * slice);
+  void* edge_scratch = nullptr;
+  if (int rc = pool_alloc(m, off_first + align16(sizeof(int32_t) * slice), st, &edge_scratch)) return rc;
+  unsigned char* S = static_cast<unsigned char*>(edge_scratch);
   // GJK work queue (only worth a launch when there are enough edges to fill warps)
-  a.gq = GjkQueue{nullptr, nullptr, 0u, 0u};
-  unsigned char* qmem = nullptr;
-  const bool use_queue = m->pool != nullptr && m->n_gjk_pairs > 0 && n_edges >= 64;
-  GjkQueueArgs b{};
-  size_t smem_b = 0;
+  void* qmem = nullptr;
+  const bool use_queue = m->n_gjk_pairs > 0 && n_edges >= 64;
+  uint32_t cap = 0;
   if (use_queue) {
-    const uint32_t cap = static_cast<uint32_t>(std::min<int64_t>(std::max<int64_t>(1 << 16, n_edges * 64), 1 << 21));
-    const size_t bytes = 256 + static_cast<size_t>(cap) * sizeof(GjkItem);
-    if (cudaMallocFromPoolAsync(reinterpret_cast<void**>(&qmem), bytes, m->pool, st) != cudaSuccess) {
-      cudaGetLastError();
-      return fail(RAMP_ERR_ALLOC, "cudaMallocFromPoolAsync(%zu) for the GJK queue failed", bytes);
+    cap = static_cast<uint32_t>(std::min<int64_t>(std::max<int64_t>(1 << 16, slice * 64), 1 << 21));
+    if (int rc = pool_alloc(m, 256 + static_cast<size_t>(cap) * sizeof(GjkItem), st, &qmem)) {
+      cudaFreeAsync(edge_scratch, st);
+      return rc;
     }
-    CUDA_TRY(cudaMemsetAsync(qmem, 0, 16, st));
-    a.gq = GjkQueue{reinterpret_cast<GjkItem*>(qmem + 256), reinterpret_cast<uint32_t*>(qmem), cap, queue_cap_hard(cap)};
-    smem_b = 16 + a.L.table_bytes;
-    if (int rc = set_smem(gjk_queue_kernel, smem_b)) return rc;
-    b.img = m->d_image; b.table_bytes = a.L.table_bytes; b.items = a.gq.items; b.count = a.gq.count; b.capacity = cap; b.cap_hard = a.gq.cap_hard;
-    b.offs = a.offs; b.nd = a.nd; b.first_invalid = a.first_invalid; b.n_edges = n_edges;
   }
-  const int eb = static_cast<int>((n_edges + 255) / 256);
-  edge_count_kernel<<<eb, 256, 0, st>>>(a);
-  edge_scan_kernel<<<1, 1024, 0, st>>>(a.offs, n_edges);
-  // the number of states is only known on the device: size the grid for the SM count
-  edge_check_kernel<<<m->sm_count, nwarps * 32, smem, st>>>(a);
-  if (use_queue) gjk_queue_kernel<<<m->sm_count * kGjkCtasPerSm, 256, smem_b, st>>>(b);
-  edge_finish_kernel<<<eb, 256, 0, st>>>(a, d_first_invalid, d_nd);
-  g_launches.fetch_add(use_queue ? 5 : 4, std::memory_order_relaxed);
+  a.img = m->d_image; a.ld = ld;
+  a.offs = reinterpret_cast<int64_t*>(S);
+  a.first_invalid = reinterpret_cast<int32_t*>(S + off_first);
+  for (int64_t e0 = 0; e0 < n_edges; e0 += slice) {
+    const int64_t ne = std::min(slice, n_edges - e0);
+    a.q0 = d_q0 + e0 * ld; a.q1 = d_q1 + e0 * ld; a.n_edges = ne; a.valid = d_valid + e0;
+    a.nd = d_nd ? d_nd + e0 : reinterpret_cast<int32_t*>(S + off_nd);
+    a.gq = GjkQueue{nullptr, nullptr, 0u, 0u};
+    GjkQueueArgs b{};
+    if (use_queue) {
+      unsigned char* Q = static_cast<unsigned char*>(qmem);
+      CUDA_TRY(cudaMemsetAsync(Q, 0, 16, st));
+      a.gq = GjkQueue{reinterpret_cast<GjkItem*>(Q + 256), reinterpret_cast<uint32_t*>(Q), cap, queue_cap_hard(cap)};
+      b.img = m->d_image; b.table_bytes = a.L.table_bytes; b.items = a.gq.items; b.count = a.gq.count; b.capacity = cap; b.cap_hard = a.gq.cap_hard;
+      b.offs = a.offs; b.nd = a.nd; b.first_invalid = a.first_invalid; b.n_edges = ne;
+    }
+    const int eb = static_cast<int>((ne + 255) / 256);
+    edge_count_kernel<<<eb, 256, 0, st>>>(a);
+    edge_scan_kernel<<<1, 1024, 0, st>>>(a.offs, ne);
+    // the number of states is only known on the device: size the grid for the SM count
+    edge_check_kernel<<<m->sm_count, nwarps * 32, smem, st>>>(a);
+    if (use_queue) gjk_queue_kernel<<<m->sm_count * kGjkCtasPerSm, 256, smem_b, st>>>(b);
+    edge_finish_kernel<<<eb, 256, 0, st>>>(a, d_first_invalid ? d_first_invalid + e0 : nullptr, d_nd ? d_nd + e0 : nullptr);
+    g_launches.fetch_add(use_queue ? 5 : 4, std::memory_order_relaxed);
+  }
   if (qmem) CUDA_TRY(cudaFreeAsync(qmem, st));
+  CUDA_TRY(cudaFreeAsync(edge_scratch, st));
   CUDA_TRY(cudaGetLastError());
   return RAMP_OK;
 }
@@ -1297,22 +1349,19 @@ int ramp_check_edges_host(const RampModel* m, const float* h_q0, const float* h_
   CUDA_TRY(cudaSetDevice(m->device));
   const size_t b_q = align16(sizeof(float) * n_edges * ld), b_v = align16(n_edges), b_i = align16(sizeof(int32_t) * n_edges);
   const size_t total = 2 * b_q + b_v + 2 * b_i;
-  unsigned char *D, *H;
-  {
-    std::lock_guard<std::mutex> lk(m->mu);
-    // device staging lives in its own buffer: ramp_check_edges uses d_scratch for its work arrays
-    if (total > m->edge_stage_cap) {
-      if (m->d_edge_stage) cudaFree(m->d_edge_stage);
-      if (m->h_edge_stage) cudaFreeHost(m->h_edge_stage);
-      m->d_edge_stage = nullptr; m->h_edge_stage = nullptr; m->edge_stage_cap = 0;
-      const size_t cap = std::max<size_t>(total, 1 << 16);
-      if (cudaMalloc(&m->d_edge_stage, cap) != cudaSuccess || cudaMallocHost(&m->h_edge_stage, cap) != cudaSuccess)
-        return fail(RAMP_ERR_ALLOC, "staging allocation (%zu B) failed", cap);
-      m->edge_stage_cap = cap;
-    }
-    D = static_cast<unsigned char*>(m->d_edge_stage);
-    H = static_cast<unsigned char*>(m->h_edge_stage);
+  // the staging buffers are the model's: one host-buffer call at a time per model
+  std::lock_guard<std::mutex> lk(m->mu);
+  if (total > m->edge_stage_cap) {
+    if (m->d_edge_stage) cudaFree(m->d_edge_stage);
+    if (m->h_edge_stage) cudaFreeHost(m->h_edge_stage);
+    m->d_edge_stage = nullptr; m->h_edge_stage = nullptr; m->edge_stage_cap = 0;
+    const size_t cap = std::max<size_t>(total, 1 << 16);
+    if (cudaMalloc(&m->d_edge_stage, cap) != cudaSuccess || cudaMallocHost(&m->h_edge_stage, cap) != cudaSuccess)
+      return fail(RAMP_ERR_ALLOC, "staging allocation (%zu B) failed", cap);
+    m->edge_stage_cap = cap;
   }
+  unsigned char* D = static_cast<unsigned char*>(m->d_edge_stage);
+  unsigned char* H = static_cast<unsigned char*>(m->h_edge_stage);
   cudaStream_t st = cudaStreamPerThread;
   std::memcpy(H, h_q0, sizeof(float) * n_edges * ld);
   std::memcpy(H + b_q, h_q1, sizeof(float) * n_edges * ld);
@@ -1453,7 +1502,7 @@ int ramp_check_host(const RampModel* m, const float* h_q, int64_t n, int32_t ld,
       CUDA_TRY(cudaStreamWaitEvent(s_tail, ev_tiles[i], 0));
     }
     if (queued) {
-      launch_queue(m, P, gq, d_hit, d_first, d_mask, s_tail);
+      launch_queue(m, P, gq, d_hit, d_first, d_mask, rows, s_tail);
       CUDA_TRY(cudaFreeAsync(qmem, s_tail));
     }
     unsigned char* Hout = staged ? H + 2 * b_q + par * b_out : nullptr;

@@ -46,6 +46,7 @@ def load_library():
         "ramp_model_set_qmap": (C.c_int, [vp, C.POINTER(D.RampQMap)]),
         "ramp_model_set_pair_active": (C.c_int, [vp, i32, i32]),
         "ramp_model_destroy": (None, [vp]),
+        "ramp_model_trim": (C.c_int, [vp]),
         "ramp_model_info": (C.c_int, [vp, C.POINTER(i32)]),
         "ramp_fk_batch": (C.c_int, [vp, vp, i64, i32, u32, vp, vp]),
         "ramp_placements_batch": (C.c_int, [vp, vp, i64, i32, u32, vp, vp]),
@@ -158,6 +159,10 @@ class GpuModel:
             if self.qmap is not None:
                 _check(self.lib.ramp_model_set_qmap(self.handle, C.byref(self.qmap.struct)), "ramp_model_set_qmap")
         self._scene_sig = sig
+
+    def trim(self) -> None:
+        """Hand the scratch pool's cached memory back to the device (ramp_model_trim)."""
+        _check(self.lib.ramp_model_trim(self.handle), "ramp_model_trim")
 
     def set_qmap(self, qmap: D.QMap) -> None:
         self.qmap = qmap

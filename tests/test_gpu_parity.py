@@ -480,3 +480,74 @@ def test_min_distance_output(built):
     assert (np.abs(d - ref) / (1e-3 + 0.02 * np.abs(ref)))[pen].max() < 1.0
     assert np.array_equal(goth["min_dist"], got["min_dist"].cpu().numpy())
     assert np.array_equal(goth["hit"], got["hit"].cpu().numpy())
+
+
+@pytest.mark.parametrize("n", [8193 + 17, 20001, 300001])
+def test_ragged_batches_never_write_past_the_outputs(built, n):
+    """A batch whose size is not a multiple of 32 leaves lanes of the last warp tile without a
+    configuration; they replay the tile's first row.  That row is made a colliding one here (its
+    hit comes from the GJK stage), so a replayed lane that queued work or stored a result would
+    write behind the caller's arrays.  Outputs are views into canary-filled buffers, through
+    ramp_check_batch, ramp_check_batch_noalloc and ramp_check_host (with first_pair and mask)."""
+    from ramp_b200 import workloads
+    from ramp_b200.engine import pinned_empty
+
+    rm, _ = _setup("ur5e/configs", "obstacles")
+    gpu = rm.gpu
+    npairs = gpu.info()["n_pairs"]
+    words = (npairs + 31) // 32
+    q = workloads.sample_q(rm.model, n, seed=1000 + n)
+    probe = gpu.check(torch.from_numpy(q[:4096]).cuda(), first_pair=True)
+    colliding = torch.nonzero(probe["hit"]).flatten().cpu().numpy()
+    tail0 = (n // 32) * 32
+    q[tail0] = q[colliding[0]]
+    qd = torch.from_numpy(q).cuda()
+    pad = 64
+    stream = torch.cuda.current_stream().cuda_stream
+
+    def canaries():
+        hit = torch.full((n + 2 * pad,), 7, dtype=torch.uint8, device="cuda")
+        first = torch.full((n + 2 * pad,), 12345, dtype=torch.int32, device="cuda")
+        mask = torch.full((n + 2 * pad, words), 0x5A5A5A5A, dtype=torch.int32, device="cuda")
+        return hit, first, mask
+
+    def intact(hit, first, mask):
+        for t, v in ((hit, 7), (first, 12345), (mask, 0x5A5A5A5A)):
+            assert bool((t[:pad] == v).all()) and bool((t[n + pad:] == v).all())
+
+    ref = None
+    for entry in ("ramp_check_batch", "ramp_check_batch_noalloc"):
+        if entry.endswith("noalloc") and n > 32768:
+            continue
+        for with_mask in (False, True):
+            hit, first, mask = canaries()
+            mask[pad : n + pad] = 0
+            args = [gpu.handle, qd.data_ptr(), n, qd.shape[1], 2 if with_mask else 0, hit[pad:].data_ptr(), first[pad:].data_ptr()]
+            if entry == "ramp_check_batch":
+                args.append(None)
+            args += [mask[pad:].data_ptr() if with_mask else None, stream]
+            assert getattr(gpu.lib, entry)(*args) == 0, gpu.lib.ramp_last_error()
+            torch.cuda.synchronize()
+            if not with_mask:
+                mask[pad : n + pad] = 0x5A5A5A5A
+            intact(hit, first, mask)
+            assert int(hit[pad + tail0]) == 1
+            if ref is None:
+                ref = (hit[pad : n + pad].clone(), first[pad : n + pad].clone())
+            assert torch.equal(hit[pad : n + pad], ref[0]) and torch.equal(first[pad : n + pad], ref[1])
+    # host-buffer call: page-locked arrays with canaries around the live range
+    nq = rm.model.nq
+    qh = pinned_empty((n, nq), np.float32)
+    qh[:] = q[:, :nq]
+    hh = pinned_empty((n + 2 * pad,), np.uint8)
+    fh = pinned_empty((n + 2 * pad,), np.int32)
+    mh = pinned_empty((n + 2 * pad, words), np.uint32)
+    hh[:], fh[:], mh[:] = 7, 12345, 0x5A5A5A5A
+    rc = gpu.lib.ramp_check_host(gpu.handle, qh.ctypes.data, n, nq, 2, hh[pad:].ctypes.data, fh[pad:].ctypes.data, None,
+                                 mh[pad:].ctypes.data)
+    assert rc == 0, gpu.lib.ramp_last_error()
+    for a, v in ((hh, 7), (fh, 12345), (mh, 0x5A5A5A5A)):
+        assert (a[:pad] == v).all() and (a[n + pad:] == v).all()
+    assert np.array_equal(hh[pad : n + pad], ref[0].cpu().numpy())
+    # first pair with every pair evaluated == first pair of the early-out call (list order)
+    assert np.array_equal(fh[pad : n + pad], ref[1].cpu().numpy())
