@@ -203,6 +203,61 @@ class _Builder:
             shapes.Convex(pts - centre)))
 
 
+    def prim(self, link, shape, xyz=(0.0, 0.0, 0.0), rpy=(0.0, 0.0, 0.0)):
+        """Attach a primitive shape at an offset in the link frame."""
+        f = self.model.frames[self.body[link]]
+        k = sum(1 for g in self.geom.geometryObjects if g.parentFrame == self.body[link])
+        self.geom.addGeometryObject(GeometryObject(
+            f"{link}_{k}", f.parentJoint, self.body[link], f.placement * SE3(rpy_to_matrix(*rpy), xyz), shape))
+
+
+def _joint_zoo():
+    """One joint of EVERY type of the vocabulary (include/ramp_b200.h RampJointType; reference
+    src/ramp/constants.py:14-23, src/ramp/motion_planner.py:268-362) in one tree with two
+    branches, placements with rotations, a primitive on most links.  Not a robot: a test
+    article for the forward-kinematics code of the rarely used joint types."""
+    b = _Builder("joint_zoo", "root")
+    ua = np.array([1.0, 2.0, -0.5])
+    ua /= np.linalg.norm(ua)
+    ub = np.array([-0.3, 0.4, 0.85])
+    ub /= np.linalg.norm(ub)
+    chain = [  # name, type, xyz, rpy, axis, lower, upper
+        ("j_free", "JointModelFreeFlyer", (0, 0, 0), (0, 0, 0), None, None, None),
+        ("j_rx", "JointModelRX", (0.1, 0, 0.05), (0.2, 0, 0), None, -2.0, 2.0),
+        ("j_ry", "JointModelRY", (0, 0.1, 0.1), (0, 0.3, 0), None, -2.0, 2.0),
+        ("j_rz", "JointModelRZ", (0, 0, 0.15), (0, 0, -0.4), None, -2.0, 2.0),
+        ("j_ru", "JointModelRevoluteUnaligned", (0.05, 0, 0.1), (0.1, 0.2, 0.3), ua, -2.5, 2.5),
+        ("j_rubx", "JointModelRUBX", (0, 0.05, 0.1), (0, 0, 0), None, None, None),
+        ("j_ruby", "JointModelRUBY", (0, 0, 0.12), (0.3, 0, 0), None, None, None),
+        ("j_rubz", "JointModelRUBZ", (0.04, 0, 0.1), (0, -0.2, 0), None, None, None),
+        ("j_rubu", "JointModelRevoluteUnboundedUnaligned", (0, 0, 0.1), (0, 0.1, 0.5), ub, None, None),
+    ]
+    prev = "root"
+    for k, (name, short, xyz, rpy, axis, lo, hi) in enumerate(chain):
+        link = f"l_{name[2:]}"
+        b.joint(name, prev, link, short, xyz, rpy, axis=axis, lower=lo, upper=hi)
+        b.prim(link, shapes.Sphere(0.03) if k % 2 else shapes.Box(0.05, 0.04, 0.06), (0.0, 0.0, 0.03))
+        prev = link
+    # second branch off the free-flying body: prismatic, planar, spherical, ZYX, translation
+    branch = [
+        ("j_px", "JointModelPX", (-0.1, 0, 0), (0, 0, 0.3), None, -0.2, 0.2),
+        ("j_py", "JointModelPY", (0, -0.1, 0.05), (0.2, 0, 0), None, -0.2, 0.2),
+        ("j_pz", "JointModelPZ", (0, 0, -0.1), (0, 0.2, 0), None, -0.2, 0.2),
+        ("j_pu", "JointModelPrismaticUnaligned", (-0.05, 0, -0.05), (0.1, 0.1, 0), ub, -0.2, 0.2),
+        ("j_planar", "JointModelPlanar", (0, -0.05, -0.1), (0.4, 0, 0), None, None, None),
+        ("j_sph", "JointModelSpherical", (0, 0, -0.12), (0, 0, 0.2), None, None, None),
+        ("j_zyx", "JointModelSphericalZYX", (0.03, 0, -0.1), (0, 0.3, 0), None, [-1.5] * 3, [1.5] * 3),
+        ("j_tr", "JointModelTranslation", (0, 0.03, -0.1), (0.2, 0, 0.1), None, [-0.15] * 3, [0.15] * 3),
+    ]
+    prev = "l_free"
+    for k, (name, short, xyz, rpy, axis, lo, hi) in enumerate(branch):
+        link = f"l_{name[2:]}"
+        b.joint(name, prev, link, short, xyz, rpy, axis=axis, lower=lo, upper=hi)
+        b.prim(link, shapes.Capsule(0.02, 0.06) if k % 2 else shapes.Cylinder(0.03, 0.05), (0.0, 0.0, -0.03), (0.3, 0.0, 0.0))
+        prev = link
+    return b
+
+
 def _panda_like(prefix: str, with_hand: bool, name: str):
     b = _Builder(name, f"{prefix}link0")
     h = PI / 2
@@ -371,6 +426,8 @@ def standin(description: str):
         b = _ur5()
     elif description in ("h1_mj_description", "h1_description"):
         b = _h1()
+    elif description == "joint_zoo":
+        b = _joint_zoo()
     else:
         return None
     return b.model, b.geom, b.mimics
@@ -456,6 +513,7 @@ CONFIGS: dict[str, dict] = {
         "acceleration_limits": {j: 1.0 for j in ("shoulder_pan_joint", "shoulder_lift_joint", "elbow_joint",
                                                   "wrist_1_joint", "wrist_2_joint", "wrist_3_joint")},
     },
+    "joint_zoo": {"standin": "joint_zoo", "disabled": [], "bare": True},
     "unitree_h1/configs": {
         "standin": "h1_mj_description", "disabled": _H1_DISABLED,
         "robot": {"base_link": "universe"},

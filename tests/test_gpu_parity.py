@@ -16,7 +16,7 @@ BAND = 1e-4
 
 ZOO = ["rrr/configs", "rrr/planar_configs", "rrr/floating_configs", "planar_rrr/configs", "rrr_mj/configs",
        "acrobot/configs", "double_pendulum", "floating", "planar", "panda/configs", "fr3/configs", "ur5e/configs",
-       "unitree_h1/configs"]
+       "unitree_h1/configs", "joint_zoo"]
 
 
 def _setup(name, scene=None):
@@ -95,7 +95,10 @@ CHECK_CASES = [("rrr/configs", None, 20000), ("rrr/planar_configs", "capsule", 2
                ("rrr/floating_configs", "capsule", 20000), ("rrr_mj/configs", "obstacles", 20000),
                ("planar_rrr/configs", "capsule", 20000), ("floating", "obstacles", 20000),
                ("panda/configs", "capsule", 20000), ("fr3/configs", "capsule", 20000),
-               ("ur5e/configs", "obstacles", 20000), ("unitree_h1/configs", None, 4000)]
+               ("ur5e/configs", "obstacles", 20000), ("unitree_h1/configs", None, 4000),
+               # one joint of every type (RUB-unaligned, Spherical, SphericalZYX, Translation ... included),
+               # on the tile path and on the one-warp-per-configuration path (n <= 8192)
+               ("joint_zoo", "capsule", 20000), ("joint_zoo", "capsule", 3000)]
 
 
 @pytest.mark.parametrize("name,scene,n", CHECK_CASES)
