@@ -8,8 +8,12 @@ conventions as restated in SURVEY App. C.1, so that the reference's in-tree robo
 robots/acrobot/acrobot.xml, robots/floating.urdf, robots/planar.urdf,
 tests/double_pendulum.urdf) load without any third-party wheel.  It replaces
 ``pinocchio.buildModelsFromUrdf`` / ``buildModelsFromMJCF`` / ``xacrodoc`` at
-reference src/ramp/pinocchio_utils.py:209-286 for those files; mesh geometry is not read
-(convex hulls are attached programmatically, see ramp_b200/standins.py).
+reference src/ramp/pinocchio_utils.py:209-286.  Collision meshes (URDF ``<mesh>``, MJCF
+``type="mesh"``) become the convex hull of the file's vertices (ramp_b200.meshes; STL / OBJ,
+``package://`` resolved against the description's directory as the reference's
+``package_dirs`` does); a collision element that cannot be turned into a shape raises
+``RobotDescriptionError`` -- none is ever skipped, a robot with a missing body would answer
+"no collision" where the reference answers "collision".
 """
 
 from __future__ import annotations
@@ -21,7 +25,8 @@ from pathlib import Path
 
 import numpy as np
 
-from ramp_b200 import shapes
+from ramp_b200 import meshes, shapes
+from ramp_b200.exceptions import RobotDescriptionError
 from ramp_b200.kinematics import (
     BODY,
     FIXED_JOINT,
@@ -147,7 +152,9 @@ def _aligned_suffix(axis: np.ndarray) -> str | None:
     return None
 
 
-def _urdf_geometry(geom: ET.Element):
+def _urdf_geometry(geom: ET.Element, link_name: str, base_dir, package_dirs):
+    if geom is None or len(geom) == 0:
+        raise RobotDescriptionError(f"link '{link_name}': <collision> without a <geometry> shape")
     child = next(iter(geom))
     if child.tag == "box":
         return shapes.Box(_floats(child.get("size"), 3))
@@ -157,11 +164,19 @@ def _urdf_geometry(geom: ET.Element):
         return shapes.Sphere(float(child.get("radius")))
     if child.tag == "capsule":
         return shapes.Capsule(float(child.get("radius")), float(child.get("length")))
-    return None  # <mesh>: not read here
+    if child.tag == "mesh":
+        filename = child.get("filename")
+        if not filename:
+            raise RobotDescriptionError(f"link '{link_name}': <mesh> without a filename")
+        path = meshes.resolve_mesh_path(filename, base_dir, package_dirs)
+        return meshes.load_convex(path, _floats(child.get("scale"), 3, 1.0))
+    raise RobotDescriptionError(f"link '{link_name}': unknown collision geometry <{child.tag}>")
 
 
-def build_models_from_urdf(root: ET.Element) -> tuple[Model, GeometryModel, list[dict]]:
-    """URDF element tree -> (Model, collision GeometryModel, mimic records).
+def build_models_from_urdf(root: ET.Element, base_dir=None, package_dirs=()) -> tuple[Model, GeometryModel, list[dict]]:
+    """URDF element tree -> (Model, collision GeometryModel, mimic records).  ``base_dir`` resolves
+    relative mesh paths, ``package_dirs`` the ``package://`` ones (the reference passes the
+    description's own directory, src/ramp/pinocchio_utils.py:240-243).
 
     Pinocchio conventions restated: depth-first from the root link with
     children ordered by joint name (urdfdom keeps joints in a name-sorted map); no root joint
@@ -188,9 +203,7 @@ def build_models_from_urdf(root: ET.Element) -> tuple[Model, GeometryModel, list
     def add_link_geoms(link_name: str, frame_id: int):
         frame = model.frames[frame_id]
         for k, col in enumerate(links[link_name].findall("collision")):
-            geometry = _urdf_geometry(col.find("geometry"))
-            if geometry is None:
-                continue
+            geometry = _urdf_geometry(col.find("geometry"), link_name, base_dir, package_dirs)
             geom_model.addGeometryObject(
                 GeometryObject(f"{link_name}_{k}", frame.parentJoint, frame_id,
                                frame.placement * _origin(col.find("origin")), geometry))
@@ -255,24 +268,54 @@ def _mj_quat(body: ET.Element) -> np.ndarray:
     return np.eye(3)
 
 
-def build_models_from_mjcf(root: ET.Element) -> tuple[Model, GeometryModel, list[dict]]:
-    """MJCF subset (bodies, hinge/slide/free joints, sphere/box/cylinder/capsule geoms,
-    joint default classes for ``range``).  Conventions restated from Pinocchio's MJCF parser:
+def build_models_from_mjcf(root: ET.Element, base_dir=None) -> tuple[Model, GeometryModel, list[dict]]:
+    """MJCF subset (bodies, hinge/slide/free joints, sphere/box/cylinder/capsule/ellipsoid/mesh
+    geoms, joint default classes for ``range``, ``<asset><mesh>`` with ``<compiler meshdir>``).
+    Conventions restated from Pinocchio's MJCF parser:
     geom ``size`` holds half extents (doubled here), a body's frame sits at ``-joint.pos``
     in its joint frame, geoms with contype = conaffinity = 0 are visual only, geometry
     objects are named after the geom (``<body>Geom_<k>`` when unnamed)."""
     assert root.tag == "mujoco", f"not an MJCF: <{root.tag}>"
     model = Model(root.get("model", "mujoco"))
     geom_model = GeometryModel()
-    class_range: dict[str, tuple[float, float]] = {}
-    for d in root.iter("default"):
-        j = d.find("joint")
-        if d.get("class") and j is not None and j.get("range"):
-            r = _floats(j.get("range"), 2)
-            class_range[d.get("class")] = (r[0], r[1])
+    compiler = root.find("compiler")
+    meshdir = compiler.get("meshdir", "") if compiler is not None else ""
+    # default classes: attributes of <joint> / <geom> / <mesh> per class, children inherit from
+    # the enclosing <default>; the class-less top-level <default> is MuJoCo's "main"
+    defaults: dict[str, dict[str, dict[str, str]]] = {"main": {}}
 
-    def visit(body: ET.Element, parent_joint: int, parent_frame: int, parent_placement: SE3):
+    def read_defaults(d: ET.Element, inherited: dict):
+        mine = {k: dict(v) for k, v in inherited.items()}
+        for tag in ("joint", "geom", "mesh"):
+            el = d.find(tag)
+            if el is not None:
+                mine.setdefault(tag, {}).update(el.attrib)
+        defaults[d.get("class") or "main"] = mine
+        for child in d.findall("default"):
+            read_defaults(child, mine)
+
+    for d in root.findall("default"):
+        read_defaults(d, {})
+
+    def attrs(el: ET.Element, childclass: str | None) -> dict[str, str]:
+        """Effective attributes of a joint / geom / mesh element: class defaults, then its own."""
+        cls = el.get("class") or childclass or "main"
+        if cls not in defaults:
+            raise RobotDescriptionError(f"<{el.tag}> refers to default class '{cls}', which is not defined")
+        return {**defaults[cls].get(el.tag, {}), **el.attrib}
+
+    mesh_assets: dict[str, tuple[str, np.ndarray]] = {}
+    for asset in root.findall("asset"):
+        for me in asset.findall("mesh"):
+            ma = attrs(me, None)
+            file = ma.get("file")
+            if file is None:
+                continue  # inline vertex data: rejected where a collision geom asks for it
+            mesh_assets[ma.get("name") or Path(file).stem] = (file, _floats(ma.get("scale"), 3, 1.0))
+
+    def visit(body: ET.Element, parent_joint: int, parent_frame: int, parent_placement: SE3, childclass: str | None = None):
         name = body.get("name")
+        childclass = body.get("childclass") or childclass
         pose = parent_placement * SE3(_mj_quat(body), _floats(body.get("pos"), 3))
         joint_id, frame_placement = parent_joint, pose
         jel = body.find("joint")
@@ -282,9 +325,10 @@ def build_models_from_mjcf(root: ET.Element) -> tuple[Model, GeometryModel, list
             jf = model.addFrame(Frame(fj.get("name", name), joint_id, parent_frame, SE3.Identity(), JOINT))
             parent_frame, frame_placement = jf, SE3.Identity()
         elif jel is not None:
-            jtype = jel.get("type", "hinge")
-            jpos = _floats(jel.get("pos"), 3)
-            axis = _floats(jel.get("axis"), 3, 0.0) if jel.get("axis") else np.array([0.0, 0.0, 1.0])
+            ja = attrs(jel, childclass)
+            jtype = ja.get("type", "hinge")
+            jpos = _floats(ja.get("pos"), 3)
+            axis = _floats(ja.get("axis"), 3, 0.0) if ja.get("axis") else np.array([0.0, 0.0, 1.0])
             suffix = _aligned_suffix(axis)
             if jtype == "hinge":
                 short = f"JointModelR{suffix}" if suffix else "JointModelRevoluteUnaligned"
@@ -294,11 +338,7 @@ def build_models_from_mjcf(root: ET.Element) -> tuple[Model, GeometryModel, list
                 short = "JointModelFreeFlyer"
             else:
                 raise ValueError(f"Unknown joint type: '{jtype}' for joint '{jel.get('name')}'")
-            rng = None
-            if jel.get("range"):
-                rng = tuple(_floats(jel.get("range"), 2))
-            elif jel.get("class") in class_range:
-                rng = class_range[jel.get("class")]
+            rng = tuple(_floats(ja.get("range"), 2)) if ja.get("range") else None
             joint_id = model.addJoint(parent_joint, short, pose * SE3(np.eye(3), jpos), jel.get("name"),
                                       axis=axis / np.linalg.norm(axis),
                                       lower=None if rng is None else rng[0],
@@ -306,11 +346,24 @@ def build_models_from_mjcf(root: ET.Element) -> tuple[Model, GeometryModel, list
             jf = model.addFrame(Frame(jel.get("name"), joint_id, parent_frame, SE3.Identity(), JOINT))
             parent_frame, frame_placement = jf, SE3(np.eye(3), -jpos)
         bid = model.addFrame(Frame(name, joint_id, parent_frame, frame_placement, BODY))
-        for k, g in enumerate(body.findall("geom")):
+        for k, g_el in enumerate(body.findall("geom")):
+            g = attrs(g_el, childclass)
             if g.get("contype") == "0" and g.get("conaffinity") == "0":
                 continue
             gtype = g.get("type", "sphere")
             size = [float(x) for x in g.get("size", "0").split()]
+            fromto_pose = None
+            if g.get("fromto") and gtype in ("capsule", "cylinder"):
+                # the segment between two points: local z along it, half length from its extent
+                ft = _floats(g.get("fromto"), 6)
+                a, b = ft[:3], ft[3:]
+                ez = b - a
+                half = 0.5 * float(np.linalg.norm(ez))
+                ez = ez / (2.0 * half) if half > 0 else np.array([0.0, 0.0, 1.0])
+                ex = np.cross(ez, [1.0, 0.0, 0.0] if abs(ez[0]) < 0.9 else [0.0, 1.0, 0.0])
+                ex /= np.linalg.norm(ex)
+                fromto_pose = SE3(np.column_stack([ex, np.cross(ez, ex), ez]), 0.5 * (a + b))
+                size = [size[0], half]
             if gtype == "sphere":
                 geometry = shapes.Sphere(size[0])
             elif gtype == "box":
@@ -319,13 +372,26 @@ def build_models_from_mjcf(root: ET.Element) -> tuple[Model, GeometryModel, list
                 geometry = shapes.Cylinder(size[0], 2.0 * size[1])
             elif gtype == "capsule":
                 geometry = shapes.Capsule(size[0], 2.0 * size[1])
+            elif gtype == "ellipsoid":
+                geometry = shapes.Ellipsoid(np.asarray(size[:3]))
+            elif gtype == "mesh":
+                mname = g.get("mesh")
+                if mname not in mesh_assets:
+                    raise RobotDescriptionError(f"body '{name}': geom refers to mesh '{mname}', which <asset> does not define by file")
+                file, scale = mesh_assets[mname]
+                mpath = Path(file)
+                if not mpath.is_absolute():
+                    mpath = Path(base_dir or ".") / meshdir / mpath
+                geometry = meshes.load_convex(mpath, scale)
             else:
-                continue  # plane / mesh / hfield are not read
-            gpl = frame_placement * SE3(_mj_quat(g), _floats(g.get("pos"), 3))
+                # plane / hfield / sdf: no finite convex stand-in exists; dropping the body would
+                # turn "collision" answers into "free"
+                raise RobotDescriptionError(f"body '{name}': collision geom of type '{gtype}' is not supported")
+            gpl = frame_placement * (fromto_pose if fromto_pose is not None else SE3(_mj_quat(g), _floats(g.get("pos"), 3)))
             geom_model.addGeometryObject(
                 GeometryObject(g.get("name") or f"{name}Geom_{k}", joint_id, bid, gpl, geometry))
         for child in body.findall("body"):
-            visit(child, joint_id, bid, frame_placement)
+            visit(child, joint_id, bid, frame_placement, childclass)
 
     world = root.find("worldbody")
     for body in world.findall("body"):
@@ -342,8 +408,9 @@ def load_description(path: Path, mappings: dict | None = None):
     """Dispatch on the suffix like reference pinocchio_utils.load_models (:247-273)."""
     path = Path(path)
     if path.suffix in (".xacro", ".urdf"):
-        return build_models_from_urdf(render_xacro(path, mappings))
+        base = path.parent.resolve()
+        return build_models_from_urdf(render_xacro(path, mappings), base, [base])
     if path.suffix == ".xml":
-        return build_models_from_mjcf(ET.parse(path).getroot())
+        return build_models_from_mjcf(ET.parse(path).getroot(), path.parent.resolve())
     msg = f"Unknown robot description file type: {path}"
     raise ValueError(msg)

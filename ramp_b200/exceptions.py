@@ -19,6 +19,12 @@ class RobotDescriptionNotFoundError(Exception):
             "from the network and this build only carries stand-ins for panda, fr3, ur5 and h1.")
 
 
+class RobotDescriptionError(Exception):
+    """A robot description cannot be turned into a model faithfully (an unreadable collision
+    mesh, an unsupported collision geometry ...).  Raised instead of skipping the element: a
+    link that silently loses its collision body makes every answer about it wrong."""
+
+
 class MissingAccelerationLimitError(Exception):
     """Acceleration limits are given for some but not all group joints."""
 

@@ -554,3 +554,32 @@ def test_ragged_batches_never_write_past_the_outputs(built, n):
     assert np.array_equal(hh[pad : n + pad], ref[0].cpu().numpy())
     # first pair with every pair evaluated == first pair of the early-out call (list order)
     assert np.array_equal(fh[pad : n + pad], ref[1].cpu().numpy())
+
+
+def test_mesh_file_robot_gives_the_box_robot_verdicts(built, tmp_path):
+    """URDF <mesh> collision elements (a 12-triangle STL cube and an OBJ cube, scaled) load as
+    convex hulls and the device gives the verdicts of the same robot built from <box> elements,
+    both matching the oracle outside the margin band."""
+    from test_meshes import _write_mesh_robot
+
+    from oracle import oracle
+    from ramp_b200 import workloads
+    from ramp_b200.desc import ModelDesc
+    from ramp_b200.robot_model import load_robot_model
+    from ramp_b200.robot_state import RobotState
+
+    prim_path, mesh_path = _write_mesh_robot(tmp_path)
+    q = np.random.default_rng(9).uniform(-3, 3, (50000, 2)).astype(np.float32)
+    masks = []
+    for path in (prim_path, mesh_path):
+        rm = load_robot_model(path)
+        RobotState(rm).add_object(workloads.reference_capsule())
+        res = rm.gpu.check(torch.from_numpy(q).cuda(), pair_mask=True)
+        ref = oracle.check(ModelDesc(rm.model, rm.collision_model), q.astype(np.float64))
+        out = np.abs(ref["pair_dist"]) > BAND
+        mask = res["pair_mask"].cpu().numpy()
+        assert ((mask == (ref["pair_dist"] <= 1e-12)) | ~out).all()
+        masks.append((mask, out))
+    both = masks[0][1] & masks[1][1]
+    assert (masks[0][0] == masks[1][0])[both].all()
+    assert (masks[0][0].any(axis=0) & ~masks[0][0].all(axis=0)).sum() >= 2
