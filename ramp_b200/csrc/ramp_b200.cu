@@ -65,8 +65,9 @@ static int fail(int code, const char* fmt, ...) {
     if (e_ != cudaSuccess) return fail(RAMP_ERR_CUDA, "%s: %s", #expr, cudaGetErrorString(e_)); \
   } while (0)
 
-struct HostGeom {
-  RampGeom g;
+// bounding / inscribed capsule of a convex vertex set on its principal axis (fit_capsules)
+struct CapsuleFit {
+  double c[3], u[3], s_out, r_out, s_in, r_in;
 };
 
 }  // namespace ramp
@@ -80,6 +81,10 @@ struct RampModel {
   std::vector<RampGeom> robot_geoms, scene_geoms;
   std::vector<int32_t> robot_pairs, scene_pairs;  // flattened [][2]
   std::vector<double> robot_verts, scene_verts;   // [][3]
+  // capsule fits of the convex geometries, by geometry index: computed once per geometry
+  // (brute-force facet enumeration), reused by every later rebuild of the image
+  std::vector<ramp::CapsuleFit> fit_cache;
+  std::vector<uint8_t> fit_valid;
   std::vector<uint8_t> pair_active;   // by the caller's pair index
   std::vector<int32_t> pair_order;    // caller's pair index -> processing index in the image
   // qmap
@@ -164,10 +169,6 @@ static void principal_axis(const std::vector<double>& v, const double* c, double
   }
   if (best <= 0) { u[0] = 0; u[1] = 0; u[2] = 1; }
 }
-
-struct CapsuleFit {
-  double c[3], u[3], s_out, r_out, s_in, r_in;
-};
 
 // Outer capsule: smallest-volume capsule on the principal axis that contains every vertex.
 // Inner capsule: largest-volume capsule on the same axis inside every facet plane of the
@@ -348,7 +349,11 @@ static int build_image(RampModel* m) {
           f.r_out = std::max(P[a], P[b]); f.s_out = std::max(0.0, P[L] - f.r_out);  // contains the ellipsoid
           f.r_in = std::min(P[L], std::min(P[a], P[b]));
         } break;
-        default: f = fit_capsules(core); break;
+        default:  // convex: cached (set_qmap / set_pair_active / set_scene rebuild the image)
+          if (m->fit_valid.size() < static_cast<size_t>(ng)) { m->fit_valid.resize(ng, 0); m->fit_cache.resize(ng); }
+          if (!m->fit_valid[g]) { m->fit_cache[g] = fit_capsules(core); m->fit_valid[g] = 1; }
+          f = m->fit_cache[g];
+          break;
       }
       // F = (Rf, c): new local frame expressed in the old one; z' = capsule axis
       double Rf[3][3] = {{1, 0, 0}, {0, 1, 0}, {0, 0, 1}};
@@ -980,6 +985,7 @@ int ramp_model_set_scene(RampModel* m, const RampGeom* geoms, int32_t n_geoms, c
   m->scene_geoms.assign(geoms, geoms + n_geoms);
   m->scene_pairs.assign(pairs, pairs + 2 * static_cast<size_t>(n_pairs));
   m->scene_verts.assign(verts, verts + 3 * static_cast<size_t>(n_verts));
+  m->fit_valid.resize(m->robot_geoms.size());  // the cached capsule fits of the old scene objects
   m->pair_active.resize(m->robot_pairs.size() / 2);  // scene pairs start active
   return build_image(m);
 }

@@ -55,6 +55,14 @@ WORKLOADS = {
                        "H1 stand-in, floating base, self-collision, 16M configs"),
     "panda_64m": Workload("panda_64m", "panda/configs", "capsule", 1 << 26, "arm",
                           "Panda stand-in convex GJK, 64M configs sharded over the GPUs"),
+    # the same robots with NON-capsule link hulls (rounded boxes, elbows, plates, blobs): the
+    # inscribed capsules fill far less of such hulls, so many more pairs reach GJK
+    "panda_boxy_64m": Workload("panda_boxy_64m", "panda_boxy/configs", "capsule", 1 << 26, "arm",
+                               "Panda stand-in with boxy (non-capsule) link hulls, convex GJK, 64M configs"),
+    "panda_boxy_4096": Workload("panda_boxy_4096", "panda_boxy/configs", "capsule", 4096, "arm",
+                                "Panda stand-in with boxy link hulls, self + capsule scene, 4096 configs"),
+    "h1_boxy_16m": Workload("h1_boxy_16m", "unitree_h1_boxy/configs", "none", 1 << 24, None,
+                            "H1 stand-in with boxy link hulls, floating base, self-collision, 16M configs"),
     "rrr_float": Workload("rrr_float", "rrr/floating_configs", "capsule", 1 << 16, "arm",
                           "in-tree floating-base rrr (primitive shapes) with the reference capsule"),
 }

@@ -167,6 +167,65 @@ def capsule_hull(p0, p1, radius: float, seed: int, n_ring: int = 16) -> np.ndarr
     return np.asarray(pts)
 
 
+def _segment_frame(p0, p1):
+    p0, p1 = np.asarray(p0, float), np.asarray(p1, float)
+    ax = p1 - p0
+    length = float(np.linalg.norm(ax))
+    ez = ax / length if length > 1e-9 else np.array([0.0, 0.0, 1.0])
+    ex = np.cross(ez, np.array([1.0, 0.0, 0.0]) if abs(ez[0]) < 0.9 else np.array([0.0, 1.0, 0.0]))
+    ex /= np.linalg.norm(ex)
+    return 0.5 * (p0 + p1), np.column_stack([ex, np.cross(ez, ex), ez]), length
+
+
+def _superellipsoid(half, n: int, power: float, rng) -> np.ndarray:
+    """n points on |x/a|^p + |y/b|^p + |z/c|^p = 1 along quasi-uniform directions (p = 2: an
+    ellipsoid, p >= 6: a box with rounded edges).  The body is convex, so every point is a
+    vertex of the hull of the set."""
+    k = np.arange(n) + 0.5
+    phi = np.arccos(1.0 - 2.0 * k / n)
+    th = np.pi * (1.0 + 5.0 ** 0.5) * k + rng.uniform(0, 2 * np.pi)
+    d = np.column_stack([np.cos(th) * np.sin(phi), np.sin(th) * np.sin(phi), np.cos(phi)])
+    d += 0.02 * rng.normal(size=d.shape)
+    half = np.asarray(half, float)
+    scale = (np.abs(d / half) ** power).sum(axis=1) ** (-1.0 / power)
+    return d * scale[:, None]
+
+
+def shaped_hull(kind: str, p0, p1, radius: float, seed: int) -> np.ndarray:
+    """Stand-in link geometry that is NOT capsule-like, around the segment p0-p1 (the same
+    segments and radii the capsule-like stand-ins use).  Real link meshes are boxy housings,
+    elbows and flat plates; an inscribed capsule fills little of such a hull, so far more
+    (configuration, pair) items fall between the inner and the outer capsule and reach GJK.
+
+    kind: ``rbox``  a box with rounded edges, 64 vertices
+          ``L``     the hull of two rounded boxes at a right angle (an elbow housing), <= 80
+          ``plate`` a flat slab, 64 vertices
+          ``blob``  an irregular ellipsoid-like body, ~100-128 vertices
+    """
+    from ramp_b200 import meshes
+
+    rng = np.random.default_rng(seed)
+    centre, R, length = _segment_frame(p0, p1)
+    radius = 0.9 * radius  # corners reach further than a capsule of the same radius would
+    hz = 0.5 * length + radius
+    if kind == "rbox":
+        local = _superellipsoid((radius, 0.8 * radius, hz), 64, 6.0, rng)
+    elif kind == "plate":
+        local = _superellipsoid((1.3 * radius, 0.4 * radius, hz), 64, 8.0, rng)
+    elif kind == "L":
+        a = _superellipsoid((0.85 * radius, 0.85 * radius, hz), 40, 6.0, rng)
+        b = _superellipsoid((1.5 * radius, 0.8 * radius, 0.8 * radius), 40, 6.0, rng)
+        b += np.array([1.1 * radius, 0.0, hz - 0.8 * radius])
+        local = meshes.convex_hull_vertices(np.concatenate([a, b]), 128)
+    elif kind == "blob":
+        pts = _superellipsoid((1.05 * radius, 0.9 * radius, hz), 128, 2.0, rng)
+        pts *= (1.0 + 0.05 * rng.uniform(-1, 1, size=(len(pts), 1)))
+        local = meshes.convex_hull_vertices(pts, 128)
+    else:
+        raise ValueError(f"unknown stand-in hull kind '{kind}'")
+    return centre + local @ R.T
+
+
 class _Builder:
     """Programmatic Model/GeometryModel construction with Pinocchio's frame bookkeeping."""
 
@@ -193,8 +252,10 @@ class _Builder:
 
     def hull(self, link, p0, p1, radius, seed):
         """Attach a convex hull, re-centred so the local origin is its bounding-sphere
-        centre (the placement absorbs the shift)."""
-        pts = capsule_hull(p0, p1, radius, seed)
+        centre (the placement absorbs the shift).  ``self.kinds`` (link -> kind of
+        ``shaped_hull``) replaces the capsule-like hull for the "boxy" variants."""
+        kind = getattr(self, "kinds", {}).get(link)
+        pts = capsule_hull(p0, p1, radius, seed) if kind is None else shaped_hull(kind, p0, p1, radius, seed)
         centre = 0.5 * (pts.min(axis=0) + pts.max(axis=0))
         f = self.model.frames[self.body[link]]
         k = sum(1 for g in self.geom.geometryObjects if g.parentFrame == self.body[link])
@@ -258,8 +319,18 @@ def _joint_zoo():
     return b
 
 
-def _panda_like(prefix: str, with_hand: bool, name: str):
+# which non-capsule shape each link of the "boxy" variants gets (shaped_hull kinds)
+_PANDA_BOXY = {"link0": "rbox", "link1": "L", "link2": "blob", "link3": "L", "link4": "rbox", "link5": "L", "link6": "blob",
+               "link7": "rbox", "hand": "plate", "leftfinger": "rbox", "rightfinger": "rbox"}
+_H1_BOXY = {"pelvis": "rbox", "torso_link": "rbox", "hip_yaw_link": "blob", "hip_roll_link": "rbox", "hip_pitch_link": "rbox",
+            "knee_link": "L", "ankle_link": "plate", "shoulder_pitch_link": "blob", "shoulder_roll_link": "rbox",
+            "shoulder_yaw_link": "L", "elbow_link": "rbox"}
+
+
+def _panda_like(prefix: str, with_hand: bool, name: str, boxy: bool = False):
     b = _Builder(name, f"{prefix}link0")
+    if boxy:
+        b.kinds = {prefix + k: v for k, v in _PANDA_BOXY.items()}
     h = PI / 2
     R = "JointModelRZ"
     J = [  # xyz, rpy, lower, upper  
@@ -353,10 +424,12 @@ _UR5_DISABLED = [("shoulder_link", "upper_arm_link"), ("wrist_2_link", "wrist_3_
                  ("forearm_link", "wrist_1_link")]
 
 
-def _h1():
+def _h1(boxy: bool = False):
     """Floating base + 19 hinges; 20 geometry-bearing links (stand-in table, from memory of
     the upstream MJCF: left leg, right leg, torso, left arm, right arm in file order)."""
     b = _Builder("h1", "world_root")
+    if boxy:
+        b.kinds = {side + k: v for k, v in _H1_BOXY.items() for side in ("", "left_", "right_")}
     b.joint("floating_base_joint", "world_root", "pelvis", "JointModelFreeFlyer", (0, 0, 0))
     b.hull("pelvis", (0, -0.06, -0.03), (0, 0.06, -0.03), 0.09, seed=300)
     seed = 301
@@ -428,6 +501,10 @@ def standin(description: str):
         b = _h1()
     elif description == "joint_zoo":
         b = _joint_zoo()
+    elif description == "panda_boxy_description":
+        b = _panda_like("panda_", True, "panda", boxy=True)
+    elif description == "h1_boxy_description":
+        b = _h1(boxy=True)
     else:
         return None
     return b.model, b.geom, b.mimics
@@ -525,3 +602,7 @@ CONFIGS: dict[str, dict] = {
                                 for j in ("shoulder_pitch", "shoulder_roll", "shoulder_yaw", "elbow")},
     },
 }
+
+# "boxy" variants: same kinematics, groups and disabled pairs, non-capsule link hulls (shaped_hull)
+CONFIGS["panda_boxy/configs"] = {**CONFIGS["panda/configs"], "standin": "panda_boxy_description"}
+CONFIGS["unitree_h1_boxy/configs"] = {**CONFIGS["unitree_h1/configs"], "standin": "h1_boxy_description"}

@@ -98,7 +98,10 @@ CHECK_CASES = [("rrr/configs", None, 20000), ("rrr/planar_configs", "capsule", 2
                ("ur5e/configs", "obstacles", 20000), ("unitree_h1/configs", None, 4000),
                # one joint of every type (RUB-unaligned, Spherical, SphericalZYX, Translation ... included),
                # on the tile path and on the one-warp-per-configuration path (n <= 8192)
-               ("joint_zoo", "capsule", 20000), ("joint_zoo", "capsule", 3000)]
+               ("joint_zoo", "capsule", 20000), ("joint_zoo", "capsule", 3000),
+               # non-capsule link hulls: rounded boxes, elbows, plates, 100-vertex blobs
+               ("panda_boxy/configs", "capsule", 20000), ("panda_boxy/configs", "capsule", 3000),
+               ("unitree_h1_boxy/configs", None, 4000)]
 
 
 @pytest.mark.parametrize("name,scene,n", CHECK_CASES)
@@ -275,7 +278,8 @@ def test_signed_distance_matches_oracle(built, name, scene, n):
 
 
 @pytest.mark.parametrize("name,scene,n", [("ur5e/configs", "obstacles", 400000), ("panda/configs", "capsule", 400000),
-                                          ("unitree_h1/configs", None, 60000), ("rrr/floating_configs", "capsule", 400000)])
+                                          ("unitree_h1/configs", None, 60000), ("rrr/floating_configs", "capsule", 400000),
+                                          ("panda_boxy/configs", "capsule", 400000), ("unitree_h1_boxy/configs", None, 100000)])
 def test_large_sweep_flags_and_first_pair(built, name, scene, n):
     """A wide sweep for rare numerical events (FP32 GJK degeneracies show up once in 10^3-10^4
     near-contact pairs): flags and first-pair indices against the oracle, margin band honoured."""
