@@ -212,6 +212,12 @@ void ramp_model_destroy(RampModel* m);
  * device to go idle first.  No reference counterpart. */
 int ramp_model_trim(RampModel* m);
 
+/* Work counters of the model since creation (or the last reset): out[0] = (configuration, pair)
+ * work items that survived every cull and went through GJK in the queue kernel, out[1] =
+ * launches of that kernel.  Waits for the device to go idle.  bench.py divides out[0] by the
+ * configurations checked.  No reference counterpart. */
+int ramp_model_counters(const RampModel* m, uint64_t out[2], int32_t reset);
+
 /* Sizes of the live model: out[0]=nq, [1]=n_joints, [2]=n_geoms (robot+scene),
  * [3]=n_pairs (robot+scene), [4]=n_act (0 if no qmap), [5]=device. */
 int ramp_model_info(const RampModel* m, int32_t out[6]);
@@ -255,7 +261,7 @@ int ramp_check_batch(const RampModel* m, const float* d_q, int64_t n, int32_t ld
  *
  *   - at most RAMP_NOALLOC_MAX_ROWS configurations per call; larger n is
  *     refused with RAMP_ERR_LIMIT (split the batch, or use ramp_check_batch);
- *   - the fixed array (about 5.6 MB) is part of the library image: every GPU
+ *   - the fixed array (about 6.5 MB) is part of the library image: every GPU
  *     that loads the library holds it until the process exits;
  *   - the first call on each device looks up the array's address
  *     (cudaGetSymbolAddress); make that first call before any stream capture;

@@ -3,6 +3,7 @@
 // shared memory traffic except the convex-vertex scans, which read the vertex table
 // the caller staged in shared memory.
 #pragma once
+#include <cuda_fp16.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
 

@@ -110,7 +110,8 @@ __global__ void __launch_bounds__(512, 1) edge_check_kernel(const __grid_constan
   uint64_t* mbar = reinterpret_cast<uint64_t*>(g_smem);
   unsigned char* tbl = g_smem + 16;
   stage_tables(tbl, a.img, a.L.table_bytes, mbar);
-  const Tables t = make_tables(tbl);
+  Tables t = make_tables(tbl);
+  t.verts = reinterpret_cast<const float4*>(a.img + t.h->off_verts);  // not staged: global memory (overflow path only)
   const int nwarps = blockDim.x >> 5, wid = threadIdx.x >> 5;
   float* slab = reinterpret_cast<float*>(tbl + a.L.table_bytes) + static_cast<size_t>(wid) * a.L.words;
   const Warp w = make_warp(t, slab, a.L);

@@ -27,6 +27,7 @@ struct GjkQueueArgs {
   const int32_t* nd;
   int32_t* first_invalid;
   int64_t n_edges;
+  unsigned long long* stats;  // per-model counters: [0] items consumed, [1] launches (nullable)
 };
 
 constexpr int kQueueChunk = 32;  // items a warp takes from the queue at a time
@@ -48,6 +49,10 @@ __global__ void __launch_bounds__(256, 2) gjk_queue_kernel(const __grid_constant
   // hard items first (see GjkQueue): virtual index i -> slot i, or cap_hard + (i - n_hard)
   const uint32_t n_hard = min(a.count[0], a.cap_hard);
   const uint32_t total = n_hard + min(a.count[1], a.capacity - a.cap_hard);
+  if (a.stats != nullptr && blockIdx.x == 0 && threadIdx.x == 0) {
+    atomicAdd(a.stats, static_cast<unsigned long long>(total));
+    atomicAdd(a.stats + 1, 1ull);
+  }
   // Work is handed out dynamically: a warp takes kQueueChunk consecutive items at a time from a
   // cursor next to the producers' counter, so every warp stays busy until the queue is empty
   // (iteration counts per item vary from 1 to 48: a static split leaves long tails).
@@ -92,9 +97,9 @@ __global__ void __launch_bounds__(256, 2) gjk_queue_kernel(const __grid_constant
       }
       if (gi != 0xffffffffu) {
         const float4* src = reinterpret_cast<const float4*>(a.items + (gi < n_hard ? gi : a.cap_hard + (gi - n_hard)));
-        const float4 r0 = __ldcs(src), r1 = __ldcs(src + 1), r2 = __ldcs(src + 2), r3 = __ldcs(src + 3), r4 = __ldcs(src + 4);
-        row = __float_as_uint(r3.w);
-        const DPair pr = t.pairs[__float_as_uint(r4.x)];
+        const float4 r0 = __ldcs(src), r1 = __ldcs(src + 1), r2 = __ldcs(src + 2), r3 = __ldcs(src + 3);
+        row = __float_as_uint(r3.z);
+        const DPair pr = t.pairs[__float_as_uint(r3.w)];
         p = static_cast<uint32_t>(pr.orig);  // results report the caller's index
         bool skip = !a.offs && row >= a.n_rows;
         if (!skip && a.stop && !a.offs) skip = a.first_pair ? static_cast<uint32_t>(a.first_pair[row]) < p : a.hit[row] != 0;
@@ -111,7 +116,7 @@ __global__ void __launch_bounds__(256, 2) gjk_queue_kernel(const __grid_constant
           rel.m[0] = r0.x; rel.m[1] = r0.y; rel.m[2] = r0.z; rel.m[3] = r0.w;
           rel.m[4] = r1.x; rel.m[5] = r1.y; rel.m[6] = r1.z; rel.m[7] = r1.w;
           rel.m[8] = r2.x; rel.m[9] = r2.y; rel.m[10] = r2.z; rel.m[11] = r2.w;
-          gjk_init(g, rel, swept_radius(ga) + swept_radius(gb), mk(r3.x, r3.y, r3.z));
+          gjk_init(g, rel, swept_radius(ga) + swept_radius(gb), unpack_dir(__float_as_uint(r3.x), __float_as_uint(r3.y)));
           active = true;
         }
       }

@@ -9,13 +9,26 @@ namespace ramp {
 // kernel appends such items to a global queue; gjk_queue_kernel drains it with full warps and
 // far more resident warps than the slab-bound validity kernel can have.
 struct __align__(16) GjkItem {
-  float rel[12];   // pose of shape b in shape a's frame
-  float v0[3];     // starting point for GJK: witness vector of the two inner capsules
-  uint32_t row;    // configuration index inside the launch's slice / flat state index (edges)
-  uint32_t p;      // pair index
-  uint32_t pad[3];
+  float rel[12];    // pose of shape b in shape a's frame
+  uint32_t dir[2];  // first search direction for GJK -- the witness vector of the two inner capsules,
+                    // normalised -- as three halves (only its direction is ever used)
+  uint32_t row;     // configuration index inside the launch's slice / flat state index (edges)
+  uint32_t p;       // pair index (processing order)
 };
-static_assert(sizeof(GjkItem) == 80, "GjkItem");
+static_assert(sizeof(GjkItem) == 64, "GjkItem");
+
+__device__ __forceinline__ void pack_dir(V3 v, uint32_t& a, uint32_t& b) {
+  const float vv = dot(v, v);
+  v = vv > 1e-24f ? v * rsqrtf(vv) : mk(1.f, 0.f, 0.f);
+  const __half2 xy = __floats2half2_rn(v.x, v.y), z0 = __floats2half2_rn(v.z, 0.f);
+  a = *reinterpret_cast<const uint32_t*>(&xy);
+  b = *reinterpret_cast<const uint32_t*>(&z0);
+}
+
+__device__ __forceinline__ V3 unpack_dir(uint32_t a, uint32_t b) {
+  const float2 xy = __half22float2(*reinterpret_cast<const __half2*>(&a)), z0 = __half22float2(*reinterpret_cast<const __half2*>(&b));
+  return mk(xy.x, xy.y, z0.x);
+}
 
 // The queue has two regions.  Items whose inner capsules are still far apart compared with the
 // shell between inner and outer capsule almost always end after one GJK iteration ("easy");
@@ -281,8 +294,9 @@ __device__ __forceinline__ void narrow_phase(const Warp& w, bool stop_at_first, 
             dst[0] = make_float4(rel.m[0], rel.m[1], rel.m[2], rel.m[3]);
             dst[1] = make_float4(rel.m[4], rel.m[5], rel.m[6], rel.m[7]);
             dst[2] = make_float4(rel.m[8], rel.m[9], rel.m[10], rel.m[11]);
-            dst[3] = make_float4(v0.x, v0.y, v0.z, __uint_as_float(row_base + c));
-            dst[4] = make_float4(__uint_as_float(p), 0.f, 0.f, 0.f);
+            uint32_t da, db;
+            pack_dir(v0, da, db);
+            dst[3] = make_float4(__uint_as_float(da), __uint_as_float(db), __uint_as_float(row_base + c), __uint_as_float(p));
             to_gjk = false;  // queued; anything past the capacity stays for the in-kernel loop
           }
         }
@@ -374,7 +388,8 @@ __global__ void __launch_bounds__(512, 1) check_kernel(const __grid_constant__ C
   uint64_t* mbar = reinterpret_cast<uint64_t*>(g_smem);
   unsigned char* tbl = g_smem + 16;
   stage_tables(tbl, a.img, a.L.table_bytes, mbar);
-  const Tables t = make_tables(tbl);
+  Tables t = make_tables(tbl);
+  t.verts = reinterpret_cast<const float4*>(a.img + t.h->off_verts);  // not staged: global memory (overflow path only)
   const int nwarps = blockDim.x >> 5, wid = threadIdx.x >> 5;
   // Teams: `team` warps share one slab and one tile.  Warp 0 of the team loads the rows and
   // runs FK, then all of them split the pair list; a named barrier per team orders the phases.

@@ -98,6 +98,7 @@ struct RampModel {
   ramp::ImgHeader hdr{};
   int n_gjk_pairs = 0;            // active pairs of the GJK class
   cudaMemPool_t pool = nullptr;   // stream-ordered scratch for the GJK work queue
+  unsigned long long* d_stats = nullptr;  // [0] GJK items the queue kernels consumed, [1] queue kernel launches
   // scratch for ramp_check_edges (offsets, nd, first_invalid) and ramp_check_host staging
   mutable std::mutex mu;
   mutable void* d_scratch = nullptr;
@@ -563,7 +564,6 @@ static int build_image(RampModel* m) {
   h.off_joints = place(dj.size() * sizeof(DJoint));
   h.off_geoms = place(dg.size() * sizeof(DGeom));
   h.off_pairs = place(dp.size() * sizeof(DPair));
-  h.off_verts = place(verts4.size() * sizeof(float));
   h.off_static = place(stat.size() * sizeof(float));
   h.off_dyn = place(dyn.size() * sizeof(int32_t));
   h.off_act = place(m->act_slot.size() * sizeof(int32_t));
@@ -571,6 +571,8 @@ static int build_image(RampModel* m) {
   h.off_cont = place(m->cont_slot.size() * sizeof(int32_t));
   h.off_refq = place(refq.size() * sizeof(float));
   h.off_plan = place(plan.size() * sizeof(int32_t));
+  // the vertex lists come last: the validity and FK kernels stage the image without them
+  h.off_verts = place(verts4.size() * sizeof(float));
   h.total_bytes = static_cast<int32_t>(off);
   h.nq = m->nq; h.n_joints = nj; h.n_geoms = ng; h.n_dyn = static_cast<int32_t>(dyn.size());
   h.n_static = n_static; h.n_pairs = np; h.n_verts = static_cast<int32_t>(verts4.size() / 4);
@@ -612,7 +614,7 @@ static int build_image(RampModel* m) {
 
 // Shared-memory plan: tables + as many warp slabs as fit (<= 16 warps).
 static int plan_slabs(const RampModel* m, int stage_row_floats, int act_cols, SlabLayout* L, int* nwarps,
-                      size_t* smem_bytes, int ld = 0, int team = 1) {
+                      size_t* smem_bytes, int ld = 0, int team = 1, bool with_verts = false) {
   const ImgHeader& h = m->hdr;
   int w = 0;
   auto take = [&](int words) { const int o = w; w += (words + 3) & ~3; return o; };
@@ -645,7 +647,11 @@ static int plan_slabs(const RampModel* m, int stage_row_floats, int act_cols, Sl
   w = (w + 3) & ~3;
   L->off_stage = take(stage_row_floats ? 32 * L->stage_stride * 4 : 0);
   L->words = w;
-  L->table_bytes = static_cast<int32_t>(align16(h.total_bytes));
+  // Only kernels that run GJK on every item keep the vertex lists in shared memory.  The validity
+  // kernels hand their GJK items to the queue kernel and touch vertices only on the rare overflow
+  // path, where they read them from global memory: the 8 - 26 KB this frees is one more slab
+  // (warp) per CTA on Panda- and H1-sized robots.
+  L->table_bytes = static_cast<int32_t>(align16(with_verts ? h.total_bytes : h.off_verts));
   const size_t fixed = 16 + L->table_bytes;
   const size_t per_warp = static_cast<size_t>(w) * 4;
   if (fixed + per_warp > static_cast<size_t>(m->max_smem))
@@ -705,7 +711,11 @@ static int check_q_args(const RampModel* m, const void* d_q, int64_t n, int32_t 
 
 // Rows are processed in slices so the GJK work queue has a bounded size.
 constexpr int64_t kSliceRows = 1 << 21;
-constexpr int64_t kQueueItemsPerRow = 3;   // capacity (1 hard + 2 easy per row); overflow is handled inside check_kernel
+// Queue capacity: 3 items per row (1 hard + 2 easy; 0.1 - 2.1 per row on the robots measured) plus a
+// floor; overflow is handled inside check_kernel.  ramp_check_batch_noalloc sizes its queue by the
+// same rule, so both entry points queue (and solve in-kernel) exactly the same items.
+constexpr int64_t kQueueItemsPerRow = 3;
+constexpr uint32_t queue_items_for(int64_t rows) { return static_cast<uint32_t>(rows * kQueueItemsPerRow + 4096); }
 constexpr int64_t kQueueMinRows = 1024;    // below this a second launch costs more than it saves
 
 constexpr int64_t kEdgeSliceEdges = 1 << 22;  // edges per launch group of ramp_check_edges
@@ -777,13 +787,13 @@ static int plan_check(const RampModel* m, int32_t ld, uint32_t flags, int64_t n,
   if (team > 1 && plan_slabs(m, 0, act_cols, &a.L, &nwarps, &smem, ld, team) != RAMP_OK) return RAMP_ERR_LIMIT;
   P->nwarps = nwarps; P->team = team; P->smem = smem;
   P->use_queue = m->pool != nullptr && m->n_gjk_pairs > 0 && n >= kQueueMinRows;
-  P->smem_b = 16 + a.L.table_bytes;
+  P->smem_b = 16 + align16(m->hdr.total_bytes);  // the queue kernel stages the whole image, vertex lists included
   return RAMP_OK;
 }
 
 // a queue for up to `rows` configurations, from the model's pool, in stream order
 static int queue_alloc(const RampModel* m, int64_t rows, cudaStream_t st, unsigned char** scratch, GjkQueue* gq) {
-  uint32_t cap_items = static_cast<uint32_t>(rows * kQueueItemsPerRow + 4096);
+  uint32_t cap_items = queue_items_for(rows);
   // test hook: a tiny queue forces the overflow path (GJK inside check_kernel)
   if (const char* e = std::getenv("RAMP_B200_QUEUE_CAP")) cap_items = static_cast<uint32_t>(std::max(1, std::atoi(e)));
   const size_t bytes = 256 + static_cast<size_t>(cap_items) * sizeof(GjkItem);
@@ -811,8 +821,8 @@ static void launch_tiles(const RampModel* m, const CheckPlan& P, const float* d_
 static void launch_queue(const RampModel* m, const CheckPlan& P, const GjkQueue& gq, uint8_t* hit, int32_t* first, uint32_t* mask,
                          int64_t rows, cudaStream_t st) {
   GjkQueueArgs b{};
-  b.img = m->d_image; b.table_bytes = P.a.L.table_bytes;
-  b.items = gq.items; b.count = gq.count; b.capacity = gq.capacity; b.cap_hard = gq.cap_hard;
+  b.img = m->d_image; b.table_bytes = static_cast<int32_t>(align16(m->hdr.total_bytes));
+  b.items = gq.items; b.count = gq.count; b.capacity = gq.capacity; b.cap_hard = gq.cap_hard; b.stats = m->d_stats;
   b.mask_words = m->hdr.mask_words;
   b.stop = !(P.a.flags & RAMP_ALL_PAIRS) && mask == nullptr;
   b.hit = hit; b.first_pair = first; b.pair_mask = mask; b.n_rows = static_cast<uint32_t>(rows);
@@ -969,6 +979,11 @@ int ramp_model_create(const RampModelDesc* d, int device, RampModel** out) {
   m->robot_verts.assign(d->verts, d->verts + 3 * static_cast<size_t>(d->n_verts));
   for (int i = 0; i < d->n_joints; ++i)
     if (d->joints[i].idx_q < 0 || d->joints[i].idx_q >= std::max(d->nq, 1)) { delete m; return fail(RAMP_ERR_INVALID, "joint %d: idx_q out of range", i); }
+  if (cudaMalloc(&m->d_stats, 16) != cudaSuccess || cudaMemset(m->d_stats, 0, 16) != cudaSuccess) {
+    cudaGetLastError();
+    ramp_model_destroy(m);
+    return fail(RAMP_ERR_ALLOC, "cudaMalloc for the model counters failed");
+  }
   if (int rc = build_image(m)) { ramp_model_destroy(m); return rc; }
   *out = m;
   return RAMP_OK;
@@ -1023,6 +1038,7 @@ void ramp_model_destroy(RampModel* m) {
   cudaDeviceSynchronize();
   if (m->d_image) cudaFree(m->d_image);
   if (m->d_scratch) cudaFree(m->d_scratch);
+  if (m->d_stats) cudaFree(m->d_stats);
   if (m->pool) cudaMemPoolDestroy(m->pool);
   for (cudaStream_t st : m->streams) if (st) cudaStreamDestroy(st);
   for (cudaEvent_t ev : m->events) if (ev) cudaEventDestroy(ev);
@@ -1037,6 +1053,17 @@ int ramp_model_trim(RampModel* m) {
   CUDA_TRY(cudaSetDevice(m->device));
   CUDA_TRY(cudaDeviceSynchronize());
   if (m->pool) CUDA_TRY(cudaMemPoolTrimTo(m->pool, 0));
+  return RAMP_OK;
+}
+
+int ramp_model_counters(const RampModel* m, uint64_t out[2], int32_t reset) {
+  if (!m || !out) return fail(RAMP_ERR_INVALID, "null argument");
+  CUDA_TRY(cudaSetDevice(m->device));
+  CUDA_TRY(cudaDeviceSynchronize());
+  unsigned long long v[2] = {0, 0};
+  CUDA_TRY(cudaMemcpy(v, m->d_stats, sizeof v, cudaMemcpyDeviceToHost));
+  out[0] = v[0]; out[1] = v[1];
+  if (reset) CUDA_TRY(cudaMemset(m->d_stats, 0, sizeof v));
   return RAMP_OK;
 }
 
@@ -1100,10 +1127,10 @@ int ramp_check_batch(const RampModel* m, const float* d_q, int64_t n, int32_t ld
 // from the fixed array below instead and calls no allocating routine at all.
 //
 // The array lives in the library image: every GPU that loads libramp_b200.so carries these
-// kNoAllocQueueBytes (about 5.6 MB) until the process exits, whether or not the entry point
+// kNoAllocQueueBytes (about 6.5 MB) until the process exits, whether or not the entry point
 // is ever used.  That is why the limit is modest.
 constexpr int64_t kNoAllocMaxRows = RAMP_NOALLOC_MAX_ROWS;
-constexpr uint32_t kNoAllocQueueItems = static_cast<uint32_t>(kNoAllocMaxRows * 2 + 4096);
+constexpr uint32_t kNoAllocQueueItems = queue_items_for(kNoAllocMaxRows);
 constexpr size_t kNoAllocQueueBytes = 256 + static_cast<size_t>(kNoAllocQueueItems) * sizeof(GjkItem);
 static __device__ __align__(256) unsigned char g_noalloc_queue[kNoAllocQueueBytes];
 
@@ -1146,15 +1173,18 @@ int ramp_check_batch_noalloc(const RampModel* m, const float* d_q, int64_t n, in
   a.hit = d_hit; a.first_pair = d_first_pair; a.pair_mask = d_pair_mask;
   int nwarps; size_t smem;
   if (int rc = plan_slabs(m, 0, m->hdr.n_act, &a.L, &nwarps, &smem, ld)) return rc;
-  const size_t smem_b = 16 + a.L.table_bytes;
+  const size_t smem_b = 16 + align16(m->hdr.total_bytes);
   // the array still holds the previous call's counter and items: only the counter has to
   // start from zero, the items below it are rewritten before they are read
   CUDA_TRY(cudaMemsetAsync(scratch, 0, 16, st));
-  a.gq = GjkQueue{reinterpret_cast<GjkItem*>(scratch + 256), reinterpret_cast<uint32_t*>(scratch), kNoAllocQueueItems, queue_cap_hard(kNoAllocQueueItems)};
+  // the capacity rule of ramp_check_batch for this many rows (not the whole array): both entry
+  // points then settle every item in the same place and give bit-identical results
+  const uint32_t cap_items = queue_items_for(n);
+  a.gq = GjkQueue{reinterpret_cast<GjkItem*>(scratch + 256), reinterpret_cast<uint32_t*>(scratch), cap_items, queue_cap_hard(cap_items)};
   check_kernel<1><<<grid_for(m, (n + 31) / 32, nwarps), nwarps * 32, smem, st>>>(a);
   GjkQueueArgs b{};
-  b.img = m->d_image; b.table_bytes = a.L.table_bytes;
-  b.items = a.gq.items; b.count = a.gq.count; b.capacity = kNoAllocQueueItems; b.cap_hard = a.gq.cap_hard;
+  b.img = m->d_image; b.table_bytes = static_cast<int32_t>(align16(m->hdr.total_bytes));
+  b.items = a.gq.items; b.count = a.gq.count; b.capacity = cap_items; b.cap_hard = a.gq.cap_hard; b.stats = m->d_stats;
   b.hit = d_hit; b.first_pair = d_first_pair; b.pair_mask = d_pair_mask; b.mask_words = m->hdr.mask_words;
   b.stop = !(flags & RAMP_ALL_PAIRS) && d_pair_mask == nullptr;
   b.n_rows = static_cast<uint32_t>(n);
@@ -1175,7 +1205,7 @@ static int launch_min_distance(const RampModel* m, const float* d_q, int64_t n, 
   a.img = m->d_image; a.q = d_q; a.n = n; a.ld = ld; a.flags = flags; a.n_sel = m->hdr.n_pairs; a.out = nullptr; a.sel = nullptr;
   a.min_out = d_min;
   int nwarps; size_t smem;
-  if (int rc = plan_slabs(m, 0, m->hdr.n_act, &a.L, &nwarps, &smem, ld)) return rc;
+  if (int rc = plan_slabs(m, 0, m->hdr.n_act, &a.L, &nwarps, &smem, ld, 1, true)) return rc;
   nwarps = std::min(nwarps, 8);
   smem = 16 + a.L.table_bytes + static_cast<size_t>(a.L.words) * 4 * nwarps;
   distance_kernel<<<grid_for(m, (n + 31) / 32, nwarps), nwarps * 32, smem, st>>>(a);
@@ -1217,7 +1247,7 @@ int ramp_distance_batch(const RampModel* m, const float* d_q, int64_t n, int32_t
     a.sel = d_sel;
   }
   int nwarps; size_t smem;
-  if (int rc = plan_slabs(m, 0, m->hdr.n_act, &a.L, &nwarps, &smem, ld)) return rc;
+  if (int rc = plan_slabs(m, 0, m->hdr.n_act, &a.L, &nwarps, &smem, ld, 1, true)) return rc;
   nwarps = std::min(nwarps, 8);
   smem = 16 + a.L.table_bytes + static_cast<size_t>(a.L.words) * 4 * nwarps;
   distance_kernel<<<grid_for(m, (n + 31) / 32, nwarps), nwarps * 32, smem, st>>>(a);
@@ -1294,7 +1324,7 @@ int ramp_check_edges(const RampModel* m, const float* d_q0, const float* d_q1, i
   // first_invalid = -2 (edge_scan_kernel / edge_finish_kernel), which no valid result can be.
   int nwarps; size_t smem;
   if (int rc = plan_slabs(m, 0, n_cols, &a.L, &nwarps, &smem)) return rc;
-  const size_t smem_b = 16 + a.L.table_bytes;
+  const size_t smem_b = 16 + align16(m->hdr.total_bytes);
   const int64_t slice = std::min<int64_t>(n_edges, kEdgeSliceEdges);
   // scratch: offs int64[n+1] | nd int32[n] | first int32[n]
   const size_t off_nd = align16(sizeof(int64_t) * (slice + 1));
@@ -1326,7 +1356,7 @@ int ramp_check_edges(const RampModel* m, const float* d_q0, const float* d_q1, i
       unsigned char* Q = static_cast<unsigned char*>(qmem);
       CUDA_TRY(cudaMemsetAsync(Q, 0, 16, st));
       a.gq = GjkQueue{reinterpret_cast<GjkItem*>(Q + 256), reinterpret_cast<uint32_t*>(Q), cap, queue_cap_hard(cap)};
-      b.img = m->d_image; b.table_bytes = a.L.table_bytes; b.items = a.gq.items; b.count = a.gq.count; b.capacity = cap; b.cap_hard = a.gq.cap_hard;
+      b.img = m->d_image; b.table_bytes = static_cast<int32_t>(align16(m->hdr.total_bytes)); b.items = a.gq.items; b.count = a.gq.count; b.capacity = cap; b.cap_hard = a.gq.cap_hard; b.stats = m->d_stats;
       b.offs = a.offs; b.nd = a.nd; b.first_invalid = a.first_invalid; b.n_edges = ne;
     }
     const int eb = static_cast<int>((ne + 255) / 256);

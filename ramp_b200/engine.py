@@ -48,6 +48,7 @@ def load_library():
         "ramp_model_destroy": (None, [vp]),
         "ramp_model_trim": (C.c_int, [vp]),
         "ramp_model_info": (C.c_int, [vp, C.POINTER(i32)]),
+        "ramp_model_counters": (C.c_int, [vp, C.POINTER(C.c_uint64), i32]),
         "ramp_fk_batch": (C.c_int, [vp, vp, i64, i32, u32, vp, vp]),
         "ramp_placements_batch": (C.c_int, [vp, vp, i64, i32, u32, vp, vp]),
         "ramp_check_batch": (C.c_int, [vp, vp, i64, i32, u32, vp, vp, vp, vp, vp]),
@@ -132,6 +133,12 @@ class GpuModel:
         out = (C.c_int32 * 6)()
         _check(self.lib.ramp_model_info(self.handle, out), "ramp_model_info")
         return dict(zip(("nq", "n_joints", "n_geoms", "n_pairs", "n_act", "device"), list(out)))
+
+    def counters(self, reset: bool = False) -> dict:
+        """GJK work items the queue kernel consumed and its launches since creation / the last reset."""
+        out = (C.c_uint64 * 2)()
+        _check(self.lib.ramp_model_counters(self.handle, out, int(reset)), "ramp_model_counters")
+        return {"gjk_items": int(out[0]), "gjk_queue_launches": int(out[1])}
 
     def sync(self, geom_model: GeometryModel) -> None:
         """Mirror mutations of the host collision model (RobotState.add_object appends
