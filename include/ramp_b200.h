@@ -276,6 +276,12 @@ int ramp_check_batch_noalloc(const RampModel* m, const float* d_q, int64_t n, in
                              uint32_t flags, uint8_t* d_hit, int32_t* d_first_pair,
                              uint32_t* d_pair_mask, void* stream);
 
+/* Pack per-configuration flags to one bit each: bit (r & 31) of d_words[r >> 5] = (d_hit[r] != 0),
+ * d_words has ceil(n / 32) words and unused bits of the last word are 0.  This is what the
+ * result gather between the GPUs of a box ships (north_star: "flags ... gathered back"): an
+ * eighth of the bytes.  No reference counterpart (a single process there). */
+int ramp_pack_flags(const RampModel* m, const uint8_t* d_hit, int64_t n, uint32_t* d_words, void* stream);
+
 /* Signed distance of selected pairs: d_dist[n, n_sel] for pair indices
  * h_pair_idx[n_sel].  Replaces pinocchio.computeDistance,
  * src/ramp/robot_state.py:360-364. */

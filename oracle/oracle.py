@@ -96,11 +96,14 @@ def check_f32(desc: ModelDesc, q: np.ndarray, nthreads: int = 0) -> np.ndarray:
     return hit
 
 
-def flops(desc: ModelDesc, q: np.ndarray) -> np.ndarray:
-    """Algorithmic FP32 flops per configuration (SURVEY 8d formula; roofline numerator)."""
+def flops(desc: ModelDesc, q: np.ndarray, stop_at_first: bool = False) -> np.ndarray:
+    """Algorithmic FP32 flops per configuration (SURVEY 8d formula; roofline numerator).
+    ``stop_at_first``: a configuration's pair list ends at its first colliding pair, as in the
+    reference's boolean call (and in the timed GPU call)."""
     q = np.ascontiguousarray(np.atleast_2d(q), dtype=np.float64)
     out = np.zeros(len(q))
-    rc = lib().orc_flops_batch(C.byref(desc.struct), _p(q, C.c_double), C.c_int64(len(q)), C.c_int(q.shape[1]), _p(out, C.c_double))
+    rc = lib().orc_flops_batch(C.byref(desc.struct), _p(q, C.c_double), C.c_int64(len(q)), C.c_int(q.shape[1]),
+                               C.c_int(int(stop_at_first)), _p(out, C.c_double))
     assert rc == 0
     return out
 

@@ -898,8 +898,11 @@ int orc_check_edges(const RampModelDesc *d, const uint8_t *active, const RampQMa
  * 63 for a root joint), 63 per movable geometry, and per pair: 11 when the
  * bounding spheres are disjoint, else the closed-form cost of the class or
  * GJK iterations x (6 (V1 + V2) + 2*33 + 150), iterations counted by THIS
- * oracle's GJK in its boolean early-out mode.  Used by bench.py for the
- * roofline numerator only. */
+ * oracle's GJK in its boolean early-out mode.  With stop_at_first the pair
+ * list of a configuration ends at its first colliding pair in list order,
+ * which is where the reference stops (src/ramp/robot_state.py:379-386) and
+ * what the timed boolean call computes.  Used by bench.py for the roofline
+ * numerator only. */
 static double bound_radius(const RampGeom *g, const double *verts) {
   switch (g->type) {
   case RAMP_SHAPE_SPHERE: return g->params[0];
@@ -916,7 +919,7 @@ static double bound_radius(const RampGeom *g, const double *verts) {
   }
 }
 
-int orc_flops_batch(const RampModelDesc *d, const double *q, int64_t n, int ld, double *flops) {
+int orc_flops_batch(const RampModelDesc *d, const double *q, int64_t n, int ld, int stop_at_first, double *flops) {
   if (check_desc(d)) return -1;
   double fk = 0;
   for (int i = 0; i < d->n_joints; ++i) {
@@ -943,13 +946,16 @@ int orc_flops_batch(const RampModelDesc *d, const double *q, int64_t n, int ld, 
       f += 11;
       if (dc > br[a] + br[b]) continue;
       const int t1 = ga->type < gb->type ? ga->type : gb->type, t2 = ga->type < gb->type ? gb->type : ga->type;
-      if (t1 == RAMP_SHAPE_SPHERE && t2 == RAMP_SHAPE_SPHERE) continue;
-      if (t1 == RAMP_SHAPE_SPHERE && t2 <= RAMP_SHAPE_CYLINDER) { f += 30; continue; }
-      if (t1 == RAMP_SHAPE_CAPSULE && t2 == RAMP_SHAPE_CAPSULE) { f += 90; continue; }
       int it = 0;
-      shape_distance(ga, oMg + 12 * a, gb, oMg + 12 * b, d->verts, 0, 0.0, &it);
-      const double v = (ga->type == RAMP_SHAPE_CONVEX ? ga->vert_count : 0) + (gb->type == RAMP_SHAPE_CONVEX ? gb->vert_count : 0);
-      f += it * (6.0 * v + 2 * 33 + 150);
+      const double dist = shape_distance(ga, oMg + 12 * a, gb, oMg + 12 * b, d->verts, 0, 0.0, &it);
+      if (t1 == RAMP_SHAPE_SPHERE && t2 == RAMP_SHAPE_SPHERE) { /* the sphere test was the whole pair */ }
+      else if (t1 == RAMP_SHAPE_SPHERE && t2 <= RAMP_SHAPE_CYLINDER) f += 30;
+      else if (t1 == RAMP_SHAPE_CAPSULE && t2 == RAMP_SHAPE_CAPSULE) f += 90;
+      else {
+        const double v = (ga->type == RAMP_SHAPE_CONVEX ? ga->vert_count : 0) + (gb->type == RAMP_SHAPE_CONVEX ? gb->vert_count : 0);
+        f += it * (6.0 * v + 2 * 33 + 150);
+      }
+      if (stop_at_first && dist <= 1e-12) break;
     }
     flops[i] = f;
   }

@@ -125,4 +125,17 @@ __global__ void __launch_bounds__(256, 1) distance_kernel(const __grid_constant_
   }
 }
 
+// ------------------------------------------------------------------ kernel: flag packing
+// uint8 flags -> one bit per configuration (bit r & 31 of word r >> 5): what the result gather
+// between GPUs ships (1/8 of the bytes).  A warp packs 32 consecutive flags with one ballot.
+__global__ void pack_flags_kernel(const uint8_t* __restrict__ hit, int64_t n, uint32_t* __restrict__ words) {
+  const int64_t nwords = (n + 31) >> 5;
+  for (int64_t w = (static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x) >> 5; w < nwords;
+       w += (static_cast<int64_t>(gridDim.x) * blockDim.x) >> 5) {
+    const int64_t r = (w << 5) + (threadIdx.x & 31);
+    const unsigned b = __ballot_sync(0xffffffffu, r < n && hit[r] != 0);
+    if ((threadIdx.x & 31) == 0) words[w] = b;
+  }
+}
+
 }  // namespace ramp

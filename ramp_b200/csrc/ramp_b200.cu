@@ -1217,6 +1217,20 @@ static int launch_min_distance(const RampModel* m, const float* d_q, int64_t n, 
 
 extern "C" {
 
+int ramp_pack_flags(const RampModel* m, const uint8_t* d_hit, int64_t n, uint32_t* d_words, void* stream) {
+  if (!m) return fail(RAMP_ERR_INVALID, "null model");
+  if (n < 0) return fail(RAMP_ERR_INVALID, "negative count");
+  if (n == 0) return RAMP_OK;
+  if (!d_hit || !d_words) return fail(RAMP_ERR_INVALID, "null device pointer");
+  CUDA_TRY(cudaSetDevice(m->device));
+  const int64_t warps = (n + 31) / 32;
+  const int blocks = static_cast<int>(std::min<int64_t>((warps + 7) / 8, static_cast<int64_t>(m->sm_count) * 8));
+  pack_flags_kernel<<<blocks, 256, 0, static_cast<cudaStream_t>(stream)>>>(d_hit, n, d_words);
+  g_launches.fetch_add(1, std::memory_order_relaxed);
+  CUDA_TRY(cudaGetLastError());
+  return RAMP_OK;
+}
+
 int ramp_distance_batch(const RampModel* m, const float* d_q, int64_t n, int32_t ld, uint32_t flags, const int32_t* h_pair_idx,
                         int32_t n_sel, float* d_dist, void* stream) {
   if (int rc = check_q_args(m, d_q, n, ld, flags)) return rc;

@@ -53,6 +53,7 @@ def load_library():
         "ramp_placements_batch": (C.c_int, [vp, vp, i64, i32, u32, vp, vp]),
         "ramp_check_batch": (C.c_int, [vp, vp, i64, i32, u32, vp, vp, vp, vp, vp]),
         "ramp_check_batch_noalloc": (C.c_int, [vp, vp, i64, i32, u32, vp, vp, vp, vp]),
+        "ramp_pack_flags": (C.c_int, [vp, vp, i64, vp, vp]),
         "ramp_distance_batch": (C.c_int, [vp, vp, i64, i32, u32, C.POINTER(i32), i32, vp, vp]),
         "ramp_check_edges": (C.c_int, [vp, vp, vp, i64, i32, C.POINTER(D.RampSpaceDesc), vp, vp, vp, vp]),
         "ramp_check_edges_host": (C.c_int, [vp, vp, vp, i64, i32, C.POINTER(D.RampSpaceDesc), vp, vp, vp]),
@@ -260,6 +261,11 @@ class GpuModel:
         """Zero-overhead variant for benchmarks: caller-owned contiguous tensors, no allocations."""
         _check(self.lib.ramp_check_batch(self.handle, q.data_ptr(), q.shape[0], q.shape[1], flags, hit.data_ptr(),
                                          None, None, None, _stream_ptr(self.device)), "ramp_check_batch")
+
+    def pack_flags(self, hit: torch.Tensor, words: torch.Tensor) -> None:
+        """uint8 flags [n] -> int32 bit words [ceil(n / 32)] on the device (ramp_pack_flags)."""
+        _check(self.lib.ramp_pack_flags(self.handle, hit.data_ptr(), hit.shape[0], words.data_ptr(), _stream_ptr(self.device)),
+               "ramp_pack_flags")
 
     def check_edges(self, q0, q1, space: D.SpaceDesc) -> dict:
         """Batched DiscreteMotionValidator (ramp_check_edges) over actuated edge end points."""

@@ -26,6 +26,7 @@ import numpy as np
 import torch
 
 from ramp_b200 import spaces
+from ramp_b200.ompl_codec import fill_ompl_state, from_ompl_state
 from ramp_b200.robot_model import RobotModel
 from ramp_b200.robot_state import RobotState
 
@@ -50,6 +51,10 @@ class GpuMotionValidator:
         p = self._p
         p._sync_gpu()
         res = p._robot_model.gpu.check_edges(q0, q1, p.space)
+        n_valid = int(res["valid"].sum().item())
+        self.valid_count += n_valid
+        self.invalid_count += int(res["valid"].numel()) - n_valid
+        self.states_checked += int(res["nd"].clamp(min=1).sum().item())
         return res
 
     def checkMotion(self, s1, s2, last_valid: list | None = None) -> bool:  # noqa: N802
@@ -83,6 +88,32 @@ class MotionPlanner:
     def as_state(self, robot_state: RobotState) -> np.ndarray:
         """Actuated values of the group (what ``as_ompl_state`` packs, reference :379-464)."""
         return np.asarray(robot_state.group_qpos(self._group_name), dtype=np.float64)
+
+    def as_ompl_state(self, robot_state: RobotState, ompl_space, state=None):
+        """The group's joint values as a compound OMPL state of ``ompl_space`` (reference :379-464).
+        With the OMPL wheel present a new ``ob.State`` is built and returned; without it pass the
+        state object to fill (anything indexable by sub-space like ``ob.State()``)."""
+        values = robot_state.group_qpos(self._group_name)
+        if state is not None:
+            fill_ompl_state(ompl_space, state, values)
+            return state
+        from ompl import base as ob  # noqa: PLC0415 - optional dependency
+
+        compound = ob.CompoundState(ompl_space)
+        fill_ompl_state(ompl_space, compound(), values)
+        return ob.State(compound)
+
+    def state_validity_checker(self, reference_state: RobotState, ompl_space):
+        """The ``(ob.State) -> bool`` callable the reference installs with
+        ``setStateValidityChecker(ob.StateValidityCheckerFn(...))`` (reference :466-483): the state's
+        joint values go into a private clone of ``reference_state``, then ``is_state_valid``."""
+        reference_robot_state = reference_state.clone()
+
+        def is_ompl_state_valid(state) -> bool:
+            reference_robot_state.set_group_qpos(self._group_name, from_ompl_state(ompl_space, state))
+            return self.is_state_valid(reference_robot_state)
+
+        return is_ompl_state_valid
 
     def set_reference_state(self, reference_state: RobotState) -> None:
         """Every q slot outside the group comes from this state (the clone the reference
@@ -245,11 +276,14 @@ class MotionPlanner:
         return solution
 
 
-def make_ompl_motion_validator(planner: MotionPlanner, si, from_ompl_state):
+def make_ompl_motion_validator(planner: MotionPlanner, si, ob=None):
     """An ``ompl.base.MotionValidator`` over the GPU validator, for installs that have the
-    OMPL wheel: ``si.setMotionValidator(make_ompl_motion_validator(...))`` right after
-    ``og.SimpleSetup`` is built (reference motion_planner.py:366)."""
-    from ompl import base as ob  # noqa: PLC0415 - optional dependency
+    OMPL wheel: ``si.setMotionValidator(make_ompl_motion_validator(planner, si))`` right after
+    ``og.SimpleSetup`` is built (reference motion_planner.py:366).  States are decoded with
+    ``ompl_codec.from_ompl_state``; ``ob`` is the ``ompl.base`` module (imported when omitted; the
+    tests pass a stand-in with a ``MotionValidator`` base class)."""
+    if ob is None:
+        from ompl import base as ob  # noqa: PLC0415 - optional dependency
 
     class _Validator(ob.MotionValidator):
         def __init__(self):
