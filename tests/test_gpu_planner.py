@@ -211,3 +211,66 @@ def test_are_states_valid_matches_is_state_valid(built):
         s.set_group_qpos("arm", states[i])
         assert planner.is_state_valid(s) == bool(got[i]), i
     assert got.any() and not got.all()
+
+
+@pytest.mark.parametrize("cfg,scene", [("rrr_mj/configs", None), ("panda/configs", "capsule"), ("ur5e/configs", "obstacles")])
+def test_sampled_always_never_against_the_oracle(built, cfg, scene):
+    """ALWAYS = a pair collides in EVERY sampled configuration, NEVER = in none
+    (the reference's TODOs, src/ramp/compute_disable_collisions.py:229-230).  The GPU's per-pair
+    AND / OR reduction against the oracle's ``pair_dist <= 0`` over the SAME samples; a pair whose
+    classification hinges on a sample inside the +-1e-4 m band is exempt."""
+    from oracle import oracle
+    from ramp_b200 import load_robot_model, workloads
+    from ramp_b200.compute_disable_collisions import DisabledReason, get_collision_pair_names, sampled_collisions
+    from ramp_b200.desc import ModelDesc
+    from ramp_b200.robot_state import RobotState
+
+    rm = load_robot_model("zoo::" + cfg)
+    rs = RobotState(rm)
+    if scene == "capsule":
+        rs.add_object(workloads.reference_capsule())
+    elif scene == "obstacles":
+        for o in workloads.obstacle_scene():
+            rs.add_object(o)
+    n, seed = 1 << 14, 5
+    found = sampled_collisions(rm, n_samples=n, seed=seed, batch=n)
+    q = workloads.sample_q_torch(rm.model, n, seed=seed, device=rm.gpu.device).cpu().numpy()  # the samples the tool drew
+    pd = oracle.check(ModelDesc(rm.model, rm.collision_model), q[:, : rm.model.nq].astype(np.float64))["pair_dist"]
+    hit, band = pd <= 1e-12, np.abs(pd) <= 1e-4
+    cm = rm.collision_model
+    got = {(a, b): r for a, b, r in found}
+    checked = 0
+    for k, pair in enumerate(cm.collisionPairs):
+        names = get_collision_pair_names(rm.model, cm, pair)
+        want = DisabledReason.ALWAYS if hit[:, k].all() else (DisabledReason.NEVER if not hit[:, k].any() else None)
+        # could a flipped in-band sample change the class?  then either answer is acceptable
+        firm_hit, firm_free = (hit[:, k] & ~band[:, k]), (~hit[:, k] & ~band[:, k])
+        ambiguous = band[:, k].any() and not (firm_hit.any() and firm_free.any())
+        if not ambiguous:
+            assert got.get(names) == want, (names, got.get(names), want)
+            checked += 1
+    assert checked >= len(cm.collisionPairs) - 2
+    assert any(r == DisabledReason.NEVER for r in got.values()) or any(r == DisabledReason.ALWAYS for r in got.values())
+
+
+@pytest.mark.parametrize("cfg", ["panda/configs", "rrr/floating_configs", "rrr/planar_configs"])
+def test_projection_matches_oracle_fk(built, cfg):
+    """the batched projection (TCP position of every state, one ramp_fk_batch call)
+    against the oracle: oMi[parent joint of the TCP frame] * frame.placement, reference
+    src/ramp/motion_planner.py:485-506 / src/ramp/robot_state.py:194-212."""
+    from oracle import oracle
+    from ramp_b200 import MotionPlanner, RobotState, load_robot_model, spaces
+    from ramp_b200.desc import ModelDesc
+
+    rm = load_robot_model("zoo::" + cfg)
+    planner = MotionPlanner(rm, "arm")
+    rs = RobotState.from_named_state(rm, "arm", "home")
+    planner.set_reference_state(rs)
+    states = spaces.sample_uniform(planner.space, 500, np.random.default_rng(2))
+    got = planner.project(states)
+    q = oracle.qmap_apply(planner._qmap, states.astype(np.float32).astype(np.float64))
+    omi = oracle.fk(ModelDesc(rm.model, rm.collision_model), q)
+    frame = rm.model.frames[rm.model.getFrameId(rm["arm"].tcp_link_name)]
+    j = frame.parentJoint - 1
+    want = omi[:, j, :, :3] @ frame.placement.translation + omi[:, j, :, 3]
+    assert got.shape == want.shape and np.abs(got - want).max() < 1e-5
