@@ -325,6 +325,36 @@ int ramp_check_host(const RampModel* m, const float* h_q, int64_t n, int32_t ld_
                     uint32_t flags, uint8_t* h_hit, int32_t* h_first_pair,
                     float* h_min_dist, uint32_t* h_pair_mask);
 
+/* Batched differential inverse kinematics over many seeds.  Every seed is a row of
+ * ACTUATED values of the group the qmap describes (ramp_model_set_qmap); it is iterated with damped
+ * least squares,  q <- clamp(q + step * J^T (J J^T + damping^2 I)^-1 e),  e = pose error of the
+ * tool frame seen from that frame (translation, rotation vector), J = its frame Jacobian in the
+ * LOCAL frame, until |e| < tolerance or max_iterations.  One-degree-of-freedom joints only
+ * (revolute, continuous, prismatic); mimic joints follow their source.
+ *   d_target        [n][12] 3x4 row-major world poses, or one pose for all seeds (one_target = 1)
+ *   d_q_out         [n, n_act] the iterated actuated values
+ *   d_err / d_ok / d_iters  [n] final |e|, |e| < tolerance, iterations used (each nullable)
+ * Replaces RobotState.differential_ik (pink + quadprog, one state at a time),
+ * src/ramp/robot_state.py:237-304, and the rejection loop that draws IK goals,
+ * examples/so_arm100_motion_planning.py:50-54.  Not the same optimiser: the reference solves a QP
+ * per iteration; what is reproduced is the contract (a configuration whose tool frame is within
+ * MAX_ERROR of the target, inside the joint limits, or failure). */
+typedef struct RampIkParams {
+  int32_t frame_parent_joint; /* index into joints[], -1 = universe */
+  int32_t max_iterations;     /* src/ramp/constants.py:10 MAX_ITERATIONS = 500 */
+  double frame_placement[12]; /* the tool frame in its parent joint, 3x4 row-major */
+  double damping;             /* lambda */
+  double step;                /* fraction of the least-squares step taken per iteration */
+  double tolerance;           /* src/ramp/constants.py:11 MAX_ERROR = 1e-3 */
+  double max_step;            /* largest change of one joint value per iteration */
+  const double* lower;        /* [n_act] bounds of the actuated values (nullable: unbounded) */
+  const double* upper;
+} RampIkParams;
+
+int ramp_ik_batch(const RampModel* m, const float* d_seed, int64_t n, int32_t ld, const float* d_target,
+                  int32_t one_target, const RampIkParams* h_params, float* d_q_out, float* d_err,
+                  uint8_t* d_ok, int32_t* d_iters, void* stream);
+
 /* Page-locked host memory for the h_* arguments of the host-buffer calls.
  * ramp_check_host / ramp_check_edges_host copy straight from and to buffers
  * that are page-locked (any allocator: they ask the driver per pointer) and go

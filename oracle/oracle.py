@@ -12,7 +12,7 @@ from pathlib import Path
 
 import numpy as np
 
-from ramp_b200.desc import ModelDesc, QMap, RampGeom, RampModelDesc, RampQMap, RampSpaceDesc, SpaceDesc
+from ramp_b200.desc import IkParams, ModelDesc, QMap, RampGeom, RampModelDesc, RampQMap, RampSpaceDesc, SpaceDesc
 
 HERE = Path(__file__).resolve().parent
 LIB_PATH = HERE / "libramp_oracle.so"
@@ -106,6 +106,24 @@ def flops(desc: ModelDesc, q: np.ndarray, stop_at_first: bool = False) -> np.nda
                                C.c_int(int(stop_at_first)), _p(out, C.c_double))
     assert rc == 0
     return out
+
+
+def ik(desc: ModelDesc, qmap: QMap, params: IkParams, seeds: np.ndarray, targets: np.ndarray) -> dict:
+    """FP64 statement of ramp_ik_batch: ``seeds`` [n, n_act] actuated values, ``targets`` [n, 3, 4] or
+    [3, 4] world poses of the tool frame.  Returns q, err, ok, iters."""
+    seeds = np.ascontiguousarray(np.atleast_2d(seeds), dtype=np.float64)
+    targets = np.ascontiguousarray(targets, dtype=np.float64)
+    one = targets.ndim == 2
+    n = len(seeds)
+    q = np.zeros((n, qmap.n_act))
+    err = np.zeros(n)
+    ok = np.zeros(n, dtype=np.uint8)
+    iters = np.zeros(n, dtype=np.int32)
+    rc = lib().orc_ik_batch(C.byref(desc.struct), C.byref(qmap.struct), C.byref(params.struct), _p(seeds, C.c_double), C.c_int64(n),
+                            C.c_int(seeds.shape[1]), _p(targets.reshape(-1), C.c_double), C.c_int(int(one)), _p(q, C.c_double),
+                            _p(err, C.c_double), _p(ok, C.c_uint8), _p(iters, C.c_int32))
+    assert rc == 0
+    return {"q": q, "err": err, "ok": ok.astype(bool), "iters": iters}
 
 
 def num_threads() -> int:

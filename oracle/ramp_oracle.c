@@ -41,6 +41,7 @@
 
 #define ORC_MAX_JOINTS 64
 #define ORC_MAX_GEOMS 256
+#define ORC_MAX_NQ 256
 #define ORC_PI 3.14159265358979323846
 
 /* ------------------------------------------------------------------ SE(3) */
@@ -888,6 +889,135 @@ int orc_check_edges(const RampModelDesc *d, const uint8_t *active, const RampQMa
     valid[e] = first < 0;
     if (first_invalid) first_invalid[e] = first;
     if (nd_out) nd_out[e] = nd;
+  }
+  return 0;
+}
+
+/* ---------------------------------------------------- batched differential IK */
+/* FP64 statement of ramp_ik_batch (include/ramp_b200.h): damped least squares on
+ * the actuated values of a group, pose error of the tool frame seen from that
+ * frame (translation, rotation vector), frame Jacobian in the LOCAL frame.
+ * The reference's own differential_ik (src/ramp/robot_state.py:237-304) is a
+ * pink / quadprog QP per iteration; what both have in common is the contract
+ * (tool frame within MAX_ERROR of the target, inside the limits, or failure),
+ * and that is what the tests compare -- plus GPU against THIS iteration. */
+static void log_so3(const double *r, double *w) {
+  const double vee[3] = {0.5 * (r[9] - r[6]), 0.5 * (r[2] - r[8]), 0.5 * (r[4] - r[1])};
+  double c = 0.5 * (r[0] + r[5] + r[10] - 1.0);
+  c = c > 1 ? 1 : (c < -1 ? -1 : c);
+  const double s = sqrt(vee[0] * vee[0] + vee[1] * vee[1] + vee[2] * vee[2]);
+  const double th = atan2(s, c);
+  if (s > 1e-8) { for (int k = 0; k < 3; ++k) w[k] = vee[k] * th / s; return; }
+  if (c > 0) { for (int k = 0; k < 3; ++k) w[k] = vee[k]; return; }
+  const double kk = 1.0 / (1.0 - c);
+  double a[3] = {sqrt(fmax((r[0] - c) * kk, 0)), sqrt(fmax((r[5] - c) * kk, 0)), sqrt(fmax((r[10] - c) * kk, 0))};
+  if (a[0] >= a[1] && a[0] >= a[2]) { a[1] = copysign(a[1], r[1] + r[4]); a[2] = copysign(a[2], r[2] + r[8]); }
+  else if (a[1] >= a[2]) { a[0] = copysign(a[0], r[1] + r[4]); a[2] = copysign(a[2], r[6] + r[9]); }
+  else { a[0] = copysign(a[0], r[2] + r[8]); a[1] = copysign(a[1], r[6] + r[9]); }
+  if (a[0] * vee[0] + a[1] * vee[1] + a[2] * vee[2] < 0) for (int k = 0; k < 3; ++k) a[k] = -a[k];
+  for (int k = 0; k < 3; ++k) w[k] = a[k] * th;
+}
+
+static void ik_column(const RampModelDesc *d, const double *oMi, int j, const unsigned char *chain, const double *tcp, double *col) {
+  for (int k = 0; k < 6; ++k) col[k] = 0;
+  if (j < 0 || !chain[j]) return;
+  const RampJoint *jt = &d->joints[j];
+  const int t = jt->type;
+  double ax[3] = {jt->axis[0], jt->axis[1], jt->axis[2]};
+  const int al = t <= 3 ? t - 1 : (t >= 5 && t <= 7 ? t - 5 : (t >= 9 && t <= 11 ? t - 9 : -1));
+  if (al >= 0) { ax[0] = al == 0; ax[1] = al == 1; ax[2] = al == 2; }
+  const double *o = oMi + 12 * j;
+  double aw[3], lw[3] = {0, 0, 0};
+  for (int r = 0; r < 3; ++r) aw[r] = o[4 * r] * ax[0] + o[4 * r + 1] * ax[1] + o[4 * r + 2] * ax[2];
+  if (t >= 9) { for (int r = 0; r < 3; ++r) lw[r] = aw[r]; }
+  else {
+    const double dx[3] = {tcp[3] - o[3], tcp[7] - o[7], tcp[11] - o[11]};
+    lw[0] = aw[1] * dx[2] - aw[2] * dx[1]; lw[1] = aw[2] * dx[0] - aw[0] * dx[2]; lw[2] = aw[0] * dx[1] - aw[1] * dx[0];
+  }
+  for (int c = 0; c < 3; ++c) {
+    col[c] = tcp[c] * lw[0] + tcp[4 + c] * lw[1] + tcp[8 + c] * lw[2];
+    if (t < 9) col[3 + c] = tcp[c] * aw[0] + tcp[4 + c] * aw[1] + tcp[8 + c] * aw[2];
+  }
+}
+
+int orc_ik_batch(const RampModelDesc *d, const RampQMap *qm, const RampIkParams *p, const double *seed, int64_t n, int ld,
+                 const double *target, int one_target, double *q_out, double *err_out, uint8_t *ok, int32_t *iters) {
+  if (check_desc(d) || !qm || !p || qm->n_act > 16) return -1;
+  const int na = qm->n_act, nj = d->n_joints;
+  int col_joint[16], mim_col[8], mim_joint[8], n_mim = 0;
+  double mim_mult[8];
+  unsigned char chain[ORC_MAX_JOINTS];
+  memset(chain, 0, sizeof chain);
+  for (int j = p->frame_parent_joint; j >= 0; j = d->joints[j].parent) chain[j] = 1;
+  for (int k = 0; k < na; ++k) {
+    col_joint[k] = -1;
+    for (int j = 0; j < nj; ++j) if (d->joints[j].idx_q == qm->act_slot[k]) col_joint[k] = j;
+    if (col_joint[k] < 0 || d->joints[col_joint[k]].type > RAMP_JOINT_PRISMATIC_UNALIGNED) return -1;
+  }
+  for (int i = 0; i < qm->n_mimic && n_mim < 8; ++i) {
+    int jd = -1, col = -1;
+    for (int j = 0; j < nj; ++j) if (d->joints[j].idx_q == qm->mimic_dst[i]) jd = j;
+    for (int k = 0; k < na; ++k) if (qm->act_slot[k] == qm->mimic_src[i]) col = k;
+    if (jd < 0 || col < 0) continue;
+    mim_col[n_mim] = col; mim_joint[n_mim] = jd; mim_mult[n_mim] = qm->mimic_mult[i]; ++n_mim;
+  }
+  const double lam2 = p->damping * p->damping, step = p->step > 0 ? p->step : 1.0, max_dq = p->max_step > 0 ? p->max_step : 1e300;
+#pragma omp parallel for schedule(dynamic, 16)
+  for (int64_t i = 0; i < n; ++i) {
+    double act[16], q[ORC_MAX_NQ], oMi[12 * ORC_MAX_JOINTS], tcp[12], dm[12], e[6], err = 1e300;
+    for (int k = 0; k < na; ++k) act[k] = seed[i * ld + k];
+    const double *tg = target + (one_target ? 0 : 12 * i);
+    int it = 0, done = 0;
+    for (;;) {
+      qmap_one(qm, d->nq, act, q);
+      fk_one(d, q, oMi);
+      if (p->frame_parent_joint < 0) memcpy(tcp, p->frame_placement, sizeof tcp);
+      else se3_mul(oMi + 12 * p->frame_parent_joint, p->frame_placement, tcp);
+      se3_inv_mul(tcp, tg, dm);
+      e[0] = dm[3]; e[1] = dm[7]; e[2] = dm[11];
+      log_so3(dm, e + 3);
+      err = 0;
+      for (int k = 0; k < 6; ++k) err += e[k] * e[k];
+      err = sqrt(err);
+      if (err < p->tolerance) { done = 1; break; }
+      if (it >= p->max_iterations) break;
+      double J[16][6], A[6][6], y[6];
+      for (int k = 0; k < na; ++k) {
+        ik_column(d, oMi, col_joint[k], chain, tcp, J[k]);
+        for (int mi = 0; mi < n_mim; ++mi) if (mim_col[mi] == k) {
+          double c2[6];
+          ik_column(d, oMi, mim_joint[mi], chain, tcp, c2);
+          for (int r = 0; r < 6; ++r) J[k][r] += mim_mult[mi] * c2[r];
+        }
+      }
+      for (int r = 0; r < 6; ++r) for (int c = 0; c < 6; ++c) {
+        double sacc = r == c ? lam2 : 0.0;
+        for (int k = 0; k < na; ++k) sacc += J[k][r] * J[k][c];
+        A[r][c] = sacc;
+      }
+      for (int r = 0; r < 6; ++r) for (int c = 0; c <= r; ++c) {  /* Cholesky, lower triangle in place */
+        double sacc = A[r][c];
+        for (int k = 0; k < c; ++k) sacc -= A[r][k] * A[c][k];
+        A[r][c] = r == c ? sqrt(fmax(sacc, 1e-300)) : sacc / A[c][c];
+      }
+      for (int r = 0; r < 6; ++r) { double sacc = e[r]; for (int k = 0; k < r; ++k) sacc -= A[r][k] * y[k]; y[r] = sacc / A[r][r]; }
+      for (int r = 5; r >= 0; --r) { double sacc = y[r]; for (int k = r + 1; k < 6; ++k) sacc -= A[k][r] * y[k]; y[r] = sacc / A[r][r]; }
+      for (int k = 0; k < na; ++k) {
+        double dq = 0;
+        for (int r = 0; r < 6; ++r) dq += J[k][r] * y[r];
+        dq *= step;
+        dq = dq > max_dq ? max_dq : (dq < -max_dq ? -max_dq : dq);
+        double v = act[k] + dq;
+        if (p->lower && v < p->lower[k]) v = p->lower[k];
+        if (p->upper && v > p->upper[k]) v = p->upper[k];
+        act[k] = v;
+      }
+      ++it;
+    }
+    for (int k = 0; k < na; ++k) q_out[i * na + k] = act[k];
+    if (err_out) err_out[i] = err;
+    if (ok) ok[i] = (uint8_t)done;
+    if (iters) iters[i] = it;
   }
   return 0;
 }

@@ -44,6 +44,7 @@
 #include "gjk_queue.cuh"
 #include "fk_distance.cuh"
 #include "edges.cuh"
+#include "ik.cuh"
 
 namespace ramp {
 
@@ -690,6 +691,7 @@ static int init_kernel_attrs(int device, int max_smem) {
   CUDA_TRY(opt_in_smem(distance_kernel, max_smem));
   CUDA_TRY(opt_in_smem(edge_check_kernel, max_smem));
   CUDA_TRY(opt_in_smem(edge_warp_kernel, max_smem));
+  CUDA_TRY(opt_in_smem(ik_kernel, max_smem));
   g_attr_done[device] = true;
   return RAMP_OK;
 }
@@ -1226,6 +1228,75 @@ int ramp_pack_flags(const RampModel* m, const uint8_t* d_hit, int64_t n, uint32_
   const int64_t warps = (n + 31) / 32;
   const int blocks = static_cast<int>(std::min<int64_t>((warps + 7) / 8, static_cast<int64_t>(m->sm_count) * 8));
   pack_flags_kernel<<<blocks, 256, 0, static_cast<cudaStream_t>(stream)>>>(d_hit, n, d_words);
+  g_launches.fetch_add(1, std::memory_order_relaxed);
+  CUDA_TRY(cudaGetLastError());
+  return RAMP_OK;
+}
+
+int ramp_ik_batch(const RampModel* m, const float* d_seed, int64_t n, int32_t ld, const float* d_target, int32_t one_target,
+                  const RampIkParams* p, float* d_q_out, float* d_err, uint8_t* d_ok, int32_t* d_iters, void* stream) {
+  if (!m || !p) return fail(RAMP_ERR_INVALID, "null argument");
+  if (!m->has_qmap) return fail(RAMP_ERR_INVALID, "ramp_ik_batch needs ramp_model_set_qmap (the group's actuated columns)");
+  if (n < 0) return fail(RAMP_ERR_INVALID, "negative batch size");
+  if (n == 0) return RAMP_OK;
+  if (!d_seed || !d_target || !d_q_out) return fail(RAMP_ERR_INVALID, "null device pointer");
+  const int n_act = m->hdr.n_act, nj = m->hdr.n_joints;
+  if (ld < n_act) return fail(RAMP_ERR_INVALID, "ld %d < %d actuated columns", ld, n_act);
+  if (n_act > kIkMaxCols) return fail(RAMP_ERR_LIMIT, "%d actuated columns > limit %d", n_act, kIkMaxCols);
+  if (p->frame_parent_joint < -1 || p->frame_parent_joint >= nj) return fail(RAMP_ERR_INVALID, "frame parent joint %d out of range", p->frame_parent_joint);
+  if (p->max_iterations < 0 || !(p->tolerance > 0) || !(p->damping >= 0)) return fail(RAMP_ERR_INVALID, "bad IK parameters");
+  IkArgs a;
+  std::memset(&a, 0, sizeof a);
+  auto joint_of_slot = [&](int slot) {
+    for (int j = 0; j < nj; ++j)
+      if (m->joints[j].idx_q == slot) return j;
+    return -1;
+  };
+  auto one_dof = [&](int j) {
+    const int t = m->joints[j].type;
+    return t <= RAMP_JOINT_PRISMATIC_UNALIGNED;  // revolute, unbounded revolute, prismatic; aligned or not
+  };
+  for (int k = 0; k < n_act; ++k) {
+    const int j = joint_of_slot(m->act_slot[k]);
+    if (j < 0 || !one_dof(j))
+      return fail(RAMP_ERR_INVALID, "actuated column %d does not drive a one-degree-of-freedom joint: not supported by ramp_ik_batch", k);
+    a.col_joint[k] = j;
+    a.lo[k] = p->lower ? static_cast<float>(p->lower[k]) : -INFINITY;
+    a.hi[k] = p->upper ? static_cast<float>(p->upper[k]) : INFINITY;
+  }
+  for (size_t i = 0; i < m->mimic_dst.size(); ++i) {
+    const int jd = joint_of_slot(m->mimic_dst[i]);
+    int col = -1;
+    for (int k = 0; k < n_act; ++k) if (m->act_slot[k] == m->mimic_src[i]) col = k;
+    if (jd < 0 || col < 0) continue;  // the source is not driven by this group
+    if (!one_dof(jd)) return fail(RAMP_ERR_INVALID, "mimic joint %d is not a one-degree-of-freedom joint", jd);
+    if (a.n_mimic >= kIkMaxMimic) return fail(RAMP_ERR_LIMIT, "more than %d mimic joints", kIkMaxMimic);
+    a.mim_col[a.n_mimic] = col; a.mim_joint[a.n_mimic] = jd; a.mim_mult[a.n_mimic] = static_cast<float>(m->mimic_mult[i]);
+    ++a.n_mimic;
+  }
+  for (int j = p->frame_parent_joint; j >= 0; j = m->joints[j].parent) a.chain |= 1ull << j;
+  a.img = m->d_image; a.seed = d_seed; a.n = n; a.ld = ld; a.target = d_target; a.target_stride = one_target ? 0 : 12;
+  a.q_out = d_q_out; a.err_out = d_err; a.ok = d_ok; a.iters_out = d_iters;
+  a.frame_joint = p->frame_parent_joint;
+  for (int k = 0; k < 12; ++k) a.frame_pl[k] = static_cast<float>(p->frame_placement[k]);
+  a.max_iter = p->max_iterations;
+  a.damping2 = static_cast<float>(p->damping * p->damping);
+  a.step = static_cast<float>(p->step > 0 ? p->step : 1.0);
+  a.tol = static_cast<float>(p->tolerance);
+  a.max_dq = static_cast<float>(p->max_step > 0 ? p->max_step : 1e30);
+  a.n_cols = n_act;
+  CUDA_TRY(cudaSetDevice(m->device));
+  int nwarps; size_t smem;
+  if (int rc = plan_slabs(m, 12 * nj, n_act, &a.L, &nwarps, &smem, ld)) return rc;
+  nwarps = std::min(nwarps, 8);
+  smem = 16 + a.L.table_bytes + static_cast<size_t>(a.L.words) * 4 * nwarps;
+  // IK batches are small (hundreds to thousands of seeds) and every seed iterates tens of times:
+  // spread the tiles over the SMs rather than filling CTAs
+  const int64_t tiles = (n + 31) / 32;
+  const int warps_per_cta = static_cast<int>(std::max<int64_t>(1, std::min<int64_t>(nwarps, (tiles + m->sm_count - 1) / m->sm_count)));
+  const int grid = static_cast<int>(std::min<int64_t>((tiles + warps_per_cta - 1) / warps_per_cta, m->sm_count));
+  smem = 16 + a.L.table_bytes + static_cast<size_t>(a.L.words) * 4 * warps_per_cta;
+  ik_kernel<<<grid, warps_per_cta * 32, smem, static_cast<cudaStream_t>(stream)>>>(a);
   g_launches.fetch_add(1, std::memory_order_relaxed);
   CUDA_TRY(cudaGetLastError());
   return RAMP_OK;

@@ -73,6 +73,12 @@ class RampSpaceDesc(C.Structure):
                 ("check_bounds", C.c_int32), ("reserved", C.c_int32)]
 
 
+class RampIkParams(C.Structure):
+    _fields_ = [("frame_parent_joint", C.c_int32), ("max_iterations", C.c_int32), ("frame_placement", C.c_double * 12),
+                ("damping", C.c_double), ("step", C.c_double), ("tolerance", C.c_double), ("max_step", C.c_double),
+                ("lower", C.POINTER(C.c_double)), ("upper", C.POINTER(C.c_double))]
+
+
 def _i32(a):
     return np.ascontiguousarray(a, dtype=np.int32)
 
@@ -169,6 +175,17 @@ class QMap:
             q[:, self.cont_slot] = np.cos(th)
             q[:, self.cont_slot + 1] = np.sin(th)
         return q
+
+
+class IkParams:
+    """Parameters of ramp_ik_batch for one tool frame (RampIkParams); keeps the bound arrays alive."""
+
+    def __init__(self, frame_parent_joint: int, frame_placement, lower, upper, *, max_iterations: int = 500,
+                 tolerance: float = 1e-3, damping: float = 0.05, step: float = 1.0, max_step: float = 0.5):
+        self.lower, self.upper = _f64(lower), _f64(upper)
+        pl = (C.c_double * 12)(*np.asarray(frame_placement, dtype=np.float64).reshape(12))
+        self.struct = RampIkParams(int(frame_parent_joint), int(max_iterations), pl, float(damping), float(step),
+                                   float(tolerance), float(max_step), _ptr(self.lower, C.c_double), _ptr(self.upper, C.c_double))
 
 
 class SpaceDesc:

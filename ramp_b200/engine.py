@@ -54,6 +54,7 @@ def load_library():
         "ramp_check_batch": (C.c_int, [vp, vp, i64, i32, u32, vp, vp, vp, vp, vp]),
         "ramp_check_batch_noalloc": (C.c_int, [vp, vp, i64, i32, u32, vp, vp, vp, vp]),
         "ramp_pack_flags": (C.c_int, [vp, vp, i64, vp, vp]),
+        "ramp_ik_batch": (C.c_int, [vp, vp, i64, i32, vp, i32, C.POINTER(D.RampIkParams), vp, vp, vp, vp, vp]),
         "ramp_distance_batch": (C.c_int, [vp, vp, i64, i32, u32, C.POINTER(i32), i32, vp, vp]),
         "ramp_check_edges": (C.c_int, [vp, vp, vp, i64, i32, C.POINTER(D.RampSpaceDesc), vp, vp, vp, vp]),
         "ramp_check_edges_host": (C.c_int, [vp, vp, vp, i64, i32, C.POINTER(D.RampSpaceDesc), vp, vp, vp]),
@@ -266,6 +267,26 @@ class GpuModel:
         """uint8 flags [n] -> int32 bit words [ceil(n / 32)] on the device (ramp_pack_flags)."""
         _check(self.lib.ramp_pack_flags(self.handle, hit.data_ptr(), hit.shape[0], words.data_ptr(), _stream_ptr(self.device)),
                "ramp_pack_flags")
+
+    def ik_batch(self, seeds, targets, params: D.IkParams) -> dict:
+        """Batched differential IK (ramp_ik_batch) on the actuated values of the group the qmap
+        describes: ``seeds`` [n, n_act]; ``targets`` [n, 3, 4] or one [3, 4] world pose of the tool
+        frame.  Returns ``q`` [n, n_act], ``err`` [n], ``ok`` bool[n], ``iters`` int32[n]."""
+        seeds = self._q(seeds)
+        n = seeds.shape[0]
+        tg = torch.as_tensor(np.asarray(targets, dtype=np.float32) if not isinstance(targets, torch.Tensor) else targets)
+        tg = tg.to(device=self.device, dtype=torch.float32).contiguous()
+        one = tg.dim() == 2
+        assert tg.shape[-2:] == (3, 4) and (one or tg.shape[0] == n)
+        n_act = self.info()["n_act"]
+        q = torch.empty((n, n_act), dtype=torch.float32, device=self.device)
+        err = torch.empty(n, dtype=torch.float32, device=self.device)
+        ok = torch.empty(n, dtype=torch.uint8, device=self.device)
+        iters = torch.empty(n, dtype=torch.int32, device=self.device)
+        _check(self.lib.ramp_ik_batch(self.handle, seeds.data_ptr(), n, seeds.shape[1], tg.data_ptr(), int(one),
+                                      C.byref(params.struct), q.data_ptr(), err.data_ptr(), ok.data_ptr(), iters.data_ptr(),
+                                      _stream_ptr(self.device)), "ramp_ik_batch")
+        return {"q": q, "err": err, "ok": ok.bool(), "iters": iters}
 
     def check_edges(self, q0, q1, space: D.SpaceDesc) -> dict:
         """Batched DiscreteMotionValidator (ramp_check_edges) over actuated edge end points."""

@@ -182,6 +182,32 @@ class RobotModel:
         return res["valid"], res["first_invalid"]
 
 
+    def ik_params(self, group_name: str, **kw):
+        """RampIkParams for the group's tool frame: its parent joint and placement, the joint
+        limits of the group's actuated values (continuous joints are unbounded), and the
+        reference's MAX_ITERATIONS / MAX_ERROR (src/ramp/constants.py:10-11) unless overridden."""
+        from ramp_b200.desc import IkParams
+
+        group = self.groups[group_name]
+        assert group.tcp_link_name, f"tcp_link_name is not defined for group '{group_name}'"
+        frame = self.model.frames[self.model.getFrameId(group.tcp_link_name)]
+        cont = set(int(c) for c in self.continuous_joint_indices)
+        lo = [-np.inf if int(i) in cont else self.model.lowerPositionLimit[int(i)] for i in group.joint_position_indices]
+        hi = [np.inf if int(i) in cont else self.model.upperPositionLimit[int(i)] for i in group.joint_position_indices]
+        return IkParams(frame.parentJoint - 1, frame.placement.rt34().reshape(-1), lo, hi, **kw)
+
+    def differential_ik_batch(self, group_name: str, seeds, target_poses, reference_state=None, **kw) -> dict:
+        """Batched differential IK: every row of ``seeds`` (actuated values of the
+        group) is iterated towards ``target_poses`` ([n, 3, 4] / [3, 4] world poses of the group's
+        tool frame).  Returns ``q``, ``err``, ``ok``, ``iters`` (torch tensors on the device).  The
+        goal-state generator of reference examples/so_arm100_motion_planning.py:50-54 in one call."""
+        from ramp_b200 import spaces
+
+        ref = None if reference_state is None else reference_state.qpos
+        self.gpu.set_qmap(spaces.make_qmap(self, group_name, ref))
+        return self.gpu.ik_batch(seeds, target_poses, self.ik_params(group_name, **kw))
+
+
 def make_groups(model: Model, configs: dict) -> dict[str, GroupModel]:
     """reference src/ramp/robot_model.py:187-246."""
     groups = {}

@@ -119,6 +119,31 @@ class RobotState:
         omi = self.robot_model.gpu.forward_kinematics(self.qpos[None].astype(np.float32))[0].cpu().numpy()
         return SE3.from_rt34(omi[frame.parentJoint - 1].astype(np.float64)) * frame.placement
 
+    def differential_ik(self, group_name: str, target_pose, iteration_callback=None) -> bool:
+        """Move the group so that its tool frame reaches ``target_pose`` ([x, y, z, qx, qy, qz, qw] or
+        a 4x4 matrix); True and the state updated on success, False and the state untouched
+        otherwise (reference src/ramp/robot_state.py:237-304).  One seed -- this state -- through
+        the batched damped-least-squares kernel (ramp_ik_batch); ``iteration_callback`` is accepted
+        for signature compatibility and called once with the final state (the iterations run on
+        the device)."""
+        pose = np.asarray(target_pose, dtype=np.float64)
+        if pose.shape == (4, 4):
+            target = pose[:3, :]
+        else:
+            assert pose.shape == (7,), "target pose: [x, y, z, qx, qy, qz, qw] or a 4x4 matrix"
+            from ramp_b200.se3 import Quaternion
+
+            qn = pose[3:] / np.linalg.norm(pose[3:])
+            target = np.concatenate([Quaternion(qn[3], qn[0], qn[1], qn[2]).matrix(), pose[:3, None]], axis=1)
+        res = self.robot_model.differential_ik_batch(group_name, self.group_qpos(group_name)[None].astype(np.float32), target,
+                                                     reference_state=self)
+        ok = bool(res["ok"][0].item())
+        if ok:
+            self.set_group_qpos(group_name, res["q"][0].cpu().numpy().astype(np.float64))
+        if iteration_callback is not None:
+            iteration_callback(self.clone())
+        return ok
+
     def add_object(self, geometry_object: GeometryObject) -> None:
         """Append a universe-attached object and pair it with every ROBOT geometry (objects
         added earlier are excluded, so scene-scene pairs are never checked) -- reference
