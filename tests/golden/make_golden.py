@@ -27,7 +27,9 @@ REF_FILES = [("rrr/configs", "robots/rrr/configs.toml"), ("rrr/planar_configs", 
              ("rrr/floating_configs", "robots/rrr/floating_configs.toml"), ("planar_rrr/configs", "robots/planar_rrr/configs.toml"),
              ("rrr_mj/configs", "robots/rrr_mj/configs.toml"), ("acrobot/configs", "robots/acrobot/configs.toml"),
              ("double_pendulum", "tests/double_pendulum.toml"), ("floating", "robots/floating.urdf"), ("planar", "robots/planar.urdf")]
-VECTORS = [("rrr/configs", "capsule"), ("rrr/floating_configs", "capsule"), ("panda/configs", "capsule"), ("ur5e/configs", "obstacles")]
+VECTORS = [("rrr/configs", "capsule"), ("rrr/floating_configs", "capsule"), ("panda/configs", "capsule"), ("ur5e/configs", "obstacles"),
+           ("panda_boxy/configs", "capsule"), ("unitree_h1/configs", "none"), ("joint_zoo", "capsule")]
+IK_VECTORS = ["panda/configs", "ur5e/configs"]
 
 
 def tables(rm) -> dict:
@@ -51,7 +53,7 @@ def tables(rm) -> dict:
 def scene_objects(name):
     from ramp_b200 import workloads
 
-    return [workloads.reference_capsule()] if name == "capsule" else workloads.obstacle_scene()
+    return {"capsule": [workloads.reference_capsule()], "obstacles": workloads.obstacle_scene(), "none": []}[name]
 
 
 def main():
@@ -78,6 +80,28 @@ def main():
         out[key + "__first_pair"] = res["first_pair"].astype(np.int32)
         out[key + "__pair_dist"] = res["pair_dist"]
         out[key + "__fk"] = oracle.fk(d, q[:8])
+    # batched IK: seeds, targets and what the FP64 iteration returns after 5 steps and at convergence
+    from ramp_b200 import spaces
+    from ramp_b200.robot_state import RobotState as RS
+
+    for zoo in IK_VECTORS:
+        rm = load_robot_model("zoo::" + zoo)
+        d = ModelDesc(rm.model, rm.collision_model)
+        qmap = spaces.make_qmap(rm, "arm", RS.from_named_state(rm, "arm", "home").qpos)
+        params = rm.ik_params("arm")
+        rng = np.random.default_rng(77)
+        lo, hi = np.maximum(params.lower, -3.0), np.minimum(params.upper, 3.0)
+        goal = rng.uniform(lo, hi, (64, qmap.n_act))
+        frame = rm.model.frames[rm.model.getFrameId(rm["arm"].tcp_link_name)]
+        omi = oracle.fk(d, oracle.qmap_apply(qmap, goal))[:, frame.parentJoint - 1]
+        pl = frame.placement.rt34()
+        targets = np.concatenate([omi[:, :, :3] @ pl[:, :3], (omi[:, :, :3] @ pl[:, 3] + omi[:, :, 3])[:, :, None]], axis=2)
+        seeds = np.clip(goal + rng.normal(scale=0.3, size=goal.shape), params.lower, params.upper).astype(np.float32).astype(np.float64)
+        five = oracle.ik(d, qmap, rm.ik_params("arm", max_iterations=5, tolerance=1e-12), seeds, targets)
+        full = oracle.ik(d, qmap, params, seeds, targets)
+        key = "ik__" + zoo.replace("/", "__")
+        out[key + "__seeds"], out[key + "__targets"] = seeds, targets
+        out[key + "__err5"], out[key + "__ok"], out[key + "__q"] = five["err"], full["ok"].astype(np.uint8), full["q"]
     np.savez_compressed(HERE / "oracle_vectors.npz", **out)
     print("wrote", HERE / "reference_tables.json", (HERE / "reference_tables.json").stat().st_size, "B;",
           HERE / "oracle_vectors.npz", (HERE / "oracle_vectors.npz").stat().st_size, "B")
