@@ -907,14 +907,14 @@ static void log_so3(const double *r, double *w) {
   c = c > 1 ? 1 : (c < -1 ? -1 : c);
   const double s = sqrt(vee[0] * vee[0] + vee[1] * vee[1] + vee[2] * vee[2]);
   const double th = atan2(s, c);
-  if (s > 1e-8) { for (int k = 0; k < 3; ++k) w[k] = vee[k] * th / s; return; }
+  if (s > 1e-4) { for (int k = 0; k < 3; ++k) w[k] = vee[k] * th / s; return; }
   if (c > 0) { for (int k = 0; k < 3; ++k) w[k] = vee[k]; return; }
   const double kk = 1.0 / (1.0 - c);
   double a[3] = {sqrt(fmax((r[0] - c) * kk, 0)), sqrt(fmax((r[5] - c) * kk, 0)), sqrt(fmax((r[10] - c) * kk, 0))};
   if (a[0] >= a[1] && a[0] >= a[2]) { a[1] = copysign(a[1], r[1] + r[4]); a[2] = copysign(a[2], r[2] + r[8]); }
   else if (a[1] >= a[2]) { a[0] = copysign(a[0], r[1] + r[4]); a[2] = copysign(a[2], r[6] + r[9]); }
   else { a[0] = copysign(a[0], r[2] + r[8]); a[1] = copysign(a[1], r[6] + r[9]); }
-  if (a[0] * vee[0] + a[1] * vee[1] + a[2] * vee[2] < 0) for (int k = 0; k < 3; ++k) a[k] = -a[k];
+  /* the largest component is positive (see ik.cuh log_so3) */
   for (int k = 0; k < 3; ++k) w[k] = a[k] * th;
 }
 

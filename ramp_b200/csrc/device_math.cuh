@@ -120,6 +120,17 @@ __device__ __noinline__ void sincos_small(float x, float* sn, float* cs) {
   *sn = s; *cs = c;
 }
 
+// Hardware sine / cosine for the validity kernels: the argument is first brought into [-pi, pi]
+// (two-term reduction by 2 pi), where MUFU's absolute error is 2^-21.4 ~ 4e-7 -- a few micrometres
+// at the end of an arm, a few per cent of the +-1e-4 m margin band.  Kernels that REPORT poses or
+// distances use sincos_small.
+__device__ __forceinline__ void sincos_fast(float x, float* sn, float* cs) {
+  const float k = rintf(x * 0.159154943091895336f);
+  float r = fmaf(-k, 6.28318548202514648f, x);
+  r = fmaf(k, 1.74845553146e-7f, r);  // 2 pi = 6.28318548202514648 - 1.74845553146e-7
+  __sincosf(r, sn, cs);
+}
+
 // M_i(q): q0..q6 are the joint's q slots (unused ones are don't-care).
 __device__ __forceinline__ Xf joint_xf(int type, float ax, float ay, float az, const float* q) {
   Xf o = xf_identity();

@@ -102,7 +102,7 @@ __global__ void __launch_bounds__(256, 1) distance_kernel(const __grid_constant_
     const int64_t row0 = tile << 5;
     load_rows(actuated ? w.act : w.q, a.q, row0, a.n, cols, a.ld, w.lane);
     if (actuated) expand_q(w);
-    fk_lane<0>(w);
+    fk_lane<0, false>(w);  // placements to the slab, with the accurate sine / cosine: distances are reported
     __syncwarp();
     const int64_t row = row0 + w.lane;
     float dmin = 3.0e38f;

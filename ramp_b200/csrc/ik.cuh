@@ -66,7 +66,9 @@ __device__ __forceinline__ V3 log_so3(const Xf& r) {
   if (a.x >= a.y && a.x >= a.z) { a.y = copysignf(a.y, r.m[1] + r.m[4]); a.z = copysignf(a.z, r.m[2] + r.m[8]); }
   else if (a.y >= a.z) { a.x = copysignf(a.x, r.m[1] + r.m[4]); a.z = copysignf(a.z, r.m[6] + r.m[9]); }
   else { a.x = copysignf(a.x, r.m[2] + r.m[8]); a.y = copysignf(a.y, r.m[6] + r.m[9]); }
-  if (dot(a, vee) < 0.f) a = -a;
+  // (the largest component is positive: within 1e-4 rad of a half turn +axis and -axis describe the
+  // same rotation to 2e-4 rad, and sin(th) * axis is rounding noise -- a fixed choice keeps FP32 and
+  // FP64 iterations on the same branch, e.g. from a stretched-out arm to a flipped tool)
   return a * th;
 }
 

@@ -26,6 +26,16 @@ constexpr int kQueueCap = kChunkPairs * kLanes;
 constexpr int kParentUniverse = -1;  // child of the universe: oMi = liMi
 constexpr int kParentRunning = -2;   // parent is the previous joint: use the register copy
 
+// Rotation part of a joint placement.  URDF / MJCF joint origins are mostly pure translations or
+// quarter / half turns about one axis (rpy multiples of pi/2): parent * placement is then a signed
+// shuffle of the parent's columns plus the translation, a third of the full 3x4 product.
+enum PlacementKind : int32_t {
+  kPlGeneral = 0, kPlIdentity = 1,
+  kPlXp = 2, kPlXm = 3, kPlXh = 4,  // about x by +90, -90, 180 degrees
+  kPlYp = 5, kPlYm = 6, kPlYh = 7,
+  kPlZp = 8, kPlZm = 9, kPlZh = 10
+};
+
 // narrow-phase class of a pair (decided on the host from the two shape types)
 enum PairClass : int32_t {
   kClsInactive = 0,
@@ -52,7 +62,7 @@ struct DJoint {  // 24 words
   int32_t gfirst, gcount;  // range in the dyn-geometry order list
   int32_t parent;          // plain parent index (-1: universe)
   int32_t nq;              // q entries the joint reads
-  int32_t pad;
+  int32_t pkind;           // PlacementKind of pl's rotation: quarter turns about one axis need no multiplications
   float pl[12];
 };
 static_assert(sizeof(DJoint) == 96, "DJoint");

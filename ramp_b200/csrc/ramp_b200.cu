@@ -243,6 +243,23 @@ static CapsuleFit fit_capsules(const std::vector<double>& v) {
   return f;
 }
 
+// PlacementKind of a 3x4 placement: which quarter / half turn about one axis its rotation is, if any
+static int32_t placement_kind(const double* pl) {
+  static const double S[11][9] = {
+      {0, 0, 0, 0, 0, 0, 0, 0, 0},                                   // general (unused)
+      {1, 0, 0, 0, 1, 0, 0, 0, 1},                                   // identity
+      {1, 0, 0, 0, 0, -1, 0, 1, 0}, {1, 0, 0, 0, 0, 1, 0, -1, 0}, {1, 0, 0, 0, -1, 0, 0, 0, -1},   // x: +90, -90, 180
+      {0, 0, 1, 0, 1, 0, -1, 0, 0}, {0, 0, -1, 0, 1, 0, 1, 0, 0}, {-1, 0, 0, 0, 1, 0, 0, 0, -1},   // y
+      {0, -1, 0, 1, 0, 0, 0, 0, 1}, {0, 1, 0, -1, 0, 0, 0, 0, 1}, {-1, 0, 0, 0, -1, 0, 0, 0, 1}};  // z
+  for (int k = 1; k <= 10; ++k) {
+    bool same = true;
+    for (int r = 0; r < 3 && same; ++r)
+      for (int c = 0; c < 3 && same; ++c) same = std::fabs(pl[4 * r + c] - S[k][3 * r + c]) < 1e-9;
+    if (same) return k;
+  }
+  return kPlGeneral;
+}
+
 // Pack the host description into the device image.  Convex hulls are re-centred on the
 // centre of their local bounding box (vertices shifted, placement composed with the shift):
 // the placed point set is unchanged, the bounding sphere / OBB get tighter.
@@ -282,6 +299,7 @@ static int build_image(RampModel* m) {
     d.save_slot = save_slot[i];
     d.parent = j.parent;  // plain parent index, for the one-warp-per-configuration kernel
     d.nq = joint_nq(j.type);
+    d.pkind = placement_kind(j.placement);
     d.ax = static_cast<float>(j.axis[0]); d.ay = static_cast<float>(j.axis[1]); d.az = static_cast<float>(j.axis[2]);
     for (int k = 0; k < 12; ++k) d.pl[k] = static_cast<float>(j.placement[k]);
   }

@@ -402,12 +402,16 @@ __device__ __forceinline__ void slide_column(Xf& o, float d) {
   for (int r = 0; r < 3; ++r) o.m[4 * r + 3] = fmaf(d, o.m[4 * r + A], o.m[4 * r + 3]);
 }
 
+// kFast: the validity kernels take the hardware sine / cosine (sincos_fast); every kernel that
+// REPORTS poses or distances keeps the 1e-7 polynomial.
+template <bool kFast = false>
 __device__ __forceinline__ Xf local_xf(const DJoint* j, const float* qv) {
   Xf o = load_table_xf(j->pl);
   const int type = j->type;
   if (type <= 3) {  // RX / RY / RZ
     float s, c;
-    sincos_small(qv[0], &s, &c);
+    if (kFast) sincos_fast(qv[0], &s, &c);
+    else sincos_small(qv[0], &s, &c);
     if (type == 1) mix_columns<1, 2>(o, c, s);
     else if (type == 2) mix_columns<2, 0>(o, c, s);
     else mix_columns<0, 1>(o, c, s);
@@ -433,10 +437,38 @@ __device__ __forceinline__ void stage_xf(const Warp& w, int slot, const Xf& x) {
   p[2] = make_float4(x.m[8], x.m[9], x.m[10], x.m[11]);
 }
 
+// parent * placement for a placement whose rotation is a quarter / half turn about one axis
+// (PlacementKind): the parent's columns, shuffled and negated, and the translation.
+template <int A, int B>
+__device__ __forceinline__ void turn_columns(Xf& o, const Xf& a, int how) {  // how: 0 = +90, 1 = -90, 2 = 180 degrees in the (A, B) plane
+#pragma unroll
+  for (int r = 0; r < 3; ++r) {
+    const float ua = a.m[4 * r + A], ub = a.m[4 * r + B];
+    o.m[4 * r + A] = how == 0 ? ub : (how == 1 ? -ub : -ua);
+    o.m[4 * r + B] = how == 0 ? -ua : (how == 1 ? ua : -ub);
+  }
+}
+
+__device__ __forceinline__ Xf mul_placement(const Xf& a, const DJoint* j) {
+  const Xf p = load_table_xf(j->pl);
+  const int kind = j->pkind;
+  if (kind == kPlGeneral) return xf_mul(a, p);
+  Xf o = a;
+#pragma unroll
+  for (int r = 0; r < 3; ++r) o.m[4 * r + 3] = fmaf(a.m[4 * r], p.m[3], fmaf(a.m[4 * r + 1], p.m[7], fmaf(a.m[4 * r + 2], p.m[11], a.m[4 * r + 3])));
+  if (kind >= kPlZp) turn_columns<0, 1>(o, a, kind - kPlZp);       // about z: columns x, y
+  else if (kind >= kPlYp) turn_columns<2, 0>(o, a, kind - kPlYp);  // about y: columns z, x
+  else if (kind >= kPlXp) turn_columns<1, 2>(o, a, kind - kPlXp);  // about x: columns y, z
+  return o;
+}
+
 // ---- forward kinematics for this lane's configuration (pinocchio::forwardKinematics +
 // updateGeometryPlacements).  kStage: 0 = geometry placements to the slab (validity path),
 // 1 = stage the oMi rows, 2 = stage the oMg rows (output kernels).
-template <int kStage>
+// oMi = oMi[parent] * placement * M(q): the placement is applied first -- for the common quarter-turn
+// and pure-translation placements that costs no multiplications for the rotation -- and the joint's
+// own motion then mixes two columns (revolute about x / y / z) or slides along one (prismatic).
+template <int kStage, bool kFast = (kStage == 0)>
 __device__ __forceinline__ void fk_joint(const Warp& w, int i, Xf& cur, bool emit) {
   const int l = w.lane;
   const DJoint* j = &w.t.joints[i];
@@ -450,11 +482,24 @@ __device__ __forceinline__ void fk_joint(const Warp& w, int i, Xf& cur, bool emi
 #pragma unroll
     for (int k = 1; k < 7; ++k) qv[k] = k < n ? qj[k * 32] : 0.f;
   }
-  const Xf loc = local_xf(j, qv);
   const int pc = j->parent_code;
-  if (pc == kParentUniverse) cur = loc;
-  else if (pc == kParentRunning) cur = xf_mul(cur, loc);
-  else cur = xf_mul(load_slab_xf(w.save, pc, l), loc);
+  if (pc == kParentUniverse) cur = load_table_xf(j->pl);
+  else cur = mul_placement(pc == kParentRunning ? cur : load_slab_xf(w.save, pc, l), j);
+  const int type = j->type;
+  if (type <= 3) {  // RX / RY / RZ
+    float s, c;
+    if (kFast) sincos_fast(qv[0], &s, &c);  // validity path: see local_xf
+    else sincos_small(qv[0], &s, &c);
+    if (type == 1) mix_columns<1, 2>(cur, c, s);
+    else if (type == 2) mix_columns<2, 0>(cur, c, s);
+    else mix_columns<0, 1>(cur, c, s);
+  } else if (type >= 9 && type <= 11) {  // PX / PY / PZ
+    if (type == 9) slide_column<0>(cur, qv[0]);
+    else if (type == 10) slide_column<1>(cur, qv[0]);
+    else slide_column<2>(cur, qv[0]);
+  } else {
+    cur = xf_mul(cur, joint_xf(type, j->ax, j->ay, j->az, qv));
+  }
   if (j->save_slot >= 0) store_slab_xf(w.save, j->save_slot, l, cur);
   if (kStage == 1) stage_xf(w, i, cur);
   const int gend = (kStage == 1 || !emit) ? j->gfirst : j->gfirst + j->gcount;
@@ -467,11 +512,11 @@ __device__ __forceinline__ void fk_joint(const Warp& w, int i, Xf& cur, bool emi
   }
 }
 
-template <int kStage>
+template <int kStage, bool kFast = (kStage == 0)>
 __device__ __forceinline__ void fk_lane(const Warp& w) {
   Xf cur = xf_identity();
 #pragma unroll 1
-  for (int i = 0; i < w.t.h->n_joints; ++i) fk_joint<kStage>(w, i, cur, true);
+  for (int i = 0; i < w.t.h->n_joints; ++i) fk_joint<kStage, kFast>(w, i, cur, true);
 }
 
 // The same for a team of kTeam warps sharing one slab: warp `tw` walks its FK plan -- a
