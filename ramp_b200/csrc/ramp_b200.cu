@@ -106,8 +106,10 @@ struct RampModel {
   mutable size_t scratch_cap = 0;
   mutable void* h_pinned = nullptr;
   mutable size_t pinned_cap = 0;
-  mutable cudaStream_t streams[3] = {nullptr, nullptr, nullptr};  // ramp_check_host pipeline: two for chunks, one for the queue kernel + D2H
-  mutable cudaEvent_t events[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};  // queue ready, tiles done x2, results copied x2
+  // ramp_check_host pipeline: kHostStreams for chunks, one for the queue kernel + D2H; events: queue
+  // ready, tiles done per chunk stream, results copied x2
+  mutable cudaStream_t streams[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
+  mutable cudaEvent_t events[7] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
   mutable void* d_edge_stage = nullptr;  // ramp_check_edges_host staging (device / pinned host)
   mutable void* h_edge_stage = nullptr;
   mutable size_t edge_stage_cap = 0;
@@ -1539,8 +1541,10 @@ void ramp_host_free(void* p) {
   if (p) cudaFreeHost(p);
 }
 
-// Host-buffer check, pipelined.  The rows move to the device in chunks on two streams, so the
-// H2D copy of chunk k+1 runs under the tile kernel of chunk k.  The tile kernels of all chunks
+// Host-buffer check, pipelined.  The rows move to the device in chunks on kHostStreams streams (and
+// as many q buffers), so the H2D copies of the next chunks run under the tile kernel of chunk k --
+// with four of them the copy engine keeps going while a queue kernel holds the SMs (UR5, 2^24 rows:
+// 1.85e9 -> 2.05e9 configurations/s against two).  The tile kernels of all chunks
 // of a section (up to 2^21 rows) feed ONE GJK queue; a third stream runs the queue kernel once
 // behind them and copies the section's results home -- a queue kernel per chunk would pay its
 // drain (warps finishing their last long items at low occupancy) every 2^18 rows.  Buffers
@@ -1548,6 +1552,8 @@ void ramp_host_free(void* p) {
 // pin_memory) are used for DMA directly; pageable ones are staged through the model's pinned
 // buffers.  (Reading a pinned q in place from the kernels was measured too: 35-46 GB/s over
 // PCIe against 55 GB/s for the copy engine, and slower end to end at every batch size.)
+constexpr int kHostStreams = 4;  // chunk streams (and q buffers) of ramp_check_host: slack for the copy engine while a queue kernel holds the SMs
+
 int ramp_check_host(const RampModel* m, const float* h_q, int64_t n, int32_t ld, uint32_t flags, uint8_t* h_hit,
                     int32_t* h_first_pair, float* h_min_dist, uint32_t* h_pair_mask) {
   if (int rc = check_q_args(m, h_q, n, ld, flags)) return rc;
@@ -1558,7 +1564,13 @@ int ramp_check_host(const RampModel* m, const float* h_q, int64_t n, int32_t ld,
   std::lock_guard<std::mutex> lk(m->mu);
   const int mw = std::max(m->hdr.mask_words, 1);
   // A SECTION is what one queue kernel covers (up to kSliceRows rows); its rows arrive in CHUNKS.
-  const int64_t chunk = std::min<int64_t>(n, 1 << 18), section = std::min<int64_t>(n, kSliceRows);
+  // A batch that fits one slice is still cut into three sections (of at least 2^18 rows): the queue
+  // kernels of the first two run under the copies of the next section and only the last third's
+  // queue kernel is exposed at the end (UR5, 2^20 rows: 0.726 -> 0.694 ms; more sections lose to
+  // their queue kernels' drains).
+  int64_t section = std::min<int64_t>(n, kSliceRows);
+  if (n <= kSliceRows) section = std::min<int64_t>(n, std::max<int64_t>(1 << 18, ((n + 2) / 3 + 31) & ~int64_t{31}));
+  const int64_t chunk = std::min<int64_t>(section, 1 << 18);
   CheckPlan P;
   const bool tiled = n > kSmallRows;
   if (tiled)
@@ -1567,7 +1579,7 @@ int ramp_check_host(const RampModel* m, const float* h_q, int64_t n, int32_t ld,
   // device: two q chunks, then two sets of result arrays (one per section parity)
   const size_t b_q = align16(sizeof(float) * chunk * ld), b_hit = align16(section), b_first = align16(sizeof(int32_t) * section),
                b_mask = align16(sizeof(uint32_t) * section * mw);
-  const size_t b_out = b_hit + b_first + b_mask, total = 2 * b_q + 2 * b_out;
+  const size_t b_out = b_hit + b_first + b_mask, total = kHostStreams * b_q + 2 * b_out;
   if (int rc = ensure_scratch(m, total)) return rc;
   const bool pin_q = is_pinned(h_q), pin_hit = is_pinned(h_hit);
   const bool pin_first = !h_first_pair || is_pinned(h_first_pair), pin_mask = !h_pair_mask || is_pinned(h_pair_mask);
@@ -1583,8 +1595,9 @@ int ramp_check_host(const RampModel* m, const float* h_q, int64_t n, int32_t ld,
     if (!st) CUDA_TRY(cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking));
   for (auto& ev : m->events)
     if (!ev) CUDA_TRY(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
-  cudaStream_t s_tail = m->streams[2];
-  cudaEvent_t ev_queue = m->events[0], ev_tiles[2] = {m->events[1], m->events[2]}, ev_out[2] = {m->events[3], m->events[4]};
+  cudaStream_t s_tail = m->streams[kHostStreams];
+  cudaEvent_t ev_queue = m->events[0], ev_out[2] = {m->events[kHostStreams + 1], m->events[kHostStreams + 2]};
+  cudaEvent_t* ev_tiles = m->events + 1;
   unsigned char* D = static_cast<unsigned char*>(m->d_scratch);
   unsigned char* H = static_cast<unsigned char*>(m->h_pinned);
   int64_t k = 0;  // chunk counter over the whole call: picks the stream and the q buffer
@@ -1592,20 +1605,20 @@ int ramp_check_host(const RampModel* m, const float* h_q, int64_t n, int32_t ld,
   for (int64_t s0 = 0; s0 < n; s0 += section, ++nsec) {
     const int64_t s1 = std::min(n, s0 + section), rows = s1 - s0;
     const int par = static_cast<int>(nsec & 1);
-    unsigned char* Dout = D + 2 * b_q + par * b_out;
+    unsigned char* Dout = D + kHostStreams * b_q + par * b_out;
     uint8_t* d_hit = Dout;
     int32_t* d_first = h_first_pair ? reinterpret_cast<int32_t*>(Dout + b_hit) : nullptr;
     uint32_t* d_mask = h_pair_mask ? reinterpret_cast<uint32_t*>(Dout + b_hit + b_first) : nullptr;
     // the result arrays of this parity were last copied out by section nsec - 2
     if (nsec >= 2)
-      for (int i = 0; i < 2; ++i) CUDA_TRY(cudaStreamWaitEvent(m->streams[i], ev_out[par], 0));
+      for (int i = 0; i < kHostStreams; ++i) CUDA_TRY(cudaStreamWaitEvent(m->streams[i], ev_out[par], 0));
     unsigned char* qmem = nullptr;
     GjkQueue gq{nullptr, nullptr, 0u, 0u};
     if (queued) {
       if (int rc = queue_alloc(m, rows, m->streams[0], &qmem, &gq)) return rc;
       CUDA_TRY(cudaMemsetAsync(qmem, 0, 16, m->streams[0]));
       CUDA_TRY(cudaEventRecord(ev_queue, m->streams[0]));
-      CUDA_TRY(cudaStreamWaitEvent(m->streams[1], ev_queue, 0));
+      for (int i = 1; i < kHostStreams; ++i) CUDA_TRY(cudaStreamWaitEvent(m->streams[i], ev_queue, 0));
     }
     // Chunk boundaries.  The kernels of the very first chunk cannot start before its copy has
     // landed and nothing hides that copy, so it is shorter (n/8, at least 2^16 rows: smaller
@@ -1617,13 +1630,13 @@ int ramp_check_host(const RampModel* m, const float* h_q, int64_t n, int32_t ld,
     }
     while (start.back() < s1) start.push_back(std::min(s1, start.back() + chunk));
     for (size_t c = 0; c + 1 < start.size(); ++c, ++k) {
-      const int b = static_cast<int>(k & 1);
+      const int b = static_cast<int>(k % kHostStreams);
       cudaStream_t st = m->streams[b];
       const int64_t off = start[c], ns = start[c + 1] - off, rel = off - s0;
       float* d_q = reinterpret_cast<float*>(D + b * b_q);
       const float* src = h_q + off * ld;
       if (!pin_q) {  // pageable q: through the pinned staging buffer the copy of chunk k - 2 read
-        if (k >= 2) CUDA_TRY(cudaStreamSynchronize(st));
+        if (k >= kHostStreams) CUDA_TRY(cudaStreamSynchronize(st));
         std::memcpy(H + b * b_q, src, sizeof(float) * ns * ld);
         src = reinterpret_cast<const float*>(H + b * b_q);
       }
@@ -1636,7 +1649,7 @@ int ramp_check_host(const RampModel* m, const float* h_q, int64_t n, int32_t ld,
     }
     // tail of the section, behind the tile kernels of both chunk streams: ONE queue kernel for
     // all its chunks, then the results go home
-    for (int i = 0; i < 2; ++i) {
+    for (int i = 0; i < kHostStreams; ++i) {
       CUDA_TRY(cudaEventRecord(ev_tiles[i], m->streams[i]));
       CUDA_TRY(cudaStreamWaitEvent(s_tail, ev_tiles[i], 0));
     }
@@ -1644,7 +1657,7 @@ int ramp_check_host(const RampModel* m, const float* h_q, int64_t n, int32_t ld,
       launch_queue(m, P, gq, d_hit, d_first, d_mask, rows, s_tail);
       CUDA_TRY(cudaFreeAsync(qmem, s_tail));
     }
-    unsigned char* Hout = staged ? H + 2 * b_q + par * b_out : nullptr;
+    unsigned char* Hout = staged ? H + kHostStreams * b_q + par * b_out : nullptr;
     CUDA_TRY(cudaMemcpyAsync(pin_hit ? h_hit + s0 : Hout, d_hit, rows, cudaMemcpyDeviceToHost, s_tail));
     if (h_first_pair)
       CUDA_TRY(cudaMemcpyAsync(pin_first ? reinterpret_cast<unsigned char*>(h_first_pair + s0) : Hout + b_hit, d_first,
