@@ -1035,6 +1035,15 @@ int ramp_model_set_qmap(RampModel* m, const RampQMap* q) {
     if (q->mimic_dst[k] < 0 || q->mimic_dst[k] >= m->nq || q->mimic_src[k] < 0 || q->mimic_src[k] >= m->nq) return fail(RAMP_ERR_INVALID, "mimic[%d] out of range", k);
   for (int k = 0; k < q->n_cont; ++k) if (q->cont_slot[k] < 0 || q->cont_slot[k] + 1 >= m->nq) return fail(RAMP_ERR_INVALID, "cont_slot[%d] out of range", k);
   std::lock_guard<std::mutex> lk(m->mu);
+  {  // the same map again (a planner re-installs its reference state before every query): nothing to rebuild
+    auto same_i = [](const std::vector<int32_t>& v, const int32_t* p, int n) { return static_cast<int>(v.size()) == n && std::equal(v.begin(), v.end(), p); };
+    auto same_d = [](const std::vector<double>& v, const double* p, int n) { return static_cast<int>(v.size()) == n && std::equal(v.begin(), v.end(), p); };
+    if (m->has_qmap && same_i(m->act_slot, q->act_slot, q->n_act) && same_i(m->mimic_dst, q->mimic_dst, q->n_mimic) &&
+        same_i(m->mimic_src, q->mimic_src, q->n_mimic) && same_d(m->mimic_mult, q->mimic_mult, q->n_mimic) &&
+        same_d(m->mimic_off, q->mimic_off, q->n_mimic) && same_i(m->cont_slot, q->cont_slot, q->n_cont) &&
+        same_d(m->ref_q, q->ref_q, m->nq))
+      return RAMP_OK;
+  }
   m->has_qmap = true;
   m->act_slot.assign(q->act_slot, q->act_slot + q->n_act);
   m->mimic_dst.assign(q->mimic_dst, q->mimic_dst + q->n_mimic);
@@ -1050,6 +1059,7 @@ int ramp_model_set_pair_active(RampModel* m, int32_t p, int32_t active) {
   if (!m) return fail(RAMP_ERR_INVALID, "null model");
   std::lock_guard<std::mutex> lk(m->mu);
   if (p < 0 || p >= static_cast<int32_t>(m->pair_active.size())) return fail(RAMP_ERR_INVALID, "pair index %d out of range", p);
+  if (m->pair_active[p] == (active ? 1 : 0)) return RAMP_OK;  // already so
   m->pair_active[p] = active ? 1 : 0;
   return build_image(m);
 }

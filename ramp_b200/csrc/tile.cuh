@@ -449,9 +449,12 @@ __device__ __forceinline__ void turn_columns(Xf& o, const Xf& a, int how) {  // 
   }
 }
 
+// kShuffle = false: always the full product (the pose-output kernels are bound by HBM and by issue
+// slots about equally; the selects of the shuffle cost them more than the FMAs they replace)
+template <bool kShuffle>
 __device__ __forceinline__ Xf mul_placement(const Xf& a, const DJoint* j) {
   const Xf p = load_table_xf(j->pl);
-  const int kind = j->pkind;
+  const int kind = kShuffle ? j->pkind : kPlGeneral;
   if (kind == kPlGeneral) return xf_mul(a, p);
   Xf o = a;
 #pragma unroll
@@ -484,7 +487,7 @@ __device__ __forceinline__ void fk_joint(const Warp& w, int i, Xf& cur, bool emi
   }
   const int pc = j->parent_code;
   if (pc == kParentUniverse) cur = load_table_xf(j->pl);
-  else cur = mul_placement(pc == kParentRunning ? cur : load_slab_xf(w.save, pc, l), j);
+  else cur = mul_placement<kStage == 0>(pc == kParentRunning ? cur : load_slab_xf(w.save, pc, l), j);
   const int type = j->type;
   if (type <= 3) {  // RX / RY / RZ
     float s, c;
