@@ -28,9 +28,9 @@
  *     ones on one model run one after the other.  ramp_model_set_scene /
  *     ramp_model_set_qmap / ramp_model_set_pair_active mutate the model and
  *     must be serialised against all compute calls by the caller;
- *   - the pool keeps what it has handed out once (the GJK work queue of a
- *     2^21-row slice is the largest block) until ramp_model_trim or
- *     ramp_model_destroy;
+ *   - the pool keeps what it has handed out once (the GJK work queue is the
+ *     largest block: 3 items of 64 B per row up to 2^21 rows, at most 1 GB
+ *     for larger batches) until ramp_model_trim or ramp_model_destroy;
  *   - there is no CPU fallback: without a CUDA device every compute call
  *     fails with RAMP_ERR_CUDA.
  */

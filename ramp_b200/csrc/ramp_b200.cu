@@ -31,6 +31,7 @@
 #include <cstring>
 #include <mutex>
 #include <new>
+#include <unordered_map>
 #include <vector>
 
 #include "../../include/ramp_b200.h"
@@ -82,10 +83,6 @@ struct RampModel {
   std::vector<RampGeom> robot_geoms, scene_geoms;
   std::vector<int32_t> robot_pairs, scene_pairs;  // flattened [][2]
   std::vector<double> robot_verts, scene_verts;   // [][3]
-  // capsule fits of the convex geometries, by geometry index: computed once per geometry
-  // (brute-force facet enumeration), reused by every later rebuild of the image
-  std::vector<ramp::CapsuleFit> fit_cache;
-  std::vector<uint8_t> fit_valid;
   std::vector<uint8_t> pair_active;   // by the caller's pair index
   std::vector<int32_t> pair_order;    // caller's pair index -> processing index in the image
   // qmap
@@ -100,6 +97,14 @@ struct RampModel {
   int n_gjk_pairs = 0;            // active pairs of the GJK class
   cudaMemPool_t pool = nullptr;   // stream-ordered scratch for the GJK work queue
   unsigned long long* d_stats = nullptr;  // [0] GJK items the queue kernels consumed, [1] queue kernel launches
+  // Observed GJK items per row (hard, easy), learnt from the counters of earlier ramp_check_batch
+  // calls: sizes the queue of large batches (see launch_check).  < 0: nothing observed yet.
+  mutable std::mutex est_mu;
+  mutable float est_hard = -1.f, est_easy = -1.f;
+  mutable uint32_t* h_counts = nullptr;    // page-locked: the last slice's hard / easy counts
+  mutable cudaEvent_t ev_counts = nullptr;
+  mutable bool counts_pending = false;
+  mutable int64_t counts_rows = 0;
   // scratch for ramp_check_edges (offsets, nd, first_invalid) and ramp_check_host staging
   mutable std::mutex mu;
   mutable void* d_scratch = nullptr;
@@ -262,6 +267,30 @@ static int32_t placement_kind(const double* pl) {
   return kPlGeneral;
 }
 
+// Capsule fits are a function of the vertex list alone and cost a brute-force facet enumeration
+// (tens of milliseconds per 100-vertex hull), while images are rebuilt often -- every set_scene /
+// set_qmap / set_pair_active, and a NEW model whenever the host removes collision pairs
+// (compute_disable_collisions).  One process-wide cache keyed by the vertex bytes serves them all.
+static CapsuleFit cached_fit(const std::vector<double>& core) {
+  struct Entry { std::vector<double> v; CapsuleFit f; };
+  static std::mutex mu;
+  static std::unordered_multimap<uint64_t, Entry> cache;
+  uint64_t h = 1469598103934665603ull;
+  const unsigned char* b = reinterpret_cast<const unsigned char*>(core.data());
+  for (size_t i = 0; i < core.size() * sizeof(double); ++i) { h ^= b[i]; h *= 1099511628211ull; }
+  {
+    std::lock_guard<std::mutex> lk(mu);
+    auto range = cache.equal_range(h);
+    for (auto it = range.first; it != range.second; ++it)
+      if (it->second.v == core) return it->second.f;
+  }
+  const CapsuleFit f = fit_capsules(core);
+  std::lock_guard<std::mutex> lk(mu);
+  if (cache.size() > 4096) cache.clear();  // bounded: a long-lived process that keeps loading new robots
+  cache.emplace(h, Entry{core, f});
+  return f;
+}
+
 // Pack the host description into the device image.  Convex hulls are re-centred on the
 // centre of their local bounding box (vertices shifted, placement composed with the shift):
 // the placed point set is unchanged, the bounding sphere / OBB get tighter.
@@ -372,9 +401,7 @@ static int build_image(RampModel* m) {
           f.r_in = std::min(P[L], std::min(P[a], P[b]));
         } break;
         default:  // convex: cached (set_qmap / set_pair_active / set_scene rebuild the image)
-          if (m->fit_valid.size() < static_cast<size_t>(ng)) { m->fit_valid.resize(ng, 0); m->fit_cache.resize(ng); }
-          if (!m->fit_valid[g]) { m->fit_cache[g] = fit_capsules(core); m->fit_valid[g] = 1; }
-          f = m->fit_cache[g];
+          f = cached_fit(core);
           break;
       }
       // F = (Rf, c): new local frame expressed in the old one; z' = capsule axis
@@ -852,6 +879,68 @@ static void launch_queue(const RampModel* m, const CheckPlan& P, const GjkQueue&
   g_launches.fetch_add(1, std::memory_order_relaxed);
 }
 
+// Per-call scratch in stream order: from the model's pool (kept between calls, so no driver
+// allocation after the first call of a size), else from the device's default pool.  Calls on
+// different streams or host threads get different blocks -- nothing here is shared.
+static int pool_alloc(const RampModel* m, size_t bytes, cudaStream_t st, void** out) {
+  const cudaError_t e = m->pool ? cudaMallocFromPoolAsync(out, bytes, m->pool, st) : cudaMallocAsync(out, bytes, st);
+  if (e != cudaSuccess) {
+    cudaGetLastError();
+    *out = nullptr;
+    return fail(RAMP_ERR_ALLOC, "stream-ordered allocation of %zu B failed: %s", bytes, cudaGetErrorString(e));
+  }
+  return RAMP_OK;
+}
+
+// Slices and queue capacity of one ramp_check_batch call.  Up to kSliceRows rows: one slice, 3 items
+// per row (the rule ramp_check_batch_noalloc shares).  Larger batches: every slice ends with the
+// drain of its queue kernel (warps finishing their last long items at low occupancy), so fewer,
+// larger slices are faster -- Panda 2^24 rows: 3.97e9 configurations/s in 2^21-row slices, 4.31e9 in
+// one slice -- but 3 items per row of queue would then be gigabytes.  The items a robot really
+// produces per row are learnt from the counters of earlier calls (0.1 for a capsule-like arm, 2 for
+// a humanoid); the queue is sized 1.5x that within kQueueBudgetBytes and the slice is as large as
+// that allows (at most 2^24 rows).  An underestimate is not an error: items that do not fit are
+// solved inside the validity kernel.
+constexpr size_t kQueueBudgetBytes = size_t{1} << 30;
+constexpr int64_t kMaxSliceRows = int64_t{1} << 24;
+
+static void plan_slices(const RampModel* m, int64_t n, int64_t* slice_rows, uint32_t* cap_items, uint32_t* cap_hard) {
+  *slice_rows = std::min(n, kSliceRows);
+  *cap_items = queue_items_for(*slice_rows);
+  *cap_hard = queue_cap_hard(*cap_items);
+  if (n <= kSliceRows) return;
+  std::lock_guard<std::mutex> lk(m->est_mu);
+  if (m->counts_pending && cudaEventQuery(m->ev_counts) == cudaSuccess) {
+    const float rows = static_cast<float>(std::max<int64_t>(m->counts_rows, 1));
+    m->est_hard = std::max(m->h_counts[0] / rows, 0.9f * m->est_hard);
+    m->est_easy = std::max(m->h_counts[1] / rows, 0.9f * m->est_easy);
+    m->counts_pending = false;
+  } else {
+    cudaGetLastError();  // cudaErrorNotReady is not an error
+  }
+  if (const char* e = std::getenv("RAMP_B200_SLICE_LOG2")) {  // experiments: fixed slice, conservative capacity
+    *slice_rows = std::min(n, int64_t{1} << std::atoi(e));
+    *cap_items = queue_items_for(*slice_rows);
+    *cap_hard = queue_cap_hard(*cap_items);
+    return;
+  }
+  if (m->est_hard < 0.f) return;  // nothing observed yet: the conservative rule
+  // (rounded up to sixteenths: repeated calls must ask the pool for the SAME size, or every call
+  // would allocate afresh -- the observed rates wobble in the fourth digit)
+  auto up16 = [](double x) { return std::ceil(x * 16.0) / 16.0; };
+  const double per_hard = std::min(1.0, up16(1.5 * m->est_hard + 0.02)), per_easy = std::min(2.0, up16(1.5 * m->est_easy + 0.04));
+  const double bytes_per_row = (per_hard + per_easy) * sizeof(GjkItem);
+  int64_t rows = static_cast<int64_t>(kQueueBudgetBytes / bytes_per_row) & ~int64_t{(1 << 18) - 1};
+  rows = std::max(kSliceRows, std::min(rows, kMaxSliceRows));
+  *slice_rows = std::min(n, rows);
+  *cap_hard = static_cast<uint32_t>(*slice_rows * per_hard) + 2048;
+  *cap_items = *cap_hard + static_cast<uint32_t>(*slice_rows * per_easy) + 2048;
+  if (std::getenv("RAMP_B200_DEBUG"))
+    std::fprintf(stderr, "[ramp] est hard %.4f easy %.4f -> slice %lld rows, cap hard %u total %u (last counts %u %u over %lld rows)\n", m->est_hard,
+                 m->est_easy, static_cast<long long>(*slice_rows), *cap_hard, *cap_items, m->h_counts[0], m->h_counts[1],
+                 static_cast<long long>(m->counts_rows));
+}
+
 static int launch_check(const RampModel* m, const float* d_q, int64_t n, int32_t ld, uint32_t flags, uint8_t* d_hit,
                         int32_t* d_first, uint32_t* d_mask, cudaStream_t st) {
   if (n <= kSmallRows) return launch_check_small(m, d_q, n, ld, flags, d_hit, d_first, d_mask, st);
@@ -859,9 +948,20 @@ static int launch_check(const RampModel* m, const float* d_q, int64_t n, int32_t
   if (int rc = plan_check(m, ld, flags, n, &P)) return rc;
   unsigned char* scratch = nullptr;
   GjkQueue gq{nullptr, nullptr, 0u, 0u};
-  if (P.use_queue)
-    if (int rc = queue_alloc(m, std::min<int64_t>(n, kSliceRows), st, &scratch, &gq)) return rc;
-  const int64_t step = P.use_queue ? kSliceRows : n;
+  int64_t step = n;
+  if (P.use_queue) {
+    uint32_t cap_items, cap_hard;
+    plan_slices(m, n, &step, &cap_items, &cap_hard);
+    if (const char* e = std::getenv("RAMP_B200_QUEUE_CAP")) {  // test hook: a tiny queue forces the overflow path
+      cap_items = static_cast<uint32_t>(std::max(1, std::atoi(e)));
+      cap_hard = queue_cap_hard(cap_items);
+    }
+    void* p = nullptr;
+    if (int rc = pool_alloc(m, 256 + static_cast<size_t>(cap_items) * sizeof(GjkItem), st, &p)) return rc;
+    scratch = static_cast<unsigned char*>(p);
+    gq = GjkQueue{reinterpret_cast<GjkItem*>(scratch + 256), reinterpret_cast<uint32_t*>(scratch), cap_items, cap_hard};
+  }
+  int64_t last_rows = 0;
   for (int64_t off = 0; off < n; off += step) {
     const int64_t ns = std::min(step, n - off);
     uint8_t* hit = d_hit + off;
@@ -870,6 +970,16 @@ static int launch_check(const RampModel* m, const float* d_q, int64_t n, int32_t
     if (P.use_queue) CUDA_TRY(cudaMemsetAsync(scratch, 0, 16, st));
     launch_tiles(m, P, d_q + off * ld, ns, 0u, hit, first, mask, gq, st);
     if (P.use_queue) launch_queue(m, P, gq, hit, first, mask, ns, st);
+    last_rows = ns;
+  }
+  if (P.use_queue && n > kSliceRows) {  // remember what this robot produced per row (read by a later call)
+    std::lock_guard<std::mutex> lk(m->est_mu);
+    if (!m->counts_pending && m->h_counts && m->ev_counts) {
+      CUDA_TRY(cudaMemcpyAsync(m->h_counts, scratch, 8, cudaMemcpyDeviceToHost, st));
+      CUDA_TRY(cudaEventRecord(m->ev_counts, st));
+      m->counts_pending = true;
+      m->counts_rows = last_rows;
+    }
   }
   if (scratch) CUDA_TRY(cudaFreeAsync(scratch, st));
   CUDA_TRY(cudaGetLastError());
@@ -883,19 +993,6 @@ static int ensure_scratch(const RampModel* m, size_t bytes) {
   const size_t cap = std::max<size_t>(bytes, 1 << 20);
   if (cudaMalloc(&m->d_scratch, cap) != cudaSuccess) return fail(RAMP_ERR_ALLOC, "cudaMalloc(%zu) for scratch failed", cap);
   m->scratch_cap = cap;
-  return RAMP_OK;
-}
-
-// Per-call scratch in stream order: from the model's pool (kept between calls, so no driver
-// allocation after the first call of a size), else from the device's default pool.  Calls on
-// different streams or host threads get different blocks -- nothing here is shared.
-static int pool_alloc(const RampModel* m, size_t bytes, cudaStream_t st, void** out) {
-  const cudaError_t e = m->pool ? cudaMallocFromPoolAsync(out, bytes, m->pool, st) : cudaMallocAsync(out, bytes, st);
-  if (e != cudaSuccess) {
-    cudaGetLastError();
-    *out = nullptr;
-    return fail(RAMP_ERR_ALLOC, "stream-ordered allocation of %zu B failed: %s", bytes, cudaGetErrorString(e));
-  }
   return RAMP_OK;
 }
 
@@ -1006,6 +1103,12 @@ int ramp_model_create(const RampModelDesc* d, int device, RampModel** out) {
     ramp_model_destroy(m);
     return fail(RAMP_ERR_ALLOC, "cudaMalloc for the model counters failed");
   }
+  if (cudaHostAlloc(reinterpret_cast<void**>(&m->h_counts), 16, cudaHostAllocPortable) != cudaSuccess ||
+      cudaEventCreateWithFlags(&m->ev_counts, cudaEventDisableTiming) != cudaSuccess) {
+    cudaGetLastError();
+    ramp_model_destroy(m);
+    return fail(RAMP_ERR_ALLOC, "allocation of the model's counter read-back failed");
+  }
   if (int rc = build_image(m)) { ramp_model_destroy(m); return rc; }
   *out = m;
   return RAMP_OK;
@@ -1022,7 +1125,6 @@ int ramp_model_set_scene(RampModel* m, const RampGeom* geoms, int32_t n_geoms, c
   m->scene_geoms.assign(geoms, geoms + n_geoms);
   m->scene_pairs.assign(pairs, pairs + 2 * static_cast<size_t>(n_pairs));
   m->scene_verts.assign(verts, verts + 3 * static_cast<size_t>(n_verts));
-  m->fit_valid.resize(m->robot_geoms.size());  // the cached capsule fits of the old scene objects
   m->pair_active.resize(m->robot_pairs.size() / 2);  // scene pairs start active
   return build_image(m);
 }
@@ -1071,6 +1173,8 @@ void ramp_model_destroy(RampModel* m) {
   if (m->d_image) cudaFree(m->d_image);
   if (m->d_scratch) cudaFree(m->d_scratch);
   if (m->d_stats) cudaFree(m->d_stats);
+  if (m->h_counts) cudaFreeHost(m->h_counts);
+  if (m->ev_counts) cudaEventDestroy(m->ev_counts);
   if (m->pool) cudaMemPoolDestroy(m->pool);
   for (cudaStream_t st : m->streams) if (st) cudaStreamDestroy(st);
   for (cudaEvent_t ev : m->events) if (ev) cudaEventDestroy(ev);

@@ -588,3 +588,36 @@ def test_mesh_file_robot_gives_the_box_robot_verdicts(built, tmp_path):
     both = masks[0][1] & masks[1][1]
     assert (masks[0][0] == masks[1][0])[both].all()
     assert (masks[0][0].any(axis=0) & ~masks[0][0].all(axis=0)).sum() >= 2
+
+
+def test_large_batches_with_learnt_queue_size_give_the_same_answers(built):
+    """Batches above one slice (2^21 rows): the first call sizes its GJK queue conservatively (3
+    items per row, 2^21-row slices); later calls size it from the item counts the earlier ones
+    left behind and use larger slices.  Flags and first pairs must not depend on that, and a
+    change of scene (other item rates) must not break it."""
+    from ramp_b200 import workloads
+
+    rm, rs = _setup("ur5e/configs", "obstacles")
+    n = (1 << 21) + 700001
+    q = torch.from_numpy(workloads.sample_q(rm.model, n, seed=99)).cuda()
+    first = rm.gpu.check(q, first_pair=True)
+    torch.cuda.synchronize()
+    for _ in range(3):
+        again = rm.gpu.check(q, first_pair=True)
+        torch.cuda.synchronize()
+        assert torch.equal(again["hit"], first["hit"]) and torch.equal(again["first_pair"], first["first_pair"])
+    small = rm.gpu.check(q[:300000], first_pair=True)  # one slice: the conservative rule
+    assert torch.equal(small["hit"], first["hit"][:300000]) and torch.equal(small["first_pair"], first["first_pair"][:300000])
+    # more obstacles -> more work items per row than the estimate knows about: still correct
+    rs.add_object(workloads.reference_capsule())
+    from ramp_b200.robot_model import create_geometry_object
+    from ramp_b200.se3 import SE3
+    from ramp_b200.shapes import Box
+
+    rs.add_object(create_geometry_object("wall", Box(0.6, 0.02, 0.8), SE3(np.eye(3), np.asarray([0.3, 0.25, 0.4]))))
+    a = rm.gpu.check(q, first_pair=True)
+    torch.cuda.synchronize()
+    b = rm.gpu.check(q, first_pair=True)
+    ref = rm.gpu.check(q[:250000], first_pair=True)
+    assert torch.equal(a["hit"], b["hit"]) and torch.equal(a["first_pair"], b["first_pair"])
+    assert torch.equal(a["hit"][:250000], ref["hit"]) and torch.equal(a["first_pair"][:250000], ref["first_pair"])
