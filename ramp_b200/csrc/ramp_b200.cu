@@ -899,10 +899,10 @@ static int pool_alloc(const RampModel* m, size_t bytes, cudaStream_t st, void** 
 // one slice -- but 3 items per row of queue would then be gigabytes.  The items a robot really
 // produces per row are learnt from the counters of earlier calls (0.1 for a capsule-like arm, 2 for
 // a humanoid); the queue is sized 1.5x that within kQueueBudgetBytes and the slice is as large as
-// that allows (at most 2^24 rows).  An underestimate is not an error: items that do not fit are
+// that allows (at most 2^26 rows).  An underestimate is not an error: items that do not fit are
 // solved inside the validity kernel.
 constexpr size_t kQueueBudgetBytes = size_t{1} << 30;
-constexpr int64_t kMaxSliceRows = int64_t{1} << 24;
+constexpr int64_t kMaxSliceRows = int64_t{1} << 26;
 
 static void plan_slices(const RampModel* m, int64_t n, int64_t* slice_rows, uint32_t* cap_items, uint32_t* cap_hard) {
   *slice_rows = std::min(n, kSliceRows);
