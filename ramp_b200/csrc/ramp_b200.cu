@@ -1684,7 +1684,16 @@ int ramp_check_host(const RampModel* m, const float* h_q, int64_t n, int32_t ld,
   // their queue kernels' drains).
   int64_t section = std::min<int64_t>(n, kSliceRows);
   if (n <= kSliceRows) section = std::min<int64_t>(n, std::max<int64_t>(1 << 18, ((n + 2) / 3 + 31) & ~int64_t{31}));
-  const int64_t chunk = std::min<int64_t>(section, 1 << 18);
+  // Chunk size: 2^18 rows, or for batches of several slices about 16 MB of rows (a power of two
+  // between 2^17 and 2^19 rows): the copy engine reaches 53 GB/s on copies of that size and 45-50
+  // on 6 MB ones (UR5, 24 B per row, 2^24 rows: 2.05e9 -> 2.13e9 configurations/s).
+  int64_t chunk = 1 << 18;
+  if (n > kSliceRows) {
+    const int64_t row_bytes = static_cast<int64_t>(sizeof(float)) * ld;
+    chunk = 1 << 17;
+    while (chunk < (1 << 19) && 2 * chunk * row_bytes <= (20 << 20)) chunk *= 2;
+  }
+  chunk = std::min(section, chunk);
   CheckPlan P;
   const bool tiled = n > kSmallRows;
   if (tiled)
