@@ -933,12 +933,10 @@ static void plan_slices(const RampModel* m, int64_t n, int64_t* slice_rows, uint
   int64_t rows = static_cast<int64_t>(kQueueBudgetBytes / bytes_per_row) & ~int64_t{(1 << 18) - 1};
   rows = std::max(kSliceRows, std::min(rows, kMaxSliceRows));
   *slice_rows = std::min(n, rows);
-  *cap_hard = static_cast<uint32_t>(*slice_rows * per_hard) + 2048;
-  *cap_items = *cap_hard + static_cast<uint32_t>(*slice_rows * per_easy) + 2048;
-  if (std::getenv("RAMP_B200_DEBUG"))
-    std::fprintf(stderr, "[ramp] est hard %.4f easy %.4f -> slice %lld rows, cap hard %u total %u (last counts %u %u over %lld rows)\n", m->est_hard,
-                 m->est_easy, static_cast<long long>(*slice_rows), *cap_hard, *cap_items, m->h_counts[0], m->h_counts[1],
-                 static_cast<long long>(m->counts_rows));
+  // (capacity for the slice rounded up to 2^20 rows: batches of slightly different sizes reuse one block)
+  const double cap_rows = static_cast<double>((*slice_rows + (1 << 20) - 1) & ~int64_t{(1 << 20) - 1});
+  *cap_hard = static_cast<uint32_t>(cap_rows * per_hard) + 2048;
+  *cap_items = *cap_hard + static_cast<uint32_t>(cap_rows * per_easy) + 2048;
 }
 
 static int launch_check(const RampModel* m, const float* d_q, int64_t n, int32_t ld, uint32_t flags, uint8_t* d_hit,
