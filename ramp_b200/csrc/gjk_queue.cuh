@@ -59,6 +59,14 @@ __global__ void __launch_bounds__(256, 2) gjk_queue_kernel(const __grid_constant
   uint32_t* cursor = a.count + 2;
   const int l = threadIdx.x & 31;
   const unsigned FULL = 0xffffffffu;
+  // A short queue (a batch of a few thousand configurations) is a latency problem: 32 items per
+  // warp would leave most of the grid idle while a few warps work through their longest item at
+  // one vertex per lane and step.  Then every warp takes only its share of the items (at least
+  // 4), does not refill before they are done, and all 32 lanes share the vertex scans of those
+  // few items from the first trip on.
+  const uint32_t warps_total = gridDim.x * (blockDim.x >> 5);
+  const uint32_t chunk = min(static_cast<uint32_t>(kQueueChunk), max(4u, (total + warps_total - 1) / warps_total));
+  const bool few = chunk <= 8;
   uint32_t lo = 0, hi = 0, row = 0, p = 0;  // [lo, hi): items this warp holds but has not started
   bool active = false, drained = false;
   GjkLane g;
@@ -71,7 +79,7 @@ __global__ void __launch_bounds__(256, 2) gjk_queue_kernel(const __grid_constant
 #pragma unroll 1
     for (int attempt = 0; attempt < kFetchAttempts; ++attempt) {
       const unsigned need = __ballot_sync(FULL, !active);
-      if (!need || (drained && lo == hi)) break;
+      if (!need || (drained && lo == hi) || (few && ~need != 0u)) break;
       uint32_t gi = 0xffffffffu;
       {
         const uint32_t rank = __popc(need & ((1u << l) - 1)), nneed = __popc(need), avail = hi - lo;
@@ -82,12 +90,12 @@ __global__ void __launch_bounds__(256, 2) gjk_queue_kernel(const __grid_constant
           lo = hi;
           if (!drained) {
             uint32_t base = 0;
-            if (l == 0) base = atomicAdd(cursor, static_cast<uint32_t>(kQueueChunk));
+            if (l == 0) base = atomicAdd(cursor, chunk);
             base = __shfl_sync(FULL, base, 0);
             if (base >= total) {
               drained = true;
             } else {
-              hi = min(base + static_cast<uint32_t>(kQueueChunk), total);
+              hi = min(base + chunk, total);
               const uint32_t r2 = rank - avail;
               if (!active && rank >= avail && r2 < hi - base) gi = base + r2;
               lo = min(base + (nneed - avail), hi);
@@ -133,7 +141,7 @@ __global__ void __launch_bounds__(256, 2) gjk_queue_kernel(const __grid_constant
     const unsigned am = __ballot_sync(FULL, active);
     const int na = __popc(am);
     V3 sa, sb;
-    if (drained && lo == hi && na <= 8) {
+    if ((few || (drained && lo == hi)) && na <= 8) {
       const V3 da = -g.v, db = rot_t(g.rel, g.v);
       if (na <= 4) { sa = coop_support<8>(am, active, A, da, t.verts); sb = coop_support<8>(am, active, B, db, t.verts); }
       else { sa = coop_support<4>(am, active, A, da, t.verts); sb = coop_support<4>(am, active, B, db, t.verts); }

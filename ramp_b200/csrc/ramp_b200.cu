@@ -748,6 +748,22 @@ static int grid_for(const RampModel* m, int64_t tiles, int nwarps) {
   return static_cast<int>(std::max<int64_t>(1, std::min<int64_t>(m->sm_count, ctas)));
 }
 
+// Launch shape of a tile kernel: one CTA per SM with every slab that fits -- unless there are
+// fewer tiles than that many slabs.  Then each CTA gets only its share of slabs (warps), so the
+// tiles of a mid-size batch spread over all SMs instead of filling the first few: 16 384 Panda
+// rows are 512 tiles = 37 full CTAs, or 148 CTAs of 4 warps that finish in a third of the time.
+// The kernels take their warp count from blockDim.
+static int spread_tiles(const RampModel* m, int64_t tiles, const SlabLayout& L, int* nwarps, size_t* smem) {
+  const int team = std::max<int>(L.team, 1);
+  const int slabs = *nwarps / team;
+  const int share = static_cast<int>(std::max<int64_t>(1, (tiles + m->sm_count - 1) / m->sm_count));
+  if (share < slabs) {
+    *smem -= static_cast<size_t>(slabs - share) * L.words * 4;
+    *nwarps = share * team;
+  }
+  return grid_for(m, tiles, *nwarps / team);
+}
+
 static int check_q_args(const RampModel* m, const void* d_q, int64_t n, int32_t ld, uint32_t flags) {
   if (!m) return fail(RAMP_ERR_INVALID, "null model");
   if (n < 0) return fail(RAMP_ERR_INVALID, "negative batch size");
@@ -768,7 +784,15 @@ constexpr uint32_t queue_items_for(int64_t rows) { return static_cast<uint32_t>(
 constexpr int64_t kQueueMinRows = 1024;    // below this a second launch costs more than it saves
 
 constexpr int64_t kEdgeSliceEdges = 1 << 22;  // edges per launch group of ramp_check_edges
-constexpr int64_t kSmallRows = 8192;  // up to here one warp per configuration is faster than 32 per warp
+// Up to here one warp per configuration is faster than 32 configurations per warp: 8192 rows for
+// an arm (Panda 32 pairs, UR5 45: 35 us against 44 us at 4096 rows, level at 8192), fewer for a
+// robot with many pairs, whose pair list takes a warp several rounds (H1, 177 pairs: 61 us
+// against 56 us at 4096 rows, 111 against 58 at 8192).
+static int64_t small_rows(const RampModel* m) {
+  static const int64_t forced = [] { const char* e = std::getenv("RAMP_B200_SMALL_ROWS"); return e ? std::atoll(e) : int64_t{-1}; }();  // experiments
+  if (forced >= 0) return forced;
+  return std::max<int64_t>(1024, 8192 * 64 / std::max(64, m->hdr.n_pairs));
+}
 
 static void plan_warp_slab(const RampModel* m, int cols, WarpSlab* L) {
   const ImgHeader& h = m->hdr;
@@ -859,10 +883,12 @@ static void launch_tiles(const RampModel* m, const CheckPlan& P, const float* d_
                          int32_t* first, uint32_t* mask, const GjkQueue& gq, cudaStream_t st) {
   CheckArgs a = P.a;
   a.q = d_q; a.n = ns; a.hit = hit; a.first_pair = first; a.pair_mask = mask; a.gq = gq; a.row_offset = row_offset;
-  const int grid = grid_for(m, (ns + 31) / 32, P.nwarps / a.L.team);
-  if (P.team == 2) check_kernel<2><<<grid, P.nwarps * 32, P.smem, st>>>(a);
-  else if (P.team == 4) check_kernel<4><<<grid, P.nwarps * 32, P.smem, st>>>(a);
-  else check_kernel<1><<<grid, P.nwarps * 32, P.smem, st>>>(a);
+  int nwarps = P.nwarps;
+  size_t smem = P.smem;
+  const int grid = spread_tiles(m, (ns + 31) / 32, a.L, &nwarps, &smem);
+  if (P.team == 2) check_kernel<2><<<grid, nwarps * 32, smem, st>>>(a);
+  else if (P.team == 4) check_kernel<4><<<grid, nwarps * 32, smem, st>>>(a);
+  else check_kernel<1><<<grid, nwarps * 32, smem, st>>>(a);
   g_launches.fetch_add(1, std::memory_order_relaxed);
 }
 
@@ -941,7 +967,7 @@ static void plan_slices(const RampModel* m, int64_t n, int64_t* slice_rows, uint
 
 static int launch_check(const RampModel* m, const float* d_q, int64_t n, int32_t ld, uint32_t flags, uint8_t* d_hit,
                         int32_t* d_first, uint32_t* d_mask, cudaStream_t st) {
-  if (n <= kSmallRows) return launch_check_small(m, d_q, n, ld, flags, d_hit, d_first, d_mask, st);
+  if (n <= small_rows(m)) return launch_check_small(m, d_q, n, ld, flags, d_hit, d_first, d_mask, st);
   CheckPlan P;
   if (int rc = plan_check(m, ld, flags, n, &P)) return rc;
   unsigned char* scratch = nullptr;
@@ -1220,7 +1246,7 @@ static int fk_common(const RampModel* m, const float* d_q, int64_t n, int32_t ld
   if (a.row_floats == 0) return RAMP_OK;
   int nwarps; size_t smem;
   if (int rc = plan_slabs(m, a.row_floats, m->hdr.n_act, &a.L, &nwarps, &smem, ld)) return rc;
-  const int grid = grid_for(m, (n + 31) / 32, nwarps);
+  const int grid = spread_tiles(m, (n + 31) / 32, a.L, &nwarps, &smem);
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   if (what == 1) {
     fk_kernel<1><<<grid, nwarps * 32, smem, st>>>(a);
@@ -1315,7 +1341,8 @@ int ramp_check_batch_noalloc(const RampModel* m, const float* d_q, int64_t n, in
   // points then settle every item in the same place and give bit-identical results
   const uint32_t cap_items = queue_items_for(n);
   a.gq = GjkQueue{reinterpret_cast<GjkItem*>(scratch + 256), reinterpret_cast<uint32_t*>(scratch), cap_items, queue_cap_hard(cap_items)};
-  check_kernel<1><<<grid_for(m, (n + 31) / 32, nwarps), nwarps * 32, smem, st>>>(a);
+  const int grid = spread_tiles(m, (n + 31) / 32, a.L, &nwarps, &smem);
+  check_kernel<1><<<grid, nwarps * 32, smem, st>>>(a);
   GjkQueueArgs b{};
   b.img = m->d_image; b.table_bytes = static_cast<int32_t>(align16(m->hdr.total_bytes));
   b.items = a.gq.items; b.count = a.gq.count; b.capacity = cap_items; b.cap_hard = a.gq.cap_hard; b.stats = m->d_stats;
@@ -1342,7 +1369,8 @@ static int launch_min_distance(const RampModel* m, const float* d_q, int64_t n, 
   if (int rc = plan_slabs(m, 0, m->hdr.n_act, &a.L, &nwarps, &smem, ld, 1, true)) return rc;
   nwarps = std::min(nwarps, 8);
   smem = 16 + a.L.table_bytes + static_cast<size_t>(a.L.words) * 4 * nwarps;
-  distance_kernel<<<grid_for(m, (n + 31) / 32, nwarps), nwarps * 32, smem, st>>>(a);
+  const int grid = spread_tiles(m, (n + 31) / 32, a.L, &nwarps, &smem);
+  distance_kernel<<<grid, nwarps * 32, smem, st>>>(a);
   g_launches.fetch_add(1, std::memory_order_relaxed);
   CUDA_TRY(cudaGetLastError());
   return RAMP_OK;
@@ -1467,7 +1495,8 @@ int ramp_distance_batch(const RampModel* m, const float* d_q, int64_t n, int32_t
   if (int rc = plan_slabs(m, 0, m->hdr.n_act, &a.L, &nwarps, &smem, ld, 1, true)) return rc;
   nwarps = std::min(nwarps, 8);
   smem = 16 + a.L.table_bytes + static_cast<size_t>(a.L.words) * 4 * nwarps;
-  distance_kernel<<<grid_for(m, (n + 31) / 32, nwarps), nwarps * 32, smem, st>>>(a);
+  const int grid = spread_tiles(m, (n + 31) / 32, a.L, &nwarps, &smem);
+  distance_kernel<<<grid, nwarps * 32, smem, st>>>(a);
   g_launches.fetch_add(1, std::memory_order_relaxed);
   if (d_sel) CUDA_TRY(cudaFreeAsync(d_sel, st));
   CUDA_TRY(cudaGetLastError());
@@ -1693,7 +1722,7 @@ int ramp_check_host(const RampModel* m, const float* h_q, int64_t n, int32_t ld,
   }
   chunk = std::min(section, chunk);
   CheckPlan P;
-  const bool tiled = n > kSmallRows;
+  const bool tiled = n > small_rows(m);
   if (tiled)
     if (int rc = plan_check(m, ld, flags, n, &P)) return rc;
   const bool queued = tiled && P.use_queue;

@@ -96,8 +96,9 @@ CHECK_CASES = [("rrr/configs", None, 20000), ("rrr/planar_configs", "capsule", 2
                ("planar_rrr/configs", "capsule", 20000), ("floating", "obstacles", 20000),
                ("panda/configs", "capsule", 20000), ("fr3/configs", "capsule", 20000),
                ("ur5e/configs", "obstacles", 20000), ("unitree_h1/configs", None, 4000),
+               ("unitree_h1/configs", None, 1500),  # (177 pairs: one warp per configuration up to 2962 rows)
                # one joint of every type (RUB-unaligned, Spherical, SphericalZYX, Translation ... included),
-               # on the tile path and on the one-warp-per-configuration path (n <= 8192)
+               # on the tile path and on the one-warp-per-configuration path (n <= 8192 for an arm)
                ("joint_zoo", "capsule", 20000), ("joint_zoo", "capsule", 3000),
                # non-capsule link hulls: rounded boxes, elbows, plates, 100-vertex blobs
                ("panda_boxy/configs", "capsule", 20000), ("panda_boxy/configs", "capsule", 3000),
