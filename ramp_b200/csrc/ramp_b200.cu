@@ -1710,7 +1710,30 @@ int ramp_check_host(const RampModel* m, const float* h_q, int64_t n, int32_t ld,
   // queue kernel is exposed at the end (UR5, 2^20 rows: 0.726 -> 0.694 ms; more sections lose to
   // their queue kernels' drains).
   int64_t section = std::min<int64_t>(n, kSliceRows);
-  if (n <= kSliceRows) section = std::min<int64_t>(n, std::max<int64_t>(1 << 18, ((n + 2) / 3 + 31) & ~int64_t{31}));
+  std::vector<int64_t> sec_start;  // section boundaries (the last entry is n)
+  if (n <= kSliceRows) {
+    const int64_t even = std::min<int64_t>(n, std::max<int64_t>(1 << 18, ((n + 2) / 3 + 31) & ~int64_t{31}));
+    std::vector<double> frac(static_cast<size_t>((n + even - 1) / even), static_cast<double>(even) / n);
+    int64_t min_rows = 1;
+    if (const char* e = std::getenv("RAMP_B200_SECTIONS")) {  // experiments: comma-separated shares
+      frac.clear();
+      min_rows = 1 << 15;
+      for (const char* c = e; *c;) { char* end; frac.push_back(std::strtod(c, &end)); c = *end ? end + 1 : end; }
+    }
+    sec_start.push_back(0);
+    double acc = 0;
+    for (size_t i = 0; i + 1 < frac.size(); ++i) {
+      acc += frac[i];
+      const int64_t b = (static_cast<int64_t>(acc * n) + 31) & ~int64_t{31};
+      if (b - sec_start.back() >= min_rows && n - b >= min_rows) sec_start.push_back(b);
+    }
+    sec_start.push_back(n);
+    section = 0;
+    for (size_t i = 0; i + 1 < sec_start.size(); ++i) section = std::max(section, sec_start[i + 1] - sec_start[i]);
+  } else {
+    for (int64_t b = 0; b < n; b += section) sec_start.push_back(b);
+    sec_start.push_back(n);
+  }
   // Chunk size: 2^18 rows, or for batches of several slices about 16 MB of rows (a power of two
   // between 2^17 and 2^19 rows): the copy engine reaches 53 GB/s on copies of that size and 45-50
   // on 6 MB ones (UR5, 24 B per row, 2^24 rows: 2.05e9 -> 2.13e9 configurations/s).
@@ -1752,8 +1775,8 @@ int ramp_check_host(const RampModel* m, const float* h_q, int64_t n, int32_t ld,
   unsigned char* H = static_cast<unsigned char*>(m->h_pinned);
   int64_t k = 0;  // chunk counter over the whole call: picks the stream and the q buffer
   int64_t nsec = 0;
-  for (int64_t s0 = 0; s0 < n; s0 += section, ++nsec) {
-    const int64_t s1 = std::min(n, s0 + section), rows = s1 - s0;
+  for (; nsec + 1 < static_cast<int64_t>(sec_start.size()); ++nsec) {
+    const int64_t s0 = sec_start[nsec], s1 = sec_start[nsec + 1], rows = s1 - s0;
     const int par = static_cast<int>(nsec & 1);
     unsigned char* Dout = D + kHostStreams * b_q + par * b_out;
     uint8_t* d_hit = Dout;
