@@ -505,6 +505,25 @@ def measure_edges(name: str, n_edges: int, steps: int, warmup: int, dev, *, seed
            "e2e": {"value": e2e_value, "unit": "states/s", "h2d_bytes_per_step": int(h0.nbytes + h1.nbytes),
                    "d2h_bytes_per_step": 9 * n_edges, "api": "ramp_check_edges_host (C ABI, host buffers)", "steps": e2e_steps},
            "gpu_launches": launches}
+    if n_edges < (1 << 18):
+        # the same call on a roadmap-sized batch (2^18 edges, one slice): the throughput regime
+        big = 1 << 18
+        b0 = spaces.sample_uniform(planner.space, big, rng)
+        b1 = np.clip(b0 + rng.normal(scale=0.4, size=b0.shape), lo, hi)
+        e0, e1 = torch.from_numpy(b0.astype(np.float32)).to(dev), torch.from_numpy(b1.astype(np.float32)).to(dev)
+        res = gpu.check_edges(e0, e1, planner.space)
+        big_states = int(res["nd"].clamp(min=1).sum().item())
+        for _ in range(2):
+            gpu.check_edges(e0, e1, planner.space)
+        torch.cuda.synchronize()
+        a.record()
+        for _ in range(steps):
+            gpu.check_edges(e0, e1, planner.space)
+        b.record()
+        torch.cuda.synchronize()
+        big_ms = a.elapsed_time(b) / steps
+        out["large_batch"] = {"edges": big, "states": big_states, "ms_per_step": big_ms, "states_per_s": big_states / (big_ms * 1e-3),
+                              "edges_per_s": big / (big_ms * 1e-3)}
     if seeds > 0:
         out["planning"] = planning_leg(seeds, cpu_queries)
     return out

@@ -70,39 +70,80 @@ struct EdgeArgs {
   DSpace sp;
 };
 
-// pass 1: nd per edge, number of states to check per edge (nd interior+end states, >= 1)
-__global__ void edge_count_kernel(const __grid_constant__ EdgeArgs a) {
-  const int64_t e = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
-  if (e >= a.n_edges) return;
-  const int nd = edge_nd(a.sp, a.q0 + e * a.ld, a.q1 + e * a.ld);
-  a.nd[e] = nd;
-  a.first_invalid[e] = INT32_MAX;
-  a.offs[e + 1] = max(nd, 1);
+// pass 1: nd per edge and the number of states to check per edge (nd interior + end states, >= 1),
+// scanned within the block of 256 edges: offs[e + 1] = inclusive prefix inside the block,
+// blk[block] = the block's total
+__global__ void __launch_bounds__(256) edge_count_kernel(const __grid_constant__ EdgeArgs a, int64_t* __restrict__ blk) {
+  __shared__ int64_t wsum[8];
+  const int64_t e = static_cast<int64_t>(blockIdx.x) * 256 + threadIdx.x;
+  const int l = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  int64_t v = 0;
+  if (e < a.n_edges) {
+    const int nd = edge_nd(a.sp, a.q0 + e * a.ld, a.q1 + e * a.ld);
+    a.nd[e] = nd;
+    a.first_invalid[e] = INT32_MAX;
+    v = max(nd, 1);
+  }
+#pragma unroll
+  for (int d = 1; d < 32; d <<= 1) {
+    const int64_t u = __shfl_up_sync(0xffffffffu, v, d);
+    if (l >= d) v += u;
+  }
+  if (l == 31) wsum[wid] = v;
+  __syncthreads();
+  int64_t before = 0;
+#pragma unroll
+  for (int k = 0; k < 8; ++k) before += k < wid ? wsum[k] : 0;
+  v += before;
+  if (e < a.n_edges) a.offs[e + 1] = v;
+  if (threadIdx.x == 255) blk[blockIdx.x] = v;
 }
 
-// pass 2: in-place inclusive scan of offs[1..n] by one CTA (offs[0] = 0)
-__global__ void __launch_bounds__(1024) edge_scan_kernel(int64_t* offs, int64_t n) {
-  __shared__ int64_t part[1024];
-  const int t = threadIdx.x;
-  const int64_t per = (n + 1023) / 1024, lo = imin64(n, t * per), hi = imin64(n, lo + per);
-  int64_t s = 0;
-  for (int64_t i = lo; i < hi; ++i) s += offs[i + 1];
-  part[t] = s;
+// pass 2a: exclusive scan of the block totals by one CTA, 1024 at a time with a running carry
+// (a slice of 2^18 edges has 1024 blocks)
+__global__ void __launch_bounds__(1024) edge_scan_kernel(int64_t* __restrict__ blk, int64_t nb, int64_t* __restrict__ offs) {
+  __shared__ int64_t wsum[32];
+  __shared__ int64_t carry_s;
+  const int t = threadIdx.x, l = t & 31, wid = t >> 5;
+  if (t == 0) carry_s = 0;
   __syncthreads();
-  for (int d = 1; d < 1024; d <<= 1) {
-    const int64_t v = t >= d ? part[t - d] : 0;
+  for (int64_t base = 0; base < nb; base += 1024) {
+    const int64_t i = base + t;
+    const int64_t own = i < nb ? blk[i] : 0;
+    int64_t v = own;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+      const int64_t u = __shfl_up_sync(0xffffffffu, v, d);
+      if (l >= d) v += u;
+    }
+    if (l == 31) wsum[wid] = v;
     __syncthreads();
-    part[t] += v;
+    if (wid == 0) {
+      int64_t ws = wsum[l];
+#pragma unroll
+      for (int d = 1; d < 32; d <<= 1) {
+        const int64_t u = __shfl_up_sync(0xffffffffu, ws, d);
+        if (l >= d) ws += u;
+      }
+      wsum[l] = ws;  // inclusive over the warps
+    }
+    __syncthreads();
+    const int64_t carry = carry_s;
+    const int64_t incl = v + (wid ? wsum[wid - 1] : 0) + carry;
+    if (i < nb) blk[i] = incl - own;  // exclusive
+    __syncthreads();
+    if (t == 1023) carry_s = incl;
     __syncthreads();
   }
-  int64_t run = t ? part[t - 1] : 0;
   // more states than a 32-bit flat index can name: offs[0] = -1 tells the check kernel to do
   // nothing and the finish kernel to report every edge of the slice as unchecked (-2)
-  if (t == 0) offs[0] = part[1023] > 0xffffffffll ? -1 : 0;
-  for (int64_t i = lo; i < hi; ++i) {
-    run += offs[i + 1];
-    offs[i + 1] = run;
-  }
+  if (t == 0) offs[0] = carry_s > 0xffffffffll ? -1 : 0;
+}
+
+// pass 2b: the blocks' offsets added to the prefixes inside the blocks
+__global__ void __launch_bounds__(256) edge_offsets_kernel(int64_t* __restrict__ offs, const int64_t* __restrict__ blk, int64_t n) {
+  const int64_t e = static_cast<int64_t>(blockIdx.x) * 256 + threadIdx.x;
+  if (blockIdx.x > 0 && e < n) offs[e + 1] += blk[blockIdx.x];
 }
 
 // pass 3: every warp tile is 32 consecutive (edge, j) states of the flattened list

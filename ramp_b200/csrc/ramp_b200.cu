@@ -783,7 +783,7 @@ constexpr int64_t kQueueItemsPerRow = 3;
 constexpr uint32_t queue_items_for(int64_t rows) { return static_cast<uint32_t>(rows * kQueueItemsPerRow + 4096); }
 constexpr int64_t kQueueMinRows = 1024;    // below this a second launch costs more than it saves
 
-constexpr int64_t kEdgeSliceEdges = 1 << 22;  // edges per launch group of ramp_check_edges
+constexpr int64_t kEdgeSliceEdges = 1 << 18;  // edges per launch group of ramp_check_edges (see there)
 // Up to here one warp per configuration is faster than 32 configurations per warp: 8192 rows for
 // an arm (Panda 32 pairs, UR5 45: 35 us against 44 us at 4096 rows, level at 8192), fewer for a
 // robot with many pairs, whose pair list takes a warp several rounds (H1, 177 pairs: 61 us
@@ -1563,27 +1563,31 @@ int ramp_check_edges(const RampModel* m, const float* d_q0, const float* d_q1, i
     CUDA_TRY(cudaGetLastError());
     return RAMP_OK;
   }
-  // Edges are processed in slices: the flat index of an interpolated state travels as 32 bits in
-  // the GJK work items, and a slice of 2^22 edges stays below 2^32 states for any mean segment
-  // count up to 1023 (edges with both ends inside the bounds have at most ~101).  A slice that
-  // still exceeds it is not checked at all: every one of its edges is reported invalid with
-  // first_invalid = -2 (edge_scan_kernel / edge_finish_kernel), which no valid result can be.
+  // Edges are processed in slices of 2^18.  The flat index of an interpolated state travels as 32
+  // bits in the GJK work items: a slice stays below 2^32 states for any mean segment count up to
+  // 16 383 (edges with both ends inside the bounds have at most ~101); one that still exceeds it is
+  // not checked at all -- every one of its edges is reported invalid with first_invalid = -2
+  // (edge_scan_kernel / edge_finish_kernel), which no valid result can be.  And the GJK queue of a
+  // slice stays a few hundred MB: 2^18 planner edges are ~4M states and ~0.15 items per state on an
+  // arm (FR3 stand-in, 2^20 edges: 2.4e9 states/s in one slice whose queue overflowed into the
+  // in-kernel path, 4.1e9 in slices of 2^18).
   int nwarps; size_t smem;
   if (int rc = plan_slabs(m, 0, n_cols, &a.L, &nwarps, &smem)) return rc;
   const size_t smem_b = 16 + align16(m->hdr.total_bytes);
   const int64_t slice = std::min<int64_t>(n_edges, kEdgeSliceEdges);
-  // scratch: offs int64[n+1] | nd int32[n] | first int32[n]
+  // scratch: offs int64[n+1] | nd int32[n] | first int32[n] | totals of the blocks of 256 edges int64[n/256]
   const size_t off_nd = align16(sizeof(int64_t) * (slice + 1));
   const size_t off_first = off_nd + align16(sizeof(int32_t) * slice);
+  const size_t off_blk = off_first + align16(sizeof(int32_t) * slice);
   void* edge_scratch = nullptr;
-  if (int rc = pool_alloc(m, off_first + align16(sizeof(int32_t) * slice), st, &edge_scratch)) return rc;
+  if (int rc = pool_alloc(m, off_blk + align16(sizeof(int64_t) * ((slice + 255) / 256)), st, &edge_scratch)) return rc;
   unsigned char* S = static_cast<unsigned char*>(edge_scratch);
   // GJK work queue (only worth a launch when there are enough edges to fill warps)
   void* qmem = nullptr;
   const bool use_queue = m->n_gjk_pairs > 0 && n_edges >= 64;
   uint32_t cap = 0;
   if (use_queue) {
-    cap = static_cast<uint32_t>(std::min<int64_t>(std::max<int64_t>(1 << 16, slice * 64), 1 << 21));
+    cap = static_cast<uint32_t>(std::min<int64_t>(std::max<int64_t>(1 << 16, slice * 64), 1 << 22));
     if (int rc = pool_alloc(m, 256 + static_cast<size_t>(cap) * sizeof(GjkItem), st, &qmem)) {
       cudaFreeAsync(edge_scratch, st);
       return rc;
@@ -1606,13 +1610,15 @@ int ramp_check_edges(const RampModel* m, const float* d_q0, const float* d_q1, i
       b.offs = a.offs; b.nd = a.nd; b.first_invalid = a.first_invalid; b.n_edges = ne;
     }
     const int eb = static_cast<int>((ne + 255) / 256);
-    edge_count_kernel<<<eb, 256, 0, st>>>(a);
-    edge_scan_kernel<<<1, 1024, 0, st>>>(a.offs, ne);
+    int64_t* blk = reinterpret_cast<int64_t*>(S + off_blk);
+    edge_count_kernel<<<eb, 256, 0, st>>>(a, blk);
+    edge_scan_kernel<<<1, 1024, 0, st>>>(blk, eb, a.offs);
+    if (eb > 1) edge_offsets_kernel<<<eb, 256, 0, st>>>(a.offs, blk, ne);
     // the number of states is only known on the device: size the grid for the SM count
     edge_check_kernel<<<m->sm_count, nwarps * 32, smem, st>>>(a);
     if (use_queue) gjk_queue_kernel<<<m->sm_count * kGjkCtasPerSm, 256, smem_b, st>>>(b);
     edge_finish_kernel<<<eb, 256, 0, st>>>(a, d_first_invalid ? d_first_invalid + e0 : nullptr, d_nd ? d_nd + e0 : nullptr);
-    g_launches.fetch_add(use_queue ? 5 : 4, std::memory_order_relaxed);
+    g_launches.fetch_add((use_queue ? 5 : 4) + (eb > 1 ? 1 : 0), std::memory_order_relaxed);
   }
   if (qmem) CUDA_TRY(cudaFreeAsync(qmem, st));
   CUDA_TRY(cudaFreeAsync(edge_scratch, st));

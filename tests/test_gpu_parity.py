@@ -212,6 +212,50 @@ def test_edges_match_oracle(built, name, scene, n_edges):
     assert unexplained == 0
 
 
+def test_edges_large_batch_matches_small_batches(built):
+    """A batch of more than one slice of edges (2^18; offsets scanned over 1000+ blocks of 256 edges)
+    gives what the same edges give in batches of 3000: same segment counts, same verdicts and first
+    invalid states but for margin-band states (the GJK of a short and of a long work queue share
+    vertex scans differently), and a sample agrees with the oracle."""
+    from oracle import oracle
+    from ramp_b200 import spaces
+    from ramp_b200.desc import ModelDesc
+
+    rm, _ = _setup("panda/configs", "capsule")
+    space = spaces.make_space(rm, "arm")
+    qmap = spaces.make_qmap(rm, "arm")
+    gpu = rm.gpu
+    gpu.set_qmap(qmap)
+    n_edges = (1 << 18) + 777
+    rng = np.random.default_rng(11)
+    q0 = spaces.sample_uniform(space, n_edges, rng).astype(np.float32)
+    q1 = (q0 + rng.normal(scale=0.3, size=q0.shape)).astype(np.float32)
+    d0, d1 = torch.from_numpy(q0).cuda(), torch.from_numpy(q1).cuda()
+    big = {k: v.cpu().numpy() for k, v in gpu.check_edges(d0, d1, space).items()}
+    valid, first, nd = (np.empty_like(big[k]) for k in ("valid", "first_invalid", "nd"))
+    for lo in range(0, n_edges, 3000):
+        part = gpu.check_edges(d0[lo:lo + 3000], d1[lo:lo + 3000], space)
+        valid[lo:lo + 3000], first[lo:lo + 3000], nd[lo:lo + 3000] = (part[k].cpu().numpy() for k in ("valid", "first_invalid", "nd"))
+    assert np.array_equal(big["nd"], nd)
+    differ = np.flatnonzero((big["valid"] != valid) | (big["first_invalid"] != first))
+    assert len(differ) <= 1e-4 * n_edges, f"{len(differ)} edges differ between one large and many small batches"
+    assert 0.05 < big["valid"].mean() < 0.95
+    d = ModelDesc(rm.model, rm.collision_model)
+    for e in differ[:20]:  # each explained by a state in the margin band
+        js = {int(big["first_invalid"][e]), int(first[e])} - {-1}
+        n_d = int(nd[e])
+        near = False
+        for j in js:
+            st = q1[e].astype(np.float64) if j >= n_d else oracle.edge_interpolate(space, q0[e], q1[e], j / n_d)
+            near = near or abs(oracle.check(d, oracle.qmap_apply(qmap, st))["min_dist"][0]) <= BAND
+        assert near
+    pick = np.r_[np.arange(100), (1 << 18) - 50 + np.arange(100), n_edges - 100 + np.arange(100)]  # across the slice boundary
+    ref = oracle.check_edges(d, qmap, space, q0[pick].astype(np.float64), q1[pick].astype(np.float64))
+    same_nd = big["nd"][pick] == ref["nd"]
+    agree = (big["valid"][pick] == ref["valid"]) & (big["first_invalid"][pick] == ref["first_invalid"])
+    assert same_nd.mean() > 0.97 and (agree | ~same_nd).mean() > 0.98
+
+
 def test_scene_update_and_pair_toggle(built):
     """add_object after the handle exists (ramp_model_set_scene) and pair (de)activation."""
     from ramp_b200 import workloads
