@@ -570,6 +570,86 @@ class CpuStateValidator:
         return {"valid": torch.tensor([self.checkMotion(a, b) for a, b in zip(q0, q1)])}
 
 
+def measure_next_rows(dev, with_cpu: bool) -> dict:
+    """The rows SURVEY 8(f) ranks next, measured on the Panda stand-in: f1 all-pairs sampling for the
+    ALWAYS / NEVER reasons, f3 clearance (smallest signed distance), f4 batched differential-IK seeds
+    (f2 is the FK and edge rows above).  Device-resident inputs; the CPU column is the oracle
+    (OpenMP, all host threads) on a bounded sample."""
+    import numpy as np
+    import torch
+
+    from ramp_b200 import RobotState, workloads
+    from ramp_b200.desc import ModelDesc
+
+    rm, _ = workloads.build("panda_64m")
+    gpu = rm.gpu
+    desc = ModelDesc(rm.model, rm.collision_model)
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+
+    def timed(fn, steps):
+        fn()
+        torch.cuda.synchronize()
+        a.record()
+        for _ in range(steps):
+            fn()
+        b.record()
+        torch.cuda.synchronize()
+        return a.elapsed_time(b) * 1e-3 / steps
+
+    out = {"workload": "next_rows", "robot": "panda/configs", "scene": "capsule", "model": "stand-in"}
+    n1 = 1 << 20
+    q = workloads.sample_q_torch(rm.model, n1, seed=5, device=dev)
+    dt = timed(lambda: gpu.check(q, pair_mask=True), 5)
+    out["f1_all_pairs_mask"] = {"configs": n1, "pairs": len(rm.collision_model.collisionPairs), "configs_per_s": n1 / dt,
+                                "api": "GpuModel.check(pair_mask=True): every pair of every configuration, one bit each"}
+    n3 = 1 << 16
+    dt = timed(lambda: gpu.clearance(q[:n3]), 2)
+    out["f3_clearance"] = {"configs": n3, "configs_per_s": n3 / dt,
+                           "api": "GpuModel.clearance: signed distance of every pair to convergence (GJK / EPA), minimum per configuration"}
+    rs = RobotState.from_named_state(rm, "arm", "home")
+    params = rm.ik_params("arm")
+    n4 = 1 << 16
+    rng = np.random.default_rng(4)
+    lo, hi = np.maximum(params.lower, -3.0), np.minimum(params.upper, 3.0)
+    goal = rng.uniform(lo, hi, (n4, len(lo)))
+    seeds = np.clip(goal + rng.normal(scale=0.3, size=goal.shape), params.lower, params.upper).astype(np.float32)
+    frame = rm.model.frames[rm.model.getFrameId(rm["arm"].tcp_link_name)]
+    from ramp_b200 import spaces
+    gpu.set_qmap(spaces.make_qmap(rm, "arm", rs.qpos))
+    omi = gpu.forward_kinematics(torch.from_numpy(goal.astype(np.float32)).to(dev), actuated=True)[:, frame.parentJoint - 1]
+    pl = torch.from_numpy(frame.placement.rt34().astype(np.float32)).to(dev)
+    targets = torch.cat([omi[:, :, :3] @ pl[:, :3], (omi[:, :, :3] @ pl[:, 3] + omi[:, :, 3]).unsqueeze(2)], dim=2).contiguous()
+    d_seeds = torch.from_numpy(seeds).to(dev)
+    res = rm.differential_ik_batch("arm", d_seeds, targets, reference_state=rs)
+    dt = timed(lambda: rm.differential_ik_batch("arm", d_seeds, targets, reference_state=rs), 3)
+    out["f4_ik_seeds"] = {"seeds": n4, "seeds_per_s": n4 / dt, "converged_fraction": float(res["ok"].float().mean().item()),
+                          "mean_iterations": float(res["iters"].float().mean().item()), "max_iterations": int(params.struct.max_iterations),
+                          "api": "RobotModel.differential_ik_batch (ramp_ik_batch): damped least squares to 1e-3, one lane per seed"}
+    # a goal-state generator keeps the seeds that converge and has no use for the last per cent that
+    # would run to the reference's 500 iterations: the same call with 64
+    res64 = rm.differential_ik_batch("arm", d_seeds, targets, reference_state=rs, max_iterations=64)
+    dt64 = timed(lambda: rm.differential_ik_batch("arm", d_seeds, targets, reference_state=rs, max_iterations=64), 3)
+    out["f4_ik_seeds"]["max_iterations_64"] = {"seeds_per_s": n4 / dt64, "converged_fraction": float(res64["ok"].float().mean().item())}
+    if with_cpu:
+        from oracle import oracle
+
+        threads = oracle.num_threads()
+        qs = q[: 1 << 15].cpu().numpy().astype(np.float64)
+        t0 = time.perf_counter()
+        oracle.check(desc, qs, mode=0, want_pair_dist=False)
+        out["f1_all_pairs_mask"]["cpu_oracle"] = {"configs_per_s": len(qs) / (time.perf_counter() - t0), "cores": threads, "sample": len(qs)}
+        qs = qs[: 1 << 13]
+        t0 = time.perf_counter()
+        oracle.check(desc, qs)
+        out["f3_clearance"]["cpu_oracle"] = {"configs_per_s": len(qs) / (time.perf_counter() - t0), "cores": threads, "sample": len(qs)}
+        k = 1 << 12
+        qmap = spaces.make_qmap(rm, "arm", rs.qpos)
+        t0 = time.perf_counter()
+        oracle.ik(desc, qmap, params, seeds[:k].astype(np.float64), targets[:k].cpu().numpy().astype(np.float64))
+        out["f4_ik_seeds"]["cpu_oracle"] = {"seeds_per_s": k / (time.perf_counter() - t0), "cores": threads, "sample": k}
+    return out
+
+
 def planning_leg(seeds: int, cpu_seeds: int) -> dict:
     """BASELINE config 3 as SURVEY 8(d) specifies it: FR3 (stand-in), start ``home``, goal
     [0, 0.25, 0, -1.25, 0, 1.5, 0] (reference examples/motion_planning.py:27), the reference capsule
@@ -697,6 +777,7 @@ def main() -> None:
             torch.cuda.empty_cache()
         subs.append(measure_fk("panda_64m", 1 << 22, 10, 3, dev))
         subs.append(measure_edges("fr3_edges", 1 << 14, 5, 3, dev, seeds=args.plan_seeds, cpu_queries=0 if args.no_cpu_baseline else args.plan_seeds))
+        subs.append(measure_next_rows(dev, not args.no_cpu_baseline))
     if rank == 0:
         out = {"metric": METRIC, "value": head["value"], "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
                "ms_per_step": head["ms_per_step"], "higher_is_better": True, "scaling": "weak", "vs_baseline": None,

@@ -105,104 +105,127 @@ __device__ __forceinline__ void ik_full_column(const Warp& w, const IkArgs& a, i
   col[0] = lin.x; col[1] = lin.y; col[2] = lin.z; col[3] = ang.x; col[4] = ang.y; col[5] = ang.z;
 }
 
-__global__ void __launch_bounds__(256, 1) ik_kernel(const __grid_constant__ IkArgs a) {
+// Persistent lanes: seeds need anything from 3 to max_iter iterations (a seed that runs into a
+// joint limit or a singularity never converges), so a lane that is finished writes its result and
+// takes the next seed -- warps draw 32 seeds at a time from a cursor -- instead of the whole tile
+// waiting for its slowest seed (one tile in four has a seed that runs to 500 iterations when 1 %
+// of the seeds do).  `cursor` is zeroed by the host.
+__global__ void __launch_bounds__(512, 1) ik_kernel(const __grid_constant__ IkArgs a, unsigned long long* __restrict__ cursor) {
   uint64_t* mbar = reinterpret_cast<uint64_t*>(g_smem);
   unsigned char* tbl = g_smem + 16;
   stage_tables(tbl, a.img, a.L.table_bytes, mbar);
   const Tables t = make_tables(tbl);
-  const int nwarps = blockDim.x >> 5, wid = threadIdx.x >> 5;
+  const int wid = threadIdx.x >> 5;
   float* slab = reinterpret_cast<float*>(tbl + a.L.table_bytes) + static_cast<size_t>(wid) * a.L.words;
   const Warp w = make_warp(t, slab, a.L);
   const int l = w.lane;
   const unsigned FULL = 0xffffffffu;
-  const int64_t ntiles = (a.n + 31) >> 5;
-  for (int64_t tile = static_cast<int64_t>(blockIdx.x) * nwarps + wid; tile < ntiles; tile += static_cast<int64_t>(gridDim.x) * nwarps) {
-    const int64_t row0 = tile << 5, row = row0 + l;
-    load_rows(w.act, a.seed, row0, a.n, a.n_cols, a.ld, l);
-    const float* tg = a.target + (row < a.n ? row : row0) * a.target_stride;
-    Xf target;
+  Xf fpl;
 #pragma unroll
-    for (int k = 0; k < 12; ++k) target.m[k] = __ldg(tg + k);
-    bool done = false;
-    float err = 3.0e38f;
-    int it = 0;
-    while (true) {
-      expand_q(w);
-      fk_lane<1>(w);
-      __syncwarp();
-      Xf fpl;
-#pragma unroll
-      for (int k = 0; k < 12; ++k) fpl.m[k] = a.frame_pl[k];
-      const Xf tcp = a.frame_joint < 0 ? fpl : xf_mul(read_staged_xf(w, a.frame_joint), fpl);
-      const Xf d = xf_inv_mul(tcp, target);  // the target seen from the frame
-      const V3 ep = trans(d), er = log_so3(d);
-      const float e[6] = {ep.x, ep.y, ep.z, er.x, er.y, er.z};
-      if (!done) {
-        err = sqrtf(dot(ep, ep) + dot(er, er));
-        done = err < a.tol;
+  for (int k = 0; k < 12; ++k) fpl.m[k] = a.frame_pl[k];
+  int64_t row = -1, lo = 0, hi = 0;  // this lane's seed (-1: idle); [lo, hi): seeds the warp holds but has not started
+  bool exhausted = false;
+  Xf target = xf_identity();
+  int it = 0;
+  for (int k = 0; k < a.n_cols; ++k) w.act[k * 32 + l] = 0.f;  // idle lanes run the kinematics too: on defined values
+  while (true) {
+    // ---- idle lanes take the next seeds
+    const unsigned need = __ballot_sync(FULL, row < 0);
+    if (need && !(exhausted && lo == hi)) {
+      const int rank = __popc(need & ((1u << l) - 1)), nneed = __popc(need);
+      if (lo == hi && !exhausted) {
+        unsigned long long base = 0;
+        if (l == 0) base = atomicAdd(cursor, 32ull);
+        base = __shfl_sync(FULL, base, 0);
+        if (static_cast<int64_t>(base) >= a.n) exhausted = true;
+        else { lo = static_cast<int64_t>(base); hi = imin64(lo + 32, a.n); }
       }
-      if (__all_sync(FULL, done || it >= a.max_iter)) break;
-      if (!done && it < a.max_iter) {
-        // A = J J^T + lambda^2 I (lower triangle, row-major packed)
-        float A[21];
+      if (row < 0 && lo + rank < hi) {
+        row = lo + rank;
+        const float* sd = a.seed + row * a.ld;
+        for (int k = 0; k < a.n_cols; ++k) w.act[k * 32 + l] = __ldg(sd + k);
+        const float* tg = a.target + row * a.target_stride;
 #pragma unroll
-        for (int i = 0; i < 21; ++i) A[i] = 0.f;
-#pragma unroll
-        for (int i = 0; i < 6; ++i) A[i * (i + 1) / 2 + i] = a.damping2;
-#pragma unroll 1
-        for (int k = 0; k < a.n_cols; ++k) {
-          float c[6];
-          ik_full_column(w, a, k, tcp, c);
-#pragma unroll
-          for (int i = 0; i < 6; ++i)
-#pragma unroll
-            for (int j = 0; j <= i; ++j) A[i * (i + 1) / 2 + j] = fmaf(c[i], c[j], A[i * (i + 1) / 2 + j]);
-        }
-        // Cholesky A = L L^T in place, then L z = e, L^T y = z
-#pragma unroll
-        for (int i = 0; i < 6; ++i) {
-#pragma unroll
-          for (int j = 0; j <= i; ++j) {
-            float s = A[i * (i + 1) / 2 + j];
-#pragma unroll
-            for (int k = 0; k < j; ++k) s = fmaf(-A[i * (i + 1) / 2 + k], A[j * (j + 1) / 2 + k], s);
-            A[i * (i + 1) / 2 + j] = i == j ? sqrtf(fmaxf(s, 1e-20f)) : s / A[j * (j + 1) / 2 + j];
-          }
-        }
-        float y[6];
-#pragma unroll
-        for (int i = 0; i < 6; ++i) {
-          float s = e[i];
-#pragma unroll
-          for (int k = 0; k < i; ++k) s = fmaf(-A[i * (i + 1) / 2 + k], y[k], s);
-          y[i] = s / A[i * (i + 1) / 2 + i];
-        }
-#pragma unroll
-        for (int i = 5; i >= 0; --i) {
-          float s = y[i];
-#pragma unroll
-          for (int k = i + 1; k < 6; ++k) s = fmaf(-A[k * (k + 1) / 2 + i], y[k], s);
-          y[i] = s / A[i * (i + 1) / 2 + i];
-        }
-#pragma unroll 1
-        for (int k = 0; k < a.n_cols; ++k) {
-          float c[6];
-          ik_full_column(w, a, k, tcp, c);
-          float dq = 0.f;
-#pragma unroll
-          for (int i = 0; i < 6; ++i) dq = fmaf(c[i], y[i], dq);
-          dq = clampf(a.step * dq, -a.max_dq, a.max_dq);
-          w.act[k * 32 + l] = clampf(w.act[k * 32 + l] + dq, a.lo[k], a.hi[k]);
-        }
-        ++it;
+        for (int k = 0; k < 12; ++k) target.m[k] = __ldg(tg + k);
+        it = 0;
       }
-      __syncwarp();
+      lo = imin64(lo + nneed, hi);
     }
-    if (row < a.n) {
+    if (__all_sync(FULL, row < 0)) {
+      if (exhausted && lo == hi) break;
+      continue;
+    }
+    __syncwarp();
+    // ---- one iteration for every lane that holds a seed
+    expand_q(w);
+    fk_lane<1>(w);
+    __syncwarp();
+    const Xf tcp = a.frame_joint < 0 ? fpl : xf_mul(read_staged_xf(w, a.frame_joint), fpl);
+    const Xf d = xf_inv_mul(tcp, target);  // the target seen from the frame
+    const V3 ep = trans(d), er = log_so3(d);
+    const float e[6] = {ep.x, ep.y, ep.z, er.x, er.y, er.z};
+    const float err = sqrtf(dot(ep, ep) + dot(er, er));
+    const bool done = err < a.tol;
+    if (row >= 0 && (done || it >= a.max_iter)) {
       for (int k = 0; k < a.n_cols; ++k) a.q_out[row * a.n_cols + k] = w.act[k * 32 + l];
       if (a.err_out) a.err_out[row] = err;
       if (a.ok) a.ok[row] = done;
       if (a.iters_out) a.iters_out[row] = it;
+      row = -1;
+    }
+    if (row >= 0) {
+      // A = J J^T + lambda^2 I (lower triangle, row-major packed)
+      float A[21];
+#pragma unroll
+      for (int i = 0; i < 21; ++i) A[i] = 0.f;
+#pragma unroll
+      for (int i = 0; i < 6; ++i) A[i * (i + 1) / 2 + i] = a.damping2;
+#pragma unroll 1
+      for (int k = 0; k < a.n_cols; ++k) {
+        float c[6];
+        ik_full_column(w, a, k, tcp, c);
+#pragma unroll
+        for (int i = 0; i < 6; ++i)
+#pragma unroll
+          for (int j = 0; j <= i; ++j) A[i * (i + 1) / 2 + j] = fmaf(c[i], c[j], A[i * (i + 1) / 2 + j]);
+      }
+      // Cholesky A = L L^T in place, then L z = e, L^T y = z
+#pragma unroll
+      for (int i = 0; i < 6; ++i) {
+#pragma unroll
+        for (int j = 0; j <= i; ++j) {
+          float s = A[i * (i + 1) / 2 + j];
+#pragma unroll
+          for (int k = 0; k < j; ++k) s = fmaf(-A[i * (i + 1) / 2 + k], A[j * (j + 1) / 2 + k], s);
+          A[i * (i + 1) / 2 + j] = i == j ? sqrtf(fmaxf(s, 1e-20f)) : s / A[j * (j + 1) / 2 + j];
+        }
+      }
+      float y[6];
+#pragma unroll
+      for (int i = 0; i < 6; ++i) {
+        float s = e[i];
+#pragma unroll
+        for (int k = 0; k < i; ++k) s = fmaf(-A[i * (i + 1) / 2 + k], y[k], s);
+        y[i] = s / A[i * (i + 1) / 2 + i];
+      }
+#pragma unroll
+      for (int i = 5; i >= 0; --i) {
+        float s = y[i];
+#pragma unroll
+        for (int k = i + 1; k < 6; ++k) s = fmaf(-A[k * (k + 1) / 2 + i], y[k], s);
+        y[i] = s / A[i * (i + 1) / 2 + i];
+      }
+#pragma unroll 1
+      for (int k = 0; k < a.n_cols; ++k) {
+        float c[6];
+        ik_full_column(w, a, k, tcp, c);
+        float dq = 0.f;
+#pragma unroll
+        for (int i = 0; i < 6; ++i) dq = fmaf(c[i], y[i], dq);
+        dq = clampf(a.step * dq, -a.max_dq, a.max_dq);
+        w.act[k * 32 + l] = clampf(w.act[k * 32 + l] + dq, a.lo[k], a.hi[k]);
+      }
+      ++it;
     }
     __syncwarp();
   }

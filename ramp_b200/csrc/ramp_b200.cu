@@ -1448,16 +1448,20 @@ int ramp_ik_batch(const RampModel* m, const float* d_seed, int64_t n, int32_t ld
   CUDA_TRY(cudaSetDevice(m->device));
   int nwarps; size_t smem;
   if (int rc = plan_slabs(m, 12 * nj, n_act, &a.L, &nwarps, &smem, ld)) return rc;
-  nwarps = std::min(nwarps, 8);
-  smem = 16 + a.L.table_bytes + static_cast<size_t>(a.L.words) * 4 * nwarps;
+  nwarps = std::min(nwarps, 16);
   // IK batches are small (hundreds to thousands of seeds) and every seed iterates tens of times:
-  // spread the tiles over the SMs rather than filling CTAs
+  // spread the seeds over the SMs rather than filling CTAs
   const int64_t tiles = (n + 31) / 32;
   const int warps_per_cta = static_cast<int>(std::max<int64_t>(1, std::min<int64_t>(nwarps, (tiles + m->sm_count - 1) / m->sm_count)));
   const int grid = static_cast<int>(std::min<int64_t>((tiles + warps_per_cta - 1) / warps_per_cta, m->sm_count));
   smem = 16 + a.L.table_bytes + static_cast<size_t>(a.L.words) * 4 * warps_per_cta;
-  ik_kernel<<<grid, warps_per_cta * 32, smem, static_cast<cudaStream_t>(stream)>>>(a);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  void* cursor = nullptr;  // the seed cursor the warps draw from
+  if (int rc = pool_alloc(m, 16, st, &cursor)) return rc;
+  CUDA_TRY(cudaMemsetAsync(cursor, 0, 16, st));
+  ik_kernel<<<grid, warps_per_cta * 32, smem, st>>>(a, static_cast<unsigned long long*>(cursor));
   g_launches.fetch_add(1, std::memory_order_relaxed);
+  CUDA_TRY(cudaFreeAsync(cursor, st));
   CUDA_TRY(cudaGetLastError());
   return RAMP_OK;
 }
