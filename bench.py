@@ -602,10 +602,10 @@ def measure_next_rows(dev, with_cpu: bool) -> dict:
     dt = timed(lambda: gpu.check(q, pair_mask=True), 5)
     out["f1_all_pairs_mask"] = {"configs": n1, "pairs": len(rm.collision_model.collisionPairs), "configs_per_s": n1 / dt,
                                 "api": "GpuModel.check(pair_mask=True): every pair of every configuration, one bit each"}
-    n3 = 1 << 16
+    n3 = 1 << 18
     dt = timed(lambda: gpu.clearance(q[:n3]), 2)
     out["f3_clearance"] = {"configs": n3, "configs_per_s": n3 / dt,
-                           "api": "GpuModel.clearance: signed distance of every pair to convergence (GJK / EPA), minimum per configuration"}
+                           "api": "GpuModel.clearance (the d_min_dist output of ramp_check_batch): smallest signed distance over the pairs, GJK / EPA to convergence for the pairs whose capsule bounds can still lower it"}
     rs = RobotState.from_named_state(rm, "arm", "home")
     params = rm.ik_params("arm")
     n4 = 1 << 16

@@ -106,19 +106,78 @@ __global__ void __launch_bounds__(256, 1) distance_kernel(const __grid_constant_
     __syncwarp();
     const int64_t row = row0 + w.lane;
     float dmin = 3.0e38f;
-    for (int k = 0; k < a.n_sel; ++k) {
-      const DPair pr = t.pairs[a.sel ? a.sel[k] : k];  // sel holds processing indices
-      const int col = a.sel ? k : pr.orig;
-      if (a.min_out && pr.cls == kClsInactive) continue;
-      const DGeom* ga = &t.geoms[pr.a];
-      const DGeom* gb = &t.geoms[pr.b];
-      const Xf rel = xf_inv_mul(geom_xf(w, ga->gslot, w.lane), geom_xf(w, gb->gslot, w.lane));
-      const int cls = pair_class_of(ga->type, gb->type);  // also for inactive pairs
-      float d = cls < kClsBoxBox ? closed_form_dist(cls, ga, gb, rel)
-                                 : gjk_signed_distance(load_shape(ga, t.verts), load_shape(gb, t.verts), rel,
-                                                       swept_radius(ga) + swept_radius(gb));
-      if (a.min_out) dmin = fminf(dmin, d);
-      else if (row < a.n) a.out[row * a.n_sel + col] = d;
+    if (a.min_out) {
+      // Smallest distance only: a pair whose OUTER capsules (or bounding spheres) are farther apart
+      // than the smallest distance known so far cannot lower it and skips GJK / EPA.  A first pass
+      // over the pairs gives that bound a good start: closed-form pairs exactly, the others by
+      // their INNER capsules, which lie inside the shapes and are therefore at least as far apart.
+      // The pair that set the bound always passes its own test (inner >= exact >= outer), so the
+      // minimum of the distances that are evaluated is the minimum over all pairs.
+      float bound = 3.0e38f;
+      auto pair_at = [&](int k) { return t.pairs[a.sel ? a.sel[k] : k]; };
+      auto rel_of = [&](const DGeom* ga, const DGeom* gb) { return xf_inv_mul(geom_xf(w, ga->gslot, w.lane), geom_xf(w, gb->gslot, w.lane)); };
+      // distance of the two capsules (half length s, radius r) around the local z axes of a pair
+      auto capsules = [&](const Xf& rel, float sa, float sb, float rsum) {
+        const V3 zb = mk(rel.m[2], rel.m[6], rel.m[10]), tb = trans(rel);
+        return seg_seg_dist(mk(0.f, 0.f, -sa), mk(0.f, 0.f, 2.f * sa), tb - zb * sb, zb * (2.f * sb)) - rsum;
+      };
+      auto lower_of = [&](const DPair& pr, const DGeom* ga, const DGeom* gb, const Xf& rel) {
+        const V3 tb = trans(rel);
+        float lower = sqrtf(dot(tb, tb)) - ga->bound_r - gb->bound_r;
+        if (pr.cls == kClsGjk) lower = fmaxf(lower, capsules(rel, ga->s_out, gb->s_out, ga->r_out + gb->r_out));
+        return lower - pr.slack;  // (slack: the pair's share of non-rigid placements)
+      };
+      for (int k = 0; k < a.n_sel; ++k) {
+        const DPair pr = pair_at(k);
+        if (pr.cls == kClsInactive) continue;
+        const DGeom* ga = &t.geoms[pr.a];
+        const DGeom* gb = &t.geoms[pr.b];
+        const Xf rel = rel_of(ga, gb);
+        if (pr.cls < kClsBoxBox) dmin = fminf(dmin, closed_form_dist(pr.cls, ga, gb, rel));
+        else if (pr.cls == kClsGjk) bound = fminf(bound, capsules(rel, ga->s_in, gb->s_in, ga->r_in + gb->r_in) + pr.slack);
+      }
+      bound = fminf(bound, dmin) + 2e-5f;
+      // The survivors, 32 pairs at a time: every lane first marks the pairs of ITS configuration
+      // that pass the bound, then the lanes work through their marks together -- each on a pair of
+      // its own, so one trip of the loop is one GJK per lane, not one pair index for the warp.
+      for (int base = 0; base < a.n_sel; base += 32) {
+        unsigned todo = 0u;
+        const int end = min(a.n_sel, base + 32);
+        for (int k = base; k < end; ++k) {
+          const DPair pr = pair_at(k);
+          if (pr.cls < kClsBoxBox) continue;  // inactive, or a closed form (done above)
+          const DGeom* ga = &t.geoms[pr.a];
+          const DGeom* gb = &t.geoms[pr.b];
+          if (lower_of(pr, ga, gb, rel_of(ga, gb)) <= bound) todo |= 1u << (k - base);
+        }
+        while (__any_sync(0xffffffffu, todo != 0u)) {
+          if (todo != 0u) {
+            const DPair pr = pair_at(base + __ffs(todo) - 1);
+            todo &= todo - 1u;
+            const DGeom* ga = &t.geoms[pr.a];
+            const DGeom* gb = &t.geoms[pr.b];
+            const Xf rel = rel_of(ga, gb);
+            if (lower_of(pr, ga, gb, rel) <= bound) {  // (the bound may have dropped since the pair was marked)
+              const float d = gjk_signed_distance(load_shape(ga, t.verts), load_shape(gb, t.verts), rel, swept_radius(ga) + swept_radius(gb));
+              dmin = fminf(dmin, d);
+              bound = fminf(bound, d + 2e-5f);
+            }
+          }
+        }
+      }
+    } else {
+      for (int k = 0; k < a.n_sel; ++k) {
+        const DPair pr = t.pairs[a.sel ? a.sel[k] : k];  // sel holds processing indices
+        const int col = a.sel ? k : pr.orig;
+        const DGeom* ga = &t.geoms[pr.a];
+        const DGeom* gb = &t.geoms[pr.b];
+        const Xf rel = xf_inv_mul(geom_xf(w, ga->gslot, w.lane), geom_xf(w, gb->gslot, w.lane));
+        const int cls = pair_class_of(ga->type, gb->type);  // also for inactive pairs
+        const float d = cls < kClsBoxBox ? closed_form_dist(cls, ga, gb, rel)
+                                         : gjk_signed_distance(load_shape(ga, t.verts), load_shape(gb, t.verts), rel,
+                                                               swept_radius(ga) + swept_radius(gb));
+        if (row < a.n) a.out[row * a.n_sel + col] = d;
+      }
     }
     if (a.min_out && row < a.n) a.min_out[row] = dmin;
     __syncwarp();

@@ -253,10 +253,12 @@ class GpuModel:
     def clearance(self, q, *, actuated: bool = False) -> torch.Tensor:
         """Smallest signed distance over the enabled pairs, float32[N] (+inf without pairs): the
         quantity the reference's PathClearanceObjective integrates (src/ramp/motion_planner.py:165-206)."""
-        d = self.distance(q, actuated=actuated)
-        if d.shape[1] == 0:
-            return torch.full((d.shape[0],), float("inf"), dtype=torch.float32, device=self.device)
-        return d.min(dim=1).values
+        q = self._q(q)
+        if self.info()["n_pairs"] == 0:
+            return torch.full((q.shape[0],), float("inf"), dtype=torch.float32, device=self.device)
+        # the d_min_dist output of ramp_check_batch: pairs whose capsule bounds cannot lower the
+        # minimum skip GJK / EPA (a tenth of the work of the full distance matrix on an arm)
+        return self.check(q, actuated=actuated, min_dist=True)["min_dist"]
 
     def check_raw(self, q: torch.Tensor, hit: torch.Tensor, flags: int = 0) -> None:
         """Zero-overhead variant for benchmarks: caller-owned contiguous tensors, no allocations."""

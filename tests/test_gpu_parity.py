@@ -535,6 +535,21 @@ def test_min_distance_output(built):
     assert np.array_equal(goth["hit"], got["hit"].cpu().numpy())
 
 
+@pytest.mark.parametrize("name,scene", [("panda/configs", "capsule"), ("ur5e/configs", "obstacles"),
+                                        ("panda_boxy/configs", "capsule"), ("unitree_h1/configs", None), ("rrr_mj/configs", "obstacles")])
+def test_pruned_min_distance_equals_the_minimum_of_all_distances(built, name, scene):
+    """The d_min_dist output skips GJK / EPA for pairs whose capsule bounds cannot lower the minimum:
+    it must be exactly the minimum of the full distance matrix (same arithmetic per pair)."""
+    from ramp_b200 import workloads
+
+    rm, _ = _setup(name, scene)
+    q = torch.from_numpy(workloads.sample_q(rm.model, 3001, seed=9).astype(np.float32)).cuda()
+    full = rm.gpu.distance(q).min(dim=1).values
+    got = rm.gpu.check(q, min_dist=True)["min_dist"]
+    assert torch.equal(full, got), float((full - got).abs().max())
+    assert torch.isfinite(got).all()
+
+
 @pytest.mark.parametrize("n", [8193 + 17, 20001, 300001])
 def test_ragged_batches_never_write_past_the_outputs(built, n):
     """A batch whose size is not a multiple of 32 leaves lanes of the last warp tile without a
