@@ -166,9 +166,9 @@ class MotionPlanner:
     def _extend(self, tree: list, parents: list, target: np.ndarray, max_step: float):
         """One RRT extension toward ``target``; returns (status, new index): 0 trapped,
         1 advanced, 2 reached."""
-        d = [spaces.distance(self.space, n, target) for n in tree]
+        d = spaces.distance_many(self.space, tree, target)
         i = int(np.argmin(d))
-        near, dist = tree[i], d[i]
+        near, dist = tree[i], float(d[i])
         reached = dist <= max_step
         new = target if reached else spaces.interpolate(self.space, near, target, max_step / dist)
         if not self.validator.checkMotion(near, new):

@@ -176,6 +176,19 @@ def distance(space: D.SpaceDesc, a, b) -> float:
     return total
 
 
+def distance_many(space: D.SpaceDesc, many, b) -> np.ndarray:
+    """``distance(space, many[i], b)`` for every row of ``many`` (a planner's nearest-neighbour query).
+    Spaces made of one-dimensional real subspaces only (revolute / prismatic joints: the sum of
+    the joint differences) are done in one numpy expression, the others row by row."""
+    many = np.asarray(many, dtype=np.float64)
+    b = np.asarray(b, dtype=np.float64)
+    subs = [_parts(s) for s in space.subspaces]
+    if all(nreal == 1 and rot is None for nreal, rot, _ in subs):
+        cols = [s["col"] for s in space.subspaces]
+        return np.abs(many[:, cols] - b[cols]).sum(axis=1)
+    return np.array([distance(space, a, b) for a in many])
+
+
 def interpolate(space: D.SpaceDesc, a, b, t: float) -> np.ndarray:
     a, b = np.asarray(a, dtype=np.float64), np.asarray(b, dtype=np.float64)
     out = np.array(a, dtype=np.float64)

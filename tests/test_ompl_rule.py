@@ -143,3 +143,18 @@ def test_batched_bounds_equal_the_per_state_rule():
         want = np.array([spaces.satisfies_bounds(space, row) for row in a])
         assert np.array_equal(spaces.satisfies_bounds_batch(space, a), want)
         assert want.any() and not want.all()
+
+
+def test_distance_many_matches_distance():
+    """The planner's vectorised nearest-neighbour distances equal CompoundStateSpace::distance row by
+    row: a space of 1-D real subspaces (fast path) and one with SO2 / SE3 parts (row-by-row path)."""
+    from ramp_b200 import load_robot_model, spaces
+
+    rng = np.random.default_rng(5)
+    for cfg in ("fr3/configs", "rrr/planar_configs", "rrr/floating_configs"):
+        rm = load_robot_model("zoo::" + cfg)
+        sp = spaces.make_space(rm, "arm")
+        pts = spaces.sample_uniform(sp, 40, rng)
+        got = spaces.distance_many(sp, pts[1:], pts[0])
+        ref = np.array([spaces.distance(sp, p, pts[0]) for p in pts[1:]])
+        assert np.allclose(got, ref, rtol=0, atol=1e-12)
