@@ -402,15 +402,19 @@ done:
 #define EPA_MAX_F 400
 typedef struct { int a, b, c; v3 n; double d; int alive; } epa_face;
 
-static int epa_make_face(const v3 *vt, int a, int b, int c, epa_face *f) {
-  /* winding (a,b,c) is counter-clockwise seen from outside; callers keep it
-   * consistent, so the normal is never re-oriented against the origin (the
-   * origin may lie ON a face of the start tetrahedron). */
+/* Face (a, b, c) of the polytope, its normal turned AWAY from `inside` (a point strictly inside
+ * the polytope: the centroid of the start tetrahedron).  Orienting every face by that test, instead
+ * of by the winding of the horizon edge it was built on, keeps normals outward when a new vertex
+ * lies in the plane of a face next to the horizon -- flat faces of box / cylinder Minkowski sums
+ * yield many coplanar support points, and a winding-derived normal then came out inverted (d < 0). */
+static int epa_make_face(const v3 *vt, int a, int b, int c, v3 inside, epa_face *f) {
   v3 n = vcross(vsub(vt[b], vt[a]), vsub(vt[c], vt[a]));
   const double l = vnorm(n);
   f->a = a; f->b = b; f->c = c; f->alive = 0;
-  if (l < 1e-300) return 0;
+  const double scale = vnorm(vsub(vt[b], vt[a])) * vnorm(vsub(vt[c], vt[a]));
+  if (l <= 1e-12 * scale || l < 1e-300) return 0; /* a sliver: no plane to speak of */
   n = vscale(n, 1.0 / l);
+  if (vdot(n, vsub(vt[a], inside)) < 0) { n = vneg(n); f->b = c; f->c = b; }
   f->n = n; f->d = vdot(n, vt[a]); f->alive = 1;
   return 1;
 }
@@ -460,14 +464,10 @@ static double epa_run(const mink_t *mk, simplex_t s, int *iters) {
   int nv = 0, nf = 0;
   if (!epa_enclose(mk, &s)) return 0.0;
   for (int i = 0; i < 4; ++i) vt[nv++] = s.p[i];
-  static const int T[4][4] = {{0, 1, 2, 3}, {0, 1, 3, 2}, {0, 2, 3, 1}, {1, 2, 3, 0}};
-  for (int i = 0; i < 4; ++i) {
-    int a = T[i][0], b = T[i][1], c = T[i][2];
-    const v3 n = vcross(vsub(vt[b], vt[a]), vsub(vt[c], vt[a]));
-    /* outward = away from the opposite vertex */
-    if (vdot(n, vsub(vt[T[i][3]], vt[a])) > 0) { const int t = b; b = c; c = t; }
-    if (!epa_make_face(vt, a, b, c, &fc[nf++])) return 0.0;
-  }
+  const v3 inside = vscale(vadd(vadd(vt[0], vt[1]), vadd(vt[2], vt[3])), 0.25);
+  static const int T[4][3] = {{0, 1, 2}, {0, 1, 3}, {0, 2, 3}, {1, 2, 3}};
+  for (int i = 0; i < 4; ++i)
+    if (!epa_make_face(vt, T[i][0], T[i][1], T[i][2], inside, &fc[nf++])) return 0.0;
   double best = 0.0;
   for (int it = 0; it < g_params.epa_max_iter; ++it) {
     int bi = -1;
@@ -480,19 +480,27 @@ static double epa_run(const mink_t *mk, simplex_t s, int *iters) {
     const v3 w = mink_support(mk, fc[bi].n);
     const double gap = vdot(fc[bi].n, w) - bd;
     if (gap <= g_params.epa_tol * (1.0 + bd) || nv >= EPA_MAX_V) break;
-    /* remove faces visible from w, collect horizon edges */
+    int dup = 0; /* a support point the polytope already has: nothing left to expand */
+    for (int k = 0; k < nv; ++k) {
+      const v3 e = vsub(vt[k], w);
+      if (vdot(e, e) <= 1e-24) dup = 1;
+    }
+    if (dup) break;
+    /* remove the faces that see w; the horizon is the set of edges with exactly ONE removed
+     * neighbour -- counted without regard to direction, so it does not depend on windings */
     int eh[EPA_MAX_F][2], ne = 0;
     for (int i = 0; i < nf; ++i) {
       if (!fc[i].alive) continue;
-      if (vdot(fc[i].n, w) - fc[i].d > 1e-14) {
+      if (vdot(fc[i].n, w) - fc[i].d > 1e-13) {
         fc[i].alive = 0;
         const int ed[3][2] = {{fc[i].a, fc[i].b}, {fc[i].b, fc[i].c}, {fc[i].c, fc[i].a}};
         for (int k = 0; k < 3; ++k) {
+          const int lo = ed[k][0] < ed[k][1] ? ed[k][0] : ed[k][1], hi = ed[k][0] < ed[k][1] ? ed[k][1] : ed[k][0];
           int found = -1;
           for (int e = 0; e < ne; ++e)
-            if (eh[e][0] == ed[k][1] && eh[e][1] == ed[k][0]) { found = e; break; }
+            if (eh[e][0] == lo && eh[e][1] == hi) { found = e; break; }
           if (found >= 0) { eh[found][0] = eh[ne - 1][0]; eh[found][1] = eh[ne - 1][1]; --ne; }
-          else if (ne < EPA_MAX_F) { eh[ne][0] = ed[k][0]; eh[ne][1] = ed[k][1]; ++ne; }
+          else if (ne < EPA_MAX_F) { eh[ne][0] = lo; eh[ne][1] = hi; ++ne; }
         }
       }
     }
@@ -504,7 +512,7 @@ static double epa_run(const mink_t *mk, simplex_t s, int *iters) {
       int slot = -1;
       for (int i = 0; i < nf; ++i) if (!fc[i].alive) { slot = i; break; }
       if (slot < 0) { if (nf >= EPA_MAX_F) { ok = 0; break; } slot = nf++; }
-      if (!epa_make_face(vt, eh[e][0], eh[e][1], wi, &fc[slot])) fc[slot].alive = 0;
+      if (!epa_make_face(vt, eh[e][0], eh[e][1], wi, inside, &fc[slot])) fc[slot].alive = 0;
     }
     if (!ok) break;
   }

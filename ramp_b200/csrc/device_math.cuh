@@ -452,7 +452,8 @@ __device__ __forceinline__ int gjk_advance(GjkLane& g, V3 sa, V3 sb, bool exact,
     g.lower = fmaxf(g.lower, om);
     if (!exact && om > g.rsum) { dist = om - g.rsum; return GJK_MISS; }  // separating plane
   }
-  bool done = g.s.n > 0 && g.vv - vw <= EPS_REL * g.vv;  // converged: |v| is the core distance
+  const bool converged = g.s.n > 0 && g.vv - vw <= EPS_REL * g.vv;  // |v| is the core distance
+  bool done = converged;
   if (!done) {
     // no dynamic register indexing (it would spill the simplex to local memory)
     if (g.s.n == 0) g.s.p[0] = w; else if (g.s.n == 1) g.s.p[1] = w; else if (g.s.n == 2) g.s.p[2] = w; else g.s.p[3] = w;
@@ -474,6 +475,13 @@ __device__ __forceinline__ int gjk_advance(GjkLane& g, V3 sa, V3 sb, bool exact,
   dist = d - g.rsum;
   // a stalled iteration far from convergence: trust the proven lower bound
   if (d <= g.rsum && g.lower > g.rsum) { dist = g.lower - g.rsum; return GJK_MISS; }
+  // The boolean verdict of an iteration that ended WITHOUT a proof (no separating plane beyond the
+  // swept radii, upper and lower bound not met: a stall at FP32 resolution, or the iteration cap):
+  // |v| is a point of A (-) B, so the true distance is at most |v| - rsum.  If that is inside the
+  // 1e-4 m margin band, "colliding" is right or in the band, whereas "free" is wrong whenever the
+  // shapes overlap -- FP32 GJK stalls a few 1e-5 m short of enclosing the origin of shallow
+  // overlaps (1 in 5e6 configurations, depths 1.1 - 2.6e-4 m: profiles/r02_parity_sweep.jsonl).
+  if (!exact && !converged && g.lower <= g.rsum && d <= g.rsum + 1e-4f) return GJK_HIT;
   return d <= g.rsum ? GJK_HIT : GJK_MISS;
 }
 

@@ -153,7 +153,17 @@ __global__ void __launch_bounds__(256, 2) gjk_queue_kernel(const __grid_constant
     }
     if (active) {
       float dist;
+#ifdef RAMP_TRACE_PAIR
+      const float t_vv = g.vv; const int t_n = g.s.n;
+      const V3 t_w = sa - apply(g.rel, sb);
+      const float t_vw = dot(g.v, t_w);
+#endif
       const int st = gjk_advance(g, sa, sb, false, dist);
+#ifdef RAMP_TRACE_PAIR
+      if (p == RAMP_TRACE_PAIR && row == 0)
+        printf("trace queue gjk: it %d n %d |v| %.9g vw/|v| %.9g -> status %d n %d |v| %.9g dist %.9g\n", g.it, t_n, sqrtf(t_vv), t_vw * rsqrtf(t_vv), st,
+               g.s.n, sqrtf(g.vv), dist);
+#endif
 #ifdef RAMP_STATS
       atomicAdd(&g_stats[1], 1ull);
       atomicAdd(&g_stats[5], static_cast<unsigned long long>(__popc(__activemask())));

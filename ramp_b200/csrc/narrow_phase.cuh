@@ -61,7 +61,8 @@ __device__ __forceinline__ float swept_radius(const DGeom* g) {
   return (g->type == SH_SPHERE || g->type == SH_CAPSULE) ? g->p0 : 0.f;
 }
 
-__device__ __forceinline__ int pair_class_of(int ta, int tb) {  // ta <= tb (pairs are stored ordered)
+__device__ __forceinline__ int pair_class_of(int ta, int tb) {  // (sphere classes are stored sphere first)
+  if (ta != SH_SPHERE && ta > tb) { const int t = ta; ta = tb; tb = t; }
   if (ta == SH_SPHERE && tb <= SH_CYLINDER) return kClsSphereSphere + tb;
   if (ta == SH_CAPSULE && tb == SH_CAPSULE) return kClsCapsuleCapsule;
   if (ta == SH_BOX && tb == SH_BOX) return kClsBoxBox;
@@ -209,6 +210,10 @@ __device__ __forceinline__ void narrow_phase(const Warp& w, bool stop_at_first, 
           const V3 zb = mk(f(pb - 3 * sb), f(pb - 2 * sb), f(pb - sb)), tb = mk(f(pb), f(pb + sb), f(pb + 2 * sb));
           const V3 wv = seg_seg_witness(ta - za * r1.x, za * (2.f * r1.x), tb - zb * r1.y, zb * (2.f * r1.y));
           keep = dot(wv, wv) <= r1.z * r1.z;
+#ifdef RAMP_TRACE_PAIR
+          if ((r0.w & 0xffff) == RAMP_TRACE_PAIR && row_base + (item & 31) == 0)
+            printf("trace stage1.5: |w| %.9g rsum_out %.9g keep %d\n", sqrtf(dot(wv, wv)), r1.z, int(keep));
+#endif
         }
         __syncwarp();  // every lane has read its item before the in-place compaction writes
         const unsigned b = __ballot_sync(FULL, keep);
@@ -261,11 +266,18 @@ __device__ __forceinline__ void narrow_phase(const Warp& w, bool stop_at_first, 
             if (rin > 0.f && vv0 < rin * rin) { record_hit(w, c, orig, want_mask); decided = true; }
             const float thr = fmaf(kHardShell, ca.y + cb.y - (ca.w + cb.w), ca.w + cb.w);  // r_out, r_in sums
             hard = vv0 < thr * thr;
+#ifdef RAMP_TRACE_PAIR
+            if (orig == RAMP_TRACE_PAIR && row_base + c == 0)
+              printf("trace stage2: |v0| %.9g rin %.9g decided %d hard %d slack %.3g\n", sqrtf(vv0), rin, int(decided), int(hard), slack);
+#endif
           }
           if (!decided) {
             const bool ov = obb_overlap(ha, hb, rel, bb ? 0.f : slack);
             if (ov && bb) record_hit(w, c, orig, want_mask);
             to_gjk = ov && !bb;
+#ifdef RAMP_TRACE_PAIR
+            if (orig == RAMP_TRACE_PAIR && row_base + c == 0) printf("trace stage2: obb overlap %d to_gjk %d\n", int(ov), int(to_gjk));
+#endif
           }
         } else if (closed_form_hit(cls, ga, gb, rel)) {
           record_hit(w, c, orig, want_mask);

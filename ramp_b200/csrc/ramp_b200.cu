@@ -472,6 +472,11 @@ static int build_image(RampModel* m) {
     }
     d.hx = static_cast<float>(hx); d.hy = static_cast<float>(hy); d.hz = static_cast<float>(hz);
     d.bound_r = static_cast<float>(br);
+    if (src.type == RAMP_SHAPE_SPHERE) {  // a sphere has no orientation: its frame is the rigid one of every pair it is in
+      const double t3[3] = {pl[3], pl[7], pl[11]};
+      for (int k = 0; k < 12; ++k) pl[k] = (k % 5 == 0) ? 1.0 : 0.0;
+      pl[3] = t3[0]; pl[7] = t3[1]; pl[11] = t3[2];
+    }
     for (int k = 0; k < 12; ++k) { d.pl[k] = static_cast<float>(pl[k]); d.opl[k] = static_cast<float>(src.placement[k]); }
     for (int i = 0; i < 3; ++i)
       for (int j = 0; j < 3; ++j) {
@@ -521,7 +526,19 @@ static int build_image(RampModel* m) {
     m->pair_order[p] = k;
     int a, b;
     geoms_of(p, a, b);
-    if (dg[a].type > dg[b].type) std::swap(a, b);
+    // Which geometry is "a", the one whose frame the pair is solved in (rel = a^-1 b, the inverse
+    // taken as the transpose): it only matters when a placement is not a rigid motion -- the
+    // reference's own scene capsule is built from an un-normalised quaternion, |R^T R - I| = 6e-4
+    // -- and then it has to be the operand the reference's arithmetic transposes, or distances come
+    // out up to 2e-4 m different.  Sphere classes: the sphere (its rotation is dropped, below), as
+    // coal's specialisations do.  Capsule / capsule is solved in world coordinates
+    // there: here in the frame of the (more) rigid one, which is the same thing.  Box / box and
+    // the GJK class: the pair's first geometry (coal's MinkowskiDiff::set).
+    {
+      const int cls_ab = pair_class(dg[a].type, dg[b].type);
+      if (cls_ab < kClsCapsuleCapsule) { if (dg[a].type > dg[b].type) std::swap(a, b); }
+      else if (cls_ab == kClsCapsuleCapsule) { if (nonrigid[a] > nonrigid[b]) std::swap(a, b); }
+    }
     DPair& d = dp[k];
     std::memset(&d, 0, sizeof d);
     d.a = static_cast<int16_t>(a); d.b = static_cast<int16_t>(b);

@@ -175,3 +175,28 @@ def test_capsule_is_swept_segment():
         d_thin, d_fat = dist(thin, ma, box, mb), dist(fat, ma, box, mb)
         if d_thin > 0.0:
             assert d_fat == pytest.approx(d_thin - 0.1, abs=1e-6)
+
+
+def test_deep_cylinder_box_penetration_with_coplanar_supports():
+    """Two poses found by the 5M-configuration GPU sweep (profiles/r02_parity_sweep.jsonl): the flat
+    cap of the cylinder against a flat box face gives EPA many support points in ONE plane.  The
+    expected depths are the minimum over 2e6 directions (then Nelder-Mead) of the support function of
+    the Minkowski difference; before the fix to epa_run's visibility test the oracle returned +0.107
+    / +0.203 (and a different depth with the shapes swapped)."""
+    cases = [([0.46854342343891586, -0.768924520186733, -0.4349967156724901, -0.7824039276186465, -0.4712425369778934, 0.1989564691339747,
+               -0.8592710834130415, 0.935761938783602, 0.7472600161475853, 0.607594770963992, -0.26913019647622605, 0.9855978028821824],
+              [-0.877776274907609, -0.3117564933656693, -0.36375362553763296, -0.7852042357784582, -0.337422411468121, -0.13667946244025087,
+               0.9313779258944908, 0.8786426800345262, -0.3400807661666772, 0.9402800718321422, 0.014780361627331803, 0.976366464164009],
+              -0.10728902115057082),
+             ([0.9099034187656029, 0.17977561070692172, 0.373840202545925, 0.6463237340080641, 0.18709062628437767, 0.6264925373330422,
+               -0.7566400682892823, 0.22672571581618772, -0.37023352738662696, 0.7584113825485769, 0.5364133699527809, -0.1124738068193623],
+              [-0.9202227285901365, -0.2548877022044138, -0.29702253749006124, 0.6317938122956098, -0.386509836875086, 0.47226838433511265,
+               0.7921948711488737, 0.24208032294738835, -0.06164637654202596, 0.8437978584167546, -0.5331087054579247, -0.12545676683813073],
+              -0.1435206731861588)]
+    cyl, box = Cylinder(0.1, 0.05), Box(0.1, 0.1, 0.3)
+    for m1, m2, depth in cases:
+        a, b = np.asarray(m1).reshape(3, 4), np.asarray(m2).reshape(3, 4)
+        A, B = SE3(a[:, :3], a[:, 3]), SE3(b[:, :3], b[:, 3])
+        d12, _ = oracle.shape_distance(cyl, A, box, B)
+        d21, _ = oracle.shape_distance(box, B, cyl, A)
+        assert abs(d12 - depth) < 2e-7 and abs(d21 - depth) < 2e-7, (d12, d21, depth)
