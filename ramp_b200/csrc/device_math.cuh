@@ -434,7 +434,7 @@ __device__ __forceinline__ void gjk_init(GjkLane& g, const Xf& rel, float rsum, 
   g.it = 0;
 }
 
-enum { GJK_CONTINUE = 0, GJK_HIT = 1, GJK_MISS = 2 };
+enum { GJK_CONTINUE = 0, GJK_HIT = 1, GJK_MISS = 2, GJK_STALL = 3 };  // STALL: exact mode only (see gjk_advance)
 
 // The simplex half of one GJK iteration: sa, sb are the support points of A along -v and of B
 // along +v (each in its own frame).  `exact`: run to convergence (distance output) instead of
@@ -453,7 +453,19 @@ __device__ __forceinline__ int gjk_advance(GjkLane& g, V3 sa, V3 sb, bool exact,
     if (!exact && om > g.rsum) { dist = om - g.rsum; return GJK_MISS; }  // separating plane
   }
   const bool converged = g.s.n > 0 && g.vv - vw <= EPS_REL * g.vv;  // |v| is the core distance
-  bool done = converged;
+  bool done = converged, dup = false;
+  // A support point that is already a vertex of the simplex (polytope corners come back bit for
+  // bit) means v cannot be improved; added again it would make a degenerate triangle whose
+  // closest-point solve is 0 / 0 (seen as "origin enclosed": box / box distances 2 - 14 % short
+  // when the relative gap at the last step was between 1e-5 and 2e-5).
+  if (exact) {  // (the boolean verdicts are validated as they are: 37M configurations, profiles/r02_parity_sweep.jsonl)
+    const V3 p0 = g.s.p[0], p1 = g.s.p[1], p2 = g.s.p[2];
+    const bool d0 = g.s.n > 0 && w.x == p0.x && w.y == p0.y && w.z == p0.z;
+    const bool d1 = g.s.n > 1 && w.x == p1.x && w.y == p1.y && w.z == p1.z;
+    const bool d2 = g.s.n > 2 && w.x == p2.x && w.y == p2.y && w.z == p2.z;
+    dup = d0 || d1 || d2;
+    done = done || dup;
+  }
   if (!done) {
     // no dynamic register indexing (it would spill the simplex to local memory)
     if (g.s.n == 0) g.s.p[0] = w; else if (g.s.n == 1) g.s.p[1] = w; else if (g.s.n == 2) g.s.p[2] = w; else g.s.p[3] = w;
@@ -479,9 +491,15 @@ __device__ __forceinline__ int gjk_advance(GjkLane& g, V3 sa, V3 sb, bool exact,
   // swept radii, upper and lower bound not met: a stall at FP32 resolution, or the iteration cap):
   // |v| is a point of A (-) B, so the true distance is at most |v| - rsum.  If that is inside the
   // 1e-4 m margin band, "colliding" is right or in the band, whereas "free" is wrong whenever the
-  // shapes overlap -- FP32 GJK stalls a few 1e-5 m short of enclosing the origin of shallow
+  // shapes overlap -- FP32 GJK stalls about 1e-4 m short of enclosing the origin of shallow
   // overlaps (1 in 5e6 configurations, depths 1.1 - 2.6e-4 m: profiles/r02_parity_sweep.jsonl).
+  // Not wider than the band: separated pairs 1 - 2e-4 m apart end the same way by the hundred per
+  // 5e6 configurations, and for them `d <= rsum` below is the right answer.
   if (!exact && !converged && g.lower <= g.rsum && d <= g.rsum + 1e-4f) return GJK_HIT;
+  // exact mode: the same unproven ending within a millimetre of contact is handed back as such --
+  // gjk_signed_distance then lets EPA look at the simplex (shallow overlaps came back as small
+  // positive distances: 7 sign changes in 4.5e7 pair distances of the UR5 stand-in)
+  if (exact && !converged && g.lower <= g.rsum && d <= 1e-3f) return GJK_STALL;  // (d: the CORE distance; a repeated vertex is no proof here)
   return d <= g.rsum ? GJK_HIT : GJK_MISS;
 }
 
@@ -517,12 +535,18 @@ __device__ __forceinline__ V3 mink_support(const GjkShape& A, const GjkShape& B,
   return sa - apply(rel, sb);
 }
 
-__device__ __noinline__ bool epa_face(const V3* vt, int a, int b, int c, EpaFace& f) {
-  V3 n = cross(vt[b] - vt[a], vt[c] - vt[a]);
+// Face (a, b, c), its normal turned AWAY from `inside` (a point strictly inside the polytope: the
+// centroid of the start tetrahedron).  Orienting by that test rather than by the winding of the
+// horizon edge keeps normals outward when the new vertex lies in the plane of a face next to the
+// horizon (flat faces of box / cylinder Minkowski sums give many coplanar support points).
+__device__ __noinline__ bool epa_face(const V3* vt, int a, int b, int c, V3 inside, EpaFace& f) {
+  const V3 e1 = vt[b] - vt[a], e2 = vt[c] - vt[a];
+  V3 n = cross(e1, e2);
   const float l2 = dot(n, n);
   f.a = a; f.b = b; f.c = c; f.alive = 0;
-  if (l2 < 1e-30f) return false;
+  if (l2 < 1e-30f || l2 <= 1e-10f * dot(e1, e1) * dot(e2, e2)) return false;  // a sliver: no plane to speak of
   n = n * rsqrtf(l2);
+  if (dot(n, vt[a] - inside) < 0.f) { n = -n; f.b = c; f.c = b; }
   f.n = n; f.d = dot(n, vt[a]); f.alive = 1;
   return true;
 }
@@ -569,14 +593,16 @@ __device__ __noinline__ float epa_depth(const GjkShape& A, const GjkShape& B, co
   V3 vt[kEpaMaxV];
   EpaFace fc[kEpaMaxF];
   int nv = 0, nf = 0;
+#ifdef RAMP_TRACE_DIST
+  const bool tr = (threadIdx.x & 31) == 0 && blockIdx.x == 0;
+  if (tr) printf("trace epa: start n %d\n", s.n);
+#endif
   if (!epa_enclose(A, B, rel, s)) return 0.f;
   for (int i = 0; i < 4; ++i) vt[nv++] = s.p[i];
-  for (int i = 0; i < 4; ++i) {  // faces (0,1,2|3) (0,1,3|2) (0,2,3|1) (1,2,3|0), wound outwards
-    int a = i == 3 ? 1 : 0, b = i < 2 ? 1 : 2, c = i == 0 ? 2 : 3;
-    const int opp = 6 - a - b - c;
-    const V3 n = cross(vt[b] - vt[a], vt[c] - vt[a]);
-    if (dot(n, vt[opp] - vt[a]) > 0.f) { const int t = b; b = c; c = t; }
-    if (!epa_face(vt, a, b, c, fc[nf++])) return 0.f;
+  const V3 inside = (vt[0] + vt[1] + vt[2] + vt[3]) * 0.25f;
+  for (int i = 0; i < 4; ++i) {  // faces (0,1,2) (0,1,3) (0,2,3) (1,2,3)
+    const int a = i == 3 ? 1 : 0, b = i < 2 ? 1 : 2, c = i == 0 ? 2 : 3;
+    if (!epa_face(vt, a, b, c, inside, fc[nf++])) return 0.f;
   }
   if (restart) {
     int worst = 0;
@@ -593,9 +619,16 @@ __device__ __noinline__ float epa_depth(const GjkShape& A, const GjkShape& B, co
     if (bi < 0) break;
     best = bd;
     const V3 w = mink_support(A, B, rel, fc[bi].n);
+#ifdef RAMP_TRACE_DIST
+    if (tr) printf("trace epa: it %d nf %d nv %d bd %.9g gap %.9g n %.4g %.4g %.4g\n", it, nf, nv, bd, dot(fc[bi].n, w) - bd, fc[bi].n.x, fc[bi].n.y, fc[bi].n.z);
+#endif
     // FP32: face normals and plane offsets carry ~1e-6 of noise, a tighter test never fires
     if (dot(fc[bi].n, w) - bd <= kEpaTol * (1.f + bd) || nv >= kEpaMaxV) break;
-    // drop the faces that see w, keep the horizon
+    bool dup = false;  // a support point the polytope already has: nothing left to expand
+    for (int k = 0; k < nv; ++k) dup = dup || (vt[k].x == w.x && vt[k].y == w.y && vt[k].z == w.z);
+    if (dup) break;
+    // drop the faces that see w; the horizon is the set of edges with exactly ONE dropped
+    // neighbour, matched without regard to direction (so it does not depend on windings)
     unsigned char eh[96][2];
     int ne = 0;
     for (int i = 0; i < nf; ++i) {
@@ -603,11 +636,12 @@ __device__ __noinline__ float epa_depth(const GjkShape& A, const GjkShape& B, co
       fc[i].alive = 0;
       const unsigned char ed[3][2] = {{fc[i].a, fc[i].b}, {fc[i].b, fc[i].c}, {fc[i].c, fc[i].a}};
       for (int k = 0; k < 3; ++k) {
+        const unsigned char lo = ed[k][0] < ed[k][1] ? ed[k][0] : ed[k][1], hi = ed[k][0] < ed[k][1] ? ed[k][1] : ed[k][0];
         int found = -1;
         for (int e = 0; e < ne; ++e)
-          if (eh[e][0] == ed[k][1] && eh[e][1] == ed[k][0]) { found = e; break; }
+          if (eh[e][0] == lo && eh[e][1] == hi) { found = e; break; }
         if (found >= 0) { eh[found][0] = eh[ne - 1][0]; eh[found][1] = eh[ne - 1][1]; --ne; }
-        else if (ne < 96) { eh[ne][0] = ed[k][0]; eh[ne][1] = ed[k][1]; ++ne; }
+        else if (ne < 96) { eh[ne][0] = lo; eh[ne][1] = hi; ++ne; }
       }
     }
     if (ne == 0) break;
@@ -617,14 +651,12 @@ __device__ __noinline__ float epa_depth(const GjkShape& A, const GjkShape& B, co
       int slot = -1;
       for (int i = 0; i < nf; ++i) if (!fc[i].alive) { slot = i; break; }
       if (slot < 0) { if (nf >= kEpaMaxF) { ok = false; break; } slot = nf++; }
-      // Expanding the polytope can only move its faces outwards.  A new face that is a sliver,
-      // or lies closer to the origin than the face it replaces, is rounding noise (w almost in
-      // the plane of the old face): the polytope would be corrupt from here on, so stop with
-      // the depth reached -- by then it is within the noise of the converged value.
-      // (bd < 0: GJK handed over a simplex that does not hold the origin -- a false "enclosed" on
-      // a sliver tetrahedron of two shapes a few mm apart; the expansion then walks to the face
-      // the origin lies beyond, and its negative offset is the separation.  Leave that alone.)
-      if (!epa_face(vt, eh[e][0], eh[e][1], nv, fc[slot]) || (bd > 0.f && fc[slot].d < bd - kEpaTol * (1.f + bd))) ok = false;
+      // (a sliver stays dead: it has no plane to test.)  Expanding the polytope can only move its
+      // faces outwards: a new face closer to the origin than the one it replaces is rounding noise
+      // (w almost in the plane of the old face) -- stop with the depth reached, which by then is
+      // within the noise of the converged value.  (bd < 0: the start tetrahedron does not hold the
+      // origin and the expansion walks to the face the origin lies beyond; leave that alone.)
+      if (epa_face(vt, eh[e][0], eh[e][1], nv, inside, fc[slot]) && bd > 0.f && fc[slot].d < bd - kEpaTol * (1.f + bd)) ok = false;
     }
     ++nv;
     if (!ok) break;
@@ -641,8 +673,13 @@ __device__ __forceinline__ float gjk_signed_distance(const GjkShape& A, const Gj
     gjk_init(g, rel, rsum, v0);
     float dist = 0.f;
     int st = GJK_CONTINUE;
-    while (st == GJK_CONTINUE) st = gjk_step(g, A, B, true, dist);
-    if (st == GJK_MISS || g.vv > 0.f) return dist;  // cores apart: |v| - radii (negative if the sweeps overlap)
+    while (st == GJK_CONTINUE) {
+      st = gjk_step(g, A, B, true, dist);
+#ifdef RAMP_TRACE_DIST
+      if ((threadIdx.x & 31) == 0 && blockIdx.x == 0) printf("trace dist: attempt %d it %d n %d |v| %.9g lower %.9g status %d dist %.9g\n", attempt, g.it, g.s.n, sqrtf(g.vv), g.lower, st, dist);
+#endif
+    }
+    if (st == GJK_MISS || (st != GJK_STALL && g.vv > 0.f)) return dist;  // cores apart: |v| - radii (negative if the sweeps overlap)
     // "enclosed": believed only if the simplex really holds the origin; else start over from
     // the face the origin lies beyond (twice at most, then take EPA's walk to that face)
     V3 from;
