@@ -256,6 +256,40 @@ def test_edges_large_batch_matches_small_batches(built):
     assert same_nd.mean() > 0.97 and (agree | ~same_nd).mean() > 0.98
 
 
+def test_cases_found_by_the_parity_sweep(built):
+    """The (configuration, pair) cases on which GPU and oracle disagreed outside the band in the first
+    5M-per-robot sweep (tests/golden/sweep_cases.jsonl): shallow overlaps the FP32 GJK
+    stalled on, a capsule / capsule pair with the non-rigid reference capsule, deep cylinder / box
+    overlaps the oracle's EPA got wrong.  Today's oracle and the GPU agree on each -- the pair's bit on
+    the one-warp-per-configuration path, on the tile path and through the signed distance."""
+    import json
+    from pathlib import Path
+
+    from oracle import oracle
+    from ramp_b200 import workloads
+    from ramp_b200.desc import ModelDesc
+
+    cases = [json.loads(line) for line in (Path(__file__).parent / "golden" / "sweep_cases.jsonl").read_text().splitlines()]
+    assert len(cases) >= 8
+    models = {}
+    for c in cases:
+        key = (c["robot"], c["scene"])
+        if key not in models:
+            models[key] = _setup(*key)[0]
+        rm = models[key]
+        d = ModelDesc(rm.model, rm.collision_model)
+        q = np.asarray(c["q"], dtype=np.float32)[None]
+        ref = oracle.check(d, q[:, : rm.model.nq].astype(np.float64))["pair_dist"][0, c["pair"]]
+        assert abs(ref) > BAND, c["note"]
+        qd = torch.from_numpy(q).cuda()
+        one = bool(rm.gpu.check(qd, pair_mask=True)["pair_mask"][0, c["pair"]])
+        filler = torch.from_numpy(workloads.sample_q(rm.model, 9000, seed=5).astype(np.float32)).cuda()
+        tile = bool(rm.gpu.check(torch.cat([qd, filler]).contiguous(), pair_mask=True)["pair_mask"][0, c["pair"]])
+        dist = float(rm.gpu.distance(qd, [c["pair"]])[0, 0])
+        assert one == (ref < 0) and tile == (ref < 0) and (dist < 0) == (ref < 0), (c["note"], ref, one, tile, dist)
+        assert abs(dist - ref) < 1e-3 + 0.025 * abs(ref), (c["note"], ref, dist)
+
+
 def test_scene_update_and_pair_toggle(built):
     """add_object after the handle exists (ramp_model_set_scene) and pair (de)activation."""
     from ramp_b200 import workloads
