@@ -72,6 +72,25 @@ if MORE:
             tot["max_pose_err"] = max(tot["max_pose_err"], float(np.abs(fk - oracle.fk(d, q64)).max()))
             tot["n"] += k
         print(json.dumps(tot), flush=True)
+        # ---- the one-warp-per-configuration kernel (calls of <= 8000 rows), same comparison
+        tot = dict(robot=name, what="small-batch path", n=0, in_band=0, bad_cfg=0, bad_pairs=0, bad_first=0)
+        ms = max(n // 5, 8000)
+        for lo in range(0, ms, 80_000):
+            k = min(80_000, ms - lo)
+            q = workloads.sample_q(rm.model, k, seed=9000 + lo).astype(np.float32)
+            ref = oracle.check(d, q[:, : rm.model.nq].astype(np.float64))
+            hit = np.empty(k, dtype=bool); first = np.empty(k, dtype=np.int32); mask = np.empty((k, len(rm.collision_model.collisionPairs)), dtype=bool)
+            for c0 in range(0, k, 2000):
+                res = rm.gpu.check(torch.from_numpy(q[c0:c0 + 2000]).cuda(), first_pair=True, pair_mask=True)
+                hit[c0:c0 + 2000], first[c0:c0 + 2000], mask[c0:c0 + 2000] = res["hit"].cpu().numpy(), res["first_pair"].cpu().numpy(), res["pair_mask"].cpu().numpy()
+            pd = ref["pair_dist"]
+            outside = np.abs(ref["min_dist"]) > BAND
+            pair_out = np.abs(pd) > BAND
+            tot["n"] += k; tot["in_band"] += int((~outside).sum())
+            tot["bad_cfg"] += int((hit != ref["hit"])[outside].sum())
+            tot["bad_pairs"] += int(((mask != (pd <= 1e-12)) & pair_out).sum())
+            tot["bad_first"] += int((first != ref["first_pair"])[pair_out.all(axis=1)].sum())
+        print(json.dumps(tot), flush=True)
         # ---- planner edges
         if "arm" not in rm.groups:
             continue
