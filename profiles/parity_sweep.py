@@ -109,6 +109,16 @@ if MORE:
             if sp["type"] in (1, 2):
                 kk = c + (2 if sp["type"] == 2 else 0)
                 q1[:, kk] = q1s[:, kk]
+        # ---- the same verdicts from ACTUATED values of the group (q map: reference state, mimic joints, continuous joints)
+        na = max(n // 5, 1000)
+        act = spaces.sample_uniform(space, na, np.random.default_rng(11)).astype(np.float32)
+        refa = oracle.check(d, oracle.qmap_apply(qmap, act.astype(np.float64)))
+        resa = rm.gpu.check(torch.from_numpy(act).cuda(), actuated=True, first_pair=True, pair_mask=True)
+        pda = refa["pair_dist"]; outa = np.abs(refa["min_dist"]) > BAND
+        print(json.dumps(dict(robot=name, what="actuated rows", n=na, in_band=int((~outa).sum()),
+                              bad_cfg=int((resa["hit"].cpu().numpy() != refa["hit"])[outa].sum()),
+                              bad_pairs=int(((resa["pair_mask"].cpu().numpy() != (pda <= 1e-12)) & (np.abs(pda) > BAND)).sum()),
+                              bad_first=int((resa["first_pair"].cpu().numpy() != refa["first_pair"])[(np.abs(pda) > BAND).all(axis=1)].sum()))), flush=True)
         got = {k_: v.cpu().numpy() for k_, v in rm.gpu.check_edges(torch.from_numpy(q0).cuda(), torch.from_numpy(q1).cuda(), space).items()}
         ref = oracle.check_edges(d, qmap, space, q0.astype(np.float64), q1.astype(np.float64))
         same_nd = got["nd"] == ref["nd"]
