@@ -40,6 +40,10 @@ struct GjkQueue {
                       // overflow stays in-kernel), [2] the consumer's cursor; zeroed by the host
   uint32_t capacity;  // items: hard region [0, cap_hard), easy region [cap_hard, capacity)
   uint32_t cap_hard;
+  // One byte per tile of 32 rows of the result arrays the queue serves (zeroed by the host).  The
+  // batch kernel keeps no GJK loop of its own: a tile that could not queue all its items sets its
+  // byte (and bumps count[3]), and recheck_kernel redoes the rows of such tiles from scratch.
+  uint8_t* tile_flags;
 };
 
 __host__ __device__ constexpr uint32_t queue_cap_hard(uint32_t capacity) { return capacity / 3; }
@@ -103,7 +107,10 @@ __device__ __forceinline__ bool closed_form_hit(int cls, const DGeom* ga, const 
 // the flag is wanted -- once any pair has hit.
 // `tw` / kTeam: this warp takes every kTeam-th chunk of `chunk_pairs` pairs (kTeam == 1: all of
 // them, in chunks of kChunkPairs -- a compile-time constant on the common path)
-template <int kTeam = 1>
+// kStage3: items that do not fit the queue are solved here, in the kernel (the planner-edge kernel).
+// The batch validity kernel passes false: it flags the tile instead (GjkQueue::tile_flags) and
+// carries neither the GJK loop's ~1500 instructions nor its 22 registers.
+template <int kTeam = 1, bool kStage3 = true>
 __device__ __forceinline__ void narrow_phase(const Warp& w, bool stop_at_first, bool stop_any, bool want_mask,
                                              const GjkQueue& gq, uint32_t row_base, int live_rows, int tw = 0,
                                              int chunk_pairs_rt = kChunkPairs) {
@@ -123,6 +130,7 @@ __device__ __forceinline__ void narrow_phase(const Warp& w, bool stop_at_first, 
     if (l == 0) c = atomicAdd(next_chunk, chunk_pairs);
     return __shfl_sync(FULL, c, 0);
   };
+  bool over = false;  // (!kStage3) an item of this tile found no room in the queue
   for (int chunk = kTeam == 1 ? 0 : take_chunk(); chunk < h->n_pairs; chunk = kTeam == 1 ? chunk + chunk_pairs : take_chunk()) {
     const int chunk_end = min(chunk + chunk_pairs, h->n_pairs);
     // Lanes past the end of the batch hold a replayed row (load_rows): they must never produce
@@ -313,15 +321,19 @@ __device__ __forceinline__ void narrow_phase(const Warp& w, bool stop_at_first, 
           }
         }
       }
-      const unsigned b = __ballot_sync(FULL, to_gjk);
-      if (to_gjk) w.queue[gn + __popc(b & ((1u << l) - 1))] = static_cast<uint16_t>(item);
-      gn += __popc(b);
+      if (!kStage3) {
+        over = over || to_gjk;
+      } else {
+        const unsigned b = __ballot_sync(FULL, to_gjk);
+        if (to_gjk) w.queue[gn + __popc(b & ((1u << l) - 1))] = static_cast<uint16_t>(item);
+        gn += __popc(b);
+      }
       __syncwarp();
     }
     // ---- stage 3: GJK.  Each lane owns one work item and advances it one iteration per
     // trip; lanes whose item finished fetch the next one from the queue, so lanes stay busy
     // although iteration counts differ per item.
-    if (gn > 0) {
+    if (kStage3 && gn > 0) {
       int next = 0, c = 0, p = 0;
       bool active = false;
       GjkLane g;
@@ -370,6 +382,10 @@ __device__ __forceinline__ void narrow_phase(const Warp& w, bool stop_at_first, 
       }
     }
     __syncwarp();
+  }
+  if (!kStage3 && __any_sync(FULL, over) && l == 0) {
+    gq.tile_flags[row_base >> 5] = 1;
+    atomicAdd(gq.count + 3, 1u);
   }
 }
 
@@ -442,7 +458,7 @@ __global__ void __launch_bounds__(512, 1) check_kernel(const __grid_constant__ C
     team_sync();
     // FK is done with the saved transforms: their region takes the next tile's rows
     if (tw == 0) tile_fetch_issue(tf, a.q, (tile + tile_step) << 5, a.n, cols, a.ld, a.L.raw_cols, w.lane);
-    narrow_phase<kTeam>(w, stop, stop && a.first_pair == nullptr, want_mask, a.gq, static_cast<uint32_t>(row0) + a.row_offset,
+    narrow_phase<kTeam, false>(w, stop, stop && a.first_pair == nullptr, want_mask, a.gq, static_cast<uint32_t>(row0) + a.row_offset,
                         static_cast<int>(imin64(32, a.n - row0)), tw, a.L.chunk_pairs);
     team_sync();
     const int64_t row = row0 + w.lane;

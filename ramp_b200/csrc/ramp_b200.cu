@@ -750,6 +750,7 @@ static int init_kernel_attrs(int device, int max_smem) {
   CUDA_TRY(opt_in_smem(check_kernel<4>, max_smem));
   CUDA_TRY(opt_in_smem(gjk_queue_kernel, max_smem));
   CUDA_TRY(opt_in_smem(check_warp_kernel, max_smem));
+  CUDA_TRY(opt_in_smem(recheck_kernel, max_smem));
   CUDA_TRY(opt_in_smem(fk_kernel<1>, max_smem));
   CUDA_TRY(opt_in_smem(fk_kernel<2>, max_smem));
   CUDA_TRY(opt_in_smem(distance_kernel, max_smem));
@@ -799,6 +800,17 @@ constexpr int64_t kSliceRows = 1 << 21;
 constexpr int64_t kQueueItemsPerRow = 3;
 constexpr uint32_t queue_items_for(int64_t rows) { return static_cast<uint32_t>(rows * kQueueItemsPerRow + 4096); }
 constexpr int64_t kQueueMinRows = 1024;    // below this a second launch costs more than it saves
+// Queue scratch: [0, 256) counters | one flag byte per tile of 32 rows (GjkQueue::tile_flags) | items
+static size_t queue_flag_bytes(int64_t rows) { return (static_cast<size_t>((rows + 31) / 32) + 255) & ~size_t{255}; }
+static size_t queue_bytes(int64_t rows, uint32_t cap_items) { return 256 + queue_flag_bytes(rows) + static_cast<size_t>(cap_items) * sizeof(GjkItem); }
+static GjkQueue queue_at(unsigned char* scratch, int64_t rows, uint32_t cap_items, uint32_t cap_hard) {
+  return GjkQueue{cap_items ? reinterpret_cast<GjkItem*>(scratch + 256 + queue_flag_bytes(rows)) : nullptr,
+                  reinterpret_cast<uint32_t*>(scratch), cap_items, cap_hard, scratch + 256};
+}
+// counters and flags start from zero for every launch group that uses the queue
+static cudaError_t queue_reset(unsigned char* scratch, int64_t rows, cudaStream_t st) {
+  return cudaMemsetAsync(scratch, 0, 256 + queue_flag_bytes(rows), st);
+}
 
 constexpr int64_t kEdgeSliceEdges = 1 << 18;  // edges per launch group of ramp_check_edges (see there)
 // Up to here one warp per configuration is faster than 32 configurations per warp: 8192 rows for
@@ -840,6 +852,24 @@ static int launch_check_small(const RampModel* m, const float* d_q, int64_t n, i
   return RAMP_OK;
 }
 
+// recheck_kernel behind a tile kernel: the rows of the tiles it flagged, one warp per configuration
+// (the shape of launch_check_small; every CTA leaves at once when nothing was flagged)
+static void launch_recheck(const RampModel* m, const float* d_q, int64_t n, int32_t ld, uint32_t flags, uint8_t* d_hit, int32_t* d_first,
+                           uint32_t* d_mask, const uint8_t* tile_flags, const uint32_t* count, cudaStream_t st) {
+  SmallArgs a;
+  a.img = m->d_image; a.table_bytes = static_cast<int32_t>(align16(m->hdr.total_bytes));
+  a.q = d_q; a.n = n; a.ld = ld; a.flags = flags; a.hit = d_hit; a.first_pair = d_first; a.pair_mask = d_mask;
+  plan_warp_slab(m, (flags & RAMP_Q_ACTUATED) ? m->hdr.n_act : m->hdr.nq, &a.L);
+  const int nwarps = 4;
+  const size_t smem = 16 + a.table_bytes + static_cast<size_t>(a.L.words) * 4 * nwarps;
+  if (smem > static_cast<size_t>(m->max_smem)) return;  // (such a model has no small-batch path either: create fails earlier)
+  const int per_sm = static_cast<int>(std::max<size_t>(1, std::min<size_t>(8, (static_cast<size_t>(m->max_smem) + 1024) / (smem + 1024))));
+  const int64_t parts = ((n + 31) / 32) * 4;
+  const int64_t blocks = std::min<int64_t>((parts + nwarps - 1) / nwarps, static_cast<int64_t>(m->sm_count) * per_sm);
+  recheck_kernel<<<static_cast<int>(blocks), nwarps * 32, smem, st>>>(a, tile_flags, count);
+  g_launches.fetch_add(1, std::memory_order_relaxed);
+}
+
 // One ramp_check_batch is: plan (slab layout, team size, shared-memory opt-in), a GJK queue from
 // the model's pool, then per slice the tile kernel and the queue kernel.  The pieces are
 // separate because ramp_check_host feeds ONE queue from the tile kernels of several chunks and
@@ -854,7 +884,7 @@ struct CheckPlan {
 static int plan_check(const RampModel* m, int32_t ld, uint32_t flags, int64_t n, CheckPlan* P) {
   CheckArgs& a = P->a;
   a.img = m->d_image; a.ld = ld; a.flags = flags; a.row_offset = 0;
-  a.gq = GjkQueue{nullptr, nullptr, 0u, 0u};
+  a.gq = GjkQueue{nullptr, nullptr, 0u, 0u, nullptr};
   // no actuated rows in this call: their part of the slab is not reserved (one more warp on Panda-sized robots)
   const int act_cols = (flags & RAMP_Q_ACTUATED) ? m->hdr.n_act : 0;
   int nwarps; size_t smem;
@@ -884,14 +914,14 @@ static int plan_check(const RampModel* m, int32_t ld, uint32_t flags, int64_t n,
 // a queue for up to `rows` configurations, from the model's pool, in stream order
 static int queue_alloc(const RampModel* m, int64_t rows, cudaStream_t st, unsigned char** scratch, GjkQueue* gq) {
   uint32_t cap_items = queue_items_for(rows);
-  // test hook: a tiny queue forces the overflow path (GJK inside check_kernel)
+  // test hook: a tiny queue forces the overflow path (flagged tiles, recheck_kernel)
   if (const char* e = std::getenv("RAMP_B200_QUEUE_CAP")) cap_items = static_cast<uint32_t>(std::max(1, std::atoi(e)));
-  const size_t bytes = 256 + static_cast<size_t>(cap_items) * sizeof(GjkItem);
+  const size_t bytes = queue_bytes(rows, cap_items);
   if (cudaMallocFromPoolAsync(reinterpret_cast<void**>(scratch), bytes, m->pool, st) != cudaSuccess) {
     cudaGetLastError();
     return fail(RAMP_ERR_ALLOC, "cudaMallocFromPoolAsync(%zu) for the GJK queue failed", bytes);
   }
-  *gq = GjkQueue{reinterpret_cast<GjkItem*>(*scratch + 256), reinterpret_cast<uint32_t*>(*scratch), cap_items, queue_cap_hard(cap_items)};
+  *gq = queue_at(*scratch, rows, cap_items, queue_cap_hard(cap_items));
   return RAMP_OK;
 }
 
@@ -907,6 +937,7 @@ static void launch_tiles(const RampModel* m, const CheckPlan& P, const float* d_
   else if (P.team == 4) check_kernel<4><<<grid, nwarps * 32, smem, st>>>(a);
   else check_kernel<1><<<grid, nwarps * 32, smem, st>>>(a);
   g_launches.fetch_add(1, std::memory_order_relaxed);
+  if (gq.tile_flags != nullptr) launch_recheck(m, d_q, ns, a.ld, a.flags, hit, first, mask, gq.tile_flags + (row_offset >> 5), gq.count, st);
 }
 
 // queue kernel; hit/first/mask are the arrays the items' row indices refer to
@@ -987,8 +1018,11 @@ static int launch_check(const RampModel* m, const float* d_q, int64_t n, int32_t
   if (n <= small_rows(m)) return launch_check_small(m, d_q, n, ld, flags, d_hit, d_first, d_mask, st);
   CheckPlan P;
   if (int rc = plan_check(m, ld, flags, n, &P)) return rc;
+  // (the tile kernel hands its GJK work to the queue; without one -- no memory pool on this device --
+  // a robot that has GJK pairs takes the one-warp-per-configuration kernel whatever the batch size)
+  if (!P.use_queue && m->n_gjk_pairs > 0) return launch_check_small(m, d_q, n, ld, flags, d_hit, d_first, d_mask, st);
   unsigned char* scratch = nullptr;
-  GjkQueue gq{nullptr, nullptr, 0u, 0u};
+  GjkQueue gq{nullptr, nullptr, 0u, 0u, nullptr};
   int64_t step = n;
   if (P.use_queue) {
     uint32_t cap_items, cap_hard;
@@ -998,9 +1032,9 @@ static int launch_check(const RampModel* m, const float* d_q, int64_t n, int32_t
       cap_hard = queue_cap_hard(cap_items);
     }
     void* p = nullptr;
-    if (int rc = pool_alloc(m, 256 + static_cast<size_t>(cap_items) * sizeof(GjkItem), st, &p)) return rc;
+    if (int rc = pool_alloc(m, queue_bytes(step, cap_items), st, &p)) return rc;
     scratch = static_cast<unsigned char*>(p);
-    gq = GjkQueue{reinterpret_cast<GjkItem*>(scratch + 256), reinterpret_cast<uint32_t*>(scratch), cap_items, cap_hard};
+    gq = queue_at(scratch, step, cap_items, cap_hard);
   }
   int64_t last_rows = 0;
   for (int64_t off = 0; off < n; off += step) {
@@ -1008,7 +1042,7 @@ static int launch_check(const RampModel* m, const float* d_q, int64_t n, int32_t
     uint8_t* hit = d_hit + off;
     int32_t* first = d_first ? d_first + off : nullptr;
     uint32_t* mask = d_mask ? d_mask + off * m->hdr.mask_words : nullptr;
-    if (P.use_queue) CUDA_TRY(cudaMemsetAsync(scratch, 0, 16, st));
+    if (P.use_queue) CUDA_TRY(queue_reset(scratch, step, st));
     launch_tiles(m, P, d_q + off * ld, ns, 0u, hit, first, mask, gq, st);
     if (P.use_queue) launch_queue(m, P, gq, hit, first, mask, ns, st);
     last_rows = ns;
@@ -1308,7 +1342,7 @@ int ramp_check_batch(const RampModel* m, const float* d_q, int64_t n, int32_t ld
 // is ever used.  That is why the limit is modest.
 constexpr int64_t kNoAllocMaxRows = RAMP_NOALLOC_MAX_ROWS;
 constexpr uint32_t kNoAllocQueueItems = queue_items_for(kNoAllocMaxRows);
-constexpr size_t kNoAllocQueueBytes = 256 + static_cast<size_t>(kNoAllocQueueItems) * sizeof(GjkItem);
+constexpr size_t kNoAllocQueueBytes = 256 + ((static_cast<size_t>((kNoAllocMaxRows + 31) / 32) + 255) & ~size_t{255}) + static_cast<size_t>(kNoAllocQueueItems) * sizeof(GjkItem);  // counters | tile flags | items
 static __device__ __align__(256) unsigned char g_noalloc_queue[kNoAllocQueueBytes];
 
 // In host code `g_noalloc_queue` is only a handle for the symbol, not an address a kernel
@@ -1353,13 +1387,14 @@ int ramp_check_batch_noalloc(const RampModel* m, const float* d_q, int64_t n, in
   const size_t smem_b = 16 + align16(m->hdr.total_bytes);
   // the array still holds the previous call's counter and items: only the counter has to
   // start from zero, the items below it are rewritten before they are read
-  CUDA_TRY(cudaMemsetAsync(scratch, 0, 16, st));
+  CUDA_TRY(queue_reset(scratch, kNoAllocMaxRows, st));
   // the capacity rule of ramp_check_batch for this many rows (not the whole array): both entry
   // points then settle every item in the same place and give bit-identical results
   const uint32_t cap_items = queue_items_for(n);
-  a.gq = GjkQueue{reinterpret_cast<GjkItem*>(scratch + 256), reinterpret_cast<uint32_t*>(scratch), cap_items, queue_cap_hard(cap_items)};
+  a.gq = queue_at(scratch, kNoAllocMaxRows, cap_items, queue_cap_hard(cap_items));
   const int grid = spread_tiles(m, (n + 31) / 32, a.L, &nwarps, &smem);
   check_kernel<1><<<grid, nwarps * 32, smem, st>>>(a);
+  launch_recheck(m, d_q, n, ld, flags, d_hit, d_first_pair, d_pair_mask, a.gq.tile_flags, a.gq.count, st);
   GjkQueueArgs b{};
   b.img = m->d_image; b.table_bytes = static_cast<int32_t>(align16(m->hdr.total_bytes));
   b.items = a.gq.items; b.count = a.gq.count; b.capacity = cap_items; b.cap_hard = a.gq.cap_hard; b.stats = m->d_stats;
@@ -1367,7 +1402,7 @@ int ramp_check_batch_noalloc(const RampModel* m, const float* d_q, int64_t n, in
   b.stop = !(flags & RAMP_ALL_PAIRS) && d_pair_mask == nullptr;
   b.n_rows = static_cast<uint32_t>(n);
   gjk_queue_kernel<<<m->sm_count * kGjkCtasPerSm, 256, smem_b, st>>>(b);
-  g_launches.fetch_add(2, std::memory_order_relaxed);
+  g_launches.fetch_add(2, std::memory_order_relaxed);  // (+1 counted by launch_recheck)
   CUDA_TRY(cudaGetLastError());
   return RAMP_OK;
 }
@@ -1621,12 +1656,12 @@ int ramp_check_edges(const RampModel* m, const float* d_q0, const float* d_q1, i
     const int64_t ne = std::min(slice, n_edges - e0);
     a.q0 = d_q0 + e0 * ld; a.q1 = d_q1 + e0 * ld; a.n_edges = ne; a.valid = d_valid + e0;
     a.nd = d_nd ? d_nd + e0 : reinterpret_cast<int32_t*>(S + off_nd);
-    a.gq = GjkQueue{nullptr, nullptr, 0u, 0u};
+    a.gq = GjkQueue{nullptr, nullptr, 0u, 0u, nullptr};
     GjkQueueArgs b{};
     if (use_queue) {
       unsigned char* Q = static_cast<unsigned char*>(qmem);
       CUDA_TRY(cudaMemsetAsync(Q, 0, 16, st));
-      a.gq = GjkQueue{reinterpret_cast<GjkItem*>(Q + 256), reinterpret_cast<uint32_t*>(Q), cap, queue_cap_hard(cap)};
+      a.gq = GjkQueue{reinterpret_cast<GjkItem*>(Q + 256), reinterpret_cast<uint32_t*>(Q), cap, queue_cap_hard(cap), nullptr};  // (the edge kernel solves what does not fit in place)
       b.img = m->d_image; b.table_bytes = static_cast<int32_t>(align16(m->hdr.total_bytes)); b.items = a.gq.items; b.count = a.gq.count; b.capacity = cap; b.cap_hard = a.gq.cap_hard; b.stats = m->d_stats;
       b.offs = a.offs; b.nd = a.nd; b.first_invalid = a.first_invalid; b.n_edges = ne;
     }
@@ -1776,6 +1811,7 @@ int ramp_check_host(const RampModel* m, const float* h_q, int64_t n, int32_t ld,
   if (tiled)
     if (int rc = plan_check(m, ld, flags, n, &P)) return rc;
   const bool queued = tiled && P.use_queue;
+  if (tiled && !queued && m->n_gjk_pairs > 0) return fail(RAMP_ERR_ALLOC, "ramp_check_host needs the device's memory pool for batches of this size");
   // device: two q chunks, then two sets of result arrays (one per section parity)
   const size_t b_q = align16(sizeof(float) * chunk * ld), b_hit = align16(section), b_first = align16(sizeof(int32_t) * section),
                b_mask = align16(sizeof(uint32_t) * section * mw);
@@ -1813,10 +1849,10 @@ int ramp_check_host(const RampModel* m, const float* h_q, int64_t n, int32_t ld,
     if (nsec >= 2)
       for (int i = 0; i < kHostStreams; ++i) CUDA_TRY(cudaStreamWaitEvent(m->streams[i], ev_out[par], 0));
     unsigned char* qmem = nullptr;
-    GjkQueue gq{nullptr, nullptr, 0u, 0u};
+    GjkQueue gq{nullptr, nullptr, 0u, 0u, nullptr};
     if (queued) {
       if (int rc = queue_alloc(m, rows, m->streams[0], &qmem, &gq)) return rc;
-      CUDA_TRY(cudaMemsetAsync(qmem, 0, 16, m->streams[0]));
+      CUDA_TRY(queue_reset(qmem, rows, m->streams[0]));
       CUDA_TRY(cudaEventRecord(ev_queue, m->streams[0]));
       for (int i = 1; i < kHostStreams; ++i) CUDA_TRY(cudaStreamWaitEvent(m->streams[i], ev_queue, 0));
     }

@@ -236,6 +236,22 @@ __device__ __forceinline__ SmallWarp make_small_warp(const Tables& t, float* sla
   return w;
 }
 
+// one configuration through the warp: row in, verdict (and first pair / mask) out
+__device__ __forceinline__ void check_row(const SmallWarp& w, const SmallArgs& a, int64_t row, int cols, bool actuated, bool stop, bool want_mask) {
+  const float* src = a.q + row * a.ld;
+  for (int k = w.lane; k < cols; k += 32) (actuated ? w.act : w.q)[k] = __ldg(src + k);
+  __syncwarp();
+  if (actuated) expand_q_warp(w);
+  const int f = check_one_config(w, stop, want_mask);
+  if (w.lane == 0) {
+    a.hit[row] = f != INT32_MAX;
+    if (a.first_pair) a.first_pair[row] = f != INT32_MAX ? f : -1;
+  }
+  if (want_mask)
+    for (int k = w.lane; k < w.t.h->mask_words; k += 32) a.pair_mask[row * w.t.h->mask_words + k] = w.mask[k];
+  __syncwarp();
+}
+
 __global__ void __launch_bounds__(128, 4) check_warp_kernel(const __grid_constant__ SmallArgs a) {
   uint64_t* mbar = reinterpret_cast<uint64_t*>(g_smem);
   unsigned char* tbl = g_smem + 16;
@@ -249,19 +265,35 @@ __global__ void __launch_bounds__(128, 4) check_warp_kernel(const __grid_constan
   // early-out only when nobody asked which pair came first
   const bool stop = !(a.flags & RAMP_ALL_PAIRS) && !want_mask && a.first_pair == nullptr;
   const int cols = actuated ? t.h->n_act : t.h->nq;
-  for (int64_t row = static_cast<int64_t>(blockIdx.x) * nwarps + wid; row < a.n; row += static_cast<int64_t>(gridDim.x) * nwarps) {
-    const float* src = a.q + row * a.ld;
-    for (int k = w.lane; k < cols; k += 32) (actuated ? w.act : w.q)[k] = __ldg(src + k);
-    __syncwarp();
-    if (actuated) expand_q_warp(w);
-    const int f = check_one_config(w, stop, want_mask);
-    if (w.lane == 0) {
-      a.hit[row] = f != INT32_MAX;
-      if (a.first_pair) a.first_pair[row] = f != INT32_MAX ? f : -1;
-    }
-    if (want_mask)
-      for (int k = w.lane; k < t.h->mask_words; k += 32) a.pair_mask[row * t.h->mask_words + k] = w.mask[k];
-    __syncwarp();
+  for (int64_t row = static_cast<int64_t>(blockIdx.x) * nwarps + wid; row < a.n; row += static_cast<int64_t>(gridDim.x) * nwarps)
+    check_row(w, a, row, cols, actuated, stop, want_mask);
+}
+
+// The rows of the tiles the batch validity kernel flagged (GjkQueue::tile_flags: a tile whose GJK
+// items did not all fit the queue -- a robot that produces more items than the queue was sized
+// for, or a call without a queue), redone from scratch with one warp per configuration.  Runs
+// between the tile kernel and the queue kernel; when nothing was flagged (count[3] == 0, the
+// normal case) every CTA leaves before it has staged anything.
+__global__ void __launch_bounds__(128, 4) recheck_kernel(const __grid_constant__ SmallArgs a, const uint8_t* __restrict__ tile_flags,
+                                                         const uint32_t* __restrict__ count) {
+  if (count[3] == 0u) return;
+  uint64_t* mbar = reinterpret_cast<uint64_t*>(g_smem);
+  unsigned char* tbl = g_smem + 16;
+  stage_tables(tbl, a.img, a.table_bytes, mbar);
+  const Tables t = make_tables(tbl);
+  const int nwarps = blockDim.x >> 5, wid = threadIdx.x >> 5;
+  float* slab = reinterpret_cast<float*>(tbl + a.table_bytes) + static_cast<size_t>(wid) * a.L.words;
+  const SmallWarp w = make_small_warp(t, slab, a.L);
+  const bool actuated = a.flags & RAMP_Q_ACTUATED;
+  const bool want_mask = a.pair_mask != nullptr;
+  const bool stop = !(a.flags & RAMP_ALL_PAIRS) && !want_mask && a.first_pair == nullptr;
+  const int cols = actuated ? t.h->n_act : t.h->nq;
+  // a warp takes a quarter of a flagged tile (8 rows): flagged tiles come in runs
+  const int64_t nparts = ((a.n + 31) >> 5) * 4;
+  for (int64_t part = static_cast<int64_t>(blockIdx.x) * nwarps + wid; part < nparts; part += static_cast<int64_t>(gridDim.x) * nwarps) {
+    if (!tile_flags[part >> 2]) continue;
+    const int64_t r0 = part * 8, r1 = imin64(a.n, r0 + 8);
+    for (int64_t row = r0; row < r1; ++row) check_row(w, a, row, cols, actuated, stop, want_mask);
   }
 }
 
