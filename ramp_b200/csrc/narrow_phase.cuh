@@ -412,7 +412,7 @@ struct CheckArgs {
 
 // ------------------------------------------------------------------ kernel: validity
 template <int kTeam>
-__global__ void __launch_bounds__(512, 1) check_kernel(const __grid_constant__ CheckArgs a) {
+__global__ void __launch_bounds__(576, 1) check_kernel(const __grid_constant__ CheckArgs a) {
   uint64_t* mbar = reinterpret_cast<uint64_t*>(g_smem);
   unsigned char* tbl = g_smem + 16;
   stage_tables(tbl, a.img, a.L.table_bytes, mbar);

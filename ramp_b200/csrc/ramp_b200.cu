@@ -677,9 +677,11 @@ static int build_image(RampModel* m) {
   return RAMP_OK;
 }
 
-// Shared-memory plan: tables + as many warp slabs as fit (<= 16 warps).
+// Shared-memory plan: tables + as many warp slabs as fit (<= max_warps; the batch validity kernel runs at
+// 106-110 registers and takes up to kCheckWarps = 18 warps per SM).
+constexpr int kCheckWarps = 18;
 static int plan_slabs(const RampModel* m, int stage_row_floats, int act_cols, SlabLayout* L, int* nwarps,
-                      size_t* smem_bytes, int ld = 0, int team = 1, bool with_verts = false) {
+                      size_t* smem_bytes, int ld = 0, int team = 1, bool with_verts = false, int max_warps = 16) {
   const ImgHeader& h = m->hdr;
   int w = 0;
   auto take = [&](int words) { const int o = w; w += (words + 3) & ~3; return o; };
@@ -722,7 +724,7 @@ static int plan_slabs(const RampModel* m, int stage_row_floats, int act_cols, Sl
   if (fixed + per_warp > static_cast<size_t>(m->max_smem))
     return fail(RAMP_ERR_LIMIT, "model needs %zu B of shared memory per CTA, device allows %d", fixed + per_warp, m->max_smem);
   const int fit = static_cast<int>((m->max_smem - fixed) / per_warp);  // slabs (= teams) that fit
-  const int teams = std::min(16 / team, fit);
+  const int teams = std::min(max_warps / team, fit);
   *nwarps = teams * team;
   *smem_bytes = fixed + per_warp * teams;
   return RAMP_OK;
@@ -888,7 +890,7 @@ static int plan_check(const RampModel* m, int32_t ld, uint32_t flags, int64_t n,
   // no actuated rows in this call: their part of the slab is not reserved (one more warp on Panda-sized robots)
   const int act_cols = (flags & RAMP_Q_ACTUATED) ? m->hdr.n_act : 0;
   int nwarps; size_t smem;
-  if (int rc = plan_slabs(m, 0, act_cols, &a.L, &nwarps, &smem, ld)) return rc;
+  if (int rc = plan_slabs(m, 0, act_cols, &a.L, &nwarps, &smem, ld, 1, false, kCheckWarps)) return rc;
   // Few slabs fit (a robot with many geometries): let teams of 2 or 4 warps share each slab and
   // split the kinematic tree and the pair list between them -- whichever team size puts the most
   // warps on an SM (H1 stand-in, 20 hulls: 6 slabs -> 6 / 12 / 16 warps: 4.6e8 / 7.6e8 / 8.1e8
@@ -898,13 +900,13 @@ static int plan_check(const RampModel* m, int32_t ld, uint32_t flags, int64_t n,
     SlabLayout L2, L4;
     int w2 = 0, w4 = 0;
     size_t s2 = 0, s4 = 0;
-    const bool ok2 = plan_slabs(m, 0, act_cols, &L2, &w2, &s2, ld, 2) == RAMP_OK;
-    const bool ok4 = plan_slabs(m, 0, act_cols, &L4, &w4, &s4, ld, 4) == RAMP_OK;
+    const bool ok2 = plan_slabs(m, 0, act_cols, &L2, &w2, &s2, ld, 2, false, kCheckWarps) == RAMP_OK;
+    const bool ok4 = plan_slabs(m, 0, act_cols, &L4, &w4, &s4, ld, 4, false, kCheckWarps) == RAMP_OK;
     if (ok2 && w2 > nwarps) team = 2;
     if (ok4 && w4 > (team == 2 ? w2 : nwarps)) team = 4;
   }
   if (const char* e = std::getenv("RAMP_B200_TEAM")) { team = std::atoi(e); team = team >= 4 ? 4 : (team >= 2 ? 2 : 1); }  // experiments
-  if (team > 1 && plan_slabs(m, 0, act_cols, &a.L, &nwarps, &smem, ld, team) != RAMP_OK) return RAMP_ERR_LIMIT;
+  if (team > 1 && plan_slabs(m, 0, act_cols, &a.L, &nwarps, &smem, ld, team, false, kCheckWarps) != RAMP_OK) return RAMP_ERR_LIMIT;
   P->nwarps = nwarps; P->team = team; P->smem = smem;
   P->use_queue = m->pool != nullptr && m->n_gjk_pairs > 0 && n >= kQueueMinRows;
   P->smem_b = 16 + align16(m->hdr.total_bytes);  // the queue kernel stages the whole image, vertex lists included

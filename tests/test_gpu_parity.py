@@ -381,17 +381,29 @@ def test_large_sweep_flags_and_first_pair(built, name, scene, n):
     assert bad_cfg == 0 and bad_first == 0
 
 
-def test_queue_overflow_falls_back_to_in_kernel_gjk(built, monkeypatch, record_property):
-    """The GJK work queue is bounded; items that do not fit are solved inside the validity
-    kernel (cold start instead of the capsule witness, so near-contact pairs may flip inside
-    the margin band).  A 100-item queue forces nearly everything down that path: the answers
-    still match the oracle outside the band."""
+def test_queue_overflow_is_rechecked(built, monkeypatch, record_property):
+    """The GJK work queue is bounded; a tile whose items do not all fit is flagged by the validity
+    kernel and recheck_kernel redoes its rows with one warp per configuration (a different GJK
+    schedule, so near-contact pairs may flip inside the margin band).  A 100-item queue sends nearly
+    every tile down that path -- through ramp_check_batch (ragged batch, flags / first pair / mask)
+    and through ramp_check_host (per chunk): the answers still match the oracle outside the band."""
+    from oracle import oracle
     from ramp_b200 import workloads
+    from ramp_b200.desc import ModelDesc
+    from ramp_b200.engine import pinned_empty
 
     rm, _ = _setup("ur5e/configs", "obstacles")
-    q = workloads.sample_q(rm.model, 20000, seed=77)
+    q = workloads.sample_q(rm.model, 20011, seed=77)
     monkeypatch.setenv("RAMP_B200_QUEUE_CAP", "100")
     _compare_check(rm, q, lambda **kw: [record_property(k, v) for k, v in kw.items()])
+    nq = rm.model.nq
+    qh = pinned_empty((len(q), nq), np.float32)
+    qh[:] = q[:, :nq]
+    hh = pinned_empty((len(q),), np.uint8)
+    rm.gpu.check_host_into(qh, hh)
+    ref = oracle.check(ModelDesc(rm.model, rm.collision_model), q[:, :nq].astype(np.float64))
+    outside = np.abs(ref["min_dist"]) > BAND
+    assert (hh.astype(bool) == ref["hit"])[outside].all()
 
 
 @pytest.mark.gpu
