@@ -33,7 +33,7 @@ else
   spec=${3:-panda_64m:4194304}
   wl=${spec%%:*}; rows=${spec##*:}
   python bench.py --workload $wl --rows $rows $short > $out/plain_$wl.log 2>&1 &&
-  ncu --set full --clock-control none --import-source on -k regex:"check_kernel|gjk_queue" -s 6 -c 4 -f \
+  ncu --set full --clock-control none --import-source on -k regex:"^(void )?check_kernel|gjk_queue" -s 6 -c 4 -f \
       -o $out/${tag}_prof_$wl python bench.py --workload $wl --rows $rows $short > $out/ncu_full_$wl.log 2>&1
 fi
 tail -n 3 $out/*.err $out/ncu_*.log 2>/dev/null | tail -n 20

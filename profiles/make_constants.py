@@ -44,7 +44,7 @@ def main(tag, specs):
         path = HERE / f"{tag}_check_{name}_metrics.txt"
         per = collections.defaultdict(list)
         for b in blocks(path):
-            key = "gjk_queue_kernel" if "gjk_queue" in b["kernel"] else ("check_kernel" if "check_kernel" in b["kernel"] else None)
+            key = "gjk_queue_kernel" if "gjk_queue" in b["kernel"] else ("check_kernel" if "check_kernel" in b["kernel"] and "recheck" not in b["kernel"] else None)
             if key:
                 per[key].append(b)
         mean = lambda bs, k: sum(b.get(k, 0.0) for b in bs) / max(len(bs), 1)
