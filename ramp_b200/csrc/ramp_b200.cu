@@ -889,7 +889,7 @@ static int plan_check(const RampModel* m, int32_t ld, uint32_t flags, int64_t n,
   a.gq = GjkQueue{nullptr, nullptr, 0u, 0u, nullptr};
   // no actuated rows in this call: their part of the slab is not reserved (one more warp on Panda-sized robots)
   const int act_cols = (flags & RAMP_Q_ACTUATED) ? m->hdr.n_act : 0;
-  int nwarps; size_t smem;
+  int nwarps = 0; size_t smem = 0;
   if (int rc = plan_slabs(m, 0, act_cols, &a.L, &nwarps, &smem, ld, 1, false, kCheckWarps)) return rc;
   // Few slabs fit (a robot with many geometries): let teams of 2 or 4 warps share each slab and
   // split the kinematic tree and the pair list between them -- whichever team size puts the most
@@ -1297,7 +1297,7 @@ static int fk_common(const RampModel* m, const float* d_q, int64_t n, int32_t ld
   a.img = m->d_image; a.q = d_q; a.n = n; a.ld = ld; a.flags = flags; a.out = d_out;
   a.row_floats = 12 * (what == 1 ? m->hdr.n_joints : m->hdr.n_geoms);
   if (a.row_floats == 0) return RAMP_OK;
-  int nwarps; size_t smem;
+  int nwarps = 0; size_t smem = 0;
   if (int rc = plan_slabs(m, a.row_floats, m->hdr.n_act, &a.L, &nwarps, &smem, ld)) return rc;
   const int grid = spread_tiles(m, (n + 31) / 32, a.L, &nwarps, &smem);
   cudaStream_t st = static_cast<cudaStream_t>(stream);
@@ -1384,7 +1384,7 @@ int ramp_check_batch_noalloc(const RampModel* m, const float* d_q, int64_t n, in
   a.row_offset = 0;
   a.img = m->d_image; a.q = d_q; a.n = n; a.ld = ld; a.flags = flags;
   a.hit = d_hit; a.first_pair = d_first_pair; a.pair_mask = d_pair_mask;
-  int nwarps; size_t smem;
+  int nwarps = 0; size_t smem = 0;
   if (int rc = plan_slabs(m, 0, m->hdr.n_act, &a.L, &nwarps, &smem, ld)) return rc;
   const size_t smem_b = 16 + align16(m->hdr.total_bytes);
   // the array still holds the previous call's counter and items: only the counter has to
@@ -1419,7 +1419,7 @@ static int launch_min_distance(const RampModel* m, const float* d_q, int64_t n, 
   DistArgs a;
   a.img = m->d_image; a.q = d_q; a.n = n; a.ld = ld; a.flags = flags; a.n_sel = m->hdr.n_pairs; a.out = nullptr; a.sel = nullptr;
   a.min_out = d_min;
-  int nwarps; size_t smem;
+  int nwarps = 0; size_t smem = 0;
   if (int rc = plan_slabs(m, 0, m->hdr.n_act, &a.L, &nwarps, &smem, ld, 1, true)) return rc;
   nwarps = std::min(nwarps, 8);
   smem = 16 + a.L.table_bytes + static_cast<size_t>(a.L.words) * 4 * nwarps;
@@ -1500,7 +1500,7 @@ int ramp_ik_batch(const RampModel* m, const float* d_seed, int64_t n, int32_t ld
   a.max_dq = static_cast<float>(p->max_step > 0 ? p->max_step : 1e30);
   a.n_cols = n_act;
   CUDA_TRY(cudaSetDevice(m->device));
-  int nwarps; size_t smem;
+  int nwarps = 0; size_t smem = 0;
   if (int rc = plan_slabs(m, 12 * nj, n_act, &a.L, &nwarps, &smem, ld)) return rc;
   nwarps = std::min(nwarps, 16);
   // IK batches are small (hundreds to thousands of seeds) and every seed iterates tens of times:
@@ -1549,7 +1549,7 @@ int ramp_distance_batch(const RampModel* m, const float* d_q, int64_t n, int32_t
     CUDA_TRY(cudaStreamSynchronize(st));  // `sel` is a pageable temporary
     a.sel = d_sel;
   }
-  int nwarps; size_t smem;
+  int nwarps = 0; size_t smem = 0;
   if (int rc = plan_slabs(m, 0, m->hdr.n_act, &a.L, &nwarps, &smem, ld, 1, true)) return rc;
   nwarps = std::min(nwarps, 8);
   smem = 16 + a.L.table_bytes + static_cast<size_t>(a.L.words) * 4 * nwarps;
@@ -1629,7 +1629,7 @@ int ramp_check_edges(const RampModel* m, const float* d_q0, const float* d_q1, i
   // slice stays a few hundred MB: 2^18 planner edges are ~4M states and ~0.15 items per state on an
   // arm (FR3 stand-in, 2^20 edges: 2.4e9 states/s in one slice whose queue overflowed into the
   // in-kernel path, 4.1e9 in slices of 2^18).
-  int nwarps; size_t smem;
+  int nwarps = 0; size_t smem = 0;
   if (int rc = plan_slabs(m, 0, n_cols, &a.L, &nwarps, &smem)) return rc;
   const size_t smem_b = 16 + align16(m->hdr.total_bytes);
   const int64_t slice = std::min<int64_t>(n_edges, kEdgeSliceEdges);
