@@ -200,3 +200,64 @@ def test_deep_cylinder_box_penetration_with_coplanar_supports():
         d12, _ = oracle.shape_distance(cyl, A, box, B)
         d21, _ = oracle.shape_distance(box, B, cyl, A)
         assert abs(d12 - depth) < 2e-7 and abs(d21 - depth) < 2e-7, (d12, d21, depth)
+
+
+def _support_value(geo, d):
+    """max over the shape of d . x, for rows of local directions d."""
+    name = type(geo).__name__
+    if name == "Box":
+        return (np.abs(d) * np.asarray(geo.halfSide)).sum(1)
+    if name == "Cylinder":
+        return geo.radius * np.linalg.norm(d[:, :2], axis=1) + geo.halfLength * np.abs(d[:, 2])
+    if name == "Capsule":
+        return geo.radius * np.linalg.norm(d, axis=1) + geo.halfLength * np.abs(d[:, 2])
+    raise AssertionError(name)
+
+
+def _signed_distance_by_direction_search(a, ma, b, mb, rng):
+    """Signed distance of two convex shapes as -min over unit n of the support function of A - B:
+    positive = separation, negative = penetration depth.  Independent of GJK / EPA."""
+    Ra, ta, Rb, tb = ma.rotation, ma.translation, mb.rotation, mb.translation
+
+    def h(n):
+        return _support_value(a, n @ Ra) + n @ ta + _support_value(b, (-n) @ Rb) - n @ tb
+
+    n = rng.normal(size=(200000, 3))
+    n /= np.linalg.norm(n, axis=1, keepdims=True)
+    hv = h(n)
+    f = lambda x: h((x / np.linalg.norm(x))[None])[0]  # noqa: E731
+    best = min((minimize(f, n[j], method="Nelder-Mead", options=dict(xatol=1e-12, fatol=1e-14, maxiter=4000)) for j in np.argsort(hv)[:4]),
+               key=lambda r: r.fun)
+    return -best.fun
+
+
+def test_signed_distances_against_a_direction_search():
+    """Boxes, cylinders and capsules in random and in axis-aligned relative poses (flat faces
+    parallel: the case that produces coplanar support points), separated and overlapping, in both
+    argument orders, against the minimum of the support function of the Minkowski difference."""
+    rng = np.random.default_rng(42)
+    makers = [lambda: Box(*rng.uniform(0.05, 0.3, 3)), lambda: Cylinder(rng.uniform(0.03, 0.12), rng.uniform(0.05, 0.3)),
+              lambda: Capsule(rng.uniform(0.03, 0.1), rng.uniform(0.05, 0.3))]
+
+    def rot(k):
+        if k % 2:  # axis-aligned up to a signed permutation
+            r = np.eye(3)[:, rng.permutation(3)] * rng.choice([-1.0, 1.0], 3)
+            if np.linalg.det(r) < 0:
+                r[:, 0] *= -1
+            return r
+        return rpy_to_matrix(*rng.uniform(-np.pi, np.pi, 3))
+
+    worst, n_pen = 0.0, 0
+    for k in range(36):
+        a, b = makers[k % 3](), makers[(k // 3) % 3]()
+        ma = SE3(rot(k), np.zeros(3))
+        mb = SE3(rot(k // 2), rng.normal(size=3) * rng.uniform(0.02, 0.3))
+        truth = _signed_distance_by_direction_search(a, ma, b, mb, rng)
+        d12, _ = oracle.shape_distance(a, ma, b, mb)
+        d21, _ = oracle.shape_distance(b, mb, a, ma)
+        tol = 2e-6 + 2e-5 * abs(truth)
+        assert abs(d12 - truth) < tol and abs(d21 - truth) < tol, (k, type(a).__name__, type(b).__name__, truth, d12, d21)
+        worst = max(worst, abs(d12 - truth), abs(d21 - truth))
+        n_pen += truth < 0
+    print("worst deviation", worst, "overlapping cases", n_pen)
+    assert 8 <= n_pen <= 28
