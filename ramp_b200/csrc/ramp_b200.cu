@@ -1004,7 +1004,7 @@ static void plan_slices(const RampModel* m, int64_t n, int64_t* slice_rows, uint
   // (rounded up to sixteenths: repeated calls must ask the pool for the SAME size, or every call
   // would allocate afresh -- the observed rates wobble in the fourth digit)
   auto up16 = [](double x) { return std::ceil(x * 16.0) / 16.0; };
-  const double per_hard = std::min(1.0, up16(1.5 * m->est_hard + 0.02)), per_easy = std::min(2.0, up16(1.5 * m->est_easy + 0.04));
+  const double per_hard = std::min(2.0, up16(1.5 * m->est_hard + 0.02)), per_easy = std::min(3.5, up16(1.5 * m->est_easy + 0.04));
   const double bytes_per_row = (per_hard + per_easy) * sizeof(GjkItem);
   int64_t rows = static_cast<int64_t>(kQueueBudgetBytes / bytes_per_row) & ~int64_t{(1 << 18) - 1};
   rows = std::max(kSliceRows, std::min(rows, kMaxSliceRows));
