@@ -36,8 +36,8 @@ __device__ __forceinline__ V3 unpack_dir(uint32_t a, uint32_t b) {
 // so the consumer kernel drains on one-iteration items and its warps finish together.
 struct GjkQueue {
   GjkItem* items;     // nullptr: no queue, GJK runs inside the validity kernel
-  uint32_t* count;    // [0] hard, [1] easy items reserved so far (may exceed the regions: the
-                      // overflow stays in-kernel), [2] the consumer's cursor; zeroed by the host
+  uint32_t* count;    // [0] hard, [1] easy items reserved so far (may exceed the regions: see tile_flags),
+                      // [2] the consumer's cursor, [3] flagged tiles; zeroed by the host
   uint32_t capacity;  // items: hard region [0, cap_hard), easy region [cap_hard, capacity); cap_hard = a quarter
   uint32_t cap_hard;
   // One byte per tile of 32 rows of the result arrays the queue serves (zeroed by the host).  The
@@ -320,7 +320,7 @@ __device__ __forceinline__ void narrow_phase(const Warp& w, bool stop_at_first, 
             uint32_t da, db;
             pack_dir(v0, da, db);
             dst[3] = make_float4(__uint_as_float(da), __uint_as_float(db), __uint_as_float(row_base + c), __uint_as_float(p));
-            to_gjk = false;  // queued; anything past the capacity stays for the in-kernel loop
+            to_gjk = false;  // queued; anything past the capacity stays: in-kernel loop (kStage3) or tile flag
           }
         }
       }

@@ -796,9 +796,10 @@ static int check_q_args(const RampModel* m, const void* d_q, int64_t n, int32_t 
 
 // Rows are processed in slices so the GJK work queue has a bounded size.
 constexpr int64_t kSliceRows = 1 << 21;
-// Queue capacity: 3 items per row (1 hard + 2 easy; 0.1 - 2.1 per row on the robots measured) plus a
-// floor; overflow is handled inside check_kernel.  ramp_check_batch_noalloc sizes its queue by the
-// same rule, so both entry points queue (and solve in-kernel) exactly the same items.
+// Queue capacity: 3 items per row (0.75 hard + 2.25 easy; 0.1 - 2.1 per row on the robots measured) plus a
+// floor; a tile whose items do not all fit is flagged and redone by recheck_kernel.
+// ramp_check_batch_noalloc sizes its queue by the same rule, so both entry points queue (and
+// recheck) exactly the same items.
 constexpr int64_t kQueueItemsPerRow = 3;
 constexpr uint32_t queue_items_for(int64_t rows) { return static_cast<uint32_t>(rows * kQueueItemsPerRow + 4096); }
 constexpr int64_t kQueueMinRows = 1024;    // below this a second launch costs more than it saves
@@ -975,8 +976,8 @@ static int pool_alloc(const RampModel* m, size_t bytes, cudaStream_t st, void** 
 // one slice -- but 3 items per row of queue would then be gigabytes.  The items a robot really
 // produces per row are learnt from the counters of earlier calls (0.1 for a capsule-like arm, 2 for
 // a humanoid); the queue is sized 1.5x that within kQueueBudgetBytes and the slice is as large as
-// that allows (at most 2^26 rows).  An underestimate is not an error: items that do not fit are
-// solved inside the validity kernel.
+// that allows (at most 2^26 rows).  An underestimate is not an error: the tiles whose items do not
+// fit are redone by recheck_kernel (slowly: one warp per configuration).
 constexpr size_t kQueueBudgetBytes = size_t{1} << 30;
 constexpr int64_t kMaxSliceRows = int64_t{1} << 26;
 
